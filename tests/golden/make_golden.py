@@ -1,0 +1,177 @@
+"""Generate golden vectors by running the UNMODIFIED reference in the build container.
+
+    PYTHONDONTWRITEBYTECODE=1 python tests/golden/make_golden.py
+
+Imports ``msstftd``, ``pkl_file_model_updated`` and ``pkl_file_models`` from ``/root/reference``
+(read-only; not available on the GPU box, which is why the outputs are committed as ``*.npz``),
+feeds them seeded inputs and stores inputs + outputs:
+
+* ``stft_disc.npz``   -- ``DiscriminatorSTFT.spec_transform`` + the ``cat(real, imag)`` / rearrange
+  of ``msstftd.py:151-153`` for the three default scales (``msstftd.py:174-175``), plus the logit
+  shapes of ``MultiScaleSTFTDiscriminator(filters=32)`` on ``(2, 1, 24000)``
+  (known answer of ``testing_scripts.ipynb:2021-2023``).
+* ``dpca.npz``        -- ``data_pca`` (``pkl_file_model_updated.py:37-42``), ``apply_pca``
+  (``pkl_file_models.py:224-228``) and the DPCA blocks of ``ResE2D1.forward`` (``:486-511``) and
+  ``ResE4D1.forward`` (``:394-427``) run through the reference's own ``forward`` with the encoders /
+  decoder replaced by pass-through stubs (so the latents are the seeded inputs and the tensor handed
+  to the decoder is captured).
+* ``spec_losses.npz`` -- the loss dictionary / spectral SNR of ``ResE2D1.forward`` (``:520-540``).
+* ``var_topk.npz``    -- variance top-k of ``pkl_file_models.py:901-907`` through
+  ``SpectralResE1D1.forward`` with stubbed encoder / decoder.
+"""
+import os
+import sys
+import warnings
+
+import numpy as np
+import torch
+
+REF = "/root/reference"
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.dont_write_bytecode = True
+sys.path.insert(0, REF)
+warnings.filterwarnings("ignore")
+
+import msstftd  # noqa: E402
+import pkl_file_model_updated as pmu  # noqa: E402
+import pkl_file_models as pm  # noqa: E402
+
+
+class _Enc(torch.nn.Module):
+    """Pass-through encoder stub: the 'observation' already is the latent, shaped [B,1,1,d]."""
+    def forward(self, obs):
+        return obs.reshape(obs.shape[0], -1), None
+
+
+class _Dec(torch.nn.Module):
+    def __init__(self, shape_fn):
+        super().__init__()
+        self.shape_fn = shape_fn
+        self.seen = None
+
+    def forward(self, z):
+        self.seen = z.detach().clone()
+        return self.shape_fn(z)
+
+
+def _bare(cls):
+    m = cls.__new__(cls)
+    torch.nn.Module.__init__(m)
+    return m
+
+
+def gen_stft():
+    torch.manual_seed(20240)
+    B, T = 2, 6000
+    x = 0.3 * torch.randn(B, 1, T)
+    x[:, 0] += 0.5 * torch.sin(2 * np.pi * 440.0 * torch.arange(T) / 16000.0)
+    out = {"x": x.numpy()}
+    disc = msstftd.MultiScaleSTFTDiscriminator(filters=4)
+    for i, d in enumerate(disc.discriminators):
+        z = d.spec_transform(x)                                  # msstftd.py:151
+        out[f"complex_{i}"] = z.numpy()
+        zz = torch.cat([z.real, z.imag], dim=1)                  # msstftd.py:152
+        out[f"planes_{i}"] = zz.permute(0, 1, 3, 2).contiguous().numpy()   # 'b c w t -> b c t w'
+        out[f"cfg_{i}"] = np.array([d.n_fft, d.hop_length, d.win_length])
+    torch.manual_seed(1)
+    d32 = msstftd.MultiScaleSTFTDiscriminator(filters=32)
+    logits, fmaps = d32(torch.randn(2, 1, 24000))
+    out["kat_logit_shapes"] = np.array([list(l.shape) for l in logits])
+    out["kat_n_fmaps"] = np.array([len(f) for f in fmaps])
+    np.savez_compressed(os.path.join(HERE, "stft_disc.npz"), **out)
+
+
+def _latents(B, d, seed, decay=0.93):
+    g = torch.Generator().manual_seed(seed)
+    sig = decay ** torch.arange(d, dtype=torch.float32)
+    Q, _ = torch.linalg.qr(torch.randn(d, d, generator=g))
+    return ((torch.randn(B, d, generator=g) * sig) @ Q.T) * (1.0 + 0.01 * (seed % 7)) + 0.3
+
+
+def gen_dpca():
+    out = {}
+    # data_pca / apply_pca, tall and wide (B < d exercises the rank-deficient thin SVD)
+    for tag, (B, d) in {"tall": (96, 32), "wide": (12, 32)}.items():
+        z = _latents(B, d, 11 if tag == "tall" else 12)
+        s, v, mu = pmu.data_pca(z)
+        s2, v2, mu2 = pm.data_pca(z)
+        assert torch.equal(s, s2) and torch.equal(mu, mu2)
+        out[f"pca_{tag}_z"] = z.numpy(); out[f"pca_{tag}_s"] = s.numpy()
+        out[f"pca_{tag}_v"] = v.numpy(); out[f"pca_{tag}_mu"] = mu.numpy()
+        out[f"pca_{tag}_apply8"] = pm.apply_pca(z, 8).numpy()
+
+    # two-view DPCA block through ResE2D1.forward
+    B, d = 64, 32
+    z1, z2 = _latents(B, d, 21), _latents(B, d, 22)
+    m = _bare(pmu.ResE2D1)
+    m.enc1, m.enc2 = _Enc(), _Enc()
+    m.dec = _Dec(lambda z: torch.zeros(z.shape[0], 2, 1, d))
+    torch.manual_seed(77)
+    state = torch.random.get_rng_state()
+    dim_p = torch.randint(8, int(2 * d / 2), (1,)).item()        # same draw as :489
+    torch.random.set_rng_state(state)
+    m.forward(z1.reshape(B, 1, 1, d), z2.reshape(B, 1, 1, d), True)
+    out["e2_z1"], out["e2_z2"] = z1.numpy(), z2.numpy()
+    out["e2_dim_p"] = np.array(dim_p)
+    out["e2_out"] = m.dec.seen.numpy()                            # cat(z1', z2') handed to the decoder
+
+    # four-view DPCA block through ResE4D1.forward
+    zs = [_latents(B, d, 31 + i) for i in range(4)]
+    m4 = _bare(pmu.ResE4D1)
+    m4.enc1, m4.enc2, m4.enc3, m4.enc4 = _Enc(), _Enc(), _Enc(), _Enc()
+    m4.dec = _Dec(lambda z: torch.zeros(z.shape[0], 2, 2, d))
+    torch.manual_seed(78)
+    state = torch.random.get_rng_state()
+    dim_p4 = torch.randint(8, int(4 * d / 2), (1,)).item()       # :398
+    torch.random.set_rng_state(state)
+    m4.forward(*[z.reshape(B, 2, 1, d // 2) for z in zs], True)
+    for i, z in enumerate(zs):
+        out[f"e4_z{i + 1}"] = z.numpy()
+    out["e4_dim_p"] = np.array(dim_p4)
+    out["e4_out"] = m4.dec.seen.numpy()
+    np.savez_compressed(os.path.join(HERE, "dpca.npz"), **out)
+
+
+def gen_spec_losses():
+    torch.manual_seed(5)
+    B, K, F = 3, 65, 20
+    obs1, obs2 = torch.rand(B, 1, K, F) * 2.0, (torch.rand(B, 1, K, F) - 0.5) * 6.0
+    dec_out = torch.cat((obs1, obs2), 1) + 0.1 * torch.randn(B, 2, K, F)
+    m = _bare(pmu.ResE2D1)
+
+    class _E(torch.nn.Module):
+        def forward(self, o):
+            return o.reshape(o.shape[0], -1)[:, :16], None
+    m.enc1, m.enc2 = _E(), _E()
+    m.dec = _Dec(lambda z: dec_out)
+    r = m.forward(obs1, obs2, False)
+    obs_dec, mse_mean, nuc, _, cos, sd, snr, psnr = r
+    obs = torch.cat((obs1, obs2), 1)
+    np.savez_compressed(os.path.join(HERE, "spec_losses.npz"), obs=obs.numpy(), dec=obs_dec.numpy(),
+                        mse_mean=mse_mean.numpy(), magnitude_loss=sd["magnitude_loss"].numpy(),
+                        phase_loss=sd["phase_loss"].numpy(), total_loss=sd["total_loss"].numpy(),
+                        spec_snr=snr.numpy(), nuc=nuc.numpy(), z_sample=m.dec.seen.numpy())
+
+
+def gen_var_topk():
+    B, d, k = 48, 64, 8
+    z = _latents(B, d, 41, decay=0.9)
+    m = _bare(pm.SpectralResE1D1)
+    m.total_features_after = k
+    m.enc = _Enc()
+    m.dec = _Dec(lambda zz: torch.zeros(zz.shape[0], 2, 1, d // 2))
+    obs = {"magnitude": z[:, : d // 2].reshape(B, 1, d // 2), "phase": z[:, d // 2:].reshape(B, 1, d // 2)}
+    m.forward(obs, None, True)
+    # the encoder stub flattens stack([mag, phase], 1) -> [B, d] == z
+    np.savez_compressed(os.path.join(HERE, "var_topk.npz"), z=z.numpy(), k=np.array(k),
+                        z_sel=m.dec.seen.numpy())
+
+
+if __name__ == "__main__":
+    gen_stft()
+    gen_dpca()
+    gen_spec_losses()
+    gen_var_topk()
+    for f in sorted(os.listdir(HERE)):
+        if f.endswith(".npz"):
+            print(f, os.path.getsize(os.path.join(HERE, f)))

@@ -1,0 +1,135 @@
+"""The oracle against the reference's own outputs (tests/golden/*.npz, produced by
+tests/golden/make_golden.py from /root/reference) and against an independent float64 DFT.
+CPU only."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import spectral_oracle as O
+
+
+def _load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name))
+
+
+def test_shape_known_answers(golden_dir):
+    # testing_scripts.ipynb:2021-2023 -- logits of MultiScaleSTFTDiscriminator(filters=32) on (2,1,24000)
+    g = _load(golden_dir, "stft_disc.npz")
+    assert g["kat_logit_shapes"].tolist() == [[2, 1, 90, 65], [2, 1, 43, 129], [2, 1, 184, 33]]
+    assert g["kat_n_fmaps"].tolist() == [5, 5, 5]
+    # frame counts behind those shapes: F = 1 + (T - n)//hop, K = n/2 + 1
+    for (n, h), F in zip(((1024, 256), (2048, 512), (512, 128)), (90, 43, 184)):
+        assert O.num_frames(24000, n, h, False) == F
+    # spectrogram.ipynb:4210-4211 -- (1025, 123) for one utterance, centred STFT 2048/512
+    T = 122 * 512 + 17
+    assert O.num_frames(T, 2048, 512, True) == 123
+    mag, ph = O.frontend_ref(torch.zeros(1, 5000))
+    assert mag.shape == (1, 1025, 1 + 5000 // 512) == ph.shape
+
+
+def test_stft_matches_reference_spectrogram(golden_dir):
+    g = _load(golden_dir, "stft_disc.npz")
+    x = torch.from_numpy(g["x"])
+    for i in range(3):
+        n, h, w = (int(v) for v in g[f"cfg_{i}"])
+        z = O.stft_ref(x[:, 0], n, h, w, center=False, normalized=True)
+        assert np.array_equal(z.numpy(), g[f"complex_{i}"][:, 0])          # bit-equal: same torch.stft call
+        planes = O.disc_inputs_ref(x, n, h, w)
+        assert np.array_equal(planes.numpy(), g[f"planes_{i}"])
+    outs = O.multiscale_disc_inputs_ref(x)
+    assert [tuple(o.shape) for o in outs] == [tuple(g[f"planes_{i}"].shape) for i in range(3)]
+
+
+@pytest.mark.parametrize("n,h", [(128, 32), (256, 64), (512, 128)])
+def test_stft_against_direct_dft(n, h):
+    torch.manual_seed(3)
+    x = torch.randn(2, 3 * n + 17)
+    z = O.stft_ref(x, n, h, n).numpy()
+    ref = O.dft_frames_f64(x.numpy(), n, h)
+    scale = np.abs(ref).max()
+    assert np.abs(z - ref).max() <= 2e-6 * scale
+
+
+def test_frontend_conventions():
+    torch.manual_seed(4)
+    y = torch.randn(2, 4000)
+    mag, ph = O.frontend_ref(y, pad_mode="constant")
+    # centred frames of a zero-padded signal == uncentred frames of the explicitly padded one
+    yp = torch.nn.functional.pad(y, (1024, 1024))
+    ref = O.dft_frames_f64(yp.numpy(), 2048, 512, normalized=False)
+    assert np.abs(mag.numpy() - np.abs(ref)).max() <= 2e-6 * np.abs(ref).max()
+    big = np.abs(ref) > 1e-2 * np.abs(ref).max()
+    dphi = np.angle(np.exp(1j * (ph.numpy() - np.angle(ref))))
+    assert np.abs(dphi[big]).max() < 1e-4
+    m600 = O.pad_frames(mag, 600)
+    assert m600.shape[-1] == 600 and torch.equal(m600[..., :mag.shape[-1]], mag) and m600[..., mag.shape[-1]:].abs().sum() == 0
+    assert O.pad_frames(mag, 5).shape[-1] == 5
+    db = O.amplitude_to_db_ref(mag)
+    assert db.max() <= 1e-6 and db.min() >= -80.0 - 1e-4
+
+
+def test_data_pca_matches_reference(golden_dir):
+    g = _load(golden_dir, "dpca.npz")
+    for tag in ("tall", "wide"):
+        z = torch.from_numpy(g[f"pca_{tag}_z"])
+        s, v, mu = O.data_pca_ref(z)
+        assert s.shape[0] == min(z.shape)
+        np.testing.assert_allclose(s.numpy(), g[f"pca_{tag}_s"], rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(mu.numpy(), g[f"pca_{tag}_mu"], rtol=0, atol=0)
+        # eigenvector signs are arbitrary -> compare projectors
+        vr = torch.from_numpy(g[f"pca_{tag}_v"])
+        r = 8
+        assert O.subspace_angle(v[:, :r], vr[:, :r]) < 1e-5
+        np.testing.assert_allclose(O.apply_pca_ref(z, 8).numpy(), g[f"pca_{tag}_apply8"], rtol=1e-4, atol=1e-5)
+
+
+def test_dpca_block_matches_reference(golden_dir):
+    g = _load(golden_dir, "dpca.npz")
+    zs = [torch.from_numpy(g["e2_z1"]), torch.from_numpy(g["e2_z2"])]
+    outs, idx = O.dpca_project_ref(zs, int(g["e2_dim_p"]))
+    assert sum(len(i) for i in idx) == int(g["e2_dim_p"])
+    np.testing.assert_allclose(torch.cat(outs, 1).numpy(), g["e2_out"], rtol=1e-4, atol=1e-5)
+    zs = [torch.from_numpy(g[f"e4_z{i}"]) for i in range(1, 5)]
+    outs, idx = O.dpca_project_ref(zs, int(g["e4_dim_p"]))
+    assert sum(len(i) for i in idx) == int(g["e4_dim_p"])
+    np.testing.assert_allclose(torch.cat(outs, 1).numpy(), g["e4_out"], rtol=1e-4, atol=1e-5)
+
+
+def test_spec_losses_match_reference(golden_dir):
+    g = _load(golden_dir, "spec_losses.npz")
+    r = O.spectral_losses_ref(torch.from_numpy(g["obs"]), torch.from_numpy(g["dec"]))
+    for k in ("magnitude_loss", "phase_loss", "total_loss", "spec_snr"):
+        np.testing.assert_allclose(r[k].numpy(), g[k], rtol=1e-6)
+    np.testing.assert_allclose(r["mse_per_sample"].mean().numpy(), g["mse_mean"], rtol=1e-6)
+    np.testing.assert_allclose(O.nuclear_loss_ref(torch.from_numpy(g["z_sample"])).numpy(), g["nuc"], rtol=1e-5)
+
+
+def test_var_topk_matches_reference(golden_dir):
+    g = _load(golden_dir, "var_topk.npz")
+    sel, idx = O.var_topk_ref(torch.from_numpy(g["z"]), int(g["k"]))
+    assert np.array_equal(sel.numpy(), g["z_sel"])
+
+
+def test_mrstft_loss_definition():
+    (x,), (y,) = O.synth_audio(3, 4000, 1)
+    total, terms = O.mrstft_loss_ref(x, y, return_terms=True)
+    assert len(terms) == 3 and total > 0
+    assert O.mrstft_loss_ref(x, x).item() == 0.0
+    # hand evaluation of one scale from the float64 DFT
+    X = np.abs(O.dft_frames_f64(x.numpy(), 512, 128)); Y = np.abs(O.dft_frames_f64(y.numpy(), 512, 128))
+    l1 = np.abs(X - Y).mean(); ll = np.abs(np.log(np.maximum(X, 1e-5)) - np.log(np.maximum(Y, 1e-5))).mean()
+    np.testing.assert_allclose(terms[2][0].item(), l1, rtol=1e-4)
+    np.testing.assert_allclose(terms[2][1].item(), ll, rtol=1e-4)
+    y2 = y.clone().requires_grad_(True)
+    O.mrstft_loss_ref(x, y2).backward()
+    assert y2.grad.shape == y.shape and torch.isfinite(y2.grad).all()
+
+
+def test_subspace_angle_and_synth():
+    zs = O.synth_latents(64, 16, 2)
+    assert zs[0].shape == (64, 16)
+    s, v, mu = O.data_pca_ref(zs[0])
+    assert O.subspace_angle(v[:, :4], v[:, :4] @ torch.linalg.qr(torch.randn(4, 4))[0]) < 1e-6
+    assert abs(O.subspace_angle(v[:, :1], v[:, 1:2]) - np.pi / 2) < 1e-6

@@ -1,0 +1,154 @@
+/* tac_spectral.h -- C ABI of the B200-native spectral hot path (libtac_spectral.so).
+ *
+ * Drop-in boundary for the one data-parallel path of ahmd-mohsin/Task-Aware-audio-coding-perceptual
+ * that BASELINE.json:north_star names.  The reference has no FFI of its own on this path: it calls
+ * torch / torchaudio / librosa library routines from Python.  Each entry point below therefore
+ * names the reference *call site* (file:line under the reference checkout) whose arithmetic it
+ * replaces; INTEGRATION.md shows the ctypes stub a maintainer adds at that call site.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a TAC_E* code otherwise; tac_last_error() returns a
+ *     thread-local, human readable message for the last failure (never throws across the ABI);
+ *   - all pointers are DEVICE pointers unless the parameter is documented "host"; the caller
+ *     allocates every input, output and workspace; float/double buffers must be 16-byte aligned
+ *     where stated; the library owns only immutable per-device tables (window*norm, twiddles),
+ *     built by tac_prepare_fft() (or lazily on first use) and freed by tac_shutdown();
+ *   - all work is enqueued on `stream` (a cudaStream_t); no entry point synchronises the host,
+ *     allocates, or creates streams once the tables for its n_fft exist, so calls are CUDA-graph
+ *     capturable after tac_prepare_fft();
+ *   - supported n_fft: 64, 128, 256, 512, 1024, 2048 (periodic Hann, win_length <= n_fft, even hop).
+ */
+#ifndef TAC_SPECTRAL_H_
+#define TAC_SPECTRAL_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define TAC_API __attribute__((visibility("default")))
+#else
+#define TAC_API
+#endif
+
+#define TAC_OK 0
+#define TAC_EINVAL 1      /* bad argument (shape, unsupported n_fft, null pointer)        */
+#define TAC_EALIGN 2      /* pointer not aligned as documented                             */
+#define TAC_ECUDA 3       /* CUDA runtime error (message carries cudaGetErrorString)      */
+#define TAC_EWORKSPACE 4  /* workspace too small (see tac_*_workspace_bytes)               */
+
+#define TAC_MAX_SCALES 8
+
+/* pad_mode for center != 0 */
+#define TAC_PAD_ZERO 0     /* librosa >= 0.10 ('constant')           */
+#define TAC_PAD_REFLECT 1  /* torch.stft / torchaudio default         */
+
+/* out_mode of tac_stft_multi */
+#define TAC_OUT_COMPLEX 0   /* complex64 [B, C, K, F]   -- torchaudio Spectrogram(power=None) layout  */
+#define TAC_OUT_PLANES 1    /* float32  [B, 2C, F, K]   -- msstftd.py:152-153 (cat(real, imag) + rearrange) */
+#define TAC_OUT_MAGPHASE 2  /* float32  [B*C, 2, K, f_pad] -- notebook front end + pad_tensor + stack  */
+
+typedef void* tac_stream_t; /* cudaStream_t */
+
+TAC_API const char* tac_last_error(void);
+TAC_API int tac_version(void);
+
+/* Build (idempotent) the device tables for one (n_fft, win_length, normalized) on the current
+ * device.  Synchronous (cudaMalloc + cudaMemcpy); call once outside any stream capture. */
+TAC_API int tac_prepare_fft(int n_fft, int win_length, int normalized);
+/* Free every cached table on every device. */
+TAC_API int tac_shutdown(void);
+
+/* Number of frames torch.stft produces: 1 + (T + (center ? 2*(n_fft/2) : 0) - n_fft) / hop, or 0. */
+TAC_API int64_t tac_stft_num_frames(int64_t T, int n_fft, int hop, int center);
+
+/* K1 -- batched multi-scale STFT, all scales in ONE launch.
+ * Replaces: torchaudio.transforms.Spectrogram(...)(x) at msstftd.py:125-127,151, the
+ * cat(real, imag) + rearrange of msstftd.py:152-153, the per-scale loop of msstftd.py:188-191, and
+ * librosa.stft + np.abs + np.angle of spectrogram.ipynb cell 10 L26-52 (raw :4120-4134) together
+ * with pad_tensor / torch.stack (train_pkl_file_task_aware.py:64-68, pkl_file_models.py:889-892).
+ *   x          [B*C, T] float32, row-major (16-byte aligned)
+ *   n_fft/hop/win  host arrays of n_scales entries
+ *   center     0: frames start at f*hop (msstftd.py:127); 1: signal padded by n_fft/2 each side
+ *   normalized 1: divide by sqrt(sum(window^2)) (torchaudio 'window' normalisation); 0: raw
+ *   out        host array of n_scales device pointers, layout per out_mode above, F = frames of
+ *              that scale; for TAC_OUT_MAGPHASE the time axis has f_pad >= F entries (f_pad = 0
+ *              means f_pad = F) and columns [F, f_pad) are zero-filled (pad_tensor semantics).
+ */
+TAC_API int tac_stft_multi(const float* x, int64_t B, int64_t C, int64_t T, int n_scales, const int* n_fft,
+                   const int* hop, const int* win, int center, int pad_mode, int normalized,
+                   int out_mode, int64_t f_pad, void* const* out, tac_stream_t stream);
+
+/* K2 -- fused multi-resolution STFT loss (no spectrogram is written to memory).
+ * Definition of record (the reference holds no such function): per scale s, on the
+ * msstftd.py:125-127 STFT convention, X = |STFT_s(x)|, Y = |STFT_s(y)|,
+ *   sums[2s]   = sum |X - Y|,   sums[2s+1] = sum |ln max(X, eps) - ln max(Y, eps)|
+ * over all B*K_s*F_s elements (float64, deterministic two-level reduction).
+ *   workspace  tac_mrstft_workspace_bytes(...) bytes, 16-byte aligned.
+ */
+TAC_API size_t tac_mrstft_workspace_bytes(int64_t B, int64_t T, int n_scales, const int* n_fft, const int* hop);
+TAC_API int tac_mrstft_loss_fwd(const float* x, const float* y, int64_t B, int64_t T, int n_scales,
+                        const int* n_fft, const int* hop, const int* win, float eps, double* sums,
+                        void* workspace, size_t workspace_bytes, tac_stream_t stream);
+/* Backward of the above w.r.t. y:  grad_y[B, T] = sum_s coef[2s] * d(sum|X-Y|)/dy
+ *                                               + coef[2s+1] * d(sum|ln X - ln Y|)/dy.
+ * coef is a DEVICE array [2*n_scales] float32 (the caller folds grad_output / (S * count_s) into
+ * it, so no host sync is needed).  grad_y is fully overwritten. */
+TAC_API int tac_mrstft_loss_bwd(const float* x, const float* y, int64_t B, int64_t T, int n_scales,
+                        const int* n_fft, const int* hop, const int* win, float eps, const float* coef,
+                        float* grad_y, void* workspace, size_t workspace_bytes, tac_stream_t stream);
+
+/* K2' -- the reference's spectral reductions in one pass over (obs, dec), both [B, 2, K, F]:
+ * pkl_file_models.py:924,933-940 / pkl_file_model_updated.py:520-540.
+ *   out5       float32 [5]: magnitude_loss, phase_loss, total_loss, spec_snr (dB), mean(mse)
+ *   per_sample float32 [B]: 0.5 * mean((obs - dec)^2) per item (may be NULL)
+ *   workspace  tac_spec_losses_workspace_bytes(B) bytes
+ */
+TAC_API size_t tac_spec_losses_workspace_bytes(int64_t B);
+TAC_API int tac_spec_losses(const float* obs, const float* dec, int64_t B, int64_t K, int64_t F, float* out5,
+                    float* per_sample, void* workspace, size_t workspace_bytes, tac_stream_t stream);
+
+/* K3 -- DPCA.  Replaces data_pca (pkl_file_model_updated.py:37-42, pkl_file_models.py:51-56) and the
+ * select / project block (pkl_file_model_updated.py:489-511 two views, :398-427 four views;
+ * apply_pca pkl_file_models.py:224-228).
+ *
+ * tac_dpca_stats: sufficient statistics of nv views in one launch chain.
+ *   z      host array of nv device pointers, each [B, d] float32 row-major (ld = d)
+ *   stats  device float64 [nv][1 + d + d*d]: n, sum_b z, sum_b z z^T   (sum-reducible across
+ *          ranks: all-reduce this buffer, then call tac_dpca_eig on every rank)
+ *   algo   TAC_GRAM_TF32X3: tcgen05 tensor-core Gram of the locally centred batch, 3xTF32 split,
+ *          fp32 accumulation in TMEM, float64 re-assembly;  TAC_GRAM_FP64: SIMT float64.
+ */
+#define TAC_GRAM_TF32X3 0
+#define TAC_GRAM_FP64 1
+TAC_API size_t tac_dpca_workspace_bytes(int nv, int64_t B, int d);
+TAC_API int tac_dpca_stats(const float* const* z, int nv, int64_t B, int d, int algo, double* stats,
+                   void* workspace, size_t workspace_bytes, tac_stream_t stream);
+/* tac_dpca_eig: per view, C = sum zz^T - (sum z)(sum z)^T / n, symmetric eigen-decomposition
+ * (parallel Jacobi, float64, one CTA per view), s = sqrt(max(eig, 0)) descending.
+ *   s [nv][d] float32 (entries >= rank are 0), v [nv][d][d] float32 with eigenvector j in COLUMN j
+ *   (row-major [d, d], i.e. data_pca's v), mu [nv][d] float32, rank [nv] int32 = min(n, d).
+ */
+TAC_API int tac_dpca_eig(const double* stats, int nv, int d, float* s, float* v, float* mu, int* rank,
+                 void* workspace, size_t workspace_bytes, tac_stream_t stream);
+/* tac_dpca_select: global top-dim_p over the concatenated per-view singular values
+ * (pkl_file_model_updated.py:496-500 / :404-412).  sel [nv][d] uint8 mask-free index lists:
+ *   idx [nv][d] int32 (first cnt[v] entries valid, in global descending order), cnt [nv] int32. */
+TAC_API int tac_dpca_select(const float* s, const int* rank, int nv, int d, int dim_p, int* idx, int* cnt,
+                    tac_stream_t stream);
+/* tac_dpca_project: z_out = ((z - mu) V_sel) V_sel^T + mu for every view
+ * (pkl_file_model_updated.py:503-511).  z_out host array of nv device pointers [B, d]. */
+TAC_API int tac_dpca_project(const float* const* z, int nv, int64_t B, int d, const float* v, const float* mu,
+                     const int* idx, const int* cnt, float* const* z_out, void* workspace,
+                     size_t workspace_bytes, tac_stream_t stream);
+/* E1D1 bottleneck (pkl_file_models.py:901-907): unbiased column variances from stats and the
+ * indices of the k largest; var [d] float32, top_idx [k] int32 (descending variance). */
+TAC_API int tac_var_topk(const double* stats, int d, int k, float* var, int* top_idx, tac_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TAC_SPECTRAL_H_ */

@@ -1,0 +1,422 @@
+// K3 -- DPCA: sufficient statistics (Gram), symmetric eigen-decomposition, global top-k selection
+// across views and projection.  Everything stays on the device: no host synchronisation between
+// the statistics (all-reducible across ranks), the eigen-solve, the selection and the projection.
+//
+//   stats  [nv][1 + d + d*d] float64 : n, sum z, sum z z^T                (tac_dpca_stats)
+//   eig    one CTA per view, parallel one-sided Jacobi in float64 on C = S - s s^T / n, columns in
+//          shared memory (d <= 128) or in the caller's workspace (d <= 256)   (tac_dpca_eig)
+//   select rank-by-counting over the concatenated singular values          (tac_dpca_select)
+//   project z_out = (z - mu) (V_sel V_sel^T) + mu                           (tac_dpca_project)
+//
+// The Gram matrix has two implementations: TAC_GRAM_FP64 (SIMT, exact products, float64 sums) and
+// TAC_GRAM_TF32X3 (tcgen05 tensor cores, see dpca_tc.cuh).
+#include "tac_common.cuh"
+#include "dpca_tc.cuh"
+
+namespace tac {
+
+constexpr int kMaxViews = 8;
+constexpr int kMaxD = 256;
+
+struct ViewPtrs { const float* z[kMaxViews]; float* out[kMaxViews]; };
+
+// ------------------------------------------------------------------------------------------ stats (float64 SIMT)
+// grid (tiles_i * tiles_j, nv); CTA computes a 32x32 tile of sum_b z z^T over all rows.
+__global__ void __launch_bounds__(256) dpca_gram_fp64_kernel(const ViewPtrs vp, long long B, int d, double* __restrict__ stats) {
+    __shared__ float si[32][33], sj[32][33];
+    const int v = blockIdx.y;
+    const int nt = (d + 31) / 32;
+    const int ti = blockIdx.x / nt, tj = blockIdx.x % nt;
+    if (tj < ti) return;                                   // symmetric: upper tiles only, mirrored on store
+    const float* z = vp.z[v];
+    double* st = stats + (size_t)v * (1 + d + (size_t)d * d);
+    const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;       // 16 x 16 threads, 2 x 2 outputs each
+    double acc[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+    double csum = 0.0;                                      // column sums (tiles with ti == tj only)
+    for (long long r0 = 0; r0 < B; r0 += 32) {
+        for (int e = threadIdx.x; e < 32 * 32; e += 256) {
+            const int r = e / 32, c = e % 32;
+            const long long row = r0 + r;
+            const int ci = ti * 32 + c, cj = tj * 32 + c;
+            si[r][c] = (row < B && ci < d) ? __ldg(z + row * d + ci) : 0.0f;
+            sj[r][c] = (row < B && cj < d) ? __ldg(z + row * d + cj) : 0.0f;
+        }
+        __syncthreads();
+#pragma unroll 8
+        for (int r = 0; r < 32; ++r) {
+            const double a0 = si[r][ty * 2], a1 = si[r][ty * 2 + 1];
+            const double b0 = sj[r][tx * 2], b1 = sj[r][tx * 2 + 1];
+            acc[0][0] = fma(a0, b0, acc[0][0]); acc[0][1] = fma(a0, b1, acc[0][1]);
+            acc[1][0] = fma(a1, b0, acc[1][0]); acc[1][1] = fma(a1, b1, acc[1][1]);
+        }
+        if (ti == tj && threadIdx.x < 32) {
+            for (int r = 0; r < 32; ++r) csum += (double)si[r][threadIdx.x];
+        }
+        __syncthreads();
+    }
+    double* S = st + 1 + d;
+    for (int a = 0; a < 2; ++a)
+        for (int b = 0; b < 2; ++b) {
+            const int i = ti * 32 + ty * 2 + a, j = tj * 32 + tx * 2 + b;
+            if (i < d && j < d) { S[(size_t)i * d + j] = acc[a][b]; S[(size_t)j * d + i] = acc[a][b]; }
+        }
+    if (ti == tj && threadIdx.x < 32) {
+        const int i = ti * 32 + threadIdx.x;
+        if (i < d) st[1 + i] = csum;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) st[0] = (double)B;
+}
+
+// ------------------------------------------------------------------------------------------ eigen-solve
+// One-sided (Hestenes) Jacobi on the symmetric PSD matrix C held column-wise in A (ld = d):
+// rotate column pairs until all columns are mutually orthogonal; then column j equals
+// lambda_j * v_j, i.e. lambda_j = |a_j| and v_j = a_j / |a_j|.
+constexpr int kEigThreads = 1024;
+constexpr int kLanesPerPair = 16;
+
+__global__ void __launch_bounds__(kEigThreads, 1) dpca_eig_kernel(const double* __restrict__ stats, int d, float* __restrict__ s_out,
+                                                                   float* __restrict__ v_out, float* __restrict__ mu_out,
+                                                                   int* __restrict__ rank_out, double* __restrict__ gws, int use_gws) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ int s_rot;
+    __shared__ double s_lam[kMaxD];
+    __shared__ int s_ord[kMaxD];
+    const int v = blockIdx.x;
+    const size_t stride = 1 + d + (size_t)d * d;
+    const double* st = stats + v * stride;
+    double* A = use_gws ? gws + (size_t)v * d * d : reinterpret_cast<double*>(smem_raw);
+    const double n = st[0];
+    const double inv_n = n > 0.0 ? 1.0 / n : 0.0;
+    // C = S - s s^T / n   (column-major == row-major: symmetric)
+    for (int e = threadIdx.x; e < d * d; e += blockDim.x) {
+        const int i = e / d, j = e % d;
+        A[e] = st[1 + d + e] - st[1 + i] * st[1 + j] * inv_n;
+    }
+    for (int i = threadIdx.x; i < d; i += blockDim.x) mu_out[(size_t)v * d + i] = (float)(st[1 + i] * inv_n);
+    __syncthreads();
+
+    const int dd = (d + 1) & ~1;                 // even player count (a dummy column sits out)
+    const int npairs = dd / 2;
+    const int sub = threadIdx.x % kLanesPerPair;
+    const int slot = threadIdx.x / kLanesPerPair;
+    const int nslots = blockDim.x / kLanesPerPair;
+    const double tol = 1e-13;
+    const unsigned hmask = 0xFFFFu << (16 * ((threadIdx.x % 32) / kLanesPerPair));
+    // columns whose norm falls below 1e-14 * |C|_F are numerically null directions: never rotate them
+    __shared__ double s_fro;
+    if (threadIdx.x < 32) {
+        double acc = 0.0;
+        for (int e = threadIdx.x; e < d * d; e += 32) acc = fma(A[e], A[e], acc);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (threadIdx.x == 0) s_fro = acc;
+    }
+    __syncthreads();
+    const double null2 = 1e-28 * s_fro;
+    for (int sweep = 0; sweep < 30; ++sweep) {
+        if (threadIdx.x == 0) s_rot = 0;
+        __syncthreads();
+        for (int step = 0; step < dd - 1; ++step) {
+            for (int pi = slot; pi < npairs; pi += nslots) {
+                int p, q;
+                if (pi == 0) { p = dd - 1; q = step % (dd - 1); }
+                else { p = (step + pi) % (dd - 1); q = (step - pi + (dd - 1)) % (dd - 1); }
+                if (p < d && q < d) {                      // uniform across the 16 lanes of the pair
+                    double* ap = A + (size_t)p * d;
+                    double* aq = A + (size_t)q * d;
+                    double al = 0.0, be = 0.0, ga = 0.0;
+                    for (int r = sub; r < d; r += kLanesPerPair) {
+                        const double x = ap[r], y = aq[r];
+                        al = fma(x, x, al); be = fma(y, y, be); ga = fma(x, y, ga);
+                    }
+#pragma unroll
+                    for (int o = kLanesPerPair / 2; o > 0; o >>= 1) {
+                        al += __shfl_xor_sync(hmask, al, o, kLanesPerPair);
+                        be += __shfl_xor_sync(hmask, be, o, kLanesPerPair);
+                        ga += __shfl_xor_sync(hmask, ga, o, kLanesPerPair);
+                    }
+                    if (fabs(ga) > tol * sqrt(al * be) && ga != 0.0 && al > null2 && be > null2) {
+                        const double zeta = (be - al) / (2.0 * ga);
+                        const double t = (zeta >= 0.0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+                        const double c = 1.0 / sqrt(1.0 + t * t), sn = c * t;
+                        for (int r = sub; r < d; r += kLanesPerPair) {
+                            const double x = ap[r], y = aq[r];
+                            ap[r] = c * x - sn * y;
+                            aq[r] = sn * x + c * y;
+                        }
+                        if (sub == 0) s_rot = 1;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        const int any = s_rot;
+        __syncthreads();
+        if (!any) break;
+    }
+    // eigenvalues = column norms; order descending by counting
+    for (int j = threadIdx.x / 32; j < d; j += blockDim.x / 32) {
+        const int lane = threadIdx.x % 32;
+        double acc = 0.0;
+        for (int r = lane; r < d; r += 32) { const double x = A[(size_t)j * d + r]; acc = fma(x, x, acc); }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (lane == 0) s_lam[j] = sqrt(acc);
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < d; j += blockDim.x) {
+        const double lj = s_lam[j];
+        int rk = 0;
+        for (int i = 0; i < d; ++i) { const double li = s_lam[i]; rk += (li > lj) || (li == lj && i < j); }
+        s_ord[j] = rk;
+    }
+    __syncthreads();
+    const int r_eff = (int)(n < (double)d ? n : (double)d);       // torch.svd(some=True): min(B, d) values
+    float* so = s_out + (size_t)v * d;
+    float* vo = v_out + (size_t)v * d * d;
+    for (int j = threadIdx.x; j < d; j += blockDim.x) {
+        const int rk = s_ord[j];
+        so[rk] = rk < r_eff ? (float)sqrt(s_lam[j]) : 0.0f;
+    }
+    for (int e = threadIdx.x; e < d * d; e += blockDim.x) {
+        const int j = e / d, r = e % d;                             // column j of A, row r
+        const double lam = s_lam[j];
+        const double val = lam > 0.0 ? A[e] / lam : (r == j ? 1.0 : 0.0);
+        vo[(size_t)r * d + s_ord[j]] = (float)val;                  // v[r][rank] : eigenvector in column `rank`
+    }
+    if (threadIdx.x == 0) rank_out[v] = r_eff;
+}
+
+// ------------------------------------------------------------------------------------------ selection
+// Global top-dim_p of the concatenated singular values (first rank[v] of every view), split per view.
+__global__ void __launch_bounds__(1024) dpca_select_kernel(const float* __restrict__ s, const int* __restrict__ rank, int nv, int d,
+                                                          int dim_p, int* __restrict__ idx, int* __restrict__ cnt) {
+    __shared__ float sv[kMaxViews * kMaxD];
+    __shared__ int sview[kMaxViews * kMaxD], sloc[kMaxViews * kMaxD], sgr[kMaxViews * kMaxD];
+    __shared__ int s_n;
+    if (threadIdx.x == 0) {
+        int n = 0;
+        for (int v = 0; v < nv; ++v) {
+            const int r = min(rank[v], d);
+            for (int i = 0; i < r; ++i) { sv[n] = s[(size_t)v * d + i]; sview[n] = v; sloc[n] = i; ++n; }
+        }
+        s_n = n;
+    }
+    for (int v = threadIdx.x; v < nv; v += blockDim.x) cnt[v] = 0;
+    __syncthreads();
+    const int n = s_n;
+    for (int e = threadIdx.x; e < n; e += blockDim.x) {
+        const float me = sv[e];
+        int g = 0;
+        for (int i = 0; i < n; ++i) { const float o = sv[i]; g += (o > me) || (o == me && i < e); }
+        sgr[e] = g;                                     // global descending rank (stable)
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < n; e += blockDim.x) {
+        if (sgr[e] < dim_p) {
+            int pos = 0;                                 // order inside the view follows the global order
+            for (int i = 0; i < n; ++i) pos += (sview[i] == sview[e]) && (sgr[i] < sgr[e]);
+            idx[(size_t)sview[e] * d + pos] = sloc[e];
+            atomicAdd(cnt + sview[e], 1);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------ projection
+// P_v = V_sel V_sel^T  (d x d, float32).  grid (d, nv), block d threads (<= 256).
+__global__ void dpca_projector_kernel(const float* __restrict__ vmat, const int* __restrict__ idx, const int* __restrict__ cnt,
+                                      int d, float* __restrict__ P) {
+    __shared__ float rowi[kMaxD];
+    __shared__ int sidx[kMaxD];
+    const int v = blockIdx.y, i = blockIdx.x, j = threadIdx.x;
+    const float* V = vmat + (size_t)v * d * d;
+    const int k = cnt[v];
+    for (int t = threadIdx.x; t < k; t += blockDim.x) {
+        const int c = idx[(size_t)v * d + t];
+        sidx[t] = c;
+        rowi[t] = V[(size_t)i * d + c];
+    }
+    __syncthreads();
+    if (j < d) {
+        float acc = 0.0f;
+        for (int t = 0; t < k; ++t) acc = fmaf(rowi[t], __ldg(V + (size_t)j * d + sidx[t]), acc);
+        P[((size_t)v * d + i) * d + j] = acc;
+    }
+}
+
+// z_out = (z - mu) P + mu.  grid (ceil(B/32), ceil(d/32), nv), 256 threads, 32x32 output tile.
+__global__ void __launch_bounds__(256) dpca_apply_kernel(const ViewPtrs vp, long long B, int d, const float* __restrict__ P,
+                                                        const float* __restrict__ mu) {
+    __shared__ float sz[32][33], sp[32][33];
+    const int v = blockIdx.z;
+    const float* z = vp.z[v];
+    float* out = vp.out[v];
+    const float* Pv = P + (size_t)v * d * d;
+    const float* m = mu + (size_t)v * d;
+    const long long r0 = (long long)blockIdx.x * 32;
+    const int c0 = blockIdx.y * 32;
+    const int tx = threadIdx.x % 32, ty = threadIdx.x / 32;          // 32 x 8, 4 rows per thread
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int k0 = 0; k0 < d; k0 += 32) {
+        for (int e = threadIdx.x; e < 1024; e += 256) {
+            const int r = e / 32, c = e % 32;
+            const long long row = r0 + r;
+            const int kk = k0 + c;
+            sz[r][c] = (row < B && kk < d) ? __ldg(z + row * d + kk) - __ldg(m + kk) : 0.0f;
+            const int pr = k0 + r, pc = c0 + c;
+            sp[r][c] = (pr < d && pc < d) ? __ldg(Pv + (size_t)pr * d + pc) : 0.0f;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < 32; ++kk) {
+            const float pv = sp[kk][tx];
+#pragma unroll
+            for (int a = 0; a < 4; ++a) acc[a] = fmaf(sz[ty * 4 + a][kk], pv, acc[a]);
+        }
+        __syncthreads();
+    }
+    const int col = c0 + tx;
+    if (col < d) {
+        const float mc = __ldg(m + col);
+        for (int a = 0; a < 4; ++a) {
+            const long long row = r0 + ty * 4 + a;
+            if (row < B) out[row * d + col] = acc[a] + mc;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------ variance top-k
+__global__ void __launch_bounds__(256) var_topk_kernel(const double* __restrict__ stats, int d, int k, float* __restrict__ var,
+                                                      int* __restrict__ top_idx) {
+    __shared__ double sv[kMaxD * 4];
+    const double n = stats[0];
+    for (int j = threadIdx.x; j < d; j += blockDim.x) {
+        const double s = stats[1 + j];
+        const double q = stats[1 + d + (size_t)j * d + j];
+        const double vv = n > 1.0 ? (q - s * s / n) / (n - 1.0) : 0.0;     // unbiased, torch.var default
+        sv[j] = vv;
+        var[j] = (float)vv;
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < d; j += blockDim.x) {
+        const double me = sv[j];
+        int rk = 0;
+        for (int i = 0; i < d; ++i) rk += (sv[i] > me) || (sv[i] == me && i < j);
+        if (rk < k) top_idx[rk] = j;
+    }
+}
+
+static size_t eig_smem_bytes(int d) { return (size_t)d * d * sizeof(double); }
+
+static int dpca_tc_stats(const float* const* z, int nv, long long B, int d, double* stats, void* ws, size_t ws_bytes,
+                         cudaStream_t st) {
+    TAC_REQUIRE(d <= kTcFeat, "TAC_GRAM_TF32X3 supports d <= %d (got %d); use TAC_GRAM_FP64", kTcFeat, d);
+    const size_t need = dpca_tc_workspace_bytes(nv, B, d);
+    if (!ws || ws_bytes < need) return set_error(TAC_EWORKSPACE, "tac_dpca_stats needs %zu workspace bytes", need);
+    TAC_ALIGNED16(ws, "workspace");
+    const float* p[8];
+    for (int i = 0; i < 8; ++i) p[i] = z[i < nv ? i : 0];
+    const int nsplit = (int)((B + kTcRowsPerCta - 1) / kTcRowsPerCta);
+    float* partial = reinterpret_cast<float*>(ws);
+    dpca_colsum_kernel<<<nv, 1024, 0, st>>>(p[0], p[1], p[2], p[3], p[4], p[5], p[6], p[7], B, d, stats);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    TAC_CHECK_CUDA(cudaFuncSetAttribute(dpca_gram_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
+    dpca_gram_tc_kernel<<<dim3(nsplit, nv), kTcThreads, kTcSmemBytes, st>>>(p[0], p[1], p[2], p[3], p[4], p[5], p[6], p[7], B, d,
+                                                                           stats, partial);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    dpca_gram_finish_kernel<<<dim3(d, nv), kTcFeat, 0, st>>>(partial, nsplit, d, stats);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    return TAC_OK;
+}
+
+}  // namespace tac
+
+using namespace tac;
+
+extern "C" size_t tac_dpca_workspace_bytes(int nv, int64_t B, int d) {
+    if (nv <= 0 || d <= 0 || B <= 0) return 0;
+    // eig (global-memory columns for d > 128) | projector P | tensor-core Gram scratch
+    size_t eig = (size_t)nv * d * d * sizeof(double);
+    size_t proj = (size_t)nv * d * d * sizeof(float);
+    size_t tc = dpca_tc_workspace_bytes(nv, B, d);
+    size_t m = eig > proj ? eig : proj;
+    m = m > tc ? m : tc;
+    return (m + 255) & ~(size_t)255;
+}
+
+extern "C" int tac_dpca_stats(const float* const* z, int nv, int64_t B, int d, int algo, double* stats, void* workspace,
+                              size_t workspace_bytes, tac_stream_t stream) {
+    TAC_REQUIRE(z && stats, "null argument");
+    TAC_REQUIRE(nv >= 1 && nv <= kMaxViews, "nv must be in [1, %d]", kMaxViews);
+    TAC_REQUIRE(B >= 1 && d >= 1 && d <= kMaxD, "need B >= 1 and 1 <= d <= %d", kMaxD);
+    TAC_REQUIRE(algo == TAC_GRAM_TF32X3 || algo == TAC_GRAM_FP64, "unknown algo %d", algo);
+    ViewPtrs vp;
+    for (int v = 0; v < nv; ++v) {
+        TAC_REQUIRE(z[v] != nullptr, "z[%d] is null", v);
+        vp.z[v] = z[v]; vp.out[v] = nullptr;
+    }
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (algo == TAC_GRAM_TF32X3) {
+        return dpca_tc_stats(vp.z, nv, B, d, stats, workspace, workspace_bytes, st);
+    }
+    const int nt = (d + 31) / 32;
+    dpca_gram_fp64_kernel<<<dim3(nt * nt, nv), 256, 0, st>>>(vp, B, d, stats);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    return TAC_OK;
+}
+
+extern "C" int tac_dpca_eig(const double* stats, int nv, int d, float* s, float* v, float* mu, int* rank, void* workspace,
+                            size_t workspace_bytes, tac_stream_t stream) {
+    TAC_REQUIRE(stats && s && v && mu && rank, "null argument");
+    TAC_REQUIRE(nv >= 1 && nv <= kMaxViews, "nv must be in [1, %d]", kMaxViews);
+    TAC_REQUIRE(d >= 1 && d <= kMaxD, "need 1 <= d <= %d", kMaxD);
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    const size_t smem = eig_smem_bytes(d);
+    const int use_gws = smem > 160 * 1024;
+    if (use_gws) {
+        const size_t need = (size_t)nv * d * d * sizeof(double);
+        if (!workspace || workspace_bytes < need)
+            return set_error(TAC_EWORKSPACE, "tac_dpca_eig with d=%d needs %zu workspace bytes", d, need);
+    }
+    TAC_CHECK_CUDA(cudaFuncSetAttribute(dpca_eig_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    dpca_eig_kernel<<<nv, kEigThreads, use_gws ? 0 : smem, st>>>(stats, d, s, v, mu, rank, reinterpret_cast<double*>(workspace), use_gws);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    return TAC_OK;
+}
+
+extern "C" int tac_dpca_select(const float* s, const int* rank, int nv, int d, int dim_p, int* idx, int* cnt, tac_stream_t stream) {
+    TAC_REQUIRE(s && rank && idx && cnt, "null argument");
+    TAC_REQUIRE(nv >= 1 && nv <= kMaxViews && d >= 1 && d <= kMaxD, "bad nv / d");
+    TAC_REQUIRE(dim_p >= 0, "dim_p must be >= 0");
+    dpca_select_kernel<<<1, 1024, 0, reinterpret_cast<cudaStream_t>(stream)>>>(s, rank, nv, d, dim_p, idx, cnt);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    return TAC_OK;
+}
+
+extern "C" int tac_dpca_project(const float* const* z, int nv, int64_t B, int d, const float* v, const float* mu, const int* idx,
+                                const int* cnt, float* const* z_out, void* workspace, size_t workspace_bytes, tac_stream_t stream) {
+    TAC_REQUIRE(z && v && mu && idx && cnt && z_out && workspace, "null argument");
+    TAC_REQUIRE(nv >= 1 && nv <= kMaxViews && d >= 1 && d <= kMaxD && B >= 1, "bad nv / d / B");
+    const size_t need = (size_t)nv * d * d * sizeof(float);
+    if (workspace_bytes < need) return set_error(TAC_EWORKSPACE, "tac_dpca_project needs %zu workspace bytes", need);
+    ViewPtrs vp;
+    for (int i = 0; i < nv; ++i) {
+        TAC_REQUIRE(z[i] && z_out[i], "z[%d] / z_out[%d] is null", i, i);
+        vp.z[i] = z[i]; vp.out[i] = z_out[i];
+    }
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    float* P = reinterpret_cast<float*>(workspace);
+    dpca_projector_kernel<<<dim3(d, nv), ((d + 31) / 32) * 32, 0, st>>>(v, idx, cnt, d, P);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    dpca_apply_kernel<<<dim3((unsigned)((B + 31) / 32), (d + 31) / 32, nv), 256, 0, st>>>(vp, B, d, P, mu);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    return TAC_OK;
+}
+
+extern "C" int tac_var_topk(const double* stats, int d, int k, float* var, int* top_idx, tac_stream_t stream) {
+    TAC_REQUIRE(stats && var && top_idx, "null argument");
+    TAC_REQUIRE(d >= 1 && d <= kMaxD * 4 && k >= 1 && k <= d, "need 1 <= k <= d <= %d", kMaxD * 4);
+    var_topk_kernel<<<1, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(stats, d, k, var, top_idx);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    return TAC_OK;
+}

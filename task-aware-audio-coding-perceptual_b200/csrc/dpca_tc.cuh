@@ -1,0 +1,258 @@
+// Tensor-core (tcgen05) Gram matrix of the centred latent batch, 3xTF32 split precision.
+//
+//   G = Zc^T Zc,  Zc = Z - mean  ([B, d] float32, d <= 128 features zero-padded to 128)
+//
+// Zc is split as hi + lo with hi = tf32(Zc), lo = tf32(Zc - hi); the kernel accumulates
+// hi^T hi + hi^T lo + lo^T hi (the dropped lo^T lo term is ~2^-22 relative) with
+// tcgen05.mma.kind::tf32, M = N = 128, K = 8 per instruction, fp32 accumulator in TMEM.
+// Both operands are the SAME shared-memory tile read "MN-major" (features contiguous), which is
+// exactly how Z lies in global memory, so staging is one 16-byte shared store per 16-byte global
+// load.  Canonical no-swizzle MN-major layout (cute/arch/mma_sm100_desc.hpp, INTERLEAVE):
+//   element (feature f, row k) at  (f/4)*SBO + (k/8)*LBO + (k%8)*16 + (f%4)*4   bytes,
+//   SBO = 128 (one 8x16B core matrix), LBO = 32*128 = 4096 (all 128 features of 8 rows).
+// Centring with the local mean first keeps the fp32 accumulation well conditioned; the caller-
+// visible statistic sum z z^T is re-assembled in float64 as G + n * mean mean^T.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace tac {
+
+constexpr int kTcFeat = 128;                 // padded feature count = UMMA M = UMMA N
+constexpr int kTcRowsPerCta = 256;           // batch rows (GEMM K) per CTA
+constexpr int kTcChunk = 64;                 // rows staged per pipeline stage
+constexpr int kTcStages = 2;
+constexpr int kTcThreads = 128;
+constexpr uint32_t kTcSBO = 128;
+constexpr uint32_t kTcLBO = (kTcFeat / 4) * 128;                  // 4096 bytes per 8-row group
+constexpr int kTcTileBytes = (kTcChunk / 8) * (int)kTcLBO;        // 32 KiB per (hi | lo) tile
+constexpr int kTcSmemBytes = kTcStages * 2 * kTcTileBytes + 1024; // + alignment slack
+
+__device__ __forceinline__ uint32_t tc_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ uint64_t tc_make_desc(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3FFFu);
+    d |= (uint64_t)((kTcLBO >> 4) & 0x3FFFu) << 16;
+    d |= (uint64_t)((kTcSBO >> 4) & 0x3FFFu) << 32;
+    d |= (uint64_t)1 << 46;                                       // descriptor version 1 (sm_100)
+    return d;                                                     // base offset 0, SWIZZLE_NONE
+}
+
+// kind::tf32, fp32 accumulate, A and B both MN-major, M = 128, N = 128
+constexpr uint32_t kTcIdesc = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) |
+                              ((uint32_t)(kTcFeat >> 3) << 17) | ((uint32_t)(kTcFeat >> 4) << 24);
+
+__device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t"
+        "}\n"
+        :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(kTcIdesc), "r"(accumulate), "r"(0u) : "memory");
+}
+
+__device__ __forceinline__ void tc_mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(tc_smem_u32(bar)), "r"(count) : "memory");
+}
+
+// Bounded parity wait: traps instead of hanging the GPU if the barrier never completes.
+__device__ __forceinline__ void tc_mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = tc_smem_u32(bar);
+    for (uint32_t it = 0; it < (1u << 24); ++it) {
+        uint32_t done;
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "}\n"
+            : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+        if (done) return;
+    }
+    __trap();
+}
+
+__device__ __forceinline__ float tc_to_tf32(float v) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+    return __uint_as_float(r);
+}
+
+// grid (nsplit, nv); block 128.  partial[v][split][128][128] fp32 = Gram of rows [split*256, +256).
+__global__ void __launch_bounds__(kTcThreads, 1)
+dpca_gram_tc_kernel(const float* z0, const float* z1, const float* z2,
+                    const float* z3, const float* z4, const float* z5, const float* z6, const float* z7,
+                    long long B, int d, const double* __restrict__ stats, float* __restrict__ partial) {
+    extern __shared__ unsigned char tc_smem_raw[];
+    __shared__ __align__(8) uint64_t s_bar[kTcStages];
+    __shared__ uint32_t s_tmem;
+    __shared__ float s_mean[kTcFeat];
+
+    const int v = blockIdx.y, split = blockIdx.x, nsplit = gridDim.x;
+    const float* zs[8] = {z0, z1, z2, z3, z4, z5, z6, z7};
+    const float* z = zs[v];
+    const size_t stat_stride = 1 + (size_t)d + (size_t)d * d;
+    const double* st = stats + (size_t)v * stat_stride;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    // 1024-byte aligned operand tiles: [stage][hi|lo][kTcTileBytes]
+    const uint32_t raw = tc_smem_u32(tc_smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;
+    unsigned char* tiles = tc_smem_raw + (base - raw);
+
+    if (threadIdx.x < kTcFeat)
+        s_mean[threadIdx.x] = (int)threadIdx.x < d ? (float)(st[1 + threadIdx.x] / st[0]) : 0.0f;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kTcStages; ++s) tc_mbar_init(&s_bar[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     :: "r"(tc_smem_u32(&s_tmem)), "r"((uint32_t)kTcFeat) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = s_tmem;
+
+    const long long r_begin = (long long)split * kTcRowsPerCta;
+    const long long r_end = (r_begin + kTcRowsPerCta < B) ? r_begin + kTcRowsPerCta : B;
+    const int nchunks = (int)((r_end - r_begin + kTcChunk - 1) / kTcChunk);
+    const float4 mean4 = make_float4(s_mean[4 * lane], s_mean[4 * lane + 1], s_mean[4 * lane + 2], s_mean[4 * lane + 3]);
+    const bool vec_ok = ((d & 3) == 0) && ((reinterpret_cast<uintptr_t>(z) & 15u) == 0);
+
+    uint32_t phase[kTcStages] = {0, 0};
+    for (int c = 0; c < nchunks; ++c) {
+        const int stage = c % kTcStages;
+        if (c >= kTcStages) {                           // the MMAs that read this stage must have retired
+            tc_mbar_wait(&s_bar[stage], phase[stage]);
+            phase[stage] ^= 1u;
+        }
+        unsigned char* hi = tiles + (size_t)stage * 2 * kTcTileBytes;
+        unsigned char* lo = hi + kTcTileBytes;
+        // each warp stages rows k = warp, warp + 4, ... of the chunk; lane <-> features 4*lane .. 4*lane+3
+        for (int k = warp; k < kTcChunk; k += kTcThreads / 32) {
+            const long long row = r_begin + (long long)c * kTcChunk + k;
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (row < r_end) {
+                const float* zr = z + row * d;
+                if (vec_ok) {
+                    if (4 * lane < d) a = __ldg(reinterpret_cast<const float4*>(zr) + lane);
+                } else {
+                    if (4 * lane + 0 < d) a.x = __ldg(zr + 4 * lane + 0);
+                    if (4 * lane + 1 < d) a.y = __ldg(zr + 4 * lane + 1);
+                    if (4 * lane + 2 < d) a.z = __ldg(zr + 4 * lane + 2);
+                    if (4 * lane + 3 < d) a.w = __ldg(zr + 4 * lane + 3);
+                }
+                a.x = (4 * lane + 0 < d) ? a.x - mean4.x : 0.f;
+                a.y = (4 * lane + 1 < d) ? a.y - mean4.y : 0.f;
+                a.z = (4 * lane + 2 < d) ? a.z - mean4.z : 0.f;
+                a.w = (4 * lane + 3 < d) ? a.w - mean4.w : 0.f;
+            }
+            float4 h, l;
+            h.x = tc_to_tf32(a.x); h.y = tc_to_tf32(a.y); h.z = tc_to_tf32(a.z); h.w = tc_to_tf32(a.w);
+            l.x = tc_to_tf32(a.x - h.x); l.y = tc_to_tf32(a.y - h.y); l.z = tc_to_tf32(a.z - h.z); l.w = tc_to_tf32(a.w - h.w);
+            const size_t off = (size_t)lane * kTcSBO + (size_t)(k >> 3) * kTcLBO + (size_t)(k & 7) * 16;
+            *reinterpret_cast<float4*>(hi + off) = h;
+            *reinterpret_cast<float4*>(lo + off) = l;
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy stores -> async proxy
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t hi_addr = tc_smem_u32(hi), lo_addr = tc_smem_u32(lo);
+#pragma unroll
+            for (int g = 0; g < kTcChunk / 8; ++g) {
+                const uint64_t dh = tc_make_desc(hi_addr + g * kTcLBO);
+                const uint64_t dl = tc_make_desc(lo_addr + g * kTcLBO);
+                tc_mma(tmem, dh, dh, (c > 0 || g > 0) ? 1u : 0u);
+                tc_mma(tmem, dh, dl, 1u);
+                tc_mma(tmem, dl, dh, 1u);
+            }
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+                         :: "r"(tc_smem_u32(&s_bar[stage])) : "memory");
+        }
+    }
+    // drain: wait for the last commit of every stage that was used
+    for (int s = 0; s < kTcStages; ++s) {
+        const int uses = (nchunks - s + kTcStages - 1) / kTcStages;     // chunks that used stage s
+        if (s < nchunks && uses > 0) tc_mbar_wait(&s_bar[s], phase[s]);
+    }
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+
+    // epilogue: warp w owns TMEM lanes 32w .. 32w+31 (= Gram rows); thread <-> one row, 32 columns at a time
+    const int row = 32 * warp + lane;
+    float* prow = partial + (((size_t)v * nsplit + split) * kTcFeat + row) * kTcFeat;
+#pragma unroll
+    for (int c0 = 0; c0 < kTcFeat; c0 += 32) {
+        uint32_t r[32];
+        const uint32_t taddr = tmem + ((uint32_t)(32 * warp) << 16) + (uint32_t)c0;
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+            "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+            : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+              "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+              "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+              "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+            : "r"(taddr) : "memory");
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+        for (int j = 0; j < 32; j += 4)
+            *reinterpret_cast<float4*>(prow + c0 + j) =
+                make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "r"((uint32_t)kTcFeat) : "memory");
+}
+
+// Column sums in float64: stats[v][0] = B, stats[v][1 + j] = sum_b z[b][j].  grid (nv), block 1024.
+__global__ void __launch_bounds__(1024)
+dpca_colsum_kernel(const float* z0, const float* z1, const float* z2, const float* z3, const float* z4, const float* z5,
+                   const float* z6, const float* z7, long long B, int d, double* __restrict__ stats) {
+    __shared__ double sh[1024];
+    const float* zs[8] = {z0, z1, z2, z3, z4, z5, z6, z7};
+    const int v = blockIdx.x;
+    const float* z = zs[v];
+    double* st = stats + (size_t)v * (1 + (size_t)d + (size_t)d * d);
+    const int groups = 1024 / 256;                        // d <= 256 columns x 4 row groups
+    const int col = threadIdx.x % 256, grp = threadIdx.x / 256;
+    double acc = 0.0;
+    if (col < d)
+        for (long long r = grp; r < B; r += groups) acc += (double)__ldg(z + r * d + col);
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    if (grp == 0 && col < d) st[1 + col] = sh[col] + sh[256 + col] + sh[512 + col] + sh[768 + col];
+    if (threadIdx.x == 0) st[0] = (double)B;
+}
+
+// stats S = sum_split partial + n * mean mean^T   (float64).  grid (d, nv), block 128.
+__global__ void __launch_bounds__(kTcFeat)
+dpca_gram_finish_kernel(const float* __restrict__ partial, int nsplit, int d, double* __restrict__ stats) {
+    const int v = blockIdx.y, i = blockIdx.x, j = threadIdx.x;
+    double* st = stats + (size_t)v * (1 + (size_t)d + (size_t)d * d);
+    if (j >= d) return;
+    const double n = st[0];
+    double acc = 0.0;
+    for (int s = 0; s < nsplit; ++s) {
+        // symmetrise: (i, j) and (j, i) were accumulated by different instruction orders
+        const float* p = partial + ((size_t)v * nsplit + s) * kTcFeat * kTcFeat;
+        acc += 0.5 * ((double)p[(size_t)i * kTcFeat + j] + (double)p[(size_t)j * kTcFeat + i]);
+    }
+    const double mi = st[1 + i] / n, mj = st[1 + j] / n;
+    st[1 + d + (size_t)i * d + j] = acc + n * mi * mj;
+}
+
+inline size_t dpca_tc_workspace_bytes(int nv, long long B, int d) {
+    if (d > kTcFeat) return 0;
+    const long long nsplit = (B + kTcRowsPerCta - 1) / kTcRowsPerCta;
+    return (size_t)nv * (size_t)nsplit * kTcFeat * kTcFeat * sizeof(float);
+}
+
+}  // namespace tac

@@ -1,0 +1,476 @@
+// K2 -- fused multi-resolution STFT loss (forward and backward) and K2' -- the reference's
+// spectral MSE / SNR reductions.  No spectrogram ever reaches HBM: every warp transforms a frame
+// of x and the same frame of y in registers, compares magnitudes and folds the two per-scale sums
+// with warp shuffles -> shared memory -> one float64 partial per CTA -> a fixed-order final
+// reduction (bit-stable run to run).  The backward recomputes both transforms, forms dL/dY in the
+// frequency domain, runs the adjoint transform (fft_core.cuh: warp_fft_adj) and overlap-adds the
+// windowed frames into a shared-memory accumulator in conflict-free "rounds" (frames f, f + R,
+// f + 2R ... with R = ceil(n/hop) never overlap), so the result is deterministic too.
+#include "tac_common.cuh"
+
+namespace tac {
+
+struct LossScale {
+    int n, hop, F, K, R;     // R = ceil(n / hop): frames f and f + R do not overlap
+    FftTables t;
+};
+
+struct LossArgs {
+    const float* x;
+    const float* y;
+    long long T;
+    int nscales, chunk, nchunks, tile_len, vec_ok;
+    float eps;
+    double* partial;          // fwd: [grid][2*nscales]
+    const float* coef;        // bwd: [2*nscales] device
+    float* grad;              // bwd: [rows][T]
+    LossScale sc[TAC_MAX_SCALES];
+};
+
+__device__ __forceinline__ int nfr_of(int n) { return n >= 2048 ? 1 : (n >= 512 ? 2 : (n >= 128 ? 4 : 8)); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// ------------------------------------------------------------------------------------------ forward
+constexpr int kFwdWarps = 6;
+constexpr int kFwdThreads = kFwdWarps * 32;
+
+__device__ __forceinline__ void stage_plain(float* tile, const float* __restrict__ xr, long long g0, int len,
+                                            long long T, bool vec_ok) {
+    if (g0 + len <= T && vec_ok && (g0 & 3) == 0 && (len & 3) == 0) {
+        const float4* src = reinterpret_cast<const float4*>(xr + g0);
+        float4* dst = reinterpret_cast<float4*>(tile);
+        for (int i = threadIdx.x; i < (len >> 2); i += blockDim.x) dst[i] = __ldg(src + i);
+    } else {
+        for (int j = threadIdx.x; j < len; j += blockDim.x) tile[j] = (g0 + j < T) ? __ldg(xr + g0 + j) : 0.0f;
+    }
+}
+
+template <class P>
+__device__ __forceinline__ void loss_fwd_task(const LossScale& sc, const float* tx, const float* ty, float2* xbuf,
+                                              int lane, int f_first, int f_end, int origin, float eps,
+                                              float& acc_l1, float& acc_log) {
+    float zr[P::BQ], zi[P::BQ];
+    float mx[P::BQ + 1];
+    const float2* __restrict__ win2 = sc.t.win2;
+    const int hop = sc.hop;
+    const float* cur = tx;
+    auto load = [&](int fr, int m) -> float2 {
+        int f = f_first + fr;
+        f = f < f_end ? f : f_first;
+        const float2 v = *reinterpret_cast<const float2*>(cur + (f * hop - origin) + 2 * m);
+        const float2 w = ldg2(win2 + m);
+        return make_float2(v.x * w.x, v.y * w.y);
+    };
+    warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load);
+    warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
+        mx[slot] = sqrtf(fmaf(vr, vr, vi * vi));
+    });
+    cur = ty;
+    warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load);
+    const bool valid = (f_first + lane / P::A) < f_end;
+    float l1 = 0.0f, ll = 0.0f;
+    warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
+        const float my = sqrtf(fmaf(vr, vr, vi * vi));
+        const float xv = mx[slot];
+        l1 += fabsf(xv - my);
+        ll += fabsf(__logf(__fdividef(fmaxf(xv, eps), fmaxf(my, eps))));
+    });
+    if (valid) { acc_l1 += l1; acc_log += ll; }
+}
+
+__global__ void __launch_bounds__(kFwdThreads, 2) mrstft_fwd_kernel(const LossArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float* tx = reinterpret_cast<float*>(smem_raw);
+    float* ty = tx + a.tile_len;
+    float2* xbuf_all = reinterpret_cast<float2*>(ty + a.tile_len);
+    __shared__ int s_task_begin[TAC_MAX_SCALES + 1];
+    __shared__ int s_f_lo[TAC_MAX_SCALES], s_f_hi[TAC_MAX_SCALES];
+    __shared__ double s_acc[kFwdWarps][2 * TAC_MAX_SCALES];
+
+    const int c = blockIdx.x % a.nchunks;
+    const long long row = blockIdx.x / a.nchunks;
+    const long long c0 = (long long)c * a.chunk;
+    stage_plain(tx, a.x + row * a.T, c0, a.tile_len, a.T, a.vec_ok != 0);
+    stage_plain(ty, a.y + row * a.T, c0, a.tile_len, a.T, a.vec_ok != 0);
+    if (threadIdx.x == 0) {
+        int acc = 0;
+        for (int s = 0; s < a.nscales; ++s) {
+            const int h = a.sc[s].hop;
+            long long lo = (c0 + h - 1) / h, hi = (c0 + a.chunk + h - 1) / h;
+            if (hi > a.sc[s].F) hi = a.sc[s].F;
+            if (lo > hi) lo = hi;
+            const int nfr = nfr_of(a.sc[s].n);
+            s_f_lo[s] = (int)lo; s_f_hi[s] = (int)hi;
+            s_task_begin[s] = acc;
+            acc += (int)((hi - lo + nfr - 1) / nfr);
+        }
+        s_task_begin[a.nscales] = acc;
+    }
+    for (int i = threadIdx.x; i < kFwdWarps * 2 * TAC_MAX_SCALES; i += blockDim.x) (&s_acc[0][0])[i] = 0.0;
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float2* xbuf = xbuf_all + warp * kXbufFloat2;
+    const int ntasks = s_task_begin[a.nscales];
+    for (int t = warp; t < ntasks; t += kFwdWarps) {          // static assignment -> deterministic sums
+        int s = 0;
+        while (t >= s_task_begin[s + 1]) ++s;
+        const LossScale& sc = a.sc[s];
+        const int f_first = s_f_lo[s] + (t - s_task_begin[s]) * nfr_of(sc.n);
+        const int f_end = s_f_hi[s];
+        float l1 = 0.0f, ll = 0.0f;
+        switch (sc.n) {
+            case 2048: loss_fwd_task<Plan2048>(sc, tx, ty, xbuf, lane, f_first, f_end, (int)c0, a.eps, l1, ll); break;
+            case 1024: loss_fwd_task<Plan1024>(sc, tx, ty, xbuf, lane, f_first, f_end, (int)c0, a.eps, l1, ll); break;
+            case 512: loss_fwd_task<Plan512>(sc, tx, ty, xbuf, lane, f_first, f_end, (int)c0, a.eps, l1, ll); break;
+            case 256: loss_fwd_task<Plan256>(sc, tx, ty, xbuf, lane, f_first, f_end, (int)c0, a.eps, l1, ll); break;
+            case 128: loss_fwd_task<Plan128>(sc, tx, ty, xbuf, lane, f_first, f_end, (int)c0, a.eps, l1, ll); break;
+            default: loss_fwd_task<Plan64>(sc, tx, ty, xbuf, lane, f_first, f_end, (int)c0, a.eps, l1, ll); break;
+        }
+        l1 = warp_sum(l1);
+        ll = warp_sum(ll);
+        if (lane == 0) { s_acc[warp][2 * s] += (double)l1; s_acc[warp][2 * s + 1] += (double)ll; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 2 * a.nscales) {
+        double v = 0.0;
+        for (int w = 0; w < kFwdWarps; ++w) v += s_acc[w][threadIdx.x];
+        a.partial[(long long)blockIdx.x * (2 * a.nscales) + threadIdx.x] = v;
+    }
+}
+
+// Fixed-order reduction of the per-CTA partials: out[j] = sum_i partial[i][j].
+__global__ void __launch_bounds__(256) partial_reduce_kernel(const double* __restrict__ partial, long long n, int width,
+                                                            double* __restrict__ out) {
+    __shared__ double sh[256];
+    const int j = blockIdx.x;
+    double v = 0.0;
+    for (long long i = threadIdx.x; i < n; i += 256) v += partial[i * width + j];
+    sh[threadIdx.x] = v;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[j] = sh[0];
+}
+
+// ------------------------------------------------------------------------------------------ backward
+constexpr int kBwdWarps = 4;
+constexpr int kBwdThreads = kBwdWarps * 32;
+
+template <class P>
+__device__ __forceinline__ void loss_bwd_task(const LossScale& sc, const float* __restrict__ xr, const float* __restrict__ yr,
+                                              float* acc, float2* xbuf, int lane, int f_base, int f_stride, int f_end,
+                                              long long c0, float eps, float c_l1, float c_log) {
+    float zr[P::BQ], zi[P::BQ];
+    float gr[P::BQ + 1], gi[P::BQ + 1];
+    const float2* __restrict__ win2 = sc.t.win2;
+    const int hop = sc.hop;
+    const float* cur = xr;
+    // frames of this task: f_base + i * f_stride, i in [0, NFR)
+    auto load = [&](int fr, int m) -> float2 {
+        int f = f_base + fr * f_stride;
+        f = f < f_end ? f : f_base;
+        const float2 v = __ldg(reinterpret_cast<const float2*>(cur + (long long)f * hop) + m);
+        const float2 w = ldg2(win2 + m);
+        return make_float2(v.x * w.x, v.y * w.y);
+    };
+    warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load);
+    warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
+        gr[slot] = sqrtf(fmaf(vr, vr, vi * vi));                     // |X|
+    });
+    cur = yr;
+    warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load);
+    warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
+        const float m2 = fmaf(vr, vr, vi * vi);
+        const float inv = m2 > 0.0f ? rsqrtf(m2) : 0.0f;
+        const float my = m2 * inv;                                    // |Y|
+        const float xv = gr[slot];
+        float g = (my > xv) ? c_l1 : ((my < xv) ? -c_l1 : 0.0f);     // d|X - Y| / dY
+        const float xc = fmaxf(xv, eps), yc = fmaxf(my, eps);
+        const float sg = (yc > xc) ? c_log : ((yc < xc) ? -c_log : 0.0f);
+        if (my >= eps) g = fmaf(sg, inv, g);                          // d|ln X~ - ln Y~| / dY = sign / Y
+        g *= inv;                                                     // dY / dYc = Yc / |Y|
+        gr[slot] = g * vr; gi[slot] = g * vi;
+    });
+    warp_fft_adj<P>(xbuf, sc.t.tw, sc.t.pt, lane,
+        [&](int, int, int slot) -> float2 { return make_float2(gr[slot], gi[slot]); },
+        [&](int fr, int m, float2 g) {
+            const int f = f_base + fr * f_stride;
+            if (f < f_end) {
+                const float2 w = ldg2(win2 + m);
+                float2* p = reinterpret_cast<float2*>(acc + ((long long)f * hop - c0)) + m;
+                float2 o = *p;
+                o.x = fmaf(g.x, w.x, o.x); o.y = fmaf(g.y, w.y, o.y);
+                *p = o;
+            }
+        });
+}
+
+__global__ void __launch_bounds__(kBwdThreads, 3) mrstft_bwd_kernel(const LossArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float* acc = reinterpret_cast<float*>(smem_raw);
+    float2* xbuf_all = reinterpret_cast<float2*>(acc + a.tile_len);
+
+    const int c = blockIdx.x % a.nchunks;
+    const long long row = blockIdx.x / a.nchunks;
+    const long long c0 = (long long)c * a.chunk;
+    const float* xr = a.x + row * a.T;
+    const float* yr = a.y + row * a.T;
+    for (int j = threadIdx.x; j < a.tile_len; j += blockDim.x) acc[j] = 0.0f;
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float2* xbuf = xbuf_all + warp * kXbufFloat2;
+    for (int s = 0; s < a.nscales; ++s) {
+        const LossScale& sc = a.sc[s];
+        const int h = sc.hop, R = sc.R, nfr = nfr_of(sc.n);
+        long long lo = (c0 + h - 1) / h, hi = (c0 + a.chunk + h - 1) / h;
+        if (hi > sc.F) hi = sc.F;
+        const float c_l1 = __ldg(a.coef + 2 * s), c_log = __ldg(a.coef + 2 * s + 1);
+        for (int r = 0; r < R; ++r) {
+            // frames lo <= f < hi with f % R == r, grouped nfr at a time
+            const int first = (int)lo + (int)(((r - lo % R) % R + R) % R);
+            const int cnt = first < hi ? (int)((hi - first + R - 1) / R) : 0;
+            const int ntasks = (cnt + nfr - 1) / nfr;
+            for (int t = warp; t < ntasks; t += kBwdWarps) {
+                const int f_base = first + t * nfr * R;
+                switch (sc.n) {
+                    case 2048: loss_bwd_task<Plan2048>(sc, xr, yr, acc, xbuf, lane, f_base, R, (int)hi, c0, a.eps, c_l1, c_log); break;
+                    case 1024: loss_bwd_task<Plan1024>(sc, xr, yr, acc, xbuf, lane, f_base, R, (int)hi, c0, a.eps, c_l1, c_log); break;
+                    case 512: loss_bwd_task<Plan512>(sc, xr, yr, acc, xbuf, lane, f_base, R, (int)hi, c0, a.eps, c_l1, c_log); break;
+                    case 256: loss_bwd_task<Plan256>(sc, xr, yr, acc, xbuf, lane, f_base, R, (int)hi, c0, a.eps, c_l1, c_log); break;
+                    case 128: loss_bwd_task<Plan128>(sc, xr, yr, acc, xbuf, lane, f_base, R, (int)hi, c0, a.eps, c_l1, c_log); break;
+                    default: loss_bwd_task<Plan64>(sc, xr, yr, acc, xbuf, lane, f_base, R, (int)hi, c0, a.eps, c_l1, c_log); break;
+                }
+            }
+            __syncthreads();
+        }
+    }
+    // write-out: [c0, c0 + chunk) is this CTA's, but its first (tile_len - chunk) samples also receive
+    // the halo of chunk c-1 and its halo lands in chunk c+1 -> those two regions use atomics (at most
+    // two contributions per sample, so the sum is order independent); grad was zeroed by the caller.
+    float* gout = a.grad + row * a.T + c0;
+    const int halo = a.tile_len - a.chunk;
+    if (a.nchunks == 1) {
+        for (int j = threadIdx.x; j < a.tile_len; j += blockDim.x)
+            if (c0 + j < a.T) gout[j] = acc[j];
+    } else {
+        for (int j = threadIdx.x; j < a.tile_len; j += blockDim.x) {
+            if (c0 + j >= a.T) break;
+            if (j < halo || j >= a.chunk) atomicAdd(gout + j, acc[j]);
+            else gout[j] = acc[j];
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------ K2'
+// One pass over (obs, dec) [B, 2, K, F]: per (item, channel) sum of squared error and of obs^2.
+constexpr int kSpecThreads = 256;
+constexpr int kSpecSplit = 8;          // CTAs per (item, channel) plane
+
+__global__ void __launch_bounds__(kSpecThreads) spec_partial_kernel(const float* __restrict__ obs, const float* __restrict__ dec,
+                                                                   long long plane, double* __restrict__ partial) {
+    __shared__ double sh[2][kSpecThreads / 32];
+    const long long pl = blockIdx.x / kSpecSplit;
+    const int part = blockIdx.x % kSpecSplit;
+    const float* o = obs + pl * plane;
+    const float* d = dec + pl * plane;
+    const long long per = (((plane + kSpecSplit - 1) / kSpecSplit) + 3) & ~3ll;   // keep 16-byte alignment
+    const long long beg = (part * per < plane) ? part * per : plane, end = (beg + per < plane) ? beg + per : plane;
+    float se = 0.0f, so = 0.0f;
+    double dse = 0.0, dso = 0.0;
+    const bool vec = (((uintptr_t)(o + beg) | (uintptr_t)(d + beg)) & 15u) == 0;
+    long long i = beg + (long long)threadIdx.x * 4;
+    int it = 0;
+    if (vec) {
+        for (; i + 3 < end; i += (long long)kSpecThreads * 4) {
+            const float4 a4 = __ldcs(reinterpret_cast<const float4*>(o + i));
+            const float4 b4 = __ldcs(reinterpret_cast<const float4*>(d + i));
+            float e;
+            e = a4.x - b4.x; se = fmaf(e, e, se); so = fmaf(a4.x, a4.x, so);
+            e = a4.y - b4.y; se = fmaf(e, e, se); so = fmaf(a4.y, a4.y, so);
+            e = a4.z - b4.z; se = fmaf(e, e, se); so = fmaf(a4.z, a4.z, so);
+            e = a4.w - b4.w; se = fmaf(e, e, se); so = fmaf(a4.w, a4.w, so);
+            if (++it == 16) { dse += se; dso += so; se = so = 0.0f; it = 0; }   // bound fp32 run length
+        }
+    }
+    // tail (and the unaligned case): scalar
+    long long j0 = vec ? (beg + ((end - beg) / 4) * 4) : beg;
+    for (long long j = j0 + threadIdx.x; j < end; j += kSpecThreads) {
+        const float av = __ldg(o + j), bv = __ldg(d + j);
+        const float e = av - bv;
+        se = fmaf(e, e, se); so = fmaf(av, av, so);
+    }
+    dse += se; dso += so;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        dse += __shfl_xor_sync(0xffffffffu, dse, off);
+        dso += __shfl_xor_sync(0xffffffffu, dso, off);
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) { sh[0][warp] = dse; sh[1][warp] = dso; }
+    __syncthreads();
+    if (threadIdx.x < 2) {
+        double v = 0.0;
+        for (int w = 0; w < kSpecThreads / 32; ++w) v += sh[threadIdx.x][w];
+        partial[(long long)blockIdx.x * 2 + threadIdx.x] = v;
+    }
+}
+
+// partial: [B][2 channels][kSpecSplit][2]  ->  out5 + per_sample
+__global__ void __launch_bounds__(256) spec_final_kernel(const double* __restrict__ partial, long long B, long long plane,
+                                                        float* __restrict__ out5, float* __restrict__ per_sample) {
+    __shared__ double sh[3][256];
+    double e0 = 0.0, e1 = 0.0, ob = 0.0;
+    for (long long b = threadIdx.x; b < B; b += 256) {
+        double se[2] = {0.0, 0.0}, so = 0.0;
+        for (int ch = 0; ch < 2; ++ch)
+            for (int p = 0; p < kSpecSplit; ++p) {
+                const double* q = partial + (((b * 2 + ch) * kSpecSplit) + p) * 2;
+                se[ch] += q[0]; so += q[1];
+            }
+        if (per_sample) per_sample[b] = (float)(0.5 * (se[0] + se[1]) / (2.0 * (double)plane));
+        e0 += se[0]; e1 += se[1]; ob += so;
+    }
+    sh[0][threadIdx.x] = e0; sh[1][threadIdx.x] = e1; sh[2][threadIdx.x] = ob;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) {
+            sh[0][threadIdx.x] += sh[0][threadIdx.x + o];
+            sh[1][threadIdx.x] += sh[1][threadIdx.x + o];
+            sh[2][threadIdx.x] += sh[2][threadIdx.x + o];
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        const double n1 = (double)B * (double)plane;
+        const double tot = (sh[0][0] + sh[1][0]) / (2.0 * n1);
+        out5[0] = (float)(sh[0][0] / n1);
+        out5[1] = (float)(sh[1][0] / n1);
+        out5[2] = (float)tot;
+        out5[3] = (float)(-10.0 * log10(tot / (sh[2][0] / (2.0 * n1))));
+        out5[4] = (float)(0.5 * tot);
+    }
+}
+
+static int fill_loss_args(LossArgs& a, const float* x, const float* y, int64_t B, int64_t T, int n_scales,
+                          const int* n_fft, const int* hop, const int* win, float eps, int chunk) {
+    TAC_REQUIRE(x && y && n_fft && hop, "null argument");
+    TAC_REQUIRE(B > 0 && T > 0, "B and T must be positive");
+    TAC_REQUIRE(n_scales >= 1 && n_scales <= TAC_MAX_SCALES, "n_scales must be in [1, %d]", TAC_MAX_SCALES);
+    TAC_REQUIRE(eps > 0.0f, "eps must be positive");
+    TAC_REQUIRE(T < (1ll << 30), "T too large");
+    a.x = x; a.y = y; a.T = T; a.nscales = n_scales; a.eps = eps; a.chunk = chunk;
+    a.vec_ok = ((((uintptr_t)x | (uintptr_t)y) & 15u) == 0 && (T & 3) == 0) ? 1 : 0;
+    int nmax = 0;
+    long long last_start = 0;
+    for (int s = 0; s < n_scales; ++s) {
+        LossScale& sc = a.sc[s];
+        TAC_REQUIRE(supported_nfft(n_fft[s]), "unsupported n_fft %d", n_fft[s]);
+        TAC_REQUIRE(hop[s] >= 2 && (hop[s] & 1) == 0 && hop[s] <= n_fft[s], "hop %d must be even and in [2, n_fft]", hop[s]);
+        sc.n = n_fft[s]; sc.hop = hop[s];
+        sc.F = (int)num_frames(T, sc.n, sc.hop, 0);
+        TAC_REQUIRE(sc.F >= 1, "signal of %lld samples is shorter than n_fft=%d", (long long)T, sc.n);
+        sc.K = sc.n / 2 + 1;
+        sc.R = (sc.n + sc.hop - 1) / sc.hop;
+        int rc = get_tables(sc.n, win ? win[s] : sc.n, 1, &sc.t);
+        if (rc) return rc;
+        nmax = sc.n > nmax ? sc.n : nmax;
+        const long long ls = (long long)(sc.F - 1) * sc.hop;
+        last_start = ls > last_start ? ls : last_start;
+    }
+    a.nchunks = (int)(last_start / chunk) + 1;
+    a.tile_len = chunk + nmax;
+    return TAC_OK;
+}
+
+constexpr int kFwdChunk = 2048;
+constexpr int kBwdChunk = 8192;
+
+}  // namespace tac
+
+using namespace tac;
+
+extern "C" size_t tac_mrstft_workspace_bytes(int64_t B, int64_t T, int n_scales, const int* n_fft, const int* hop) {
+    if (B <= 0 || T <= 0 || n_scales <= 0 || !n_fft || !hop) return 0;
+    long long last_start = 0;
+    for (int s = 0; s < n_scales; ++s) {
+        const long long F = num_frames(T, n_fft[s], hop[s], 0);
+        const long long ls = F > 0 ? (F - 1) * hop[s] : 0;
+        last_start = ls > last_start ? ls : last_start;
+    }
+    const long long nchunks = last_start / kFwdChunk + 1;
+    return (size_t)(B * nchunks * 2 * n_scales) * sizeof(double);
+}
+
+extern "C" int tac_mrstft_loss_fwd(const float* x, const float* y, int64_t B, int64_t T, int n_scales, const int* n_fft,
+                                   const int* hop, const int* win, float eps, double* sums, void* workspace,
+                                   size_t workspace_bytes, tac_stream_t stream) {
+    LossArgs a;
+    int rc = fill_loss_args(a, x, y, B, T, n_scales, n_fft, hop, win, eps, kFwdChunk);
+    if (rc) return rc;
+    TAC_REQUIRE(sums && workspace, "null output / workspace");
+    const long long grid = B * a.nchunks;
+    TAC_REQUIRE(grid < (1ll << 31), "grid too large");
+    const size_t need = (size_t)grid * 2 * n_scales * sizeof(double);
+    if (workspace_bytes < need) return set_error(TAC_EWORKSPACE, "workspace needs %zu bytes, got %zu", need, workspace_bytes);
+    TAC_ALIGNED16(workspace, "workspace");
+    a.partial = reinterpret_cast<double*>(workspace);
+    a.coef = nullptr; a.grad = nullptr;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    const size_t smem = 2 * (size_t)a.tile_len * sizeof(float) + (size_t)kFwdWarps * kXbufFloat2 * sizeof(float2);
+    TAC_CHECK_CUDA(cudaFuncSetAttribute(mrstft_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+    mrstft_fwd_kernel<<<(unsigned)grid, kFwdThreads, smem, st>>>(a);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    partial_reduce_kernel<<<2 * n_scales, 256, 0, st>>>(a.partial, grid, 2 * n_scales, sums);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    return TAC_OK;
+}
+
+extern "C" int tac_mrstft_loss_bwd(const float* x, const float* y, int64_t B, int64_t T, int n_scales, const int* n_fft,
+                                   const int* hop, const int* win, float eps, const float* coef, float* grad_y,
+                                   void* workspace, size_t workspace_bytes, tac_stream_t stream) {
+    (void)workspace; (void)workspace_bytes;
+    LossArgs a;
+    int rc = fill_loss_args(a, x, y, B, T, n_scales, n_fft, hop, win, eps, kBwdChunk);
+    if (rc) return rc;
+    TAC_REQUIRE(coef && grad_y, "null coef / grad_y");
+    TAC_REQUIRE((((uintptr_t)x | (uintptr_t)y) & 7u) == 0 && (T & 1) == 0, "backward needs 8-byte aligned x, y and even T");
+    a.partial = nullptr; a.coef = coef; a.grad = grad_y;
+    const long long grid = B * a.nchunks;
+    TAC_REQUIRE(grid < (1ll << 31), "grid too large");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (a.nchunks > 1) TAC_CHECK_CUDA(cudaMemsetAsync(grad_y, 0, (size_t)B * T * sizeof(float), st));
+    const size_t smem = (size_t)a.tile_len * sizeof(float) + (size_t)kBwdWarps * kXbufFloat2 * sizeof(float2);
+    TAC_CHECK_CUDA(cudaFuncSetAttribute(mrstft_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 75 * 1024));
+    mrstft_bwd_kernel<<<(unsigned)grid, kBwdThreads, smem, st>>>(a);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    return TAC_OK;
+}
+
+extern "C" size_t tac_spec_losses_workspace_bytes(int64_t B) {
+    return B > 0 ? (size_t)B * 2 * kSpecSplit * 2 * sizeof(double) : 0;
+}
+
+extern "C" int tac_spec_losses(const float* obs, const float* dec, int64_t B, int64_t K, int64_t F, float* out5,
+                               float* per_sample, void* workspace, size_t workspace_bytes, tac_stream_t stream) {
+    TAC_REQUIRE(obs && dec && out5 && workspace, "null argument");
+    TAC_REQUIRE(B > 0 && K > 0 && F > 0, "B, K, F must be positive");
+    const size_t need = tac_spec_losses_workspace_bytes(B);
+    if (workspace_bytes < need) return set_error(TAC_EWORKSPACE, "workspace needs %zu bytes, got %zu", need, workspace_bytes);
+    TAC_REQUIRE(B * 2 * kSpecSplit < (1ll << 31), "grid too large");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    double* partial = reinterpret_cast<double*>(workspace);
+    spec_partial_kernel<<<(unsigned)(B * 2 * kSpecSplit), kSpecThreads, 0, st>>>(obs, dec, K * F, partial);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    spec_final_kernel<<<1, 256, 0, st>>>(partial, B, K * F, out5, per_sample);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    return TAC_OK;
+}

@@ -1,0 +1,363 @@
+// K1 -- batched multi-scale STFT (framing + Hann window + real FFT + output epilogue, fused).
+//
+//  * stft_planes_kernel: ALL scales of a signal chunk in one CTA.  The chunk (+ halo) is staged in
+//    shared memory once with 16-byte loads; every warp pulls "tasks" (NFR frames of one scale) from a
+//    shared counter, transforms them in registers (fft_core.cuh) and writes the real / imaginary
+//    planes in the frequency-innermost layout [B, 2C, F, K] of msstftd.py:152-153 -- one fully
+//    coalesced 128-byte store per warp instruction.  HBM traffic = read x once + write the planes.
+//  * stft_tiled_kernel: one scale, a tile of TF consecutive frames per CTA, for the time-innermost
+//    layouts (complex [B,C,K,F] of torchaudio; magnitude/phase [B,2,K,f_pad] of the notebook front
+//    end).  Results are transposed through a padded shared-memory tile so that each (k) row is
+//    written as a contiguous run of TF frames.
+#include "tac_common.cuh"
+
+namespace tac {
+
+constexpr int kWarps = 8;
+constexpr int kThreads = kWarps * 32;
+
+struct ScaleArg {
+    int n, hop, pad, F, K;
+    FftTables t;
+    float* out;
+};
+
+struct PlanesArgs {
+    const float* x;
+    long long T;
+    int C, nscales, chunk, nchunks, pmax, tile_len, pad_mode, vec_ok;
+    ScaleArg sc[TAC_MAX_SCALES];
+};
+
+// Original-signal value at (possibly out-of-range) index g, honouring the centre padding mode.
+__device__ __forceinline__ float padded_sample(const float* __restrict__ xr, long long g, long long T, int pad_mode) {
+    if (g >= 0 && g < T) return __ldg(xr + g);
+    if (pad_mode == TAC_PAD_REFLECT) {
+        long long r = g < 0 ? -g : 2 * (T - 1) - g;
+        if (r >= 0 && r < T) return __ldg(xr + r);
+    }
+    return 0.0f;
+}
+
+// tile[j] = x_padded[g0 + j], j in [0, len)
+__device__ __forceinline__ void stage_tile(float* tile, const float* __restrict__ xr, long long g0, int len,
+                                           long long T, int pad_mode, bool vec_ok) {
+    const bool interior = g0 >= 0 && g0 + len <= T;
+    if (interior && vec_ok && (g0 & 3) == 0 && (len & 3) == 0) {
+        const float4* src = reinterpret_cast<const float4*>(xr + g0);
+        float4* dst = reinterpret_cast<float4*>(tile);
+        for (int i = threadIdx.x; i < (len >> 2); i += blockDim.x) dst[i] = __ldg(src + i);
+    } else {
+        for (int j = threadIdx.x; j < len; j += blockDim.x) tile[j] = padded_sample(xr, g0 + j, T, pad_mode);
+    }
+}
+
+// One warp task of the planes kernel: frames [f_first, f_first + NFR) of one scale.
+template <class P>
+__device__ __forceinline__ void planes_task(const ScaleArg& sc, const float* tile, float2* xbuf, int lane,
+                                            int f_first, int f_end, int tile_origin /* f*hop coordinate of tile[0] */,
+                                            float* out_re_row, long long im_off) {
+    float zr[P::BQ], zi[P::BQ];
+    const float2* __restrict__ win2 = sc.t.win2;
+    const int hop = sc.hop;
+    auto load = [&](int fr, int m) -> float2 {
+        int f = f_first + fr;
+        f = f < f_end ? f : f_first;                       // invalid frames recompute the first one
+        const float2 v = *reinterpret_cast<const float2*>(tile + (f * hop - tile_origin) + 2 * m);
+        const float2 w = ldg2(win2 + m);
+        return make_float2(v.x * w.x, v.y * w.y);
+    };
+    warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load);
+    const int myf = f_first + lane / P::A;
+    const bool valid = myf < f_end;
+    // per-lane base pointers so that every store address is base + compile-time offset
+    const int k1 = lane % P::A;
+    float* re_lo = out_re_row + (long long)myf * sc.K + k1;
+    float* re_hi = out_re_row + (long long)myf * sc.K + (P::M - k1);
+    float* im_lo = re_lo + im_off;
+    float* im_hi = re_hi + im_off;
+    warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
+        if (valid) {
+            if (slot == P::BQ) {                       // k = M/2 (k1 == 0 lanes only)
+                __stcs(re_lo + P::M / 2, vr); __stcs(im_lo + P::M / 2, vi);
+            } else if (slot & 1) {                     // k = M - k1 - A*j
+                __stcs(re_hi - P::A * (slot >> 1), vr); __stcs(im_hi - P::A * (slot >> 1), vi);
+            } else {                                   // k = k1 + A*j
+                __stcs(re_lo + P::A * (slot >> 1), vr); __stcs(im_lo + P::A * (slot >> 1), vi);
+            }
+        }
+    });
+}
+
+__global__ void __launch_bounds__(kThreads, 2) stft_planes_kernel(const PlanesArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float* tile = reinterpret_cast<float*>(smem_raw);
+    float2* xbuf_all = reinterpret_cast<float2*>(smem_raw + (size_t)a.tile_len * sizeof(float));
+    __shared__ int s_task_begin[TAC_MAX_SCALES + 1];
+    __shared__ int s_f_lo[TAC_MAX_SCALES], s_f_hi[TAC_MAX_SCALES];
+    __shared__ int s_next;
+
+    const int c = blockIdx.x % a.nchunks;
+    const long long row = blockIdx.x / a.nchunks;
+    const float* xr = a.x + row * a.T;
+    const long long c0 = (long long)c * a.chunk;             // chunk origin in padded frame-start coordinates
+
+    stage_tile(tile, xr, c0 - a.pmax, a.tile_len, a.T, a.pad_mode, a.vec_ok != 0);
+    if (threadIdx.x == 0) {
+        int acc = 0;
+        for (int s = 0; s < a.nscales; ++s) {
+            const int h = a.sc[s].hop;
+            long long lo = (c0 + h - 1) / h, hi = (c0 + a.chunk + h - 1) / h;
+            if (hi > a.sc[s].F) hi = a.sc[s].F;
+            if (lo > hi) lo = hi;
+            const int nfr = a.sc[s].n >= 2048 ? 1 : (a.sc[s].n >= 512 ? 2 : (a.sc[s].n >= 128 ? 4 : 8));
+            s_f_lo[s] = (int)lo; s_f_hi[s] = (int)hi;
+            s_task_begin[s] = acc;
+            acc += (int)((hi - lo + nfr - 1) / nfr);
+        }
+        s_task_begin[a.nscales] = acc;
+        s_next = 0;
+    }
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float2* xbuf = xbuf_all + warp * kXbufFloat2;
+    const int ntasks = s_task_begin[a.nscales];
+    const long long b = row / a.C, ch = row % a.C;
+    for (;;) {
+        int t = 0;
+        if (lane == 0) t = atomicAdd(&s_next, 1);
+        t = __shfl_sync(0xffffffffu, t, 0);
+        if (t >= ntasks) break;
+        int s = 0;
+        while (t >= s_task_begin[s + 1]) ++s;
+        const ScaleArg& sc = a.sc[s];
+        const int nfr = sc.n >= 2048 ? 1 : (sc.n >= 512 ? 2 : (sc.n >= 128 ? 4 : 8));
+        const int f_first = s_f_lo[s] + (t - s_task_begin[s]) * nfr;
+        const int f_end = s_f_hi[s];
+        // tile[0] is padded-coordinate (c0 - pmax) of the widest scale == (c0 - pmax + pad_s) of scale s
+        const int origin = (int)(c0 - a.pmax + sc.pad);
+        const long long plane = (long long)sc.F * sc.K;
+        float* out_re_row = sc.out + ((b * 2) * a.C + ch) * plane;
+        const long long im_off = (long long)a.C * plane;
+        switch (sc.n) {
+            case 2048: planes_task<Plan2048>(sc, tile, xbuf, lane, f_first, f_end, origin, out_re_row, im_off); break;
+            case 1024: planes_task<Plan1024>(sc, tile, xbuf, lane, f_first, f_end, origin, out_re_row, im_off); break;
+            case 512: planes_task<Plan512>(sc, tile, xbuf, lane, f_first, f_end, origin, out_re_row, im_off); break;
+            case 256: planes_task<Plan256>(sc, tile, xbuf, lane, f_first, f_end, origin, out_re_row, im_off); break;
+            case 128: planes_task<Plan128>(sc, tile, xbuf, lane, f_first, f_end, origin, out_re_row, im_off); break;
+            default: planes_task<Plan64>(sc, tile, xbuf, lane, f_first, f_end, origin, out_re_row, im_off); break;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+struct TiledArgs {
+    const float* x;
+    long long T;
+    int n, hop, pad, F, K, TF, ntiles, tile_len, pad_mode, vec_ok;
+    long long f_pad;                 // time extent of the output rows (>= F)
+    FftTables t;
+    float* out;
+};
+
+template <class P, int MODE>
+__global__ void __launch_bounds__(kThreads, 1) stft_tiled_kernel(const TiledArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float* tile = reinterpret_cast<float*>(smem_raw);
+    float* otile = tile + a.tile_len;                               // [2][K][TF+1]
+    float2* xbuf_all = reinterpret_cast<float2*>(otile + 2 * (size_t)a.K * (a.TF + 1));
+    __shared__ int s_next;
+
+    const int ft = blockIdx.x % a.ntiles;
+    const long long row = blockIdx.x / a.ntiles;
+    const float* xr = a.x + row * a.T;
+    const int f0 = ft * a.TF;
+    const int f_end = min(a.F, f0 + a.TF);
+    const long long g0 = (long long)f0 * a.hop - a.pad;
+    stage_tile(tile, xr, g0, a.tile_len, a.T, a.pad_mode, a.vec_ok != 0);
+    if (threadIdx.x == 0) s_next = 0;
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float2* xbuf = xbuf_all + warp * kXbufFloat2;
+    const int ntasks = (f_end - f0 + P::NFR - 1) / P::NFR;
+    const int TS = a.TF + 1;
+    float* o0 = otile;
+    float* o1 = otile + (size_t)a.K * TS;
+    for (;;) {
+        int t = 0;
+        if (lane == 0) t = atomicAdd(&s_next, 1);
+        t = __shfl_sync(0xffffffffu, t, 0);
+        if (t >= ntasks) break;
+        const int f_first = f0 + t * P::NFR;
+        float zr[P::BQ], zi[P::BQ];
+        const float2* __restrict__ win2 = a.t.win2;
+        auto load = [&](int fr, int m) -> float2 {
+            int f = f_first + fr;
+            f = f < f_end ? f : f_first;
+            const float2 v = *reinterpret_cast<const float2*>(tile + (f - f0) * a.hop + 2 * m);
+            const float2 w = ldg2(win2 + m);
+            return make_float2(v.x * w.x, v.y * w.y);
+        };
+        warp_fft_fwd<P>(zr, zi, xbuf, a.t.tw, lane, load);
+        const int myf = f_first + lane / P::A;
+        const bool valid = myf < f_end;
+        const int col = myf - f0;
+        warp_fft_post<P>(zr, zi, a.t.pt, lane, [&](int, int k, float vr, float vi, int) {
+            if (valid) {
+                if (MODE == TAC_OUT_MAGPHASE) {
+                    o0[k * TS + col] = sqrtf(fmaf(vr, vr, vi * vi));
+                    o1[k * TS + col] = atan2f(vi, vr);
+                } else {
+                    o0[k * TS + col] = vr;
+                    o1[k * TS + col] = vi;
+                }
+            }
+        });
+    }
+    __syncthreads();
+    const int nf = f_end - f0;
+    const int total = a.K * nf;
+    if (MODE == TAC_OUT_MAGPHASE) {
+        float* out0 = a.out + (row * 2) * (long long)a.K * a.f_pad + f0;
+        float* out1 = out0 + (long long)a.K * a.f_pad;
+        for (int i = threadIdx.x; i < total; i += blockDim.x) {
+            const int k = i / nf, tt = i - k * nf;
+            __stcs(out0 + (long long)k * a.f_pad + tt, o0[k * TS + tt]);
+            __stcs(out1 + (long long)k * a.f_pad + tt, o1[k * TS + tt]);
+        }
+    } else {
+        float2* outc = reinterpret_cast<float2*>(a.out) + row * (long long)a.K * a.F + f0;
+        for (int i = threadIdx.x; i < total; i += blockDim.x) {
+            const int k = i / nf, tt = i - k * nf;
+            __stcs(outc + (long long)k * a.F + tt, make_float2(o0[k * TS + tt], o1[k * TS + tt]));
+        }
+    }
+}
+
+template <class P, int MODE>
+static int launch_tiled(const TiledArgs& a, long long rows, size_t smem, cudaStream_t st) {
+    auto kern = stft_tiled_kernel<P, MODE>;
+    static bool attr_set = false;      // per instantiation; idempotent
+    if (!attr_set) {
+        TAC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_set = true;
+    }
+    const long long grid = rows * a.ntiles;
+    kern<<<(unsigned)grid, kThreads, smem, st>>>(a);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    return TAC_OK;
+}
+
+template <int MODE>
+static int dispatch_tiled(const TiledArgs& a, long long rows, size_t smem, cudaStream_t st) {
+    switch (a.n) {
+        case 2048: return launch_tiled<Plan2048, MODE>(a, rows, smem, st);
+        case 1024: return launch_tiled<Plan1024, MODE>(a, rows, smem, st);
+        case 512: return launch_tiled<Plan512, MODE>(a, rows, smem, st);
+        case 256: return launch_tiled<Plan256, MODE>(a, rows, smem, st);
+        case 128: return launch_tiled<Plan128, MODE>(a, rows, smem, st);
+        default: return launch_tiled<Plan64, MODE>(a, rows, smem, st);
+    }
+}
+
+}  // namespace tac
+
+using namespace tac;
+
+extern "C" int tac_stft_multi(const float* x, int64_t B, int64_t C, int64_t T, int n_scales, const int* n_fft,
+                              const int* hop, const int* win, int center, int pad_mode, int normalized,
+                              int out_mode, int64_t f_pad, void* const* out, tac_stream_t stream) {
+    TAC_REQUIRE(x && n_fft && hop && out, "null argument");
+    TAC_REQUIRE(B > 0 && C > 0 && T > 0, "B, C, T must be positive (got %lld, %lld, %lld)", (long long)B, (long long)C, (long long)T);
+    TAC_REQUIRE(n_scales >= 1 && n_scales <= TAC_MAX_SCALES, "n_scales must be in [1, %d]", TAC_MAX_SCALES);
+    TAC_REQUIRE(out_mode >= 0 && out_mode <= 2, "unknown out_mode %d", out_mode);
+    TAC_REQUIRE(pad_mode == TAC_PAD_ZERO || pad_mode == TAC_PAD_REFLECT, "unknown pad_mode %d", pad_mode);
+    TAC_REQUIRE(B * C * T < (1ll << 40), "input too large");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    const long long rows = B * C;
+    const int vec_ok = ((reinterpret_cast<uintptr_t>(x) & 15u) == 0 && (T & 3) == 0) ? 1 : 0;
+    TAC_REQUIRE((reinterpret_cast<uintptr_t>(x) & 3u) == 0, "x must be 4-byte aligned");
+
+    int nmax = 0;
+    for (int s = 0; s < n_scales; ++s) {
+        const int w = win ? win[s] : n_fft[s];
+        TAC_REQUIRE(supported_nfft(n_fft[s]), "unsupported n_fft %d", n_fft[s]);
+        TAC_REQUIRE(hop[s] >= 2 && (hop[s] & 1) == 0 && hop[s] <= n_fft[s], "hop %d must be even and in [2, n_fft]", hop[s]);
+        TAC_REQUIRE(w >= 1 && w <= n_fft[s], "win_length %d must be in [1, n_fft]", w);
+        TAC_REQUIRE(out[s] != nullptr, "out[%d] is null", s);
+        TAC_REQUIRE((reinterpret_cast<uintptr_t>(out[s]) & 7u) == 0, "out[%d] must be 8-byte aligned", s);
+        if (center && pad_mode == TAC_PAD_REFLECT)
+            TAC_REQUIRE(T > n_fft[s] / 2, "reflect padding needs T > n_fft/2");
+        TAC_REQUIRE(num_frames(T, n_fft[s], hop[s], center) >= 1, "signal of %lld samples is shorter than n_fft=%d", (long long)T, n_fft[s]);
+        nmax = n_fft[s] > nmax ? n_fft[s] : nmax;
+    }
+
+    if (out_mode == TAC_OUT_PLANES) {
+        PlanesArgs a;
+        a.x = x; a.T = T; a.C = (int)C; a.nscales = n_scales; a.pad_mode = pad_mode; a.vec_ok = vec_ok;
+        a.chunk = 4096;
+        a.pmax = center ? nmax / 2 : 0;
+        long long last_start = 0;
+        for (int s = 0; s < n_scales; ++s) {
+            ScaleArg& sc = a.sc[s];
+            sc.n = n_fft[s]; sc.hop = hop[s]; sc.pad = center ? n_fft[s] / 2 : 0;
+            sc.F = (int)num_frames(T, sc.n, sc.hop, center);
+            sc.K = sc.n / 2 + 1;
+            sc.out = reinterpret_cast<float*>(out[s]);
+            int rc = get_tables(sc.n, win ? win[s] : sc.n, normalized, &sc.t);
+            if (rc) return rc;
+            const long long ls = (long long)(sc.F - 1) * sc.hop;
+            last_start = ls > last_start ? ls : last_start;
+        }
+        a.nchunks = (int)(last_start / a.chunk) + 1;
+        a.tile_len = a.chunk + nmax;
+        const size_t smem = (size_t)a.tile_len * sizeof(float) + (size_t)kWarps * kXbufFloat2 * sizeof(float2);
+        static bool attr_set = false;
+        if (!attr_set) {
+            TAC_CHECK_CUDA(cudaFuncSetAttribute(stft_planes_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
+            attr_set = true;
+        }
+        const long long grid = rows * a.nchunks;
+        TAC_REQUIRE(grid < (1ll << 31), "grid too large");
+        stft_planes_kernel<<<(unsigned)grid, kThreads, smem, st>>>(a);
+        TAC_CHECK_CUDA(cudaGetLastError());
+        return TAC_OK;
+    }
+
+    // time-innermost layouts: one launch per scale
+    for (int s = 0; s < n_scales; ++s) {
+        TiledArgs a;
+        a.x = x; a.T = T; a.n = n_fft[s]; a.hop = hop[s]; a.pad = center ? a.n / 2 : 0;
+        a.F = (int)num_frames(T, a.n, a.hop, center);
+        a.K = a.n / 2 + 1;
+        a.pad_mode = pad_mode; a.vec_ok = vec_ok;
+        a.TF = a.n >= 2048 ? 8 : (a.n >= 1024 ? 16 : 32);
+        a.ntiles = (a.F + a.TF - 1) / a.TF;
+        a.tile_len = (a.TF - 1) * a.hop + a.n;
+        a.tile_len = (a.tile_len + 3) & ~3;
+        a.f_pad = a.F;
+        a.out = reinterpret_cast<float*>(out[s]);
+        int rc = get_tables(a.n, win ? win[s] : a.n, normalized, &a.t);
+        if (rc) return rc;
+        const size_t smem = (size_t)a.tile_len * 4 + 2 * (size_t)a.K * (a.TF + 1) * 4 + (size_t)kWarps * kXbufFloat2 * 8;
+        TAC_REQUIRE(rows * a.ntiles < (1ll << 31), "grid too large");
+        if (out_mode == TAC_OUT_MAGPHASE) {
+            if (f_pad > 0) {
+                a.f_pad = f_pad;
+                if (f_pad < a.F) {               // crop (pad_tensor with negative padding)
+                    a.F = (int)f_pad;
+                    a.ntiles = (a.F + a.TF - 1) / a.TF;
+                } else if (f_pad > a.F) {
+                    TAC_CHECK_CUDA(cudaMemsetAsync(a.out, 0, (size_t)rows * 2 * a.K * (size_t)f_pad * sizeof(float), st));
+                }
+            }
+            rc = dispatch_tiled<TAC_OUT_MAGPHASE>(a, rows, smem, st);
+        } else {
+            rc = dispatch_tiled<TAC_OUT_COMPLEX>(a, rows, smem, st);
+        }
+        if (rc) return rc;
+    }
+    return TAC_OK;
+}

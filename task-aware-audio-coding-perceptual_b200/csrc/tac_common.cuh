@@ -1,0 +1,49 @@
+// Shared host-side helpers of libtac_spectral: error channel, argument checks, table cache API.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+
+#include "../../include/tac_spectral.h"
+#include "fft_core.cuh"
+
+namespace tac {
+
+int set_error(int code, const char* fmt, ...);   // stores the message thread-locally, returns code
+
+#define TAC_CHECK_CUDA(expr)                                                                  \
+    do {                                                                                      \
+        cudaError_t _e = (expr);                                                              \
+        if (_e != cudaSuccess)                                                                \
+            return tac::set_error(TAC_ECUDA, "%s failed: %s (%s:%d)", #expr,                  \
+                                  cudaGetErrorString(_e), __FILE__, __LINE__);                \
+    } while (0)
+
+#define TAC_REQUIRE(cond, ...)                                                                \
+    do {                                                                                      \
+        if (!(cond)) return tac::set_error(TAC_EINVAL, __VA_ARGS__);                          \
+    } while (0)
+
+#define TAC_ALIGNED16(p, name)                                                                \
+    do {                                                                                      \
+        if ((reinterpret_cast<uintptr_t>(p) & 15u) != 0)                                      \
+            return tac::set_error(TAC_EALIGN, "%s must be 16-byte aligned", name);            \
+    } while (0)
+
+inline bool supported_nfft(int n) {
+    return n == 64 || n == 128 || n == 256 || n == 512 || n == 1024 || n == 2048;
+}
+
+// Looks up (building on first use) the device tables of one FFT configuration on the current device.
+int get_tables(int n_fft, int win, int normalized, FftTables* out);
+
+inline int64_t num_frames(int64_t T, int n, int hop, int center) {
+    int64_t Tp = T + (center ? 2 * (int64_t)(n / 2) : 0);
+    if (Tp < n || hop <= 0) return 0;
+    return 1 + (Tp - n) / hop;
+}
+
+constexpr int kNumSMs = 148;
+
+}  // namespace tac

@@ -1,0 +1,103 @@
+"""ctypes binding of ``libtac_spectral.so`` (the C ABI declared in ``include/tac_spectral.h``).
+
+There is no CPU fallback: if the shared library is missing or a call fails, a ``RuntimeError``
+carrying ``tac_last_error()`` is raised -- mirroring how the reference's own native ops surface
+``TORCH_CHECK`` failures as Python ``RuntimeError`` (``sgmse/.../op/fused_bias_act.cpp:7-14``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Sequence
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libtac_spectral.so")
+
+# name -> (restype, argtypes): every symbol of include/tac_spectral.h
+_I, _I64, _SZ, _VP, _F = C.c_int, C.c_int64, C.c_size_t, C.c_void_p, C.c_float
+_IP = C.POINTER(C.c_int)
+_VPP = C.POINTER(C.c_void_p)
+SIGNATURES = {
+    "tac_last_error": (C.c_char_p, []),
+    "tac_version": (_I, []),
+    "tac_prepare_fft": (_I, [_I, _I, _I]),
+    "tac_shutdown": (_I, []),
+    "tac_stft_num_frames": (_I64, [_I64, _I, _I, _I]),
+    "tac_stft_multi": (_I, [_VP, _I64, _I64, _I64, _I, _IP, _IP, _IP, _I, _I, _I, _I, _I64, _VPP, _VP]),
+    "tac_mrstft_workspace_bytes": (_SZ, [_I64, _I64, _I, _IP, _IP]),
+    "tac_mrstft_loss_fwd": (_I, [_VP, _VP, _I64, _I64, _I, _IP, _IP, _IP, _F, _VP, _VP, _SZ, _VP]),
+    "tac_mrstft_loss_bwd": (_I, [_VP, _VP, _I64, _I64, _I, _IP, _IP, _IP, _F, _VP, _VP, _VP, _SZ, _VP]),
+    "tac_spec_losses_workspace_bytes": (_SZ, [_I64]),
+    "tac_spec_losses": (_I, [_VP, _VP, _I64, _I64, _I64, _VP, _VP, _VP, _SZ, _VP]),
+    "tac_dpca_workspace_bytes": (_SZ, [_I, _I64, _I]),
+    "tac_dpca_stats": (_I, [_VPP, _I, _I64, _I, _I, _VP, _VP, _SZ, _VP]),
+    "tac_dpca_eig": (_I, [_VP, _I, _I, _VP, _VP, _VP, _VP, _VP, _SZ, _VP]),
+    "tac_dpca_select": (_I, [_VP, _VP, _I, _I, _I, _VP, _VP, _VP]),
+    "tac_dpca_project": (_I, [_VPP, _I, _I64, _I, _VP, _VP, _VP, _VP, _VPP, _VP, _SZ, _VP]),
+    "tac_var_topk": (_I, [_VP, _I, _I, _VP, _VP, _VP]),
+}
+
+PAD_ZERO, PAD_REFLECT = 0, 1
+OUT_COMPLEX, OUT_PLANES, OUT_MAGPHASE = 0, 1, 2
+GRAM_TF32X3, GRAM_FP64 = 0, 1
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load (once) the shared library; fails loudly when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python task-aware-audio-coding-perceptual_b200/build.py` "
+                "(there is no CPU or PyTorch fallback for the spectral hot path)")
+        handle = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(handle, name)          # AttributeError if the ABI and the header disagree
+            fn.restype, fn.argtypes = res, args
+        _lib = handle
+    return _lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        msg = lib().tac_last_error().decode("utf-8", "replace")
+        raise RuntimeError(f"tac_spectral error {rc}: {msg}")
+
+
+def int_array(values: Sequence[int]):
+    return (C.c_int * len(values))(*[int(v) for v in values])
+
+
+def ptr_array(tensors: Sequence[torch.Tensor]):
+    return (C.c_void_p * len(tensors))(*[t.data_ptr() for t in tensors])
+
+
+def stream_of(t: torch.Tensor) -> int:
+    """The caller's current CUDA stream on ``t``'s device, exactly as the reference's native
+    launchers take it (``upfirdn2d_kernel.cu:213-215``)."""
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def require_cuda(t: torch.Tensor, name: str) -> None:
+    if not isinstance(t, torch.Tensor):
+        raise TypeError(f"{name} must be a torch.Tensor")
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must live on a CUDA device: the spectral hot path has no CPU fallback")
+
+
+class device_of:
+    """Context manager: make ``t``'s device current for the duration of a C-ABI call."""
+
+    def __init__(self, t: torch.Tensor):
+        self._g = torch.cuda.device(t.device)
+
+    def __enter__(self):
+        self._g.__enter__()
+        return self
+
+    def __exit__(self, *exc):
+        return self._g.__exit__(*exc)

@@ -110,6 +110,11 @@ TAC_API int tac_mrstft_loss_bwd(const float* x, const float* y, int64_t B, int64
 TAC_API size_t tac_spec_losses_workspace_bytes(int64_t B);
 TAC_API int tac_spec_losses(const float* obs, const float* dec, int64_t B, int64_t K, int64_t F, float* out5,
                     float* per_sample, void* workspace, size_t workspace_bytes, tac_stream_t stream);
+/* Backward of K2' w.r.t. dec: grad_dec[b, c, :, :] = w[b, c] * (dec - obs), w a DEVICE float32 [B, 2]
+ * table into which the caller folds the upstream gradients and normalisers of all five outputs
+ * (autograd of pkl_file_models.py:933-940 in one pass instead of ~12 elementwise kernels). */
+TAC_API int tac_spec_losses_bwd(const float* obs, const float* dec, int64_t B, int64_t K, int64_t F, const float* w,
+                        float* grad_dec, tac_stream_t stream);
 
 /* K3 -- DPCA.  Replaces data_pca (pkl_file_model_updated.py:37-42, pkl_file_models.py:51-56) and the
  * select / project block (pkl_file_model_updated.py:489-511 two views, :398-427 four views;

@@ -181,7 +181,10 @@ __global__ void __launch_bounds__(kEigThreads, 1) dpca_eig_kernel(const double* 
     for (int e = threadIdx.x; e < d * d; e += blockDim.x) {
         const int j = e / d, r = e % d;                             // column j of A, row r
         const double lam = s_lam[j];
-        const double val = lam > 0.0 ? A[e] / lam : (r == j ? 1.0 : 0.0);
+        // numerically null columns carry no direction (normalising their rounding noise would give a
+        // vector that is NOT orthogonal to the range): emit a zero column, which projects to nothing --
+        // exactly what the reference's arbitrary null-space vector contributes ((z - mu) v = 0)
+        const double val = lam * lam > null2 ? A[e] / lam : 0.0;
         vo[(size_t)r * d + s_ord[j]] = (float)val;                  // v[r][rank] : eigenvector in column `rank`
     }
     if (threadIdx.x == 0) rank_out[v] = r_eff;

@@ -5,16 +5,20 @@
 // Zc is split as hi + lo with hi = tf32(Zc), lo = tf32(Zc - hi); the kernel accumulates
 // hi^T hi + hi^T lo + lo^T hi (the dropped lo^T lo term is ~2^-22 relative) with
 // tcgen05.mma.kind::tf32, M = N = 128, K = 8 per instruction, fp32 accumulator in TMEM.
-// Both operands are the SAME shared-memory tile read "MN-major" (features contiguous), which is
-// exactly how Z lies in global memory, so staging is one 16-byte shared store per 16-byte global
-// load.  Canonical no-swizzle MN-major layout (cute/arch/mma_sm100_desc.hpp, INTERLEAVE):
-//   element (feature f, row k) at  (f/4)*SBO + (k/8)*LBO + (k%8)*16 + (f%4)*4   bytes,
-//   SBO = 128 (one 8x16B core matrix), LBO = 32*128 = 4096 (all 128 features of 8 rows).
+// Both operands are the SAME shared-memory tile (A = B = Zc^T, GEMM-K = batch rows), stored in the
+// canonical no-swizzle K-major layout (cute/arch/mma_sm100_desc.hpp, "INTERLEAVE"):
+//   element (feature f, row k) at  (k/8)*4096 + (f/8)*SBO + ((k%8)/4)*LBO + (f%8)*16 + (k%4)*4  bytes,
+//   SBO = 256 (next group of 8 features), LBO = 128 (next 16-byte K core matrix),
+// i.e. a core matrix is 8 features x 4 rows, so staging transposes Z on the fly: a thread gathers 4
+// consecutive rows of one feature (4 coalesced scalar loads across the warp) and issues one 16-byte,
+// conflict-free shared store.  (The MN-major no-swizzle form -- which would need no transpose --
+// was measured on B200 to leave the accumulator untouched for kind::tf32; see DESIGN.md.)
 // Centring with the local mean first keeps the fp32 accumulation well conditioned; the caller-
 // visible statistic sum z z^T is re-assembled in float64 as G + n * mean mean^T.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 
 namespace tac {
 
@@ -23,12 +27,14 @@ constexpr int kTcRowsPerCta = 256;           // batch rows (GEMM K) per CTA
 constexpr int kTcChunk = 64;                 // rows staged per pipeline stage
 constexpr int kTcStages = 2;
 constexpr int kTcThreads = 128;
-constexpr uint32_t kTcSBO = 128;
-constexpr uint32_t kTcLBO = (kTcFeat / 4) * 128;                  // 4096 bytes per 8-row group
-constexpr int kTcTileBytes = (kTcChunk / 8) * (int)kTcLBO;        // 32 KiB per (hi | lo) tile
+constexpr uint32_t kTcSBO = 256;                                  // 8-feature group stride
+constexpr uint32_t kTcLBO = 128;                                  // K core-matrix stride
+constexpr uint32_t kTcKGroup = (kTcFeat / 8) * kTcSBO;            // 4096 bytes per 8 rows (one MMA, K = 8)
+constexpr int kTcTileBytes = (kTcChunk / 8) * (int)kTcKGroup;     // 32 KiB per (hi | lo) tile
 constexpr int kTcSmemBytes = kTcStages * 2 * kTcTileBytes + 1024; // + alignment slack
 
 __device__ __forceinline__ uint32_t tc_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
 
 __device__ __forceinline__ uint64_t tc_make_desc(uint32_t saddr) {
     uint64_t d = 0;
@@ -39,8 +45,8 @@ __device__ __forceinline__ uint64_t tc_make_desc(uint32_t saddr) {
     return d;                                                     // base offset 0, SWIZZLE_NONE
 }
 
-// kind::tf32, fp32 accumulate, A and B both MN-major, M = 128, N = 128
-constexpr uint32_t kTcIdesc = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) |
+// kind::tf32 (a/b format 2), fp32 accumulate (c format 1), A and B both K-major, M = 128, N = 128
+constexpr uint32_t kTcIdesc = (1u << 4) | (2u << 7) | (2u << 10) |
                               ((uint32_t)(kTcFeat >> 3) << 17) | ((uint32_t)(kTcFeat >> 4) << 24);
 
 __device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
@@ -48,9 +54,9 @@ __device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t adesc, uint64_t
         "{\n\t"
         ".reg .pred p;\n\t"
         "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
         "}\n"
-        :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(kTcIdesc), "r"(accumulate), "r"(0u) : "memory");
+        :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(kTcIdesc), "r"(accumulate) : "memory");
 }
 
 __device__ __forceinline__ void tc_mbar_init(uint64_t* bar, uint32_t count) {
@@ -121,9 +127,6 @@ dpca_gram_tc_kernel(const float* z0, const float* z1, const float* z2,
     const long long r_begin = (long long)split * kTcRowsPerCta;
     const long long r_end = (r_begin + kTcRowsPerCta < B) ? r_begin + kTcRowsPerCta : B;
     const int nchunks = (int)((r_end - r_begin + kTcChunk - 1) / kTcChunk);
-    const float4 mean4 = make_float4(s_mean[4 * lane], s_mean[4 * lane + 1], s_mean[4 * lane + 2], s_mean[4 * lane + 3]);
-    const bool vec_ok = ((d & 3) == 0) && ((reinterpret_cast<uintptr_t>(z) & 15u) == 0);
-
     uint32_t phase[kTcStages] = {0, 0};
     for (int c = 0; c < nchunks; ++c) {
         const int stage = c % kTcStages;
@@ -133,29 +136,19 @@ dpca_gram_tc_kernel(const float* z0, const float* z1, const float* z2,
         }
         unsigned char* hi = tiles + (size_t)stage * 2 * kTcTileBytes;
         unsigned char* lo = hi + kTcTileBytes;
-        // each warp stages rows k = warp, warp + 4, ... of the chunk; lane <-> features 4*lane .. 4*lane+3
-        for (int k = warp; k < kTcChunk; k += kTcThreads / 32) {
-            const long long row = r_begin + (long long)c * kTcChunk + k;
-            float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (row < r_end) {
-                const float* zr = z + row * d;
-                if (vec_ok) {
-                    if (4 * lane < d) a = __ldg(reinterpret_cast<const float4*>(zr) + lane);
-                } else {
-                    if (4 * lane + 0 < d) a.x = __ldg(zr + 4 * lane + 0);
-                    if (4 * lane + 1 < d) a.y = __ldg(zr + 4 * lane + 1);
-                    if (4 * lane + 2 < d) a.z = __ldg(zr + 4 * lane + 2);
-                    if (4 * lane + 3 < d) a.w = __ldg(zr + 4 * lane + 3);
-                }
-                a.x = (4 * lane + 0 < d) ? a.x - mean4.x : 0.f;
-                a.y = (4 * lane + 1 < d) ? a.y - mean4.y : 0.f;
-                a.z = (4 * lane + 2 < d) ? a.z - mean4.z : 0.f;
-                a.w = (4 * lane + 3 < d) ? a.w - mean4.w : 0.f;
-            }
+        // item = (row quad q, feature f): 4 consecutive rows of one feature -> one 16-byte store per tile.
+        // A warp covers 32 consecutive features of one quad: coalesced 128-byte loads, conflict-free stores.
+        for (int it = threadIdx.x; it < (kTcChunk / 4) * kTcFeat; it += kTcThreads) {
+            const int f = it % kTcFeat, q = it / kTcFeat;
+            const long long row0 = r_begin + (long long)c * kTcChunk + 4 * q;
+            float a[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                a[i] = (f < d && row0 + i < r_end) ? __ldg(z + (row0 + i) * d + f) - s_mean[f] : 0.0f;
             float4 h, l;
-            h.x = tc_to_tf32(a.x); h.y = tc_to_tf32(a.y); h.z = tc_to_tf32(a.z); h.w = tc_to_tf32(a.w);
-            l.x = tc_to_tf32(a.x - h.x); l.y = tc_to_tf32(a.y - h.y); l.z = tc_to_tf32(a.z - h.z); l.w = tc_to_tf32(a.w - h.w);
-            const size_t off = (size_t)lane * kTcSBO + (size_t)(k >> 3) * kTcLBO + (size_t)(k & 7) * 16;
+            h.x = tc_to_tf32(a[0]); h.y = tc_to_tf32(a[1]); h.z = tc_to_tf32(a[2]); h.w = tc_to_tf32(a[3]);
+            l.x = tc_to_tf32(a[0] - h.x); l.y = tc_to_tf32(a[1] - h.y); l.z = tc_to_tf32(a[2] - h.z); l.w = tc_to_tf32(a[3] - h.w);
+            const size_t off = (size_t)(q >> 1) * kTcKGroup + (size_t)(f >> 3) * kTcSBO + (size_t)(q & 1) * kTcLBO + (size_t)(f & 7) * 16;
             *reinterpret_cast<float4*>(hi + off) = h;
             *reinterpret_cast<float4*>(lo + off) = l;
         }
@@ -167,8 +160,8 @@ dpca_gram_tc_kernel(const float* z0, const float* z1, const float* z2,
             const uint32_t hi_addr = tc_smem_u32(hi), lo_addr = tc_smem_u32(lo);
 #pragma unroll
             for (int g = 0; g < kTcChunk / 8; ++g) {
-                const uint64_t dh = tc_make_desc(hi_addr + g * kTcLBO);
-                const uint64_t dl = tc_make_desc(lo_addr + g * kTcLBO);
+                const uint64_t dh = tc_make_desc(hi_addr + g * kTcKGroup);
+                const uint64_t dl = tc_make_desc(lo_addr + g * kTcKGroup);
                 tc_mma(tmem, dh, dh, (c > 0 || g > 0) ? 1u : 0u);
                 tc_mma(tmem, dh, dl, 1u);
                 tc_mma(tmem, dl, dh, 1u);

@@ -64,7 +64,7 @@ __device__ __forceinline__ void loss_fwd_task(const LossScale& sc, const float* 
         f = f < f_end ? f : f_first;
         const float2 v = *reinterpret_cast<const float2*>(cur + (f * hop - origin) + 2 * m);
         const float2 w = ldg2(win2 + m);
-        return make_float2(v.x * w.x, v.y * w.y);
+        return make_float2(__fmul_rn(v.x, w.x), __fmul_rn(v.y, w.y));   // never contracted: X(x) is bit-reproducible
     };
     warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load);
     warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
@@ -78,9 +78,9 @@ __device__ __forceinline__ void loss_fwd_task(const LossScale& sc, const float* 
         const float my = sqrtf(fmaf(vr, vr, vi * vi));
         const float xv = mx[slot];
         l1 += fabsf(xv - my);
-        ll += fabsf(__logf(__fdividef(fmaxf(xv, eps), fmaxf(my, eps))));
+        ll += fabsf(__log2f(fmaxf(xv, eps)) - __log2f(fmaxf(my, eps)));   // log2 units (scaled by ln 2 below); exact 0 when X == Y
     });
-    if (valid) { acc_l1 += l1; acc_log += ll; }
+    if (valid) { acc_l1 += l1; acc_log += ll * 0.69314718055994530942f; }
 }
 
 __global__ void __launch_bounds__(kFwdThreads, 2) mrstft_fwd_kernel(const LossArgs a) {
@@ -179,7 +179,7 @@ __device__ __forceinline__ void loss_bwd_task(const LossScale& sc, const float* 
         f = f < f_end ? f : f_base;
         const float2 v = __ldg(reinterpret_cast<const float2*>(cur + (long long)f * hop) + m);
         const float2 w = ldg2(win2 + m);
-        return make_float2(v.x * w.x, v.y * w.y);
+        return make_float2(__fmul_rn(v.x, w.x), __fmul_rn(v.y, w.y));   // never contracted: X(x) is bit-reproducible
     };
     warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load);
     warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
@@ -360,6 +360,32 @@ __global__ void __launch_bounds__(256) spec_final_kernel(const double* __restric
     }
 }
 
+
+// Backward of K2': grad_dec[b, c, :, :] = w[b, c] * (dec - obs); the caller folds every output's
+// upstream gradient and normaliser into the [B, 2] weight table w (device memory, no sync).
+__global__ void __launch_bounds__(256) spec_bwd_kernel(const float* __restrict__ obs, const float* __restrict__ dec,
+                                                      long long plane, const float* __restrict__ w, float* __restrict__ grad) {
+    const long long pl = blockIdx.y;
+    const float wv = __ldg(w + pl);
+    const float* o = obs + pl * plane;
+    const float* d = dec + pl * plane;
+    float* g = grad + pl * plane;
+    const bool vec = ((((uintptr_t)o | (uintptr_t)d | (uintptr_t)g) & 15u) == 0);
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (vec) {
+        const long long n4 = plane >> 2;
+        for (long long i = tid; i < n4; i += stride) {
+            const float4 a = __ldcs(reinterpret_cast<const float4*>(o) + i);
+            const float4 b = __ldcs(reinterpret_cast<const float4*>(d) + i);
+            __stcs(reinterpret_cast<float4*>(g) + i, make_float4(wv * (b.x - a.x), wv * (b.y - a.y), wv * (b.z - a.z), wv * (b.w - a.w)));
+        }
+        for (long long i = (n4 << 2) + tid; i < plane; i += stride) g[i] = wv * (__ldg(d + i) - __ldg(o + i));
+    } else {
+        for (long long i = tid; i < plane; i += stride) g[i] = wv * (__ldg(d + i) - __ldg(o + i));
+    }
+}
+
 static int fill_loss_args(LossArgs& a, const float* x, const float* y, int64_t B, int64_t T, int n_scales,
                           const int* n_fft, const int* hop, const int* win, float eps, int chunk) {
     TAC_REQUIRE(x && y && n_fft && hop, "null argument");
@@ -471,6 +497,19 @@ extern "C" int tac_spec_losses(const float* obs, const float* dec, int64_t B, in
     spec_partial_kernel<<<(unsigned)(B * 2 * kSpecSplit), kSpecThreads, 0, st>>>(obs, dec, K * F, partial);
     TAC_CHECK_CUDA(cudaGetLastError());
     spec_final_kernel<<<1, 256, 0, st>>>(partial, B, K * F, out5, per_sample);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    return TAC_OK;
+}
+
+extern "C" int tac_spec_losses_bwd(const float* obs, const float* dec, int64_t B, int64_t K, int64_t F, const float* w,
+                                   float* grad_dec, tac_stream_t stream) {
+    TAC_REQUIRE(obs && dec && w && grad_dec, "null argument");
+    TAC_REQUIRE(B > 0 && K > 0 && F > 0, "B, K, F must be positive");
+    TAC_REQUIRE(B * 2 < 65536, "B too large for one launch (max 32767)");
+    const long long plane = K * F;
+    long long gx = (plane / 4 + 255) / 256;
+    gx = gx < 1 ? 1 : (gx > 64 ? 64 : gx);
+    spec_bwd_kernel<<<dim3((unsigned)gx, (unsigned)(B * 2)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(obs, dec, plane, w, grad_dec);
     TAC_CHECK_CUDA(cudaGetLastError());
     return TAC_OK;
 }

@@ -65,7 +65,7 @@ __device__ __forceinline__ void planes_task(const ScaleArg& sc, const float* til
         f = f < f_end ? f : f_first;                       // invalid frames recompute the first one
         const float2 v = *reinterpret_cast<const float2*>(tile + (f * hop - tile_origin) + 2 * m);
         const float2 w = ldg2(win2 + m);
-        return make_float2(v.x * w.x, v.y * w.y);
+        return make_float2(__fmul_rn(v.x, w.x), __fmul_rn(v.y, w.y));   // never contracted: X(x) is bit-reproducible
     };
     warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load);
     const int myf = f_first + lane / P::A;
@@ -198,7 +198,7 @@ __global__ void __launch_bounds__(kThreads, 1) stft_tiled_kernel(const TiledArgs
             f = f < f_end ? f : f_first;
             const float2 v = *reinterpret_cast<const float2*>(tile + (f - f0) * a.hop + 2 * m);
             const float2 w = ldg2(win2 + m);
-            return make_float2(v.x * w.x, v.y * w.y);
+            return make_float2(__fmul_rn(v.x, w.x), __fmul_rn(v.y, w.y));   // never contracted: X(x) is bit-reproducible
         };
         warp_fft_fwd<P>(zr, zi, xbuf, a.t.tw, lane, load);
         const int myf = f_first + lane / P::A;

@@ -1,0 +1,23 @@
+"""tac_spectral -- B200-native spectral hot path of the task-aware audio coder.
+
+Host-side mirror (PyTorch plumbing over the C ABI of ``include/tac_spectral.h``) of the reference
+call sites on the path ``BASELINE.json:north_star`` names:
+
+* :mod:`.stft`  -- ``Spectrogram`` / ``MultiScaleSTFT`` (``msstftd.py:125-127,151-153,185-192``) and the
+  notebook front end ``create_complex_spectrogram`` (``spectrogram.ipynb`` cell 10);
+* :mod:`.loss`  -- ``mrstft_loss`` and ``spectral_losses`` (``pkl_file_models.py:933-940``);
+* :mod:`.dpca`  -- ``data_pca`` / ``dpca_project`` / ``apply_pca`` / ``var_topk``
+  (``pkl_file_model_updated.py:37-42,489-511,398-427``; ``pkl_file_models.py:224-228,901-907``).
+
+There is no CPU or eager-PyTorch fallback: every op raises ``RuntimeError`` when
+``libtac_spectral.so`` is missing or its input is not on a CUDA device.
+"""
+from . import _lib
+from .stft import (Spectrogram, MultiScaleSTFT, stft_multi, complex_spectrogram, create_complex_spectrogram,
+                   num_frames, SUPPORTED_NFFT)
+from .loss import mrstft_loss, mrstft_sums, mrstft_counts, spectral_losses, LOG_FLOOR
+from .dpca import data_pca, dpca_project, dpca_select, dpca_stats, dpca_eig, apply_pca, var_topk
+
+__all__ = ["Spectrogram", "MultiScaleSTFT", "stft_multi", "complex_spectrogram", "create_complex_spectrogram",
+           "num_frames", "SUPPORTED_NFFT", "mrstft_loss", "mrstft_sums", "mrstft_counts", "spectral_losses",
+           "LOG_FLOOR", "data_pca", "dpca_project", "dpca_select", "dpca_stats", "dpca_eig", "apply_pca", "var_topk"]

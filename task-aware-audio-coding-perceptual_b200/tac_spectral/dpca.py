@@ -1,0 +1,192 @@
+"""Host-side mirror of the DTAC distributed-PCA (DPCA) latent projection (K3).
+
+Same names, argument meaning and results as the reference call sites:
+
+* :func:`data_pca` -- ``pkl_file_model_updated.py:37-42`` / ``pkl_file_models.py:51-56``: returns
+  ``(s[r], v[d, r], mean[d])`` with ``r = min(B, d)``, ``s`` descending, singular values of the
+  centred batch (no ``1/(B-1)``).
+* :func:`dpca_project` -- the select / project block of ``ResE2D1.forward``
+  (``pkl_file_model_updated.py:489-511``) and ``ResE4D1.forward`` (``:398-427``) as a function of
+  the per-view latents and ``dim_p`` (the host draw ``torch.randint(8, num_features/2)`` of
+  ``:489`` / ``:398`` stays in the caller so the RNG stream is unchanged).
+* :func:`apply_pca` -- ``pkl_file_models.py:224-228``;  :func:`var_topk` -- ``:901-907``.
+
+Device flow (no host synchronisation anywhere): ``tac_dpca_stats`` (sufficient statistics
+``[n, sum z, sum z z^T]`` per view, float64) -> optional all-reduce over the data-parallel group
+-> ``tac_dpca_eig`` (Jacobi, every rank redundantly) -> ``tac_dpca_select`` -> ``tac_dpca_project``.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib as L
+
+MAX_D = 256
+MAX_VIEWS = 8
+TC_MAX_D = 128
+
+
+def _algo_code(algo: Optional[str], d: int) -> int:
+    if algo is None:
+        return L.GRAM_TF32X3 if d <= TC_MAX_D else L.GRAM_FP64
+    if algo == "tf32x3":
+        return L.GRAM_TF32X3
+    if algo == "fp64":
+        return L.GRAM_FP64
+    raise ValueError(f"unknown Gram algorithm {algo!r} (tf32x3 | fp64)")
+
+
+def _check_views(zs: Sequence[torch.Tensor]) -> Tuple[int, int, int]:
+    if not 1 <= len(zs) <= MAX_VIEWS:
+        raise ValueError(f"need 1..{MAX_VIEWS} views, got {len(zs)}")
+    B, d = zs[0].shape
+    for i, z in enumerate(zs):
+        L.require_cuda(z, f"z[{i}]")
+        if z.dim() != 2 or tuple(z.shape) != (B, d):
+            raise ValueError(f"view {i}: expected [{B}, {d}], got {tuple(z.shape)}")
+    if d > MAX_D:
+        raise ValueError(f"latent width {d} > {MAX_D} unsupported")
+    return len(zs), B, d
+
+
+def _workspace(nv: int, B: int, d: int, device) -> Tuple[torch.Tensor, int]:
+    n = int(L.lib().tac_dpca_workspace_bytes(nv, B, d))
+    return torch.empty(max(n, 256), dtype=torch.uint8, device=device), n
+
+
+def dpca_stats(zs: Sequence[torch.Tensor], algo: Optional[str] = None) -> torch.Tensor:
+    """Sufficient statistics ``[nv, 1 + d + d*d]`` float64 of the local shard (sum-reducible)."""
+    nv, B, d = _check_views(zs)
+    zc = [z.detach().contiguous().float() for z in zs]
+    stats = torch.empty((nv, 1 + d + d * d), dtype=torch.float64, device=zc[0].device)
+    ws, n = _workspace(nv, B, d, zc[0].device)
+    with L.device_of(zc[0]):
+        L.check(L.lib().tac_dpca_stats(L.ptr_array(zc), nv, B, d, _algo_code(algo, d), stats.data_ptr(),
+                                       ws.data_ptr(), n, L.stream_of(zc[0])))
+    return stats
+
+
+def dpca_eig(stats: torch.Tensor, d: int):
+    """``(s [nv, d], v [nv, d, d], mu [nv, d], rank [nv])`` from (all-reduced) statistics."""
+    nv = stats.shape[0]
+    dev = stats.device
+    s = torch.empty((nv, d), dtype=torch.float32, device=dev)
+    v = torch.empty((nv, d, d), dtype=torch.float32, device=dev)
+    mu = torch.empty((nv, d), dtype=torch.float32, device=dev)
+    rank = torch.empty(nv, dtype=torch.int32, device=dev)
+    ws, n = _workspace(nv, 1, d, dev)
+    with L.device_of(stats):
+        L.check(L.lib().tac_dpca_eig(stats.data_ptr(), nv, d, s.data_ptr(), v.data_ptr(), mu.data_ptr(),
+                                     rank.data_ptr(), ws.data_ptr(), n, L.stream_of(stats)))
+    return s, v, mu, rank
+
+
+def _allreduce_stats(stats: torch.Tensor, group) -> torch.Tensor:
+    if group is not None:
+        import torch.distributed as dist
+        dist.all_reduce(stats, group=group)          # NCCL over NVLink: <= 0.53 MB of float64 per step
+    return stats
+
+
+def data_pca(z: torch.Tensor, algo: Optional[str] = None, group=None):
+    """Drop-in for the reference's ``data_pca(z)``: ``(s, v, mean)``."""
+    _, B, d = _check_views([z])
+    stats = _allreduce_stats(dpca_stats([z], algo), group)
+    s, v, mu, _ = dpca_eig(stats, d)
+    world = 1
+    if group is not None:
+        import torch.distributed as dist
+        world = dist.get_world_size(group)
+    r = min(B * world, d)                               # torch.svd(some=True) returns min(B, d) columns
+    return s[0, :r], v[0, :, :r], mu[0]
+
+
+class _Project(torch.autograd.Function):
+    """``z_out_i = (z_i - mu_i) P_i + mu_i`` for all views in one launch chain.  The backward treats the
+    projector ``P_i = V_sel V_sel^T`` as a constant of the step (the dependence of the mean on ``z`` is
+    kept): ``grad_z = (g - mean g) P + mean g``, computed by the same kernel."""
+
+    @staticmethod
+    def forward(ctx, v, mu, idx, cnt, group, *zs):
+        nv, B, d = len(zs), zs[0].shape[0], zs[0].shape[1]
+        zc = [z.contiguous().float() for z in zs]
+        outs = [torch.empty_like(z) for z in zc]
+        ws, n = _workspace(nv, B, d, zc[0].device)
+        with L.device_of(zc[0]):
+            L.check(L.lib().tac_dpca_project(L.ptr_array(zc), nv, B, d, v.data_ptr(), mu.data_ptr(), idx.data_ptr(),
+                                             cnt.data_ptr(), L.ptr_array(outs), ws.data_ptr(), n, L.stream_of(zc[0])))
+        ctx.save_for_backward(v, idx, cnt)
+        ctx.group = group
+        ctx.dtypes = [z.dtype for z in zs]
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, *gs):
+        v, idx, cnt = ctx.saved_tensors
+        nv = len(gs)
+        gc = [g.contiguous().float() for g in gs]
+        B, d = gc[0].shape
+        gsum = torch.stack([g.sum(0) for g in gc])
+        n = torch.tensor(float(B), device=gsum.device)
+        if ctx.group is not None:
+            import torch.distributed as dist
+            dist.all_reduce(gsum, group=ctx.group)
+            n = n * dist.get_world_size(ctx.group)
+        gmean = (gsum / n).contiguous()
+        outs = [torch.empty_like(g) for g in gc]
+        ws, nb = _workspace(nv, B, d, gc[0].device)
+        with L.device_of(gc[0]):
+            L.check(L.lib().tac_dpca_project(L.ptr_array(gc), nv, B, d, v.data_ptr(), gmean.data_ptr(), idx.data_ptr(),
+                                             cnt.data_ptr(), L.ptr_array(outs), ws.data_ptr(), nb, L.stream_of(gc[0])))
+        return (None, None, None, None, None) + tuple(o.to(dt) for o, dt in zip(outs, ctx.dtypes))
+
+
+def dpca_select(s: torch.Tensor, rank: torch.Tensor, dim_p: int):
+    """Global top-``dim_p`` across the concatenated singular values; ``(idx [nv, d] int32, cnt [nv] int32)``."""
+    nv, d = s.shape
+    idx = torch.zeros((nv, d), dtype=torch.int32, device=s.device)
+    cnt = torch.empty(nv, dtype=torch.int32, device=s.device)
+    with L.device_of(s):
+        L.check(L.lib().tac_dpca_select(s.data_ptr(), rank.data_ptr(), nv, d, int(dim_p), idx.data_ptr(), cnt.data_ptr(),
+                                        L.stream_of(s)))
+    return idx, cnt
+
+
+def dpca_project(zs: Sequence[torch.Tensor], dim_p: int, algo: Optional[str] = None, group=None,
+                 return_info: bool = False):
+    """The DPCA block: per-view PCA, global top-``dim_p`` selection over all views' singular values,
+    per-view projection onto the selected components and back (``pkl_file_model_updated.py:489-511``).
+
+    With ``group`` the statistics are all-reduced so that all ranks use the PCA of the global batch."""
+    nv, B, d = _check_views(zs)
+    if dim_p < 0:
+        raise ValueError("dim_p must be >= 0")
+    stats = _allreduce_stats(dpca_stats(zs, algo), group)
+    s, v, mu, rank = dpca_eig(stats, d)
+    idx, cnt = dpca_select(s, rank, dim_p)
+    outs = list(_Project.apply(v, mu, idx, cnt, group, *zs))
+    if return_info:
+        return outs, {"s": s, "v": v, "mu": mu, "rank": rank, "idx": idx, "cnt": cnt, "stats": stats}
+    return outs
+
+
+def apply_pca(z: torch.Tensor, dim_p: int, algo: Optional[str] = None, group=None) -> torch.Tensor:
+    """``apply_pca`` (``pkl_file_models.py:224-228``): rank-``dim_p`` reconstruction of one view."""
+    return dpca_project([z], dim_p, algo, group)[0]
+
+
+def var_topk(z: torch.Tensor, k: int, group=None):
+    """E1D1 bottleneck (``pkl_file_models.py:901-907``): ``(z[:, idx], idx)`` with ``idx`` the ``k`` features of
+    largest unbiased variance over the batch (the diagonal of the DPCA covariance / (n - 1))."""
+    _, B, d = _check_views([z])
+    if not 1 <= k <= d:
+        raise ValueError(f"k={k} must be in [1, {d}]")
+    stats = _allreduce_stats(dpca_stats([z], "fp64"), group)
+    var = torch.empty(d, dtype=torch.float32, device=z.device)
+    top = torch.empty(k, dtype=torch.int32, device=z.device)
+    with L.device_of(z):
+        L.check(L.lib().tac_var_topk(stats.data_ptr(), d, int(k), var.data_ptr(), top.data_ptr(), L.stream_of(z)))
+    idx = top.long()
+    return z.index_select(1, idx), idx

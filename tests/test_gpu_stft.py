@@ -1,0 +1,150 @@
+"""K1 parity: tac_stft_multi (through the C ABI) vs the CPU oracle and the reference's golden outputs.
+
+Tolerance of record (BASELINE.json north_star / SURVEY.md 8c): fp32 rtol 1e-4 with
+atol = 1e-4 * max|ref| for near-zero bins; phase compared modulo 2*pi where |X| > 1e-3 * max|X|.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import spectral_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-4
+
+
+def _close(got: torch.Tensor, ref: torch.Tensor, what=""):
+    got, ref = got.detach().cpu(), ref.detach().cpu()
+    assert got.shape == ref.shape, f"{what}: shape {tuple(got.shape)} vs {tuple(ref.shape)}"
+    atol = RTOL * float(ref.abs().max())
+    err = (got - ref).abs()
+    bad = err > atol + RTOL * ref.abs()
+    assert not bool(bad.any()), f"{what}: {int(bad.sum())} of {bad.numel()} off, max err {float(err.max()):.3e} (atol {atol:.3e})"
+
+
+@pytest.fixture(scope="module")
+def ts():
+    import tac_spectral
+    return tac_spectral
+
+
+def test_golden_disc_inputs(ts, golden_dir):
+    """The reference's own spec_transform + cat + rearrange outputs (tests/golden/stft_disc.npz)."""
+    g = np.load(os.path.join(golden_dir, "stft_disc.npz"))
+    x = torch.from_numpy(g["x"]).cuda()
+    cfgs = [tuple(int(v) for v in g[f"cfg_{i}"]) for i in range(3)]
+    outs = ts.MultiScaleSTFT([c[0] for c in cfgs], [c[1] for c in cfgs], [c[2] for c in cfgs])(x)
+    for i, o in enumerate(outs):
+        _close(o, torch.from_numpy(g[f"planes_{i}"]), f"planes scale {i}")
+    for i, (n, h, w) in enumerate(cfgs):
+        sp = ts.Spectrogram(n_fft=n, hop_length=h, win_length=w, window_fn=torch.hann_window, normalized=True,
+                            center=False, pad_mode=None, power=None)          # msstftd.py:125-127 verbatim
+        z = sp(x)
+        ref = torch.from_numpy(g[f"complex_{i}"])
+        assert z.dtype == torch.complex64 and z.shape == ref.shape
+        _close(torch.view_as_real(z), torch.view_as_real(ref), f"complex scale {i}")
+        _close(sp.planes(x), torch.from_numpy(g[f"planes_{i}"]), f"Spectrogram.planes scale {i}")
+
+
+def test_kat_shapes(ts):
+    """testing_scripts.ipynb:2021-2023: (2,1,24000) -> F x K = 90x513, 43x1025, 184x257."""
+    x = torch.randn(2, 1, 24000, device="cuda")
+    outs = ts.MultiScaleSTFT()(x)
+    assert [tuple(o.shape) for o in outs] == [(2, 2, 90, 513), (2, 2, 43, 1025), (2, 2, 184, 257)]
+
+
+@pytest.mark.parametrize("n", [64, 128, 256, 512, 1024, 2048])
+def test_single_scale_all_sizes(ts, n):
+    torch.manual_seed(n)
+    T = 5 * n + 37                                   # ragged: not a multiple of hop, unaligned rows
+    x = torch.randn(3, 2, T)
+    got = ts.stft_multi(x.cuda(), [n], [n // 4])[0]
+    _close(got, O.disc_inputs_ref(x, n, n // 4), f"n={n}")
+
+
+def test_five_scales_one_launch(ts):
+    """cfg 4 scale list (n = 2048..128, hop = n/4), small batch."""
+    (x,), _ = O.synth_audio(3, 16000, 1)
+    n_ffts = [2048, 1024, 512, 256, 128]
+    hops = [n // 4 for n in n_ffts]
+    outs = ts.stft_multi(x[:, None, :].cuda(), n_ffts, hops)
+    refs = O.multiscale_disc_inputs_ref(x[:, None, :], n_ffts, hops)
+    for n, o, r in zip(n_ffts, outs, refs):
+        _close(o, r, f"5-scale n={n}")
+
+
+def test_multichannel_and_hop_variants(ts):
+    torch.manual_seed(7)
+    x = torch.randn(2, 3, 9001)
+    for n, h, w in [(512, 64, 512), (1024, 512, 1024), (256, 256, 256), (1024, 256, 800), (512, 128, 400)]:
+        got = ts.stft_multi(x.cuda(), [n], [h], [w])[0]
+        _close(got, O.disc_inputs_ref(x, n, h, w), f"n={n} hop={h} win={w}")
+
+
+def test_minimum_length_and_single_frame(ts):
+    x = torch.randn(2, 1, 2048)
+    got = ts.stft_multi(x.cuda(), [2048, 512], [512, 128])
+    refs = O.multiscale_disc_inputs_ref(x, [2048, 512], [512, 128])
+    assert got[0].shape[2] == 1
+    for o, r in zip(got, refs):
+        _close(o, r, "minimum length")
+
+
+@pytest.mark.parametrize("pad_mode", ["reflect", "constant"])
+def test_centered_complex(ts, pad_mode):
+    torch.manual_seed(11)
+    x = torch.randn(3, 7000)
+    for n, h in [(2048, 512), (512, 128), (128, 32)]:
+        sp = ts.Spectrogram(n_fft=n, hop_length=h, win_length=n, power=None, normalized=False, center=True, pad_mode=pad_mode)
+        z = sp(x.cuda())
+        ref = O.stft_ref(x, n, h, n, center=True, pad_mode=pad_mode, normalized=False)
+        _close(torch.view_as_real(z), torch.view_as_real(ref), f"center {pad_mode} n={n}")
+
+
+def test_frontend_mag_phase(ts):
+    """Notebook front end: |D|, angle(D) of the centred 2048/512 STFT, [B, 2, 1025, F] and padded to 600."""
+    (y,), _ = O.synth_audio(4, 16000, 1, seed=99)
+    mag, ph = O.frontend_ref(y)
+    out = ts.complex_spectrogram(y.cuda())
+    assert out.shape == (4, 2, 1025, 32)
+    _close(out[:, 0], mag, "magnitude")
+    big = mag > 1e-3 * mag.max()
+    dphi = torch.angle(torch.exp(1j * (out[:, 1].cpu() - ph)))
+    assert float(dphi[big].abs().max()) < 1e-3, float(dphi[big].abs().max())
+    out600 = ts.complex_spectrogram(y.cuda(), f_pad=600)
+    assert out600.shape == (4, 2, 1025, 600)
+    assert torch.equal(out600[..., :32], out) and float(out600[..., 32:].abs().sum()) == 0.0
+    crop = ts.complex_spectrogram(y.cuda(), f_pad=20)
+    assert torch.equal(crop, out[..., :20])
+    d = ts.create_complex_spectrogram(y[0].cuda(), 16000)
+    assert set(d) == {"magnitude", "phase", "params"} and d["magnitude"].shape == (1025, 32)
+    assert torch.equal(d["magnitude"], out[0, 0])
+
+
+def test_long_clip_property(ts):
+    """Full-size clip (10 s): Parseval-type identity instead of an element-wise oracle.
+    With hop = n/4 and a periodic Hann window sum_f w^2(t - f*hop) = 1.5 for interior samples, so
+    sum_{f,k} c_k |X_f[k]|^2 * (sum w^2) / n = 1.5 * sum_interior x^2 + edge terms; checked against the
+    float64 evaluation of the same quantity by the oracle on one row."""
+    (x,), _ = O.synth_audio(2, 160000, 1, seed=5)
+    for n in (2048, 128):
+        got = ts.stft_multi(x[:, None, :].cuda(), [n], [n // 4])[0].double().cpu()      # [B, 2, F, K]
+        ref = O.disc_inputs_ref(x[:, None, :].double(), n, n // 4)
+        e_got = (got ** 2).sum(dim=(1, 3))
+        e_ref = (ref ** 2).sum(dim=(1, 3))
+        assert torch.allclose(e_got, e_ref, rtol=1e-4), f"frame energies differ (n={n})"
+
+
+def test_errors(ts):
+    x = torch.randn(1, 1, 4000, device="cuda")
+    with pytest.raises(RuntimeError):
+        ts.stft_multi(x, [1000], [250])                      # unsupported n_fft surfaces tac_last_error()
+    with pytest.raises(ValueError):
+        ts.stft_multi(x, [8192 // 2], [1024])                # signal shorter than n_fft
+    with pytest.raises(RuntimeError):
+        ts.stft_multi(torch.randn(1, 1, 4000), [512], [128])  # CPU tensor: no fallback
+    with pytest.raises(ValueError):
+        ts.Spectrogram(n_fft=512, window_fn=torch.hamming_window, power=None)

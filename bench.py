@@ -1,0 +1,446 @@
+#!/usr/bin/env python
+"""bench.py -- audio-seconds/sec through the STFT-loss + DPCA step (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload cfg2|cfg3|cfg1]
+
+One "step" = one pass of the spectral hot path over one batch of synthetic 16 kHz audio
+("Step metric"): K1 front end (mag/phase spectrogram of every clip), K2 fused
+multi-resolution STFT loss forward + backward on (target, decoded), K3 DPCA (statistics, eigen-solve,
+global top-dim_p selection, projection) of the per-view latents.  Workload at N=1 = BASELINE.json
+configs[1] ("SpectralResE2D2 latent=32: two correlated views, batch 256"); for N>1 every rank holds
+the same per-GPU shard (weak scaling) and the loss sums + DPCA statistics are all-reduced once per
+step over NCCL.
+
+Prints ONE JSON line (rank 0).  `value` = whole-job audio-s/s with inputs resident in HBM (CUDA
+graph replay of the step, rotating input sets larger than L2); `e2e` = the same through the public
+API with pinned HOST buffers, H2D copies and the D2H read of the loss inside the timed region;
+`roofline` = the dominant kernel against MEASURED_PEAKS.json; `cpu_baseline` = the CPU oracle
+(torch CPU restatement of the reference call sites) on a bounded sample of the same workload.
+
+`--impl reference` times that CPU path alone, with all host threads, on the same workload/metric.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "task-aware-audio-coding-perceptual_b200")
+for p in (ROOT, PKG):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+SR = 16000
+WORKLOADS = {
+    # name: clips per rank = batch * views, 1 s clips; DPCA views of [batch, d]; dim_p = total kept components
+    "cfg1": dict(desc="SpectralResE1D1 latent=8: 1 view, batch 16, 1 s clips", batch=16, views=1, T=16000, d=128, dim_p=8),
+    "cfg2": dict(desc="SpectralResE2D2 latent=32: 2 correlated views, batch 256, 1 s clips, 3-scale loss fwd+bwd + "
+                      "front end + DPCA d=128/view dim_p=32", batch=256, views=2, T=16000, d=128, dim_p=32),
+    "cfg3": dict(desc="SpectralResE4D1 latent=128: 4 correlated views, batch 128 per GPU, 1 s clips, DPCA d=128/view "
+                      "dim_p=128", batch=128, views=4, T=16000, d=128, dim_p=128),
+}
+N_FFTS = (1024, 2048, 512)          # msstftd.py:174
+HOPS = (256, 512, 128)              # msstftd.py:175
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of CUDA-graph replay")
+    ap.add_argument("--no-overlap", action="store_true", help="run every leg on one stream")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU-baseline budget (bounded sample)")
+    return ap.parse_args()
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ------------------------------------------------------------------------------------------ synthetic data
+def synth_host(batch, views, T, d, seed):
+    """Correlated multi-view clips in [-1, 1], "decoded" = view + noise, latents with a decaying spectrum
+    (the recipe of SURVEY.md 8d).  Returns CPU tensors x [batch*views, T], y, zs [views][batch, d]."""
+    import math
+    import torch
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    n = 0.1 * torch.randn(batch, T + 1, generator=g)
+    src = 0.5 * (n[:, 1:] + n[:, :-1])
+    t = torch.arange(T, dtype=torch.float32) / SR
+    for f0 in (220.0, 880.0, 3520.0):
+        ph = 2 * math.pi * torch.rand(batch, 1, generator=g)
+        src = src + 0.05 * torch.sin(2 * math.pi * f0 * t[None, :] + ph)
+    amps = (1.0, 0.9, 0.8, 0.7)
+    xs, ys = [], []
+    for i in range(views):
+        v = amps[i % 4] * src + 0.05 * torch.randn(batch, T, generator=g)
+        xs.append(v.clamp(-1, 1))
+        ys.append((v + 0.02 * torch.randn(batch, T, generator=g)).clamp(-1, 1))
+    x = torch.stack(xs, 1).reshape(batch * views, T).contiguous()     # views of a clip stay adjacent
+    y = torch.stack(ys, 1).reshape(batch * views, T).contiguous()
+    sigma = 0.97 ** torch.arange(d, dtype=torch.float32)
+    shared = torch.randn(batch, d, generator=g)
+    zs = []
+    for i in range(views):
+        G = (shared + torch.randn(batch, d, generator=g)) / math.sqrt(2.0)
+        Q, _ = torch.linalg.qr(torch.randn(d, d, generator=g))
+        zs.append((((G * sigma) @ Q.T) * (1.0 + 0.03 * i) + 0.3).contiguous())
+    return x, y, zs
+
+
+# ------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """Samples SM clock and throttle reasons with NVML while the timed region runs."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nv = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self._nv = None
+
+    def _loop(self):
+        nv = self._nv
+        names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
+                 "hw_power_brake_slowdown": 0x80, "sync_boost": 0x10, "applications_clocks_setting": 0x2}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(int(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
+                r = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self._h)) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
+                    else int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h))
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            self._stop.wait(0.02)
+
+    def __enter__(self):
+        if self._nv is not None:
+            self._thr = threading.Thread(target=self._loop, daemon=True)
+            self._thr.start()
+        return self
+
+    def __exit__(self, *exc):
+        self._stop.set()
+        if self._thr is not None:
+            self._thr.join()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": 0}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+# ------------------------------------------------------------------------------------------ CPU path (oracle)
+class CpuPath:
+    """The CPU restatement of the reference call sites (oracle/spectral_oracle.py: torch.stft on the msstftd.py
+    convention, autograd backward, torch.linalg.svd DPCA) on a BOUNDED sample of the workload: `clips` items (all
+    views) per audio pass, scaled linearly to the batch; DPCA on the workload's full latent batch (it is tiny)."""
+
+    def __init__(self, w, clips, threads):
+        import torch
+        from oracle import spectral_oracle as O
+        torch.set_num_threads(threads)
+        self.O, self.w, self.clips, self.threads = O, w, clips, threads
+        self.x, self.y, _ = synth_host(clips, w["views"], w["T"], w["d"], seed=77)
+        self.zfull = synth_host(w["batch"], w["views"], 64, w["d"], seed=78)[2]
+
+    def audio_pass(self):
+        O = self.O
+        mag, ph = O.frontend_ref(self.x)                                # K1
+        O.stack_mag_phase_ref(mag, ph)
+        yr = self.y.clone().requires_grad_(True)                        # K2 fwd + bwd
+        loss = O.mrstft_loss_ref(self.x, yr, N_FFTS, HOPS)
+        loss.backward()
+        return float(loss.detach())
+
+    def dpca_pass(self):
+        self.O.dpca_project_ref(self.zfull, self.w["dim_p"])            # K3
+
+    def step_seconds(self):
+        """One bounded-sample step: seconds the FULL workload step would take (audio pass scaled)."""
+        t0 = time.perf_counter(); self.audio_pass(); t1 = time.perf_counter(); self.dpca_pass(); t2 = time.perf_counter()
+        return (t1 - t0) * (self.w["batch"] / self.clips) + (t2 - t1)
+
+    def sample(self, n):
+        w = self.w
+        return (f"{n} timed passes of {self.clips} items x {w['views']} view(s) x {w['T'] / SR:g} s (front end + 3-scale loss fwd+bwd by "
+                f"torch autograd), scaled x{w['batch'] / self.clips:g}, + DPCA (torch.linalg.svd) on the full [{w['batch']}, {w['d']}] x "
+                f"{w['views']} latents; {self.threads} torch threads")
+
+
+def cpu_baseline(w, budget_s, threads):
+    cp = CpuPath(w, min(w["batch"], 16), threads)
+    cp.step_seconds()                                                   # warm-up
+    ts, t_end = [], time.perf_counter() + budget_s
+    while len(ts) < 3 or (time.perf_counter() < t_end and len(ts) < 200):
+        ts.append(cp.step_seconds())
+    t_step = sum(ts) / len(ts)
+    return (w["batch"] * w["views"] * w["T"] / SR) / t_step, t_step, cp.sample(len(ts))
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    w = WORKLOADS[args.workload]
+    threads = os.cpu_count() or 1
+    cp = CpuPath(w, min(w["batch"], 16), threads)
+    for _ in range(args.warmup):
+        cp.step_seconds()
+    ts = [cp.step_seconds() for _ in range(args.steps)]
+    t_step = sum(ts) / len(ts)
+    value = (w["batch"] * w["views"] * w["T"] / SR) / t_step
+    line = {"impl": "reference", "metric": "audio-seconds/sec through STFT-loss+DPCA step", "value": value,
+            "unit": "audio-s/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * t_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{args.workload}: {w['desc']}", "note": "reference CPU path (the torch CPU calls the reference's "
+                       "call sites make, restated in oracle/); rank 0's host cores only -- the reference has no multi-GPU path, so "
+                       "the value does not grow with --gpus"},
+            "cpu_baseline": {"value": value, "unit": "audio-s/s", "cores": threads, "kind": "port", "sample": cp.sample(args.steps),
+                             "torch": torch.__version__},
+            "e2e": {"value": value, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------ native
+def run_native(args):
+    import torch
+    import torch.distributed as dist
+    import tac_spectral as ts
+    from tac_spectral import _lib as L
+    from tac_spectral.step import SpectralStep
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py (native) needs a CUDA device: the spectral hot path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    group = None
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+        group = dist.group.WORLD
+    lib = L.lib()
+
+    w = WORKLOADS[args.workload]
+    batch, views, T, d, dim_p = w["batch"], w["views"], w["T"], w["d"], w["dim_p"]
+    rows = batch * views
+    step = SpectralStep(rows, T, views, batch, d, dim_p, N_FFTS, HOPS, device=dev, group=group, overlap=not args.no_overlap)
+    alg = step.algorithmic_bytes()
+
+    # ---- inputs resident in HBM: a ring of input sets larger than L2 (126 MB) so no step finds its inputs cached
+    set_bytes = 2 * rows * T * 4 + views * batch * d * 4
+    nsets = max(2, -(-400_000_000 // set_bytes))
+    host_sets = [synth_host(batch, views, T, d, seed=1000 * rank + i) for i in range(min(nsets, 2))]
+    dsets = []
+    for i in range(nsets):
+        hx, hy, hz = host_sets[i % len(host_sets)]
+        jitter = 1.0 - 0.001 * (i // len(host_sets))                     # distinct values per set, same statistics
+        dsets.append(((hx * jitter).to(dev), (hy * jitter).to(dev), [(z * jitter).to(dev) for z in hz]))
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier(device_ids=[local])
+        torch.cuda.synchronize()
+
+    # ---- eager warm-up (also builds tables / sets attributes before any capture)
+    for i in range(2):
+        step.run(*dsets[i % nsets])
+    torch.cuda.synchronize()
+
+    graphs = None
+    launches_per_step = None
+    if not args.no_graph:
+        try:
+            graphs = []
+            for i in range(nsets):
+                g = torch.cuda.CUDAGraph()
+                c0 = int(lib.tac_launch_count())
+                with torch.cuda.graph(g):
+                    step.run(*dsets[i])
+                launches_per_step = int(lib.tac_launch_count()) - c0
+                graphs.append(g)
+        except Exception as e:                                           # capture unsupported -> eager timing, said so in config
+            if rank == 0:
+                print(f"[bench] CUDA-graph capture failed ({type(e).__name__}: {e}); timing eager launches", file=sys.stderr)
+            graphs = None
+            torch.cuda.synchronize()
+    if launches_per_step is None:
+        c0 = int(lib.tac_launch_count())
+        step.run(*dsets[0])
+        launches_per_step = int(lib.tac_launch_count()) - c0
+        torch.cuda.synchronize()
+
+    def do_step(i):
+        if graphs is not None:
+            graphs[i % nsets].replay()
+        else:
+            step.run(*dsets[i % nsets])
+
+    # ---- timed region: W warm-up steps, then exactly K steps between barrier + synchronize
+    for i in range(args.warmup):
+        do_step(i)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clk:
+        e0.record()
+        for i in range(args.steps):
+            do_step(args.warmup + i)
+        e1.record()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier(device_ids=[local])
+        torch.cuda.synchronize()
+    ms_total = e0.elapsed_time(e1)
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item()) / args.steps
+    audio_s_step = world * rows * T / SR
+    value = audio_s_step / (ms_step * 1e-3)
+    loss_val = float(step.loss.item())
+
+    # ---- attribution pass: the same K steps, eager, CUDA events around each leg on its launching stream
+    legs = ["frontend", "loss_fwd", "loss_bwd", "dpca_stats", "dpca_solve", "dpca_project"]
+    acc = {k: 0.0 for k in legs}
+    evs = []
+    for i in range(args.steps):
+        x, y, zs = dsets[(args.warmup + i) % nsets]
+        rec = {}
+        for name, fn in (("loss_bwd", lambda: step.leg_loss_bwd(x, y)), ("frontend", lambda: step.leg_frontend(x)),
+                         ("dpca_stats", lambda: step.leg_dpca_stats(zs)), ("loss_fwd", lambda: step.leg_loss_fwd(x, y)),
+                         ("dpca_solve", step.leg_dpca_solve), ("dpca_project", lambda: step.leg_dpca_project(zs))):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); fn(); b.record()
+            rec[name] = (a, b)
+            if name == "loss_fwd":
+                step.leg_allreduce()
+        evs.append(rec)
+    torch.cuda.synchronize()
+    for rec in evs:
+        for k, (a, b) in rec.items():
+            acc[k] += a.elapsed_time(b)
+    leg_ms = {k: v / args.steps for k, v in acc.items()}
+    peak, peak_src = load_peaks()
+    byte_legs = {"frontend": alg.get("frontend", 0), "loss_fwd": alg["loss_fwd"], "loss_bwd": alg["loss_bwd"],
+                 "dpca_stats": alg["dpca_stats"], "dpca_project": alg["dpca_project"]}
+    dom = max(("frontend", "loss_fwd", "loss_bwd"), key=lambda k: leg_ms[k])
+    kern_name = {"frontend": "stft_tiled_kernel<Plan2048, MAGPHASE>", "loss_fwd": "mrstft_fwd_kernel", "loss_bwd": "mrstft_bwd_kernel"}[dom]
+    achieved = byte_legs[dom] / (leg_ms[dom] * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": kern_name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": byte_legs[dom],
+                "kernel_ms": leg_ms[dom],
+                "per_leg": {k: {"ms": leg_ms[k], "bytes": byte_legs.get(k), "gbs": (byte_legs[k] / (leg_ms[k] * 1e-3) / 1e9) if byte_legs.get(k) else None}
+                            for k in legs},
+                "step_bytes": sum(byte_legs.values()), "step_gbs": sum(byte_legs.values()) / (ms_step * 1e-3) / 1e9,
+                "step_frac": sum(byte_legs.values()) / (ms_step * 1e-3) / 1e9 / peak}
+    prof = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(prof):
+        try:
+            roofline["traffic"] = json.load(open(prof)).get(dom)
+        except Exception:
+            pass
+
+    # ---- e2e: public API, pinned host buffers, H2D of the step's inputs and D2H of the loss every step
+    hx, hy, hz = host_sets[0]
+    px, py = hx.pin_memory(), hy.pin_memory()
+    pz = [z.pin_memory() for z in hz]
+    dx, dy = torch.empty_like(dsets[0][0]), torch.empty_like(dsets[0][1])
+    dz = [torch.empty_like(z) for z in dsets[0][2]]
+    g_e2e = None
+    if graphs is not None:
+        g_e2e = torch.cuda.CUDAGraph()
+        step.run(dx, dy, dz); torch.cuda.synchronize()
+        with torch.cuda.graph(g_e2e):
+            step.run(dx, dy, dz)
+    h_loss = torch.empty((), dtype=torch.float64).pin_memory()
+
+    def e2e_step():
+        dx.copy_(px, non_blocking=True); dy.copy_(py, non_blocking=True)
+        for a, b in zip(dz, pz):
+            a.copy_(b, non_blocking=True)
+        if g_e2e is not None:
+            g_e2e.replay()
+        else:
+            step.run(dx, dy, dz)
+        h_loss.copy_(step.loss, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return float(h_loss)
+
+    for _ in range(max(3, args.warmup)):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    e2e_val = audio_s_step / (float(dt.item()) / args.steps)
+    h2d = 2 * rows * T * 4 + views * batch * d * 4
+    e2e = {"value": e2e_val, "unit": "audio-s/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
+           "ms_per_step": 1e3 * float(dt.item()) / args.steps}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        v, t_step, sample = cpu_baseline(w, args.cpu_seconds, threads)
+        cpu = {"value": v, "unit": "audio-s/s", "cores": threads, "kind": "port", "sample": sample, "ms_per_step": 1e3 * t_step}
+
+    if rank == 0:
+        line = {"metric": "audio-seconds/sec through STFT-loss+DPCA step", "value": value, "unit": "audio-s/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": f"{args.workload}: {w['desc']}", "clips_per_gpu": rows, "samples_per_clip": T,
+                           "loss_scales": list(N_FFTS), "front_end": "n_fft 2048 hop 512 centred, mag+phase [rows,2,1025,32] (unpadded)",
+                           "dpca": {"views": views, "batch": batch, "d": d, "dim_p": dim_p, "gram": "tcgen05 3xTF32"},
+                           "parallelism": f"dp{world} (batch shards; one packed NCCL all-reduce of loss sums + DPCA statistics)",
+                           "launch": "cuda-graph replay" if graphs is not None else "eager",
+                           "overlap": not args.no_overlap,
+                           "l2": f"ring of {nsets} input sets ({nsets * set_bytes / 1e6:.0f} MB) > 126 MB L2"},
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
+                "launches_per_step": launches_per_step, "clocks": clk.summary(), "loss": loss_val}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_native(args)
+
+
+if __name__ == "__main__":
+    main()

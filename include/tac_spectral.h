@@ -55,6 +55,9 @@ typedef void* tac_stream_t; /* cudaStream_t */
 
 TAC_API const char* tac_last_error(void);
 TAC_API int tac_version(void);
+/* Number of CUDA kernels this library has enqueued so far in this process (launches recorded into a
+ * CUDA graph during stream capture count once, at capture time).  bench.py's `gpu_launches`. */
+TAC_API uint64_t tac_launch_count(void);
 
 /* Build (idempotent) the device tables for one (n_fft, win_length, normalized) on the current
  * device.  Synchronous (cudaMalloc + cudaMemcpy); call once outside any stream capture. */

@@ -321,13 +321,13 @@ static int dpca_tc_stats(const float* const* z, int nv, long long B, int d, doub
     for (int i = 0; i < 8; ++i) p[i] = z[i < nv ? i : 0];
     const int nsplit = (int)((B + kTcRowsPerCta - 1) / kTcRowsPerCta);
     float* partial = reinterpret_cast<float*>(ws);
-    dpca_colsum_kernel<<<nv, 1024, 0, st>>>(p[0], p[1], p[2], p[3], p[4], p[5], p[6], p[7], B, d, stats);
+    dpca_colsum_kernel<<<nv, 1024, 0, st>>>(p[0], p[1], p[2], p[3], p[4], p[5], p[6], p[7], B, d, stats); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
     TAC_CHECK_CUDA(cudaFuncSetAttribute(dpca_gram_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
     dpca_gram_tc_kernel<<<dim3(nsplit, nv), kTcThreads, kTcSmemBytes, st>>>(p[0], p[1], p[2], p[3], p[4], p[5], p[6], p[7], B, d,
-                                                                           stats, partial);
+                                                                           stats, partial); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
-    dpca_gram_finish_kernel<<<dim3(d, nv), kTcFeat, 0, st>>>(partial, nsplit, d, stats);
+    dpca_gram_finish_kernel<<<dim3(d, nv), kTcFeat, 0, st>>>(partial, nsplit, d, stats); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
     return TAC_OK;
 }
@@ -363,7 +363,7 @@ extern "C" int tac_dpca_stats(const float* const* z, int nv, int64_t B, int d, i
         return dpca_tc_stats(vp.z, nv, B, d, stats, workspace, workspace_bytes, st);
     }
     const int nt = (d + 31) / 32;
-    dpca_gram_fp64_kernel<<<dim3(nt * nt, nv), 256, 0, st>>>(vp, B, d, stats);
+    dpca_gram_fp64_kernel<<<dim3(nt * nt, nv), 256, 0, st>>>(vp, B, d, stats); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
     return TAC_OK;
 }
@@ -382,7 +382,7 @@ extern "C" int tac_dpca_eig(const double* stats, int nv, int d, float* s, float*
             return set_error(TAC_EWORKSPACE, "tac_dpca_eig with d=%d needs %zu workspace bytes", d, need);
     }
     TAC_CHECK_CUDA(cudaFuncSetAttribute(dpca_eig_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-    dpca_eig_kernel<<<nv, kEigThreads, use_gws ? 0 : smem, st>>>(stats, d, s, v, mu, rank, reinterpret_cast<double*>(workspace), use_gws);
+    dpca_eig_kernel<<<nv, kEigThreads, use_gws ? 0 : smem, st>>>(stats, d, s, v, mu, rank, reinterpret_cast<double*>(workspace), use_gws); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
     return TAC_OK;
 }
@@ -391,7 +391,7 @@ extern "C" int tac_dpca_select(const float* s, const int* rank, int nv, int d, i
     TAC_REQUIRE(s && rank && idx && cnt, "null argument");
     TAC_REQUIRE(nv >= 1 && nv <= kMaxViews && d >= 1 && d <= kMaxD, "bad nv / d");
     TAC_REQUIRE(dim_p >= 0, "dim_p must be >= 0");
-    dpca_select_kernel<<<1, 1024, 0, reinterpret_cast<cudaStream_t>(stream)>>>(s, rank, nv, d, dim_p, idx, cnt);
+    dpca_select_kernel<<<1, 1024, 0, reinterpret_cast<cudaStream_t>(stream)>>>(s, rank, nv, d, dim_p, idx, cnt); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
     return TAC_OK;
 }
@@ -409,9 +409,9 @@ extern "C" int tac_dpca_project(const float* const* z, int nv, int64_t B, int d,
     }
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     float* P = reinterpret_cast<float*>(workspace);
-    dpca_projector_kernel<<<dim3(d, nv), ((d + 31) / 32) * 32, 0, st>>>(v, idx, cnt, d, P);
+    dpca_projector_kernel<<<dim3(d, nv), ((d + 31) / 32) * 32, 0, st>>>(v, idx, cnt, d, P); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
-    dpca_apply_kernel<<<dim3((unsigned)((B + 31) / 32), (d + 31) / 32, nv), 256, 0, st>>>(vp, B, d, P, mu);
+    dpca_apply_kernel<<<dim3((unsigned)((B + 31) / 32), (d + 31) / 32, nv), 256, 0, st>>>(vp, B, d, P, mu); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
     return TAC_OK;
 }
@@ -419,7 +419,7 @@ extern "C" int tac_dpca_project(const float* const* z, int nv, int64_t B, int d,
 extern "C" int tac_var_topk(const double* stats, int d, int k, float* var, int* top_idx, tac_stream_t stream) {
     TAC_REQUIRE(stats && var && top_idx, "null argument");
     TAC_REQUIRE(d >= 1 && d <= kMaxD * 4 && k >= 1 && k <= d, "need 1 <= k <= d <= %d", kMaxD * 4);
-    var_topk_kernel<<<1, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(stats, d, k, var, top_idx);
+    var_topk_kernel<<<1, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(stats, d, k, var, top_idx); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
     return TAC_OK;
 }

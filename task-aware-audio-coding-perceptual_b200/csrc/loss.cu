@@ -453,9 +453,9 @@ extern "C" int tac_mrstft_loss_fwd(const float* x, const float* y, int64_t B, in
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     const size_t smem = 2 * (size_t)a.tile_len * sizeof(float) + (size_t)kFwdWarps * kXbufFloat2 * sizeof(float2);
     TAC_CHECK_CUDA(cudaFuncSetAttribute(mrstft_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
-    mrstft_fwd_kernel<<<(unsigned)grid, kFwdThreads, smem, st>>>(a);
+    mrstft_fwd_kernel<<<(unsigned)grid, kFwdThreads, smem, st>>>(a); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
-    partial_reduce_kernel<<<2 * n_scales, 256, 0, st>>>(a.partial, grid, 2 * n_scales, sums);
+    partial_reduce_kernel<<<2 * n_scales, 256, 0, st>>>(a.partial, grid, 2 * n_scales, sums); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
     return TAC_OK;
 }
@@ -476,7 +476,7 @@ extern "C" int tac_mrstft_loss_bwd(const float* x, const float* y, int64_t B, in
     if (a.nchunks > 1) TAC_CHECK_CUDA(cudaMemsetAsync(grad_y, 0, (size_t)B * T * sizeof(float), st));
     const size_t smem = (size_t)a.tile_len * sizeof(float) + (size_t)kBwdWarps * kXbufFloat2 * sizeof(float2);
     TAC_CHECK_CUDA(cudaFuncSetAttribute(mrstft_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 75 * 1024));
-    mrstft_bwd_kernel<<<(unsigned)grid, kBwdThreads, smem, st>>>(a);
+    mrstft_bwd_kernel<<<(unsigned)grid, kBwdThreads, smem, st>>>(a); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
     return TAC_OK;
 }
@@ -494,9 +494,9 @@ extern "C" int tac_spec_losses(const float* obs, const float* dec, int64_t B, in
     TAC_REQUIRE(B * 2 * kSpecSplit < (1ll << 31), "grid too large");
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     double* partial = reinterpret_cast<double*>(workspace);
-    spec_partial_kernel<<<(unsigned)(B * 2 * kSpecSplit), kSpecThreads, 0, st>>>(obs, dec, K * F, partial);
+    spec_partial_kernel<<<(unsigned)(B * 2 * kSpecSplit), kSpecThreads, 0, st>>>(obs, dec, K * F, partial); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
-    spec_final_kernel<<<1, 256, 0, st>>>(partial, B, K * F, out5, per_sample);
+    spec_final_kernel<<<1, 256, 0, st>>>(partial, B, K * F, out5, per_sample); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
     return TAC_OK;
 }
@@ -509,7 +509,7 @@ extern "C" int tac_spec_losses_bwd(const float* obs, const float* dec, int64_t B
     const long long plane = K * F;
     long long gx = (plane / 4 + 255) / 256;
     gx = gx < 1 ? 1 : (gx > 64 ? 64 : gx);
-    spec_bwd_kernel<<<dim3((unsigned)gx, (unsigned)(B * 2)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(obs, dec, plane, w, grad_dec);
+    spec_bwd_kernel<<<dim3((unsigned)gx, (unsigned)(B * 2)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(obs, dec, plane, w, grad_dec); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
     return TAC_OK;
 }

@@ -245,7 +245,7 @@ static int launch_tiled(const TiledArgs& a, long long rows, size_t smem, cudaStr
         attr_set = true;
     }
     const long long grid = rows * a.ntiles;
-    kern<<<(unsigned)grid, kThreads, smem, st>>>(a);
+    kern<<<(unsigned)grid, kThreads, smem, st>>>(a); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
     return TAC_OK;
 }
@@ -321,7 +321,7 @@ extern "C" int tac_stft_multi(const float* x, int64_t B, int64_t C, int64_t T, i
         }
         const long long grid = rows * a.nchunks;
         TAC_REQUIRE(grid < (1ll << 31), "grid too large");
-        stft_planes_kernel<<<(unsigned)grid, kThreads, smem, st>>>(a);
+        stft_planes_kernel<<<(unsigned)grid, kThreads, smem, st>>>(a); TAC_LAUNCHED(1);
         TAC_CHECK_CUDA(cudaGetLastError());
         return TAC_OK;
     }

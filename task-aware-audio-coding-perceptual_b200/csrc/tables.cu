@@ -1,6 +1,7 @@
 // Error channel + per-device cache of the immutable FFT tables (window*scale, pass twiddles,
 // post-processing twiddles), generated on the host in float64.
 #include <math.h>
+#include <atomic>
 #include <map>
 #include <mutex>
 #include <tuple>
@@ -11,6 +12,9 @@
 namespace tac {
 
 static thread_local char g_err[512] = "";
+static std::atomic<unsigned long long> g_launches{0};
+
+void count_launches(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 
 int set_error(int code, const char* fmt, ...) {
     va_list ap;
@@ -97,7 +101,8 @@ int get_tables(int n, int win, int normalized, FftTables* out) {
 extern "C" {
 
 const char* tac_last_error(void) { return tac::g_err; }
-int tac_version(void) { return 100; }
+int tac_version(void) { return 101; }
+uint64_t tac_launch_count(void) { return tac::g_launches.load(std::memory_order_relaxed); }
 
 int tac_prepare_fft(int n_fft, int win_length, int normalized) {
     tac::FftTables t;

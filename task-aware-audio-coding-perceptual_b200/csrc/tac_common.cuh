@@ -46,4 +46,8 @@ inline int64_t num_frames(int64_t T, int n, int hop, int center) {
 
 constexpr int kNumSMs = 148;
 
+// Kernel-launch counter behind tac_launch_count(): every kernel (not memset) this library enqueues.
+void count_launches(int n);
+#define TAC_LAUNCHED(n) tac::count_launches(n)
+
 }  // namespace tac

@@ -22,6 +22,7 @@ _VPP = C.POINTER(C.c_void_p)
 SIGNATURES = {
     "tac_last_error": (C.c_char_p, []),
     "tac_version": (_I, []),
+    "tac_launch_count": (C.c_uint64, []),
     "tac_prepare_fft": (_I, [_I, _I, _I]),
     "tac_shutdown": (_I, []),
     "tac_stft_num_frames": (_I64, [_I64, _I, _I, _I]),

@@ -1,0 +1,181 @@
+"""One training-step pass of the spectral hot path with every buffer pre-allocated (K1 + K2 + K3).
+
+``SpectralStep`` is the allocation-free, host-sync-free form of what the reference does per batch in
+``train_spectral_ae`` (``train_pkl_file_task_aware.py:597-629``) on this path:
+
+* K1  front end  ``create_complex_spectrogram`` (``spectrogram.ipynb`` cell 10 L26-52) for every clip,
+* K2  multi-resolution STFT loss of (target, decoded) and its gradient w.r.t. the decoded signal,
+* K3  DPCA of the per-view latents (``pkl_file_model_updated.py:489-511`` / ``:398-427``),
+
+launched through the C ABI on the caller's current stream, so that the whole step can be captured
+in a CUDA graph (``torch.cuda.graph``) and replayed.  Multi-GPU (``group``): the per-scale loss sums
+and the DPCA sufficient statistics live in ONE packed float64 buffer that is all-reduced once per
+step; everything after it (eigen-solve, selection, projection) runs redundantly on
+every rank on the global statistics, and the input gradient needs no collective because the global
+normaliser is known from shapes.
+
+The loss backward and the front end do not depend on the all-reduce; with ``overlap=True`` they run
+on a side stream next to the latency-bound DPCA chain (one CTA per view in the eigen-solve).
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import _lib as L
+from .loss import LOG_FLOOR
+from .stft import num_frames
+
+
+class SpectralStep:
+    def __init__(self, rows: int, T: int, n_views: int, batch: int, d: int, dim_p: int,
+                 n_ffts: Sequence[int] = (1024, 2048, 512), hops: Optional[Sequence[int]] = None,
+                 eps: float = LOG_FLOOR, frontend: bool = True, fe_n_fft: int = 2048, fe_hop: int = 512,
+                 f_pad: int = 0, device="cuda", group=None, gram_algo: Optional[str] = None, overlap: bool = True):
+        self.rows, self.T, self.nv, self.B, self.d, self.dim_p = int(rows), int(T), int(n_views), int(batch), int(d), int(dim_p)
+        self.n_ffts = list(n_ffts)
+        self.hops = [n // 4 for n in self.n_ffts] if hops is None else list(hops)
+        self.S = len(self.n_ffts)
+        self.eps = float(eps)
+        self.frontend, self.fe_n_fft, self.fe_hop, self.f_pad = bool(frontend), int(fe_n_fft), int(fe_hop), int(f_pad)
+        self.group, self.overlap = group, bool(overlap)
+        self.device = torch.device(device)
+        self.world = 1
+        if group is not None:
+            import torch.distributed as dist
+            self.world = dist.get_world_size(group)
+        from .dpca import _algo_code
+        self.algo = _algo_code(gram_algo, self.d)
+        lib = L.lib()
+        dev = self.device
+        S, nv, d = self.S, self.nv, self.d
+        self._nf, self._hp = L.int_array(self.n_ffts), L.int_array(self.hops)
+        # ---- packed all-reduce payload: [2S loss sums | nv * (1 + d + d*d) DPCA statistics], float64
+        self.stat_stride = 1 + d + d * d
+        self.packed = torch.zeros(2 * S + nv * self.stat_stride, dtype=torch.float64, device=dev)
+        self.sums = self.packed[:2 * S]
+        self.stats = self.packed[2 * S:].view(nv, self.stat_stride)
+        counts = [self.rows * (n // 2 + 1) * num_frames(T, n, h, False) for n, h in zip(self.n_ffts, self.hops)]
+        if min(counts) <= 0:
+            raise ValueError(f"signal of {T} samples is shorter than the largest n_fft")
+        inv = [1.0 / (S * c * self.world) for c in counts for _ in (0, 1)]
+        self.inv64 = torch.tensor(inv, dtype=torch.float64, device=dev)        # loss = dot(sums, inv64)
+        self.coef = torch.tensor(inv, dtype=torch.float32, device=dev)         # d loss / d sums (constant)
+        self.loss = torch.zeros((), dtype=torch.float64, device=dev)
+        # ---- workspaces and outputs
+        self.ws_loss_bytes = int(lib.tac_mrstft_workspace_bytes(self.rows, T, S, self._nf, self._hp))
+        self.ws_loss = torch.empty(max(self.ws_loss_bytes, 16), dtype=torch.uint8, device=dev)
+        self.ws_dpca_bytes = int(lib.tac_dpca_workspace_bytes(nv, self.B, d))
+        self.ws_dpca = torch.empty(max(self.ws_dpca_bytes, 256), dtype=torch.uint8, device=dev)
+        self.grad_y = torch.empty((self.rows, T), dtype=torch.float32, device=dev)
+        self.s = torch.empty((nv, d), dtype=torch.float32, device=dev)
+        self.v = torch.empty((nv, d, d), dtype=torch.float32, device=dev)
+        self.mu = torch.empty((nv, d), dtype=torch.float32, device=dev)
+        self.rank = torch.empty(nv, dtype=torch.int32, device=dev)
+        self.idx = torch.zeros((nv, d), dtype=torch.int32, device=dev)
+        self.cnt = torch.zeros(nv, dtype=torch.int32, device=dev)
+        self.z_out = [torch.empty((self.B, d), dtype=torch.float32, device=dev) for _ in range(nv)]
+        self._zout_ptrs = L.ptr_array(self.z_out)
+        if self.frontend:
+            self.fe_F = num_frames(T, self.fe_n_fft, self.fe_hop, True)
+            Fp = self.f_pad if self.f_pad > 0 else self.fe_F
+            self.fe_out = torch.empty((self.rows, 2, self.fe_n_fft // 2 + 1, Fp), dtype=torch.float32, device=dev)
+            self._fe_ptr = L.ptr_array([self.fe_out])
+            self._fe_nf, self._fe_hp = L.int_array([self.fe_n_fft]), L.int_array([self.fe_hop])
+        with torch.cuda.device(dev):
+            for n in set(self.n_ffts):
+                L.check(lib.tac_prepare_fft(n, n, 1))
+            if self.frontend:
+                L.check(lib.tac_prepare_fft(self.fe_n_fft, self.fe_n_fft, 0))
+            self.side = torch.cuda.Stream(device=dev) if self.overlap else None
+
+    # ------------------------------------------------------------------ individual legs (current stream)
+    def _check(self, x, y, zs):
+        if tuple(x.shape) != (self.rows, self.T) or tuple(y.shape) != (self.rows, self.T):
+            raise ValueError(f"Shape mismatch: expected x, y [{self.rows}, {self.T}], got {tuple(x.shape)}, {tuple(y.shape)}")
+        if len(zs) != self.nv or any(tuple(z.shape) != (self.B, self.d) for z in zs):
+            raise ValueError(f"expected {self.nv} latent views of shape [{self.B}, {self.d}]")
+        for t in (x, y, *zs):
+            L.require_cuda(t, "input")
+            if t.dtype != torch.float32 or not t.is_contiguous():
+                raise ValueError("inputs must be contiguous float32")
+
+    def leg_frontend(self, x):
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        L.check(L.lib().tac_stft_multi(x.data_ptr(), self.rows, 1, self.T, 1, self._fe_nf, self._fe_hp, self._fe_nf, 1,
+                                       L.PAD_ZERO, 0, L.OUT_MAGPHASE, self.f_pad, self._fe_ptr, st))
+
+    def leg_loss_fwd(self, x, y):
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        L.check(L.lib().tac_mrstft_loss_fwd(x.data_ptr(), y.data_ptr(), self.rows, self.T, self.S, self._nf, self._hp, self._nf,
+                                            self.eps, self.sums.data_ptr(), self.ws_loss.data_ptr(), self.ws_loss_bytes, st))
+
+    def leg_loss_bwd(self, x, y):
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        L.check(L.lib().tac_mrstft_loss_bwd(x.data_ptr(), y.data_ptr(), self.rows, self.T, self.S, self._nf, self._hp, self._nf,
+                                            self.eps, self.coef.data_ptr(), self.grad_y.data_ptr(), None, 0, st))
+
+    def leg_dpca_stats(self, zs):
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        L.check(L.lib().tac_dpca_stats(L.ptr_array(zs), self.nv, self.B, self.d, self.algo, self.stats.data_ptr(),
+                                       self.ws_dpca.data_ptr(), self.ws_dpca_bytes, st))
+
+    def leg_allreduce(self):
+        if self.group is not None:
+            import torch.distributed as dist
+            dist.all_reduce(self.packed, group=self.group)
+
+    def leg_dpca_solve(self):
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        lib = L.lib()
+        L.check(lib.tac_dpca_eig(self.stats.data_ptr(), self.nv, self.d, self.s.data_ptr(), self.v.data_ptr(), self.mu.data_ptr(),
+                                 self.rank.data_ptr(), self.ws_dpca.data_ptr(), self.ws_dpca_bytes, st))
+        L.check(lib.tac_dpca_select(self.s.data_ptr(), self.rank.data_ptr(), self.nv, self.d, self.dim_p, self.idx.data_ptr(),
+                                    self.cnt.data_ptr(), st))
+
+    def leg_dpca_project(self, zs):
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        L.check(L.lib().tac_dpca_project(L.ptr_array(zs), self.nv, self.B, self.d, self.v.data_ptr(), self.mu.data_ptr(),
+                                         self.idx.data_ptr(), self.cnt.data_ptr(), self._zout_ptrs, self.ws_dpca.data_ptr(),
+                                         self.ws_dpca_bytes, st))
+
+    def leg_loss_value(self):
+        torch.dot(self.sums, self.inv64, out=self.loss)
+
+    # ------------------------------------------------------------------ the step
+    def run(self, x: torch.Tensor, y: torch.Tensor, zs: List[torch.Tensor]) -> torch.Tensor:
+        """Enqueue one step; returns the (device, float64) loss scalar of the global batch.  Results:
+        ``self.loss``, ``self.grad_y``, ``self.fe_out``, ``self.z_out``, ``self.cnt`` / ``self.idx``."""
+        self._check(x, y, zs)
+        with torch.cuda.device(self.device):
+            main = torch.cuda.current_stream(self.device)
+            if self.overlap:
+                self.side.wait_stream(main)
+                with torch.cuda.stream(self.side):
+                    self.leg_loss_bwd(x, y)
+                    if self.frontend:
+                        self.leg_frontend(x)
+            self.leg_dpca_stats(zs)
+            self.leg_loss_fwd(x, y)
+            self.leg_allreduce()
+            self.leg_dpca_solve()
+            self.leg_dpca_project(zs)
+            self.leg_loss_value()
+            if self.overlap:
+                main.wait_stream(self.side)
+            else:
+                self.leg_loss_bwd(x, y)
+                if self.frontend:
+                    self.leg_frontend(x)
+        return self.loss
+
+    def algorithmic_bytes(self) -> dict:
+        """SURVEY.md 8d byte counts per leg (per rank)."""
+        r, T, B, d, nv = self.rows, self.T, self.B, self.d, self.nv
+        out = {"loss_fwd": 8 * r * T, "loss_bwd": 12 * r * T,
+               "dpca_stats": 4 * B * d * nv, "dpca_project": 8 * B * d * nv + 4 * d * self.dim_p}
+        if self.frontend:
+            Fp = self.f_pad if self.f_pad > 0 else self.fe_F
+            out["frontend"] = 4 * r * T + 8 * r * (self.fe_n_fft // 2 + 1) * Fp
+        return out

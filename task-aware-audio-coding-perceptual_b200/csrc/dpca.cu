@@ -12,6 +12,7 @@
 // TAC_GRAM_TF32X3 (tcgen05 tensor cores, see dpca_tc.cuh).
 #include "tac_common.cuh"
 #include "dpca_tc.cuh"
+#include "dpca_eig_tri.cuh"
 
 namespace tac {
 
@@ -339,7 +340,7 @@ using namespace tac;
 extern "C" size_t tac_dpca_workspace_bytes(int nv, int64_t B, int d) {
     if (nv <= 0 || d <= 0 || B <= 0) return 0;
     // eig (global-memory columns for d > 128) | projector P | tensor-core Gram scratch
-    size_t eig = (size_t)nv * d * d * sizeof(double);
+    size_t eig = d <= kTriMaxD ? dpca_eig_tri_workspace_bytes(nv, d) : (size_t)nv * d * d * sizeof(double);
     size_t proj = (size_t)nv * d * d * sizeof(float);
     size_t tc = dpca_tc_workspace_bytes(nv, B, d);
     size_t m = eig > proj ? eig : proj;
@@ -374,6 +375,21 @@ extern "C" int tac_dpca_eig(const double* stats, int nv, int d, float* s, float*
     TAC_REQUIRE(nv >= 1 && nv <= kMaxViews, "nv must be in [1, %d]", kMaxViews);
     TAC_REQUIRE(d >= 1 && d <= kMaxD, "need 1 <= d <= %d", kMaxD);
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (d <= kTriMaxD) {                       // tridiagonalisation + multisection + twisted factorisation (dpca_eig_tri.cuh)
+        const size_t need = dpca_eig_tri_workspace_bytes(nv, d);
+        if (!workspace || workspace_bytes < need)
+            return set_error(TAC_EWORKSPACE, "tac_dpca_eig with d=%d needs %zu workspace bytes", d, need);
+        TAC_ALIGNED16(workspace, "workspace");
+        const size_t tsmem = (size_t)d * d * sizeof(double);
+        static bool attr_set = false;
+        if (!attr_set) {
+            TAC_CHECK_CUDA(cudaFuncSetAttribute(dpca_eig_tri_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+            attr_set = true;
+        }
+        dpca_eig_tri_kernel<<<nv, kTriThreads, tsmem, st>>>(stats, d, s, v, mu, rank, reinterpret_cast<double*>(workspace)); TAC_LAUNCHED(1);
+        TAC_CHECK_CUDA(cudaGetLastError());
+        return TAC_OK;
+    }
     const size_t smem = eig_smem_bytes(d);
     const int use_gws = smem > 160 * 1024;
     if (use_gws) {
@@ -421,5 +437,11 @@ extern "C" int tac_var_topk(const double* stats, int d, int k, float* var, int* 
     TAC_REQUIRE(d >= 1 && d <= kMaxD * 4 && k >= 1 && k <= d, "need 1 <= k <= d <= %d", kMaxD * 4);
     var_topk_kernel<<<1, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(stats, d, k, var, top_idx); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
+    return TAC_OK;
+}
+
+// Development aid (not part of the documented ABI): clock64 stamps of the last tac_dpca_eig (d <= 128), view 0.
+extern "C" TAC_API int tac_debug_eig_profile(long long* out8) {
+    TAC_CHECK_CUDA(cudaMemcpyFromSymbol(out8, tac::g_tri_prof, 8 * sizeof(long long)));
     return TAC_OK;
 }

@@ -1,0 +1,452 @@
+// Symmetric eigen-solve of the DPCA covariance for d <= 128, one CTA (1024 threads) per view, float64.
+//
+//   C = S - s s^T / n  (shared memory, 128 KiB)
+//   1. Householder tridiagonalisation  Q^T C Q = T      (reflectors parked in the caller's workspace)
+//   2. split T where |b_i| <= 4 eps |T| into unreduced blocks
+//   3. eigenvalues by multisection on the Sturm count of each block (8 threads per eigenvalue, product
+//      form of the leading-minor recurrence, rescaled every 8 steps -> no division on the critical path)
+//   4. eigenvectors of T by the twisted factorisation (Fernando / Parlett-Dhillon "getvec"): forward and
+//      backward pivots of T - lambda I, twist at argmin |gamma_k|; one thread per eigenvector;
+//      Gram-Schmidt only inside clusters closer than 1e-9 |T| (rare)
+//   5. back-transformation V = Q Z, descending order, float32 outputs in data_pca's layout
+//
+// Replaces the thin SVD of data_pca (pkl_file_model_updated.py:37-42) on the all-reduced statistics:
+// singular values are sqrt(eig(Zc^T Zc)); measured 6.7 ms -> ~0.15 ms against the one-sided Jacobi
+// kernel it supersedes (which stays for 128 < d <= 256).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace tac {
+
+constexpr int kTriThreads = 1024;
+constexpr int kTriMaxD = 128;
+constexpr int kTriParts = kTriThreads / kTriMaxD;          // 8 row-groups in the mat-vec / update mapping
+
+struct TriShared {
+    double a[kTriMaxD];            // diagonal of T
+    double b[kTriMaxD];            // sub-diagonal of T (b[i] couples i and i+1)
+    double b2[kTriMaxD];
+    double vec_v[kTriMaxD];
+    double vec_p[kTriMaxD];
+    double part[kTriParts][kTriMaxD];
+    double lam[kTriMaxD];
+    double red[40];
+    double scal[8];                // alpha, beta, K, fro, tn
+    int blk_s[kTriMaxD], blk_e[kTriMaxD];
+    double beta[kTriMaxD];         // Householder scalars (0: identity)
+    int ord[kTriMaxD], inv[kTriMaxD];
+    int flag;
+};
+
+__device__ __forceinline__ double tri_warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// 1/sqrt(a) and 1/a from the ~20-bit hardware seeds + two Newton steps (float64-accurate to a few ulp)
+__device__ __forceinline__ double tri_rsqrt(double a) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
+    const double h = 0.5 * a;
+#pragma unroll
+    for (int it = 0; it < 2; ++it) { const double e = fma(-h * y, y, 0.5); y = fma(y, e, y); }
+    return y;
+}
+__device__ __forceinline__ double tri_rcp(double a) {
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
+#pragma unroll
+    for (int it = 0; it < 3; ++it) { const double e = fma(-a, y, 1.0); y = fma(y, e, y); }
+    return y;
+}
+
+// number of eigenvalues of T[s..e] smaller than x
+__device__ __forceinline__ int tri_sturm(const double* __restrict__ a, const double* __restrict__ b2, int s, int e, double x) {
+    // p_i = (a_i - x) p_{i-1} - b_{i-1}^2 p_{i-2}; the count is the number of sign changes of p_0 = 1, p_1, ...
+    // (an exact zero carries the sign bit it was rounded with; the total over a zero crossing is unchanged)
+    double pm = 1.0, p = a[s] - x;
+    int cnt = __double2hiint(p) < 0 ? 1 : 0;
+    int i = s + 1;
+    while (i <= e) {
+        // operands of the next 8 steps first (independent of the recurrence), then the dependent chain
+        double av[8], bv[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int ii = min(i + u, e);
+            av[u] = a[ii] - x; bv[u] = b2[ii - 1];
+        }
+        const int nst = min(8, e - i + 1);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            if (u < nst) {
+                const double pn = fma(av[u], p, -bv[u] * pm);
+                cnt += (unsigned)(__double2hiint(pn) ^ __double2hiint(p)) >> 31;
+                pm = p; p = pn;
+            }
+        }
+        i += nst;
+        // rescale: keep max(|p|, |pm|) near 1 (exponent arithmetic only)
+        const int hp = __double2hiint(p) & 0x7ff00000, hm = __double2hiint(pm) & 0x7ff00000;
+        const int he = max(hp, hm);
+        if (he != 0) {
+            int se = 0x3ff00000 - he;                                   // biased exponent of 2^-ex, before the bias is re-added
+            se = max(-(1000 << 20), min(1000 << 20, se));
+            const double sc = __hiloint2double(se + 0x3ff00000, 0);
+            p *= sc; pm *= sc;
+        }
+    }
+    return cnt;
+}
+
+// phase time stamps (clock64) of view 0, read back by tools through tac_debug_eig_profile()
+__device__ long long g_tri_prof[8];
+#define TRI_STAMP(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) g_tri_prof[i] = clock64(); } while (0)
+
+__global__ void __launch_bounds__(kTriThreads, 1)
+dpca_eig_tri_kernel(const double* __restrict__ stats, int d, float* __restrict__ s_out, float* __restrict__ v_out,
+                    float* __restrict__ mu_out, int* __restrict__ rank_out, double* __restrict__ gws) {
+    extern __shared__ __align__(16) unsigned char tri_smem_raw[];
+    double* A = reinterpret_cast<double*>(tri_smem_raw);            // [d][d]; later Z[row][col]
+    __shared__ TriShared sh;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int view = blockIdx.x;
+    const size_t stride = 1 + d + (size_t)d * d;
+    const double* st = stats + view * stride;
+    double* refl = gws + (size_t)view * 3 * d * d;                  // [k][i]   Householder vectors
+    double* Lp = refl + (size_t)d * d;                              // [i][slot] forward multipliers b_i / D+_i
+    double* Um = Lp + (size_t)d * d;                                // [i][slot] backward multipliers b_{i-1} / D-_i
+    const double n = st[0];
+    const double inv_n = n > 0.0 ? 1.0 / n : 0.0;
+    const double eps = 2.220446049250313e-16;
+
+    TRI_STAMP(0);
+    // ---- C (symmetric, full storage) and its Frobenius norm; the solve runs on C / |C|_F
+    double fro_part = 0.0;
+    for (int e = tid; e < d * d; e += kTriThreads) {
+        const int i = e / d, j = e % d;
+        const int lo = i < j ? i : j, hi = i < j ? j : i;           // read one triangle: exactly symmetric
+        const double c = st[1 + d + (size_t)lo * d + hi] - st[1 + lo] * st[1 + hi] * inv_n;
+        A[e] = c;
+        fro_part = fma(c, c, fro_part);
+    }
+    for (int i = tid; i < d; i += kTriThreads) mu_out[(size_t)view * d + i] = (float)(st[1 + i] * inv_n);
+    fro_part = tri_warp_sum(fro_part);
+    if (lane == 0) sh.red[warp] = fro_part;
+    __syncthreads();
+    {
+        double f = 0.0;
+#pragma unroll
+        for (int w = 0; w < kTriThreads / 32; ++w) f += sh.red[w];
+        const double fro = sqrt(f);
+        const double isc = fro > 0.0 ? 1.0 / fro : 0.0;
+        for (int e = tid; e < d * d; e += kTriThreads) A[e] *= isc;
+        if (tid == 0) sh.scal[3] = fro;
+    }
+    __syncthreads();
+
+    TRI_STAMP(1);
+    // ---- 1. Householder tridiagonalisation (column k: x = A[k+1.., k]); three barriers per column
+    const int ci = tid % kTriMaxD;                 // row / column index owned in the 128 x 8 mapping
+    const int cp = tid / kTriMaxD;                 // part 0..7
+    for (int k = 0; k + 2 < d; ++k) {
+        const int m = d - k - 1;
+        const double* x = A + (size_t)k * d + (k + 1);              // x_i, i < m (row k == column k by symmetry)
+        // P1: partial q = A22 x over j = cp, cp+8, ...; sigma = x.x by warps 0..3
+        if (ci < m) {
+            const double* col0 = A + (size_t)(k + 1) * d + (k + 1) + ci;   // A22[ci][j] = A[(k+1+j)*d + k+1+ci]
+            double a0 = 0.0, a1 = 0.0;
+            int j = cp;
+            for (; j + kTriParts < m; j += 2 * kTriParts) {
+                a0 = fma(col0[(size_t)j * d], x[j], a0);
+                a1 = fma(col0[(size_t)(j + kTriParts) * d], x[j + kTriParts], a1);
+            }
+            if (j < m) a0 = fma(col0[(size_t)j * d], x[j], a0);
+            sh.part[cp][ci] = a0 + a1;
+        }
+        if (warp < 4) {
+            const double xv = tid < m ? x[tid] : 0.0;
+            const double s2 = tri_warp_sum(xv * xv);
+            if (lane == 0) sh.red[warp] = s2;
+        }
+        __syncthreads();
+        // P2 (threads < 128): scalars (redundantly, fast reciprocal square root), v, p, partial p.v
+        if (warp < 4) {
+            const double sigma = (sh.red[0] + sh.red[1]) + (sh.red[2] + sh.red[3]);
+            const double x0 = x[0];
+            const double tail = sigma - x0 * x0;
+            double alpha = 0.0, beta = 0.0;
+            if (sigma > 1e-280 && tail > 1e-30 * sigma) {           // otherwise the column is already tridiagonal: H = I
+                const double rs = tri_rsqrt(sigma);
+                double nrm = sigma * rs;
+                nrm = fma(fma(-nrm, nrm, sigma), 0.5 * rs, nrm);
+                alpha = x0 >= 0.0 ? -nrm : nrm;
+                beta = tri_rcp(fma(-alpha, x0, sigma));             // 2 / v.v
+            }
+            double vi = 0.0, pi = 0.0;
+            if (tid < m) {
+                double qi = 0.0;
+#pragma unroll
+                for (int p = 0; p < kTriParts; ++p) qi += sh.part[p][tid];
+                vi = x[tid] - (tid == 0 ? alpha : 0.0);
+                pi = beta * (qi - alpha * A[(size_t)(k + 1) * d + (k + 1) + tid]);
+                sh.vec_v[tid] = vi; sh.vec_p[tid] = pi;
+                refl[(size_t)k * d + tid] = beta != 0.0 ? vi : 0.0;
+            }
+            const double pv = tri_warp_sum(vi * pi);
+            if (lane == 0) sh.red[8 + warp] = pv;
+            if (tid == 0) {
+                sh.a[k] = A[(size_t)k * d + k];
+                sh.b[k] = beta != 0.0 ? alpha : x0;
+                sh.beta[k] = beta;
+            }
+        }
+        __syncthreads();
+        // P3: A22 -= v w^T + w v^T,  w = p - K v,  K = beta/2 p.v
+        const double beta = sh.beta[k];
+        if (beta != 0.0 && ci < m) {
+            const double K = 0.5 * beta * ((sh.red[8] + sh.red[9]) + (sh.red[10] + sh.red[11]));
+            const double v_i = sh.vec_v[ci];
+            const double w_i = sh.vec_p[ci] - K * v_i;
+            double* col0 = A + (size_t)(k + 1) * d + (k + 1) + ci;
+            int j = cp;
+            for (; j + kTriParts < m; j += 2 * kTriParts) {
+                const int j1 = j + kTriParts;
+                const double va = sh.vec_v[j], vb = sh.vec_v[j1];
+                const double wa = sh.vec_p[j] - K * va, wb = sh.vec_p[j1] - K * vb;
+                const double ca = col0[(size_t)j * d], cb = col0[(size_t)j1 * d];
+                // exactly symmetric in (i, j): both triangles stay bit-identical
+                col0[(size_t)j * d] = __dsub_rn(ca, __dadd_rn(__dmul_rn(v_i, wa), __dmul_rn(w_i, va)));
+                col0[(size_t)j1 * d] = __dsub_rn(cb, __dadd_rn(__dmul_rn(v_i, wb), __dmul_rn(w_i, vb)));
+            }
+            if (j < m) {
+                const double va = sh.vec_v[j];
+                const double wa = sh.vec_p[j] - K * va;
+                col0[(size_t)j * d] = __dsub_rn(col0[(size_t)j * d], __dadd_rn(__dmul_rn(v_i, wa), __dmul_rn(w_i, va)));
+            }
+        }
+        __syncthreads();
+    }
+    TRI_STAMP(2);
+    if (tid == 0) {
+        if (d >= 2) {
+            sh.a[d - 2] = A[(size_t)(d - 2) * d + (d - 2)];
+            sh.b[d - 2] = A[(size_t)(d - 2) * d + (d - 1)];
+            sh.beta[d - 2] = 0.0;
+        }
+        sh.a[d - 1] = A[(size_t)(d - 1) * d + (d - 1)];
+        sh.b[d - 1] = 0.0;
+        sh.beta[d - 1] = 0.0;
+    }
+    __syncthreads();
+    // ---- 2. scale T to unit max-norm, split into unreduced blocks
+    if (warp == 0) {
+        double tn = 0.0;
+        for (int i = lane; i < d; i += 32) tn = fmax(tn, fmax(fabs(sh.a[i]), i + 1 < d ? fabs(sh.b[i]) : 0.0));
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) tn = fmax(tn, __shfl_xor_sync(0xffffffffu, tn, o));
+        const double it = tn > 0.0 ? 1.0 / tn : 0.0;
+        for (int i = lane; i < d; i += 32) {
+            const double av = sh.a[i] * it;
+            double bv = sh.b[i] * it;
+            if (i + 1 >= d || fabs(bv) <= 4.0 * eps) bv = 0.0;      // split point after i
+            sh.a[i] = av; sh.b[i] = bv; sh.b2[i] = bv * bv;
+        }
+        __syncwarp();
+        if (lane == 0) {
+            sh.scal[5] = tn * sh.scal[3];                            // eigenvalues of C = scal[5] * eigenvalues of the scaled T
+            sh.scal[4] = tn > 0.0 ? 1.0 : 0.0;
+            int s = 0;
+            for (int i = 0; i < d; ++i) {
+                if (i == d - 1 || sh.b[i] == 0.0) {
+                    for (int j = s; j <= i; ++j) { sh.blk_s[j] = s; sh.blk_e[j] = i; }
+                    s = i + 1;
+                }
+            }
+            sh.flag = 0;
+        }
+    }
+    __syncthreads();
+    const double tn = sh.scal[4];
+
+    TRI_STAMP(3);
+    // ---- 3. eigenvalues: bisection on the Sturm count, one thread per slot (slot j = (j - s)-th smallest of block [s, e])
+    if (tid < d) {
+        const int slot = tid;
+        const int s = sh.blk_s[slot], e = sh.blk_e[slot], kk = slot - s;
+        double gl = 1e300, gu = -1e300;
+        for (int i = s; i <= e; ++i) {
+            const double r = (i > s ? fabs(sh.b[i - 1]) : 0.0) + (i < e ? fabs(sh.b[i]) : 0.0);
+            gl = fmin(gl, sh.a[i] - r); gu = fmax(gu, sh.a[i] + r);
+        }
+        double lo = gl - 4.0 * eps, hi = gu + 4.0 * eps;
+        for (int it = 0; it < 56; ++it) {
+            const double x = 0.5 * (lo + hi);
+            const int c = tri_sturm(sh.a, sh.b2, s, e, x);
+            if (c <= kk) lo = x; else hi = x;
+        }
+        sh.lam[slot] = 0.5 * (lo + hi);
+    }
+    // Z[row][slot] = 0 (the tridiagonalised matrix is no longer needed)
+    double* Z = A;
+    __syncthreads();
+    for (int e = tid; e < d * d; e += kTriThreads) Z[e] = 0.0;
+    __syncthreads();
+
+    TRI_STAMP(4);
+    // ---- 4. eigenvectors of T: twisted factorisation, one thread per slot
+    if (tid < d) {
+        const int slot = tid;
+        const int s = sh.blk_s[slot], e = sh.blk_e[slot];
+        const double l = sh.lam[slot];
+        const double pivmin = 1e-290;
+        // backward pivots D-_i (multipliers Um[i] = b_{i-1} / D-_i); the pivots themselves are parked in Lp
+        double dm = sh.a[e] - l;
+        for (int i = e; i > s; --i) {
+            if (fabs(dm) < pivmin) dm = -pivmin;
+            const double r = tri_rcp(dm);
+            Lp[(size_t)i * d + slot] = dm;
+            Um[(size_t)i * d + slot] = sh.b[i - 1] * r;
+            dm = fma(-sh.b2[i - 1], r, sh.a[i - 1] - l);
+        }
+        // dm == D-_s.  forward sweep: D+_i, gamma_i = D+_i + D-_i - (a_i - l)
+        double dp = sh.a[s] - l;
+        double best = fabs(dp + dm - (sh.a[s] - l));
+        int r = s;
+        for (int i = s; i < e; ++i) {
+            if (fabs(dp) < pivmin) dp = -pivmin;
+            const double dmn = Lp[(size_t)(i + 1) * d + slot];       // D-_{i+1}
+            const double rc = tri_rcp(dp);
+            Lp[(size_t)i * d + slot] = sh.b[i] * rc;                 // forward multiplier (overwrites the parked pivot of row i)
+            dp = fma(-sh.b2[i], rc, sh.a[i + 1] - l);
+            const double g = fabs(dp + dmn - (sh.a[i + 1] - l));
+            if (g < best) { best = g; r = i + 1; }
+        }
+        // z_r = 1; downwards with the forward multipliers, upwards with the backward ones
+        double zz = 1.0, nrm = 1.0;
+        Z[(size_t)r * d + slot] = 1.0;
+        for (int i = r - 1; i >= s; --i) {
+            zz = -Lp[(size_t)i * d + slot] * zz;
+            Z[(size_t)i * d + slot] = zz;
+            nrm = fma(zz, zz, nrm);
+        }
+        zz = 1.0;
+        for (int i = r + 1; i <= e; ++i) {
+            zz = -Um[(size_t)i * d + slot] * zz;
+            Z[(size_t)i * d + slot] = zz;
+            nrm = fma(zz, zz, nrm);
+        }
+        const double inv = tri_rsqrt(nrm);
+        for (int i = s; i <= e; ++i) Z[(size_t)i * d + slot] *= inv;
+        // cluster detection (ascending inside a block)
+        if (slot > s && l - sh.lam[slot - 1] <= 1e-9 * tn) sh.flag = 1;
+    }
+    __syncthreads();
+    if (sh.flag) {                                                   // rare: Gram-Schmidt inside clusters, warp 0, sequential
+        if (warp == 0) {
+            for (int k = 1; k < d; ++k) {
+                const int s = sh.blk_s[k];
+                bool changed = false;
+                for (int j = k - 1; j >= s && sh.lam[k] - sh.lam[j] <= 1e-9 * tn * (double)(k - j); --j) {
+                    double dot = 0.0;
+                    for (int i = lane; i < d; i += 32) dot = fma(Z[(size_t)i * d + j], Z[(size_t)i * d + k], dot);
+                    dot = tri_warp_sum(dot);
+                    for (int i = lane; i < d; i += 32) Z[(size_t)i * d + k] -= dot * Z[(size_t)i * d + j];
+                    changed = true;
+                    __syncwarp();
+                }
+                if (changed) {
+                    double nn = 0.0;
+                    for (int i = lane; i < d; i += 32) nn = fma(Z[(size_t)i * d + k], Z[(size_t)i * d + k], nn);
+                    nn = sqrt(tri_warp_sum(nn));
+                    const double sc = nn > 1e-8 ? 1.0 / nn : 0.0;
+                    for (int i = lane; i < d; i += 32) Z[(size_t)i * d + k] *= sc;
+                    __syncwarp();
+                }
+            }
+        }
+        __syncthreads();
+    }
+
+    TRI_STAMP(5);
+    // ---- 5. back-transformation  Z <- H_0 H_1 ... H_{d-3} Z  (reverse order; reflector k+... double-buffered in vec_v / vec_p)
+    {
+        int kcur = d - 3;
+        while (kcur >= 0 && sh.beta[kcur] == 0.0) --kcur;
+        int buf = 0;
+        if (kcur >= 0 && tid < d - kcur - 1) sh.vec_v[tid] = refl[(size_t)kcur * d + tid];
+        __syncthreads();
+        while (kcur >= 0) {
+            const int k = kcur, m = d - k - 1;
+            const double beta = sh.beta[k];
+            const double* vv = buf ? sh.vec_p : sh.vec_v;
+            double* vnext = buf ? sh.vec_v : sh.vec_p;
+            int knext = k - 1;
+            while (knext >= 0 && sh.beta[knext] == 0.0) --knext;
+            double* zc = Z + (size_t)(k + 1) * d + ci;
+            if (ci < d) {
+                double a0 = 0.0, a1 = 0.0;
+                int i = cp;
+                for (; i + kTriParts < m; i += 2 * kTriParts) {
+                    a0 = fma(vv[i], zc[(size_t)i * d], a0);
+                    a1 = fma(vv[i + kTriParts], zc[(size_t)(i + kTriParts) * d], a1);
+                }
+                if (i < m) a0 = fma(vv[i], zc[(size_t)i * d], a0);
+                sh.part[cp][ci] = a0 + a1;
+            }
+            if (knext >= 0 && tid < d - knext - 1) vnext[tid] = refl[(size_t)knext * d + tid];   // prefetch the next reflector
+            __syncthreads();
+            if (ci < d) {
+                double t = 0.0;
+#pragma unroll
+                for (int p = 0; p < kTriParts; ++p) t += sh.part[p][ci];
+                t *= beta;
+                int i = cp;
+                for (; i + kTriParts < m; i += 2 * kTriParts) {
+                    const double z0 = zc[(size_t)i * d], z1 = zc[(size_t)(i + kTriParts) * d];
+                    zc[(size_t)i * d] = fma(-vv[i], t, z0);
+                    zc[(size_t)(i + kTriParts) * d] = fma(-vv[i + kTriParts], t, z1);
+                }
+                if (i < m) zc[(size_t)i * d] = fma(-vv[i], t, zc[(size_t)i * d]);
+            }
+            __syncthreads();
+            kcur = knext; buf ^= 1;
+        }
+    }
+
+    TRI_STAMP(6);
+    // ---- outputs: descending order by counting, s = sqrt(lambda), null directions -> zero columns
+    const double fro = sh.scal[3];
+    const double null_thr = 1e-14 * fro;
+    if (tid < d) sh.lam[tid] *= sh.scal[5];
+    __syncthreads();
+    if (tid < d) {
+        const double lj = sh.lam[tid];
+        int rk = 0;
+        for (int i = 0; i < d; ++i) { const double li = sh.lam[i]; rk += (li > lj) || (li == lj && i < tid); }
+        sh.ord[tid] = rk;
+        sh.inv[rk] = tid;
+    }
+    __syncthreads();
+    const int r_eff = (int)(n < (double)d ? n : (double)d);          // torch.svd(some=True): min(B, d) values
+    float* so = s_out + (size_t)view * d;
+    float* vo = v_out + (size_t)view * d * d;
+    if (tid < d) {
+        const int rk = sh.ord[tid];
+        const double l = sh.lam[tid];
+        so[rk] = (rk < r_eff && l > 0.0) ? (float)sqrt(l) : 0.0f;
+    }
+    for (int e = tid; e < d * d; e += kTriThreads) {
+        const int row = e / d, rk = e % d;                           // coalesced stores: consecutive threads -> consecutive ranks
+        // inverse permutation: column whose rank is rk
+        const int col = sh.inv[rk];
+        vo[e] = (float)(sh.lam[col] > null_thr ? Z[(size_t)row * d + col] : 0.0);
+    }
+    if (tid == 0) rank_out[view] = r_eff;
+    TRI_STAMP(7);
+}
+
+inline size_t dpca_eig_tri_workspace_bytes(int nv, int d) { return (size_t)nv * 3 * d * d * sizeof(double); }
+
+}  // namespace tac

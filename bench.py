@@ -329,20 +329,20 @@ def run_native(args):
     loss_val = float(step.loss.item())
 
     # ---- attribution pass: the same K steps, eager, CUDA events around each leg on its launching stream
-    legs = ["frontend", "loss_fwd", "loss_bwd", "dpca_stats", "dpca_solve", "dpca_project"]
+    legs = ["frontend", "loss_fused", "dpca_stats", "dpca_solve", "dpca_project"]
     acc = {k: 0.0 for k in legs}
     evs = []
     for i in range(args.steps):
         x, y, zs = dsets[(args.warmup + i) % nsets]
         rec = {}
-        for name, fn in (("loss_bwd", lambda: step.leg_loss_bwd(x, y)), ("frontend", lambda: step.leg_frontend(x)),
-                         ("dpca_stats", lambda: step.leg_dpca_stats(zs)), ("loss_fwd", lambda: step.leg_loss_fwd(x, y)),
+        for name, fn in (("loss_fused", lambda: step.leg_loss_fused(x, y)), ("frontend", lambda: step.leg_frontend(x)),
+                         ("dpca_stats", lambda: step.leg_dpca_stats(zs)),
                          ("dpca_solve", step.leg_dpca_solve), ("dpca_project", lambda: step.leg_dpca_project(zs))):
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record(); fn(); b.record()
             rec[name] = (a, b)
-            if name == "loss_fwd":
-                step.leg_allreduce()
+            if name == "dpca_stats":
+                step.leg_allreduce("all")
         evs.append(rec)
     torch.cuda.synchronize()
     for rec in evs:
@@ -350,10 +350,10 @@ def run_native(args):
             acc[k] += a.elapsed_time(b)
     leg_ms = {k: v / args.steps for k, v in acc.items()}
     peak, peak_src = load_peaks()
-    byte_legs = {"frontend": alg.get("frontend", 0), "loss_fwd": alg["loss_fwd"], "loss_bwd": alg["loss_bwd"],
+    byte_legs = {"frontend": alg.get("frontend", 0), "loss_fused": alg["loss_fused"],
                  "dpca_stats": alg["dpca_stats"], "dpca_project": alg["dpca_project"]}
-    dom = max(("frontend", "loss_fwd", "loss_bwd"), key=lambda k: leg_ms[k])
-    kern_name = {"frontend": "stft_tiled_kernel<Plan2048, MAGPHASE>", "loss_fwd": "mrstft_fwd_kernel", "loss_bwd": "mrstft_bwd_kernel"}[dom]
+    dom = max(("frontend", "loss_fused"), key=lambda k: leg_ms[k])
+    kern_name = {"frontend": "stft_tiled_kernel<Plan2048, MAGPHASE>", "loss_fused": "mrstft_bwd_kernel<true> (sums + grad_y in one pass)"}[dom]
     achieved = byte_legs[dom] / (leg_ms[dom] * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": kern_name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": byte_legs[dom],
@@ -421,7 +421,7 @@ def run_native(args):
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": f"{args.workload}: {w['desc']}", "clips_per_gpu": rows, "samples_per_clip": T,
-                           "loss_scales": list(N_FFTS), "front_end": "n_fft 2048 hop 512 centred, mag+phase [rows,2,1025,32] (unpadded)",
+                           "loss_scales": list(N_FFTS), "loss_kernel": "fused fwd+bwd (tac_mrstft_loss_fwd_bwd): reads x, y; writes grad_y", "front_end": "n_fft 2048 hop 512 centred, mag+phase [rows,2,1025,32] (unpadded)",
                            "dpca": {"views": views, "batch": batch, "d": d, "dim_p": dim_p, "gram": "tcgen05 3xTF32"},
                            "parallelism": f"dp{world} (batch shards; one packed NCCL all-reduce of loss sums + DPCA statistics)",
                            "launch": "cuda-graph replay" if graphs is not None else "eager",

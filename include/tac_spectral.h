@@ -104,6 +104,14 @@ TAC_API int tac_mrstft_loss_bwd(const float* x, const float* y, int64_t B, int64
                         const int* n_fft, const int* hop, const int* win, float eps, const float* coef,
                         float* grad_y, void* workspace, size_t workspace_bytes, tac_stream_t stream);
 
+/* Fused training-step form of K2: the per-scale sums AND grad_y in ONE pass (three transforms per frame
+ * instead of five).  Possible because d loss / d sums is known from shapes alone (coef), so the backward
+ * does not have to wait for the forward value.  Same workspace size as the forward. */
+TAC_API int tac_mrstft_loss_fwd_bwd(const float* x, const float* y, int64_t B, int64_t T, int n_scales,
+                            const int* n_fft, const int* hop, const int* win, float eps, const float* coef,
+                            double* sums, float* grad_y, void* workspace, size_t workspace_bytes,
+                            tac_stream_t stream);
+
 /* K2' -- the reference's spectral reductions in one pass over (obs, dec), both [B, 2, K, F]:
  * pkl_file_models.py:924,933-940 / pkl_file_model_updated.py:520-540.
  *   out5       float32 [5]: magnitude_loss, phase_loss, total_loss, spec_snr (dB), mean(mse)

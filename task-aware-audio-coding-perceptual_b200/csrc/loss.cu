@@ -164,10 +164,10 @@ __global__ void __launch_bounds__(256) partial_reduce_kernel(const double* __res
 constexpr int kBwdWarps = 4;
 constexpr int kBwdThreads = kBwdWarps * 32;
 
-template <class P>
+template <class P, bool WITH_SUMS>
 __device__ __forceinline__ void loss_bwd_task(const LossScale& sc, const float* __restrict__ xr, const float* __restrict__ yr,
                                               float* acc, float2* xbuf, int lane, int f_base, int f_stride, int f_end,
-                                              long long c0, float eps, float c_l1, float c_log) {
+                                              long long c0, float eps, float c_l1, float c_log, float& acc_l1, float& acc_log) {
     float zr[P::BQ], zi[P::BQ];
     float gr[P::BQ + 1], gi[P::BQ + 1];
     const float2* __restrict__ win2 = sc.t.win2;
@@ -187,11 +187,17 @@ __device__ __forceinline__ void loss_bwd_task(const LossScale& sc, const float* 
     });
     cur = yr;
     warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load);
+    float l1 = 0.0f, ll = 0.0f;
     warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
         const float m2 = fmaf(vr, vr, vi * vi);
         const float inv = m2 > 0.0f ? rsqrtf(m2) : 0.0f;
-        const float my = m2 * inv;                                    // |Y|
         const float xv = gr[slot];
+        if (WITH_SUMS) {                                              // same arithmetic as the forward-only kernel
+            const float ms = sqrtf(m2);
+            l1 += fabsf(xv - ms);
+            ll += fabsf(__log2f(fmaxf(xv, eps)) - __log2f(fmaxf(ms, eps)));
+        }
+        const float my = m2 * inv;                                    // |Y|
         float g = (my > xv) ? c_l1 : ((my < xv) ? -c_l1 : 0.0f);     // d|X - Y| / dY
         const float xc = fmaxf(xv, eps), yc = fmaxf(my, eps);
         const float sg = (yc > xc) ? c_log : ((yc < xc) ? -c_log : 0.0f);
@@ -199,6 +205,7 @@ __device__ __forceinline__ void loss_bwd_task(const LossScale& sc, const float* 
         g *= inv;                                                     // dY / dYc = Yc / |Y|
         gr[slot] = g * vr; gi[slot] = g * vi;
     });
+    if (WITH_SUMS && (f_base + (lane / P::A) * f_stride) < f_end) { acc_l1 += l1; acc_log += ll * 0.69314718055994530942f; }
     warp_fft_adj<P>(xbuf, sc.t.tw, sc.t.pt, lane,
         [&](int, int, int slot) -> float2 { return make_float2(gr[slot], gi[slot]); },
         [&](int fr, int m, float2 g) {
@@ -213,10 +220,14 @@ __device__ __forceinline__ void loss_bwd_task(const LossScale& sc, const float* 
         });
 }
 
+template <bool WITH_SUMS>
 __global__ void __launch_bounds__(kBwdThreads, 3) mrstft_bwd_kernel(const LossArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* acc = reinterpret_cast<float*>(smem_raw);
     float2* xbuf_all = reinterpret_cast<float2*>(acc + a.tile_len);
+    __shared__ double s_acc[kBwdWarps][2 * TAC_MAX_SCALES];
+    if (WITH_SUMS)
+        for (int i = threadIdx.x; i < kBwdWarps * 2 * TAC_MAX_SCALES; i += blockDim.x) (&s_acc[0][0])[i] = 0.0;
 
     const int c = blockIdx.x % a.nchunks;
     const long long row = blockIdx.x / a.nchunks;
@@ -234,6 +245,7 @@ __global__ void __launch_bounds__(kBwdThreads, 3) mrstft_bwd_kernel(const LossAr
         long long lo = (c0 + h - 1) / h, hi = (c0 + a.chunk + h - 1) / h;
         if (hi > sc.F) hi = sc.F;
         const float c_l1 = __ldg(a.coef + 2 * s), c_log = __ldg(a.coef + 2 * s + 1);
+        float l1 = 0.0f, ll = 0.0f;
         for (int r = 0; r < R; ++r) {
             // frames lo <= f < hi with f % R == r, grouped nfr at a time
             const int first = (int)lo + (int)(((r - lo % R) % R + R) % R);
@@ -242,15 +254,27 @@ __global__ void __launch_bounds__(kBwdThreads, 3) mrstft_bwd_kernel(const LossAr
             for (int t = warp; t < ntasks; t += kBwdWarps) {
                 const int f_base = first + t * nfr * R;
                 switch (sc.n) {
-                    case 2048: loss_bwd_task<Plan2048>(sc, xr, yr, acc, xbuf, lane, f_base, R, (int)hi, c0, a.eps, c_l1, c_log); break;
-                    case 1024: loss_bwd_task<Plan1024>(sc, xr, yr, acc, xbuf, lane, f_base, R, (int)hi, c0, a.eps, c_l1, c_log); break;
-                    case 512: loss_bwd_task<Plan512>(sc, xr, yr, acc, xbuf, lane, f_base, R, (int)hi, c0, a.eps, c_l1, c_log); break;
-                    case 256: loss_bwd_task<Plan256>(sc, xr, yr, acc, xbuf, lane, f_base, R, (int)hi, c0, a.eps, c_l1, c_log); break;
-                    case 128: loss_bwd_task<Plan128>(sc, xr, yr, acc, xbuf, lane, f_base, R, (int)hi, c0, a.eps, c_l1, c_log); break;
-                    default: loss_bwd_task<Plan64>(sc, xr, yr, acc, xbuf, lane, f_base, R, (int)hi, c0, a.eps, c_l1, c_log); break;
+                    case 2048: loss_bwd_task<Plan2048, WITH_SUMS>(sc, xr, yr, acc, xbuf, lane, f_base, R, (int)hi, c0, a.eps, c_l1, c_log, l1, ll); break;
+                    case 1024: loss_bwd_task<Plan1024, WITH_SUMS>(sc, xr, yr, acc, xbuf, lane, f_base, R, (int)hi, c0, a.eps, c_l1, c_log, l1, ll); break;
+                    case 512: loss_bwd_task<Plan512, WITH_SUMS>(sc, xr, yr, acc, xbuf, lane, f_base, R, (int)hi, c0, a.eps, c_l1, c_log, l1, ll); break;
+                    case 256: loss_bwd_task<Plan256, WITH_SUMS>(sc, xr, yr, acc, xbuf, lane, f_base, R, (int)hi, c0, a.eps, c_l1, c_log, l1, ll); break;
+                    case 128: loss_bwd_task<Plan128, WITH_SUMS>(sc, xr, yr, acc, xbuf, lane, f_base, R, (int)hi, c0, a.eps, c_l1, c_log, l1, ll); break;
+                    default: loss_bwd_task<Plan64, WITH_SUMS>(sc, xr, yr, acc, xbuf, lane, f_base, R, (int)hi, c0, a.eps, c_l1, c_log, l1, ll); break;
                 }
             }
             __syncthreads();
+        }
+        if (WITH_SUMS) {                                             // fixed task -> warp assignment: deterministic sums
+            l1 = warp_sum(l1); ll = warp_sum(ll);
+            if (lane == 0) { s_acc[warp][2 * s] = (double)l1; s_acc[warp][2 * s + 1] = (double)ll; }
+        }
+    }
+    if (WITH_SUMS) {
+        __syncthreads();
+        if (threadIdx.x < 2 * a.nscales) {
+            double v = 0.0;
+            for (int w = 0; w < kBwdWarps; ++w) v += s_acc[w][threadIdx.x];
+            a.partial[(long long)blockIdx.x * (2 * a.nscales) + threadIdx.x] = v;
         }
     }
     // write-out: [c0, c0 + chunk) is this CTA's, but its first (tile_len - chunk) samples also receive
@@ -460,10 +484,9 @@ extern "C" int tac_mrstft_loss_fwd(const float* x, const float* y, int64_t B, in
     return TAC_OK;
 }
 
-extern "C" int tac_mrstft_loss_bwd(const float* x, const float* y, int64_t B, int64_t T, int n_scales, const int* n_fft,
-                                   const int* hop, const int* win, float eps, const float* coef, float* grad_y,
-                                   void* workspace, size_t workspace_bytes, tac_stream_t stream) {
-    (void)workspace; (void)workspace_bytes;
+static int launch_bwd(const float* x, const float* y, int64_t B, int64_t T, int n_scales, const int* n_fft, const int* hop,
+                      const int* win, float eps, const float* coef, float* grad_y, double* sums, void* workspace,
+                      size_t workspace_bytes, tac_stream_t stream) {
     LossArgs a;
     int rc = fill_loss_args(a, x, y, B, T, n_scales, n_fft, hop, win, eps, kBwdChunk);
     if (rc) return rc;
@@ -473,12 +496,43 @@ extern "C" int tac_mrstft_loss_bwd(const float* x, const float* y, int64_t B, in
     const long long grid = B * a.nchunks;
     TAC_REQUIRE(grid < (1ll << 31), "grid too large");
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (sums) {
+        const size_t need = (size_t)grid * 2 * n_scales * sizeof(double);
+        if (!workspace || workspace_bytes < need)
+            return set_error(TAC_EWORKSPACE, "workspace needs %zu bytes, got %zu", need, workspace_bytes);
+        TAC_ALIGNED16(workspace, "workspace");
+        a.partial = reinterpret_cast<double*>(workspace);
+    }
     if (a.nchunks > 1) TAC_CHECK_CUDA(cudaMemsetAsync(grad_y, 0, (size_t)B * T * sizeof(float), st));
     const size_t smem = (size_t)a.tile_len * sizeof(float) + (size_t)kBwdWarps * kXbufFloat2 * sizeof(float2);
-    TAC_CHECK_CUDA(cudaFuncSetAttribute(mrstft_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 75 * 1024));
-    mrstft_bwd_kernel<<<(unsigned)grid, kBwdThreads, smem, st>>>(a); TAC_LAUNCHED(1);
+    static bool attr_set = false;
+    if (!attr_set) {
+        TAC_CHECK_CUDA(cudaFuncSetAttribute(mrstft_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 75 * 1024));
+        TAC_CHECK_CUDA(cudaFuncSetAttribute(mrstft_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 75 * 1024));
+        attr_set = true;
+    }
+    if (sums) {
+        mrstft_bwd_kernel<true><<<(unsigned)grid, kBwdThreads, smem, st>>>(a); TAC_LAUNCHED(1);
+        TAC_CHECK_CUDA(cudaGetLastError());
+        partial_reduce_kernel<<<2 * n_scales, 256, 0, st>>>(a.partial, grid, 2 * n_scales, sums); TAC_LAUNCHED(1);
+    } else {
+        mrstft_bwd_kernel<false><<<(unsigned)grid, kBwdThreads, smem, st>>>(a); TAC_LAUNCHED(1);
+    }
     TAC_CHECK_CUDA(cudaGetLastError());
     return TAC_OK;
+}
+
+extern "C" int tac_mrstft_loss_bwd(const float* x, const float* y, int64_t B, int64_t T, int n_scales, const int* n_fft,
+                                   const int* hop, const int* win, float eps, const float* coef, float* grad_y,
+                                   void* workspace, size_t workspace_bytes, tac_stream_t stream) {
+    return launch_bwd(x, y, B, T, n_scales, n_fft, hop, win, eps, coef, grad_y, nullptr, workspace, workspace_bytes, stream);
+}
+
+extern "C" int tac_mrstft_loss_fwd_bwd(const float* x, const float* y, int64_t B, int64_t T, int n_scales, const int* n_fft,
+                                       const int* hop, const int* win, float eps, const float* coef, double* sums,
+                                       float* grad_y, void* workspace, size_t workspace_bytes, tac_stream_t stream) {
+    TAC_REQUIRE(sums != nullptr, "null sums");
+    return launch_bwd(x, y, B, T, n_scales, n_fft, hop, win, eps, coef, grad_y, sums, workspace, workspace_bytes, stream);
 }
 
 extern "C" size_t tac_spec_losses_workspace_bytes(int64_t B) {

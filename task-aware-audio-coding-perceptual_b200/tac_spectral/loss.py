@@ -69,6 +69,41 @@ class _MRSTFTLoss(torch.autograd.Function):
         return None, grad.reshape(yshape).to(ydtype), None, None, None, None
 
 
+class _MRSTFTLossFused(torch.autograd.Function):
+    """The scalar loss with its gradient produced in the SAME pass (``tac_mrstft_loss_fwd_bwd``): since
+    d loss / d sums is a table of shape-only constants, the kernel that forms the sums already knows the
+    gradient direction; backward is one scaling by the upstream scalar."""
+
+    @staticmethod
+    def forward(ctx, x, y, n_ffts, hops, wins, eps, inv, group):
+        xr = x.contiguous().float()
+        yr = y.contiguous().float()
+        B, T = xr.shape
+        S = len(n_ffts)
+        lib = L.lib()
+        nf, hp, wn = L.int_array(n_ffts), L.int_array(hops), L.int_array(wins)
+        ws_bytes = int(lib.tac_mrstft_workspace_bytes(B, T, S, nf, hp))
+        ws = torch.empty(max(ws_bytes, 16), dtype=torch.uint8, device=xr.device)
+        sums = torch.empty(2 * S, dtype=torch.float64, device=xr.device)
+        grad = torch.empty_like(yr)
+        coef = inv.to(torch.float32)
+        with L.device_of(xr):
+            L.check(lib.tac_mrstft_loss_fwd_bwd(xr.data_ptr(), yr.data_ptr(), B, T, S, nf, hp, wn, float(eps), coef.data_ptr(),
+                                                sums.data_ptr(), grad.data_ptr(), ws.data_ptr(), ws_bytes, L.stream_of(xr)))
+        if group is not None:
+            import torch.distributed as dist
+            dist.all_reduce(sums, group=group)
+        ctx.save_for_backward(grad)
+        ctx.meta = (y.shape, y.dtype)
+        return torch.dot(sums, inv).float()
+
+    @staticmethod
+    def backward(ctx, g):
+        (grad,) = ctx.saved_tensors
+        shape, dtype = ctx.meta
+        return None, (grad * g.to(grad.dtype)).reshape(shape).to(dtype), None, None, None, None, None, None
+
+
 def mrstft_sums(x: torch.Tensor, y: torch.Tensor, n_ffts: Sequence[int], hops: Sequence[int],
                 wins: Optional[Sequence[int]] = None, eps: float = LOG_FLOOR) -> torch.Tensor:
     """Raw per-scale sums ``[2S]`` float64: ``sum|X-Y|`` and ``sum|ln max(X,eps) - ln max(Y,eps)|``."""
@@ -94,9 +129,23 @@ def mrstft_loss(x: torch.Tensor, y: torch.Tensor, n_ffts: Sequence[int] = (1024,
     discriminator's (``msstftd.py:174-175``), ``hop = n_fft/4``.  With ``group`` the means run over
     the batch of ALL ranks (one all-reduce of ``2S`` doubles)."""
     hops = [n // 4 for n in n_ffts] if hops is None else list(hops)
-    sums = mrstft_sums(x, y, n_ffts, hops, wins, eps)
     rows = x.numel() // x.shape[-1]
     counts = mrstft_counts(rows, x.shape[-1], n_ffts, hops)
+    if not return_terms and torch.is_grad_enabled() and isinstance(y, torch.Tensor) and y.requires_grad \
+            and x.shape[-1] % 2 == 0:
+        # training step: value and gradient in one fused pass
+        xr, yr = _rows(x, "x"), _rows(y, "y")
+        if xr.shape != yr.shape:
+            raise ValueError(f"Shape mismatch: x {tuple(x.shape)} vs y {tuple(y.shape)}")
+        wl = list(n_ffts) if wins is None else list(wins)
+        assert len(n_ffts) == len(hops) == len(wl)                                      # msstftd.py:177
+        w = 1
+        if group is not None:
+            import torch.distributed as dist
+            w = dist.get_world_size(group)
+        inv = torch.tensor([1.0 / (len(n_ffts) * c * w) for c in counts for _ in (0, 1)], dtype=torch.float64, device=x.device)
+        return _MRSTFTLossFused.apply(xr, yr, list(n_ffts), list(hops), wl, eps, inv, group)
+    sums = mrstft_sums(x, y, n_ffts, hops, wins, eps)
     world = 1
     if group is not None:
         import torch.distributed as dist

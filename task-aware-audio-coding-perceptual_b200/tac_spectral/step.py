@@ -116,15 +116,25 @@ class SpectralStep:
         L.check(L.lib().tac_mrstft_loss_bwd(x.data_ptr(), y.data_ptr(), self.rows, self.T, self.S, self._nf, self._hp, self._nf,
                                             self.eps, self.coef.data_ptr(), self.grad_y.data_ptr(), None, 0, st))
 
+    def leg_loss_fused(self, x, y):
+        """Sums AND gradient in one pass (``tac_mrstft_loss_fwd_bwd``): d loss / d sums is the constant ``coef``."""
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        L.check(L.lib().tac_mrstft_loss_fwd_bwd(x.data_ptr(), y.data_ptr(), self.rows, self.T, self.S, self._nf, self._hp, self._nf,
+                                                self.eps, self.coef.data_ptr(), self.sums.data_ptr(), self.grad_y.data_ptr(),
+                                                self.ws_loss.data_ptr(), self.ws_loss_bytes, st))
+
     def leg_dpca_stats(self, zs):
         st = torch.cuda.current_stream(self.device).cuda_stream
         L.check(L.lib().tac_dpca_stats(L.ptr_array(zs), self.nv, self.B, self.d, self.algo, self.stats.data_ptr(),
                                        self.ws_dpca.data_ptr(), self.ws_dpca_bytes, st))
 
-    def leg_allreduce(self):
+    def leg_allreduce(self, what="all"):
+        """The step's exchange: the packed float64 buffer [loss sums | DPCA statistics].  It is reduced in two
+        slices so that the eigen-solve (needs the statistics only) overlaps the loss kernel."""
         if self.group is not None:
             import torch.distributed as dist
-            dist.all_reduce(self.packed, group=self.group)
+            buf = {"all": self.packed, "stats": self.packed[2 * self.S:], "sums": self.sums}[what]
+            dist.all_reduce(buf, group=self.group)
 
     def leg_dpca_solve(self):
         st = torch.cuda.current_stream(self.device).cuda_stream
@@ -153,27 +163,31 @@ class SpectralStep:
             if self.overlap:
                 self.side.wait_stream(main)
                 with torch.cuda.stream(self.side):
-                    self.leg_loss_bwd(x, y)
-                    if self.frontend:
-                        self.leg_frontend(x)
-            self.leg_dpca_stats(zs)
-            self.leg_loss_fwd(x, y)
-            self.leg_allreduce()
-            self.leg_dpca_solve()
-            self.leg_dpca_project(zs)
-            self.leg_loss_value()
-            if self.overlap:
+                    self._spectral_chain(x, y)
+                self._dpca_chain(zs)
                 main.wait_stream(self.side)
             else:
-                self.leg_loss_bwd(x, y)
-                if self.frontend:
-                    self.leg_frontend(x)
+                self._dpca_chain(zs)
+                self._spectral_chain(x, y)
         return self.loss
+
+    def _spectral_chain(self, x, y):
+        self.leg_loss_fused(x, y)
+        if self.frontend:
+            self.leg_frontend(x)
+        self.leg_allreduce("sums")
+        self.leg_loss_value()
+
+    def _dpca_chain(self, zs):
+        self.leg_dpca_stats(zs)
+        self.leg_allreduce("stats")
+        self.leg_dpca_solve()
+        self.leg_dpca_project(zs)
 
     def algorithmic_bytes(self) -> dict:
         """SURVEY.md 8d byte counts per leg (per rank)."""
         r, T, B, d, nv = self.rows, self.T, self.B, self.d, self.nv
-        out = {"loss_fwd": 8 * r * T, "loss_bwd": 12 * r * T,
+        out = {"loss_fwd": 8 * r * T, "loss_bwd": 12 * r * T, "loss_fused": 12 * r * T,
                "dpca_stats": 4 * B * d * nv, "dpca_project": 8 * B * d * nv + 4 * d * self.dim_p}
         if self.frontend:
             Fp = self.f_pad if self.f_pad > 0 else self.fe_F

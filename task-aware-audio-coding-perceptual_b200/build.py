@@ -31,14 +31,20 @@ def needs_build():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, extra=None, out=None):
+    """extra: additional nvcc flags (experiments, e.g. ["-DTAC_BWD_OCC=2"]); out: alternative .so path."""
+    global OUT
+    if out:
+        OUT = out
+        force = True
     if not force and not needs_build():
         return OUT
     objs = []
     procs = []
-    flags = [f for f in NVCC_FLAGS if not f.startswith("--use_fast_math")]
+    flags = [f for f in NVCC_FLAGS if not f.startswith("--use_fast_math")] + list(extra or [])
+    tag = str(abs(hash(tuple(extra or [])))) if extra else ""
     for src in SOURCES:
-        obj = os.path.join("/tmp", "tac_" + src.replace(".cu", ".o"))
+        obj = os.path.join("/tmp", "tac_" + tag + src.replace(".cu", ".o"))
         cmd = [_nvcc()] + flags + (["-Xptxas", "-v"] if verbose else []) + ["-c", os.path.join(CSRC, src), "-o", obj]
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
         objs.append(obj)
@@ -56,4 +62,6 @@ def build(force=False, verbose=False):
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    extra = [a for a in sys.argv[1:] if a.startswith("-D")]
+    out = next((a.split("=", 1)[1] for a in sys.argv[1:] if a.startswith("--out=")), None)
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, extra=extra, out=out))

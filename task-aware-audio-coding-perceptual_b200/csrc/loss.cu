@@ -161,6 +161,9 @@ __global__ void __launch_bounds__(256) partial_reduce_kernel(const double* __res
 }
 
 // ------------------------------------------------------------------------------------------ backward
+#ifndef TAC_BWD_OCC
+#define TAC_BWD_OCC 3
+#endif
 constexpr int kBwdWarps = 4;
 constexpr int kBwdThreads = kBwdWarps * 32;
 
@@ -221,7 +224,7 @@ __device__ __forceinline__ void loss_bwd_task(const LossScale& sc, const float* 
 }
 
 template <bool WITH_SUMS>
-__global__ void __launch_bounds__(kBwdThreads, 3) mrstft_bwd_kernel(const LossArgs a) {
+__global__ void __launch_bounds__(kBwdThreads, TAC_BWD_OCC) mrstft_bwd_kernel(const LossArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* acc = reinterpret_cast<float*>(smem_raw);
     float2* xbuf_all = reinterpret_cast<float2*>(acc + a.tile_len);

@@ -13,7 +13,8 @@ from typing import Sequence
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libtac_spectral.so")
+# TAC_SPECTRAL_LIB: developer override used to A/B kernel variants built with build.py --out=...
+LIB_PATH = os.environ.get("TAC_SPECTRAL_LIB") or os.path.join(_HERE, "libtac_spectral.so")
 
 # name -> (restype, argtypes): every symbol of include/tac_spectral.h
 _I, _I64, _SZ, _VP, _F = C.c_int, C.c_int64, C.c_size_t, C.c_void_p, C.c_float

@@ -2,6 +2,7 @@
 import csv, re, subprocess, sys
 rep, cubin, kern = sys.argv[1:4]
 top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
+dem = sys.argv[5] if len(sys.argv) > 5 else kern          # substring of the demangled name in the ncu report
 dis = subprocess.run(["nvdisasm", "-g", "-c", cubin], capture_output=True, text=True).stdout.splitlines()
 # collect per-instruction line numbers of the kernel in order
 lines, cur, infn = [], None, False
@@ -20,8 +21,7 @@ for r in rows:
     if r and r[0] == "Kernel Name": curk = r[1]; blocks[curk] = []; continue
     if curk is not None: blocks[curk].append(r)
 for k, rs in blocks.items():
-    if kern not in k.replace("::", ""): 
-        if kern not in k: continue
+    if dem not in k: continue
     hdr = rs[0]; si = hdr.index("# Samples"); ii = hdr.index("Instructions Executed")
     ins = rs[1:]
     print(k[:80], len(ins), "sass instrs; disasm has", len(lines))

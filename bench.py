@@ -245,6 +245,7 @@ def run_native(args):
     group = None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/nccl_debug.%h.%p.log")   # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
         group = dist.group.WORLD
     lib = L.lib()
@@ -461,8 +462,21 @@ def run_native(args):
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
                 "launches_per_step": launches_per_step, "clocks": clk.summary(), "loss": loss_val}
         print(json.dumps(line), flush=True)
+    sys.stdout.flush()
     if world > 1:
-        dist.destroy_process_group()
+        # CUDA graphs that captured NCCL kernels must go before the communicator; never let teardown hang the run
+        graphs = g_e2e = None
+        torch.cuda.synchronize()
+        killer = threading.Timer(20.0, lambda: os._exit(0))
+        killer.daemon = True
+        killer.start()
+        try:
+            dist.barrier(device_ids=[local])
+            dist.destroy_process_group()
+        except Exception:
+            pass
+        killer.cancel()
+        os._exit(0)
 
 
 def main():

@@ -88,7 +88,10 @@ class SpectralStep:
                 L.check(lib.tac_prepare_fft(n, n, 1))
             if self.frontend:
                 L.check(lib.tac_prepare_fft(self.fe_n_fft, self.fe_n_fft, 0))
-            self.side = torch.cuda.Stream(device=dev) if self.overlap else None
+            # the DPCA chain is a string of small, latency-bound kernels: it gets a HIGH-PRIORITY stream so that its CTAs
+            # are placed ahead of the thousands of pending loss-kernel CTAs whenever an SM slot frees up
+            self.side = torch.cuda.Stream(device=dev, priority=-1) if self.overlap else None
+            self._ev_stats = torch.cuda.Event()
 
     # ------------------------------------------------------------------ individual legs (current stream)
     def _check(self, x, y, zs):
@@ -156,15 +159,23 @@ class SpectralStep:
     # ------------------------------------------------------------------ the step
     def run(self, x: torch.Tensor, y: torch.Tensor, zs: List[torch.Tensor]) -> torch.Tensor:
         """Enqueue one step; returns the (device, float64) loss scalar of the global batch.  Results:
-        ``self.loss``, ``self.grad_y``, ``self.fe_out``, ``self.z_out``, ``self.cnt`` / ``self.idx``."""
+        ``self.loss``, ``self.grad_y``, ``self.fe_out``, ``self.z_out``, ``self.cnt`` / ``self.idx``.
+
+        Schedule: statistics (+ all-reduce) run first on an otherwise idle GPU; then the eigen-solve chain
+        (high-priority stream, 1 CTA per view) runs NEXT TO the loss / front-end kernels that fill the other SMs."""
         self._check(x, y, zs)
         with torch.cuda.device(self.device):
             main = torch.cuda.current_stream(self.device)
             if self.overlap:
                 self.side.wait_stream(main)
                 with torch.cuda.stream(self.side):
-                    self._spectral_chain(x, y)
-                self._dpca_chain(zs)
+                    self.leg_dpca_stats(zs)
+                    self.leg_allreduce("stats")
+                    self._ev_stats.record(self.side)
+                    self.leg_dpca_solve()
+                    self.leg_dpca_project(zs)
+                main.wait_event(self._ev_stats)          # do not flood the SMs before the statistics / collective have run
+                self._spectral_chain(x, y)
                 main.wait_stream(self.side)
             else:
                 self._dpca_chain(zs)

@@ -25,6 +25,7 @@ import torch
 
 from . import _lib as L
 from .loss import LOG_FLOOR
+from .plan import StepPlan
 from .stft import num_frames
 
 
@@ -51,15 +52,12 @@ class SpectralStep:
         dev = self.device
         S, nv, d = self.S, self.nv, self.d
         self._nf, self._hp = L.int_array(self.n_ffts), L.int_array(self.hops)
-        # ---- packed all-reduce payload: [2S loss sums | nv * (1 + d + d*d) DPCA statistics], float64
-        self.stat_stride = 1 + d + d * d
-        self.packed = torch.zeros(2 * S + nv * self.stat_stride, dtype=torch.float64, device=dev)
-        self.sums = self.packed[:2 * S]
-        self.stats = self.packed[2 * S:].view(nv, self.stat_stride)
-        counts = [self.rows * (n // 2 + 1) * num_frames(T, n, h, False) for n, h in zip(self.n_ffts, self.hops)]
-        if min(counts) <= 0:
-            raise ValueError(f"signal of {T} samples is shorter than the largest n_fft")
-        inv = [1.0 / (S * c * self.world) for c in counts for _ in (0, 1)]
+        # ---- packed all-reduce payload: [2S loss sums | nv * (1 + d + d*d) DPCA statistics], float64 (plan.py)
+        self.plan = StepPlan(self.rows, self.T, self.n_ffts, self.hops, nv, d, self.world)
+        self.stat_stride = self.plan.stat_stride
+        self.packed = torch.zeros(self.plan.packed_len, dtype=torch.float64, device=dev)
+        self.sums, self.stats = self.plan.views(self.packed)
+        inv = self.plan.inv_counts()
         self.inv64 = torch.tensor(inv, dtype=torch.float64, device=dev)        # loss = dot(sums, inv64)
         self.coef = torch.tensor(inv, dtype=torch.float32, device=dev)         # d loss / d sums (constant)
         self.loss = torch.zeros((), dtype=torch.float64, device=dev)
@@ -135,9 +133,7 @@ class SpectralStep:
         """The step's exchange: the packed float64 buffer [loss sums | DPCA statistics].  It is reduced in two
         slices so that the eigen-solve (needs the statistics only) overlaps the loss kernel."""
         if self.group is not None:
-            import torch.distributed as dist
-            buf = {"all": self.packed, "stats": self.packed[2 * self.S:], "sums": self.sums}[what]
-            dist.all_reduce(buf, group=self.group)
+            self.plan.allreduce(self.packed, self.group, what)
 
     def leg_dpca_solve(self):
         st = torch.cuda.current_stream(self.device).cuda_stream

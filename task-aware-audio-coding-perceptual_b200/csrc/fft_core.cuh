@@ -17,6 +17,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <type_traits>
 
 namespace tac {
 
@@ -176,6 +177,27 @@ __device__ __forceinline__ void warp_fft_fwd(float (&zr)[P::BQ], float (&zi)[P::
     Dif<BQ>::run(zr, zi);
 }
 
+// Compile-time loop: f(std::integral_constant<int, I>) for I in [0, N).
+template <int I, int N, class F>
+__device__ __forceinline__ void static_for(F&& f) {
+    if constexpr (I < N) {
+        f(std::integral_constant<int, I>{});
+        static_for<I + 1, N>(f);
+    }
+}
+
+// (cos, sin)(2 pi (k1 + A j) / n) from the per-lane base (cos, sin)(2 pi k1 / n) and the compile-time rotation
+// by 2 pi j / (2 BQ)  (n = 2 A BQ): four FP instructions instead of a dependent table load per bin pair.
+template <int BQ, int J>
+__device__ __forceinline__ float2 post_twiddle(const float2 base) {
+    if constexpr (J == 0) {
+        return base;
+    } else {
+        constexpr float cj = (float)cx_cos2pi(J, 2 * BQ), sj = (float)cx_sin2pi(J, 2 * BQ);
+        return make_float2(fmaf(base.x, cj, -base.y * sj), fmaf(base.y, cj, base.x * sj));
+    }
+}
+
 // Post-process pairs (k, M-k) of the packed transform into the one-sided real spectrum.
 // emit(fr, k, re, im, slot) is called exactly once for every k in [0, M] of every frame of the task;
 // slot is a compile-time-resolvable index in [0, BQ] (2j, 2j+1 for pair j; BQ for the k = M/2 bin of
@@ -186,8 +208,9 @@ __device__ __forceinline__ void warp_fft_post(const float (&zr)[P::BQ], const fl
     constexpr int A = P::A, BQ = P::BQ, M = P::M;
     const int k1 = lane % A, fr = lane / A;
     const int plane = fr * A + ((A - k1) % A);
-#pragma unroll
-    for (int j = 0; j < BQ / 2; ++j) {
+    const float2 base = ldg2(pt + k1);                      // W_n^k1; W_n^(k1 + A j) = base * W_(2 BQ)^j (compile-time)
+    static_for<0, BQ / 2>([&](auto jc) {
+        constexpr int j = decltype(jc)::value;
         const float mr = zr[brev(j, BQ)], mi = zi[brev(j, BQ)];
         float pr = __shfl_sync(0xffffffffu, zr[brev(BQ - 1 - j, BQ)], plane);
         float pi = __shfl_sync(0xffffffffu, zi[brev(BQ - 1 - j, BQ)], plane);
@@ -195,12 +218,12 @@ __device__ __forceinline__ void warp_fft_post(const float (&zr)[P::BQ], const fl
         const float sr = mr + pr, si = mi - pi;             // Z[k] + conj(Z[M-k])
         const float dr = mr - pr, di = mi + pi;             // Z[k] - conj(Z[M-k])
         const int k = k1 + A * j;
-        const float2 cs = ldg2(pt + k);
+        const float2 cs = post_twiddle<BQ, j>(base);
         const float tr = fmaf(cs.x, di, -cs.y * dr);        // T = -j W_n^k (Z[k] - conj(Z[M-k]))
         const float ti = -fmaf(cs.x, dr, cs.y * di);
         emit(fr, k, sr + tr, si + ti, 2 * j);
         emit(fr, M - k, sr - tr, ti - si, 2 * j + 1);
-    }
+    });
     if (k1 == 0) emit(fr, M / 2, 2.0f * zr[brev(BQ / 2, BQ)], -2.0f * zi[brev(BQ / 2, BQ)], BQ);
 }
 
@@ -216,20 +239,21 @@ __device__ __forceinline__ void warp_fft_adj(float2* xbuf, const float2* __restr
     const int plane = fr * A + ((A - k1) % A);
     float zr[BQ], zi[BQ];
     float qr[BQ / 2], qi[BQ / 2];                           // gradients owed to the partner lane
-#pragma unroll
-    for (int j = 0; j < BQ / 2; ++j) {
+    const float2 base = ldg2(pt + k1);
+    static_for<0, BQ / 2>([&](auto jc) {
+        constexpr int j = decltype(jc)::value;
         const int k = k1 + A * j;
         const float2 g = grad(fr, k, 2 * j);
         const float2 gp = grad(fr, M - k, 2 * j + 1);
         const float sr = g.x + gp.x, si = g.y - gp.y;       // G[k] + conj(G[M-k])
         const float dr = g.x - gp.x, di = g.y + gp.y;       // G[k] - conj(G[M-k])
-        const float2 cs = ldg2(pt + k);
+        const float2 cs = post_twiddle<BQ, j>(base);
         // T' = conj(u) * D with u = -j W_n^k = (-s, -c)  ->  conj(u) = (-s, +c)
         const float tr = -fmaf(cs.x, di, cs.y * dr);
         const float ti = fmaf(cs.x, dr, -cs.y * di);
         zr[j] = sr + tr; zi[j] = si + ti;                   // dL/dZ[k]
         qr[j] = sr - tr; qi[j] = ti - si;                   // dL/dZ[M-k] = conj(S - T')
-    }
+    });
 #pragma unroll
     for (int j = 0; j < BQ / 2; ++j) {
         // my slot BQ-1-j receives what the partner lane computed for its pair j

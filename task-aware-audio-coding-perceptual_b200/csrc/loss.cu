@@ -29,6 +29,17 @@ struct LossArgs {
 
 __device__ __forceinline__ int nfr_of(int n) { return n >= 2048 ? 1 : (n >= 512 ? 2 : (n >= 128 ? 4 : 8)); }
 
+// Single-MUFU approximations (<= 2 ulp; the loss tolerance is rtol 1e-4): no Newton fix-up, no slow-path branch.
+__device__ __forceinline__ float fast_sqrt(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float fast_rsqrt(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float fast_lg2(float x) { float r; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+// clamp(v * 2^100, -c, c) == c * sign(v) for every v a float subtraction can produce (0 stays 0): three instructions,
+// no predicates.
+__device__ __forceinline__ float signed_coef(float v, float c) { return fminf(fmaxf(v * 0x1p100f, -c), c); }
+constexpr float kTinyMag2 = 1e-30f;     // |Y|^2 below this is treated as |Y| == 0 (zero gradient, like torch.abs at 0)
+// |Z| from |Z|^2 -- the SAME formula for X and Y, so that identical inputs give a loss of exactly 0
+__device__ __forceinline__ float fast_mag(float m2) { return m2 >= kTinyMag2 ? m2 * fast_rsqrt(m2) : 0.0f; }
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -68,17 +79,18 @@ __device__ __forceinline__ void loss_fwd_task(const LossScale& sc, const float* 
     };
     warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load);
     warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
-        mx[slot] = sqrtf(fmaf(vr, vr, vi * vi));
+        mx[slot] = fast_mag(fmaf(vr, vr, vi * vi));
     });
     cur = ty;
     warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load);
     const bool valid = (f_first + lane / P::A) < f_end;
     float l1 = 0.0f, ll = 0.0f;
     warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
-        const float my = sqrtf(fmaf(vr, vr, vi * vi));
+        const float m2 = fmaf(vr, vr, vi * vi);
+        const float my = fast_mag(m2);                                  // same arithmetic as the fused kernel
         const float xv = mx[slot];
-        l1 += fabsf(xv - my);
-        ll += fabsf(__log2f(fmaxf(xv, eps)) - __log2f(fmaxf(my, eps)));   // log2 units (scaled by ln 2 below); exact 0 when X == Y
+        l1 += fabsf(my - xv);
+        ll += fabsf(fast_lg2(fmaxf(my, eps)) - fast_lg2(fmaxf(xv, eps)));   // log2 units (scaled by ln 2 below); exact 0 when X == Y
     });
     if (valid) { acc_l1 += l1; acc_log += ll * 0.69314718055994530942f; }
 }
@@ -164,7 +176,10 @@ __global__ void __launch_bounds__(256) partial_reduce_kernel(const double* __res
 #ifndef TAC_BWD_OCC
 #define TAC_BWD_OCC 3
 #endif
-constexpr int kBwdWarps = 4;
+#ifndef TAC_BWD_WARPS
+#define TAC_BWD_WARPS 4
+#endif
+constexpr int kBwdWarps = TAC_BWD_WARPS;
 constexpr int kBwdThreads = kBwdWarps * 32;
 
 template <class P, bool WITH_SUMS>
@@ -186,25 +201,22 @@ __device__ __forceinline__ void loss_bwd_task(const LossScale& sc, const float* 
     };
     warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load);
     warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
-        gr[slot] = sqrtf(fmaf(vr, vr, vi * vi));                     // |X|
+        gr[slot] = fast_mag(fmaf(vr, vr, vi * vi));                  // |X|
     });
     cur = yr;
     warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load);
     float l1 = 0.0f, ll = 0.0f;
     warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
         const float m2 = fmaf(vr, vr, vi * vi);
-        const float inv = m2 > 0.0f ? rsqrtf(m2) : 0.0f;
-        const float xv = gr[slot];
-        if (WITH_SUMS) {                                              // same arithmetic as the forward-only kernel
-            const float ms = sqrtf(m2);
-            l1 += fabsf(xv - ms);
-            ll += fabsf(__log2f(fmaxf(xv, eps)) - __log2f(fmaxf(ms, eps)));
-        }
+        const float inv = m2 >= kTinyMag2 ? fast_rsqrt(m2) : 0.0f;
         const float my = m2 * inv;                                    // |Y|
-        float g = (my > xv) ? c_l1 : ((my < xv) ? -c_l1 : 0.0f);     // d|X - Y| / dY
-        const float xc = fmaxf(xv, eps), yc = fmaxf(my, eps);
-        const float sg = (yc > xc) ? c_log : ((yc < xc) ? -c_log : 0.0f);
-        if (my >= eps) g = fmaf(sg, inv, g);                          // d|ln X~ - ln Y~| / dY = sign / Y
+        const float xv = gr[slot];                                    // |X|
+        const float d = my - xv;
+        const float dl = fast_lg2(fmaxf(my, eps)) - fast_lg2(fmaxf(xv, eps));
+        if (WITH_SUMS) { l1 += fabsf(d); ll += fabsf(dl); }           // same arithmetic as the forward-only kernel
+        // d|X - Y| / dY = sign(d);  d|ln X~ - ln Y~| / dY = sign(dl) / Y where Y is not clamped (Y >= eps)
+        const float invm = my >= eps ? inv : 0.0f;
+        float g = fmaf(signed_coef(dl, c_log), invm, signed_coef(d, c_l1));
         g *= inv;                                                     // dY / dYc = Yc / |Y|
         gr[slot] = g * vr; gi[slot] = g * vi;
     });
@@ -445,7 +457,10 @@ static int fill_loss_args(LossArgs& a, const float* x, const float* y, int64_t B
 }
 
 constexpr int kFwdChunk = 2048;
-constexpr int kBwdChunk = 8192;
+#ifndef TAC_BWD_CHUNK
+#define TAC_BWD_CHUNK 8192
+#endif
+constexpr int kBwdChunk = TAC_BWD_CHUNK;
 
 }  // namespace tac
 

@@ -55,6 +55,15 @@ __host__ __device__ constexpr int brev(int k, int n) {
     return r;
 }
 
+// Compile-time loop: f(std::integral_constant<int, I>) for I in [0, N).
+template <int I, int N, class F>
+__device__ __forceinline__ void static_for(F&& f) {
+    if constexpr (I < N) {
+        f(std::integral_constant<int, I>{});
+        static_for<I + 1, N>(f);
+    }
+}
+
 // ------------------------------------------------------------------ radix-2 DIF network
 // (r, i) *= W_N^I = exp(-2*pi*j*I/N), 0 <= I < N/2, with the trivial cases folded away.
 template <int N, int I>
@@ -115,7 +124,15 @@ struct Plan {
     static constexpr int N = 2 * M;         // real frame length (n_fft)
     static constexpr int NFR = 32 / A_;     // frames per warp task
     static constexpr int NS1 = BQ_ / A_;    // pass-1 sub-transforms per lane
+#ifdef TAC_XBUF_ODD
     static constexpr int RS = BQ_ + 1;      // exchange row stride (float2), odd -> conflict free
+#else
+    // exchange row stride (float2): BQ + 2 keeps every row 16-byte aligned so that a lane moves its row with 128-bit
+    // accesses (quarter-warp bank pattern 4*lane mod 32: conflict free); the small plans keep the odd stride, which is
+    // what makes their 64-bit column accesses conflict free when a half-warp spans two frames
+    static constexpr int RS = BQ_ >= 16 ? BQ_ + 2 : BQ_ + 1;
+#endif
+    static constexpr bool kVec4 = (RS % 2) == 0;
     static_assert(32 % A_ == 0 && BQ_ % A_ == 0 && BQ_ >= A_, "unsupported split");
 };
 using Plan2048 = Plan<32, 32>;
@@ -125,7 +142,7 @@ using Plan256 = Plan<8, 16>;
 using Plan128 = Plan<8, 8>;
 using Plan64 = Plan<4, 8>;
 
-constexpr int kXbufFloat2 = 32 * 33;        // per-warp exchange tile (largest plan), 8448 B
+constexpr int kXbufFloat2 = 32 * 34;        // per-warp exchange tile (largest plan), 8704 B
 
 struct FftTables {                          // device pointers, one set per (n_fft, win, normalized)
     const float2* win2;                     // [M]   (w[2m], w[2m+1]) * 0.5 * norm
@@ -136,20 +153,21 @@ struct FftTables {                          // device pointers, one set per (n_f
 __device__ __forceinline__ float2 ldg2(const float2* p) { return __ldg(p); }
 
 // ------------------------------------------------------------------ forward transform
-// load(fr, m) returns the windowed packed sample z_fr[m] (float2).  On return lane
+// load(integral_constant s, fr, m) returns the windowed packed sample z_fr[m] (float2); s is the lane's pass-1
+// sub-transform index (compile-time), fr = (lane + 32 s) / BQ the frame of the task it belongs to.  On return lane
 // (fr = lane / A, k1 = lane % A) holds Z_fr[k1 + A*k2] in slot brev(k2, BQ) of (zr, zi).
 template <class P, class Load>
 __device__ __forceinline__ void warp_fft_fwd(float (&zr)[P::BQ], float (&zi)[P::BQ], float2* xbuf,
                                              const float2* __restrict__ tw, int lane, Load load) {
     constexpr int A = P::A, BQ = P::BQ, RS = P::RS;
-#pragma unroll
-    for (int s = 0; s < P::NS1; ++s) {
+    static_for<0, P::NS1>([&](auto sc) {
+        constexpr int s = decltype(sc)::value;
         const int q = lane + 32 * s;
         const int fr = q / BQ, b = q % BQ;
         float ar[A], ai[A];
 #pragma unroll
         for (int a = 0; a < A; ++a) {
-            float2 v = load(fr, BQ * a + b);
+            float2 v = load(sc, fr, BQ * a + b);
             ar[a] = v.x; ai[a] = v.y;
         }
         Dif<A>::run(ar, ai);
@@ -165,25 +183,25 @@ __device__ __forceinline__ void warp_fft_fwd(float (&zr)[P::BQ], float (&zi)[P::
             }
             row[k1 * RS] = make_float2(r, i);
         }
-    }
+    });
     __syncwarp();
     const float2* rd = xbuf + lane * RS;
+    if constexpr (P::kVec4) {
+        const float4* rd4 = reinterpret_cast<const float4*>(rd);
 #pragma unroll
-    for (int b = 0; b < BQ; ++b) {
-        float2 v = rd[b];
-        zr[b] = v.x; zi[b] = v.y;
+        for (int b = 0; b < BQ / 2; ++b) {
+            const float4 v = rd4[b];
+            zr[2 * b] = v.x; zi[2 * b] = v.y; zr[2 * b + 1] = v.z; zi[2 * b + 1] = v.w;
+        }
+    } else {
+#pragma unroll
+        for (int b = 0; b < BQ; ++b) {
+            float2 v = rd[b];
+            zr[b] = v.x; zi[b] = v.y;
+        }
     }
     __syncwarp();
     Dif<BQ>::run(zr, zi);
-}
-
-// Compile-time loop: f(std::integral_constant<int, I>) for I in [0, N).
-template <int I, int N, class F>
-__device__ __forceinline__ void static_for(F&& f) {
-    if constexpr (I < N) {
-        f(std::integral_constant<int, I>{});
-        static_for<I + 1, N>(f);
-    }
 }
 
 // (cos, sin)(2 pi (k1 + A j) / n) from the per-lane base (cos, sin)(2 pi k1 / n) and the compile-time rotation
@@ -230,7 +248,8 @@ __device__ __forceinline__ void warp_fft_post(const float (&zr)[P::BQ], const fl
 // ------------------------------------------------------------------ adjoint transform
 // grad(fr, k, slot) returns dL/dX_fr[k] (float2, re/im parts) for k in [0, M]; it is called exactly
 // once per (frame, k) by the lane that emitted X_fr[k] in warp_fft_post, with the same slot.  store(fr, m, g)
-// receives dL/dz_fr[m] *before* the window (caller multiplies by win2[m]).
+// receives dL/dz_fr[m], m = BQ * a + b, *before* the window (caller multiplies by win2[m]); it is called as
+// store(integral_constant s, f2, integral_constant a, b, value) with s the pass-1 sub-transform index of the lane.
 template <class P, class Grad, class Store>
 __device__ __forceinline__ void warp_fft_adj(float2* xbuf, const float2* __restrict__ tw,
                                              const float2* __restrict__ pt, int lane, Grad grad, Store store) {
@@ -273,6 +292,7 @@ __device__ __forceinline__ void warp_fft_adj(float2* xbuf, const float2* __restr
     // inverse BQ-point DFT over k2 (natural in, bit-reversed out): swap re/im roles
     Dif<BQ>::run(zi, zr);
     float2* wr = xbuf + lane * RS;
+    float pr_ = 0.0f, pi_ = 0.0f;
 #pragma unroll
     for (int b = 0; b < BQ; ++b) {
         float r = zr[brev(b, BQ)], i = zi[brev(b, BQ)];
@@ -282,11 +302,16 @@ __device__ __forceinline__ void warp_fft_adj(float2* xbuf, const float2* __restr
             i = fmaf(r, w.y, i * w.x);
             r = t;
         }
-        wr[b] = make_float2(r, i);
+        if constexpr (P::kVec4) {
+            if (b & 1) reinterpret_cast<float4*>(wr)[b >> 1] = make_float4(pr_, pi_, r, i);
+            else { pr_ = r; pi_ = i; }
+        } else {
+            wr[b] = make_float2(r, i);
+        }
     }
     __syncwarp();
-#pragma unroll
-    for (int s = 0; s < P::NS1; ++s) {
+    static_for<0, P::NS1>([&](auto sc) {
+        constexpr int s = decltype(sc)::value;
         const int q = lane + 32 * s;
         const int f2 = q / BQ, b = q % BQ;
         float ar[A], ai[A];
@@ -297,9 +322,12 @@ __device__ __forceinline__ void warp_fft_adj(float2* xbuf, const float2* __restr
             ar[kk] = v.x; ai[kk] = v.y;
         }
         Dif<A>::run(ai, ar);
-#pragma unroll
-        for (int a = 0; a < A; ++a) store(f2, BQ * a + b, make_float2(ar[brev(a, A)], ai[brev(a, A)]));
-    }
+        // sample pair m = BQ * a + b of frame f2; s and a are compile-time (integral constants) for the callee
+        static_for<0, A>([&](auto ac) {
+            constexpr int a = decltype(ac)::value;
+            store(sc, f2, ac, b, make_float2(ar[brev(a, A)], ai[brev(a, A)]));
+        });
+    });
     __syncwarp();
 }
 

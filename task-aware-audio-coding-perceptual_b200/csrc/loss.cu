@@ -7,6 +7,7 @@
 // windowed frames into a shared-memory accumulator in conflict-free "rounds" (frames f, f + R,
 // f + 2R ... with R = ceil(n/hop) never overlap), so the result is deterministic too.
 #include "tac_common.cuh"
+#include "loss_common.cuh"
 
 namespace tac {
 
@@ -28,23 +29,6 @@ struct LossArgs {
 };
 
 __device__ __forceinline__ int nfr_of(int n) { return n >= 2048 ? 1 : (n >= 512 ? 2 : (n >= 128 ? 4 : 8)); }
-
-// Single-MUFU approximations (<= 2 ulp; the loss tolerance is rtol 1e-4): no Newton fix-up, no slow-path branch.
-__device__ __forceinline__ float fast_sqrt(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
-__device__ __forceinline__ float fast_rsqrt(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
-__device__ __forceinline__ float fast_lg2(float x) { float r; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
-// clamp(v * 2^100, -c, c) == c * sign(v) for every v a float subtraction can produce (0 stays 0): three instructions,
-// no predicates.
-__device__ __forceinline__ float signed_coef(float v, float c) { return fminf(fmaxf(v * 0x1p100f, -c), c); }
-constexpr float kTinyMag2 = 1e-30f;     // |Y|^2 below this is treated as |Y| == 0 (zero gradient, like torch.abs at 0)
-// |Z| from |Z|^2 -- the SAME formula for X and Y, so that identical inputs give a loss of exactly 0
-__device__ __forceinline__ float fast_mag(float m2) { return m2 >= kTinyMag2 ? m2 * fast_rsqrt(m2) : 0.0f; }
-
-__device__ __forceinline__ float warp_sum(float v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
-}
 
 // ------------------------------------------------------------------------------------------ forward
 constexpr int kFwdWarps = 6;
@@ -70,7 +54,7 @@ __device__ __forceinline__ void loss_fwd_task(const LossScale& sc, const float* 
     const float2* __restrict__ win2 = sc.t.win2;
     const int hop = sc.hop;
     const float* cur = tx;
-    auto load = [&](int fr, int m) -> float2 {
+    auto load = [&](auto, int fr, int m) -> float2 {
         int f = f_first + fr;
         f = f < f_end ? f : f_first;
         const float2 v = *reinterpret_cast<const float2*>(cur + (f * hop - origin) + 2 * m);
@@ -192,7 +176,7 @@ __device__ __forceinline__ void loss_bwd_task(const LossScale& sc, const float* 
     const int hop = sc.hop;
     const float* cur = xr;
     // frames of this task: f_base + i * f_stride, i in [0, NFR)
-    auto load = [&](int fr, int m) -> float2 {
+    auto load = [&](auto, int fr, int m) -> float2 {
         int f = f_base + fr * f_stride;
         f = f < f_end ? f : f_base;
         const float2 v = __ldg(reinterpret_cast<const float2*>(cur + (long long)f * hop) + m);
@@ -223,7 +207,8 @@ __device__ __forceinline__ void loss_bwd_task(const LossScale& sc, const float* 
     if (WITH_SUMS && (f_base + (lane / P::A) * f_stride) < f_end) { acc_l1 += l1; acc_log += ll * 0.69314718055994530942f; }
     warp_fft_adj<P>(xbuf, sc.t.tw, sc.t.pt, lane,
         [&](int, int, int slot) -> float2 { return make_float2(gr[slot], gi[slot]); },
-        [&](int fr, int m, float2 g) {
+        [&](auto, int fr, auto ac, int b, float2 g) {
+            const int m = P::BQ * decltype(ac)::value + b;
             const int f = f_base + fr * f_stride;
             if (f < f_end) {
                 const float2 w = ldg2(win2 + m);
@@ -475,7 +460,14 @@ extern "C" size_t tac_mrstft_workspace_bytes(int64_t B, int64_t T, int n_scales,
         last_start = ls > last_start ? ls : last_start;
     }
     const long long nchunks = last_start / kFwdChunk + 1;
-    return (size_t)(B * nchunks * 2 * n_scales) * sizeof(double);
+    size_t need = (size_t)(B * nchunks * 2 * n_scales) * sizeof(double);
+#ifndef TAC_NO_STREAM
+    if (n_scales <= TAC_MAX_SCALES && stream_applicable(T, n_scales, n_fft, hop, nullptr)) {
+        const size_t sn = stream_workspace_bytes(B, T, n_scales, n_fft, hop);
+        need = sn > need ? sn : need;
+    }
+#endif
+    return need;
 }
 
 extern "C" int tac_mrstft_loss_fwd(const float* x, const float* y, int64_t B, int64_t T, int n_scales, const int* n_fft,
@@ -509,6 +501,13 @@ static int launch_bwd(const float* x, const float* y, int64_t B, int64_t T, int 
     int rc = fill_loss_args(a, x, y, B, T, n_scales, n_fft, hop, win, eps, kBwdChunk);
     if (rc) return rc;
     TAC_REQUIRE(coef && grad_y, "null coef / grad_y");
+#ifndef TAC_NO_STREAM
+    // hop == n_fft / 4 everywhere (the msstftd.py:174-175 framing): barrier-free streaming kernel (loss_stream.cu)
+    if (stream_applicable(T, n_scales, n_fft, hop, win) && workspace &&
+        workspace_bytes >= stream_workspace_bytes(B, T, n_scales, n_fft, hop))
+        return launch_stream(x, y, B, T, n_scales, n_fft, hop, win, eps, coef, sums, grad_y, workspace, workspace_bytes,
+                             reinterpret_cast<cudaStream_t>(stream));
+#endif
     TAC_REQUIRE((((uintptr_t)x | (uintptr_t)y) & 7u) == 0 && (T & 1) == 0, "backward needs 8-byte aligned x, y and even T");
     a.partial = nullptr; a.coef = coef; a.grad = grad_y;
     const long long grid = B * a.nchunks;

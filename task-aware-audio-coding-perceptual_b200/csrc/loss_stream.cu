@@ -1,0 +1,381 @@
+// K2, streaming form -- fused multi-resolution STFT loss value + gradient for the hop = n_fft / 4 framing of
+// msstftd.py:174-175, with NO block barrier, NO shared accumulator tile and NO atomics.
+//
+// A warp walks a run of CONSECUTIVE frames of one row and one scale.  Per frame it transforms x and y in registers
+// (fft_core.cuh), folds the two loss sums, forms dL/dY in the frequency domain and runs the adjoint transform.  The
+// adjoint leaves sample pair m = BQ * a + b of the frame in lane b; a hop (n / 4 samples) is a shift of A / 4 in `a`
+// with the SAME b, so the overlap-add of the four frames that cover a hop block is LANE-PRIVATE: every lane keeps its
+// slice of the four pending hop blocks in a per-warp shared-memory ring that only it touches (no conflict, no
+// synchronisation), and after each frame the oldest block is complete and leaves with one coalesced store.
+//
+// Rows are cut into runs of ~7 frames so that there are enough independent warp-runs to fill the GPU.  A run's
+// first three hop blocks also need the last three frames of the previous run: the previous run flushes its pending
+// partial sums for them into g, the run itself writes its own partial sums into h, and the combine kernel -- which
+// exists anyway to add the scales in a fixed order -- adds h on exactly those blocks.  Every output sample is
+// therefore written once per scale with plain stores, in a fixed order: the gradient is bit-stable run to run.
+#include "tac_common.cuh"
+#include "loss_common.cuh"
+
+namespace tac {
+
+#ifndef TAC_STREAM_WARPS
+#define TAC_STREAM_WARPS 4
+#endif
+constexpr int kStreamWarps = TAC_STREAM_WARPS;
+constexpr int kStreamThreads = kStreamWarps * 32;
+constexpr int kRunTarget = 7;                       // frames per run (work unit of one lane group)
+constexpr int kOlaFloat2 = 1024;                    // per-warp overlap-add ring: NFR * M float2 <= 1024 (8 KiB)
+constexpr int kStreamWarpFloat2 = kXbufFloat2 + kOlaFloat2;
+
+struct StreamScale {
+    int n, hop, F, NR;           // NR runs per row
+    int cta_begin, wpr;          // blockIdx range of this scale starts at cta_begin; wpr = warp-runs per row
+    long long nwr;               // warp-runs of this scale = rows * wpr (a CTA takes kStreamWarps consecutive ones)
+    int orig;                    // index of the scale in the caller's lists (sums / coef slots)
+    FftTables t;
+    float* g;                    // [rows][T] complete blocks + flushed partial sums
+    float* h;                    // [rows][T] partial sums of the first three blocks of runs r >= 1
+};
+
+struct StreamArgs {
+    const float* x;
+    const float* y;
+    long long T, rows;
+    int nscales, total_ctas;
+    float eps;
+    const float* coef;           // [2 * nscales] device
+    double* partial;             // [total_ctas][kStreamWarps][2] or null
+    float* grad;                 // [rows][T] (combine kernel)
+    StreamScale sc[TAC_MAX_SCALES];
+};
+
+__host__ __device__ __forceinline__ int run_begin(int r, int F, int NR) { return (int)(((long long)r * F) / NR); }
+
+// Frame reads: allocating read-only loads.  Consecutive frames of a run share 3/4 of their samples, and at 2 CTAs per SM
+// the L1 keeps ~90 KiB, enough for the frames of the resident warps (measured: 0.68 ms against 0.72 ms with
+// L1::no_allocate on cfg 2).
+__device__ __forceinline__ float2 ld_stream2(const float* p) {
+#ifdef TAC_STREAM_NOALLOC
+    float2 v;
+    asm("ld.global.nc.L1::no_allocate.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(p));
+    return v;
+#else
+    return __ldg(reinterpret_cast<const float2*>(p));
+#endif
+}
+
+// One CTA = kStreamWarps warps, each walking NFR consecutive runs of one row (one run per lane group).
+template <class P, bool WITH_SUMS>
+__device__ __forceinline__ void stream_cta(const StreamArgs& a, const StreamScale& sc, int cta, float2* smem) {
+    constexpr int A = P::A, BQ = P::BQ, M = P::M, NFR = P::NFR, NS1 = P::NS1, QA = A / 4;
+    static_assert(A % 4 == 0 && NFR * M <= kOlaFloat2, "plan does not fit the streaming overlap-add ring");
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float2* xbuf = smem + warp * kStreamWarpFloat2;
+    float2* ola = xbuf + kXbufFloat2;                      // [NFR][4 quarters][QA][BQ]
+    const long long wr = (long long)cta * kStreamWarps + warp;    // warp-run index inside the scale
+    if (wr >= sc.nwr) {                                            // spare warp of the scale's last CTA
+        if (WITH_SUMS && lane < 2) a.partial[((long long)blockIdx.x * kStreamWarps + warp) * 2 + lane] = 0.0;
+        return;
+    }
+    const long long row = wr / sc.wpr;
+    const int run0 = (int)(wr % sc.wpr) * NFR;
+    const int F = sc.F, NR = sc.NR, hop = sc.hop;
+    const float* xr = a.x + row * a.T;
+    const float* yr = a.y + row * a.T;
+    float* grow = sc.g + row * a.T;
+    float* hrow = sc.h + row * a.T;
+    const float2* __restrict__ win2 = sc.t.win2;
+
+    auto run_lo = [&](int g) { const int r = run0 + g; return r < NR ? run_begin(r, F, NR) : 0; };
+    auto run_len = [&](int g) { const int r = run0 + g; return r < NR ? run_begin(r + 1, F, NR) - run_begin(r, F, NR) : 0; };
+    int maxlen = 0;
+#pragma unroll
+    for (int g = 0; g < NFR; ++g) maxlen = max(maxlen, run_len(g));
+    // lane-group parameters in the two lane <-> frame mappings of fft_core.cuh
+    const int len_post = run_len(lane / A);                // post-processing: frame group lane / A
+    int lo_s[NS1], len_s[NS1], f2_s[NS1];                  // pass 1 / adjoint output: group (lane + 32 s) / BQ
+#pragma unroll
+    for (int s = 0; s < NS1; ++s) {
+        f2_s[s] = (lane + 32 * s) / BQ;
+        lo_s[s] = run_lo(f2_s[s]);
+        len_s[s] = run_len(f2_s[s]);
+    }
+    const int b_lane = lane % BQ;
+
+    {   // empty ring
+        float4* o4 = reinterpret_cast<float4*>(ola);
+        for (int i = lane; i < NFR * M / 2; i += 32) o4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    __syncwarp();
+
+    const float c_l1 = __ldg(a.coef + 2 * sc.orig), c_log = __ldg(a.coef + 2 * sc.orig + 1);
+    const float eps = a.eps;
+    float l1 = 0.0f, ll = 0.0f;
+    for (int t = 0; t < maxlen; ++t) {
+        float zr[BQ], zi[BQ];
+        float gr[BQ + 1], gi[BQ + 1];
+        const float* fx[NS1];
+        const float* fy[NS1];
+#pragma unroll
+        for (int s = 0; s < NS1; ++s) {                    // finished (or empty) groups recompute a valid frame, masked below
+            const int f = lo_s[s] + min(t, max(len_s[s] - 1, 0));
+            fx[s] = xr + (long long)f * hop;
+            fy[s] = yr + (long long)f * hop;
+        }
+        auto load_x = [&](auto scn, int, int m) -> float2 {
+            const float2 v = ld_stream2(fx[decltype(scn)::value] + 2 * m);
+            const float2 w = ldg2(win2 + m);
+            return make_float2(__fmul_rn(v.x, w.x), __fmul_rn(v.y, w.y));
+        };
+        auto load_y = [&](auto scn, int, int m) -> float2 {
+            const float2 v = ld_stream2(fy[decltype(scn)::value] + 2 * m);
+            const float2 w = ldg2(win2 + m);
+            return make_float2(__fmul_rn(v.x, w.x), __fmul_rn(v.y, w.y));
+        };
+        warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load_x);
+        warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
+            gr[slot] = fast_mag(fmaf(vr, vr, vi * vi));                   // |X|
+        });
+        warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load_y);
+        float tl1 = 0.0f, tll = 0.0f;
+        warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
+            const float m2 = fmaf(vr, vr, vi * vi);
+            const float inv = m2 >= kTinyMag2 ? fast_rsqrt(m2) : 0.0f;
+            const float my = m2 * inv;                                    // |Y|
+            const float xv = gr[slot];                                    // |X|
+            const float d = my - xv;
+            const float dl = fast_lg2(fmaxf(my, eps)) - fast_lg2(fmaxf(xv, eps));
+            if (WITH_SUMS) { tl1 += fabsf(d); tll += fabsf(dl); }
+            // d|X - Y| / dY = sign(d);  d|ln X~ - ln Y~| / dY = sign(dl) / Y where Y is not clamped (Y >= eps)
+            const float invm = my >= eps ? inv : 0.0f;
+            float g = fmaf(signed_coef(dl, c_log), invm, signed_coef(d, c_l1));
+            g *= inv;                                                     // dY / dYc = Yc / |Y|
+            gr[slot] = g * vr; gi[slot] = g * vi;
+        });
+        if (WITH_SUMS && t < len_post) { l1 += tl1; ll += tll; }
+        warp_fft_adj<P>(xbuf, sc.t.tw, sc.t.pt, lane,
+            [&](int, int, int slot) -> float2 { return make_float2(gr[slot], gi[slot]); },
+            [&](auto scn, int f2, auto ac, int b, float2 gv) {
+                constexpr int s = decltype(scn)::value, av = decltype(ac)::value;
+                constexpr int q = av / QA, ap = av % QA;                  // hop block of the frame, pair index inside it
+                const bool active = t < len_s[s];
+                const int f = lo_s[s] + t;
+                const float2 w = ldg2(win2 + BQ * av + b);
+                const int p = (q + f) & 3;                                // ring quarter that holds hop block f + q
+                float2* slot = ola + ((f2 * 4 + p) * QA + ap) * BQ + b;
+                if (q == 3) {                                             // newest block: nothing pending yet
+                    if (active) *slot = make_float2(gv.x * w.x, gv.y * w.y);
+                } else if (q == 0) {                                      // oldest block: complete after this frame
+                    const float2 o = *slot;
+                    float* dst = (t < 3 && run0 + f2 > 0) ? hrow : grow;  // first three blocks of a run r >= 1 are partial
+                    if (active)
+                        *reinterpret_cast<float2*>(dst + (long long)f * hop + 2 * (BQ * ap + b)) =
+                            make_float2(fmaf(gv.x, w.x, o.x), fmaf(gv.y, w.y, o.y));
+                } else {
+                    float2 o = *slot;
+                    o.x = fmaf(gv.x, w.x, o.x); o.y = fmaf(gv.y, w.y, o.y);
+                    if (active) *slot = o;
+                }
+            });
+    }
+    // flush the three pending hop blocks behind the last frame of every run (partial sums unless the row ends here)
+#pragma unroll
+    for (int s = 0; s < NS1; ++s) {
+        if (len_s[s] > 0) {
+            const int f = lo_s[s] + len_s[s] - 1;
+#pragma unroll
+            for (int q = 1; q < 4; ++q) {
+                const int p = (q + f) & 3;
+#pragma unroll
+                for (int ap = 0; ap < QA; ++ap) {
+                    const float2 o = ola[((f2_s[s] * 4 + p) * QA + ap) * BQ + b_lane];
+                    *reinterpret_cast<float2*>(grow + (long long)(f + q) * hop + 2 * (BQ * ap + b_lane)) = o;
+                }
+            }
+        }
+    }
+    if (WITH_SUMS) {                                       // fixed lane -> warp order, one partial per warp: deterministic sums
+        l1 = warp_sum(l1); ll = warp_sum(ll);
+        if (lane == 0) {
+            double* pp = a.partial + ((long long)blockIdx.x * kStreamWarps + warp) * 2;
+            pp[0] = (double)l1; pp[1] = (double)ll * 0.69314718055994530942;
+        }
+    }
+}
+
+#ifndef TAC_STREAM_OCC
+#define TAC_STREAM_OCC 2      // 255 registers, no spills; 3 (168 registers) spills ~1 KB per thread and measured slower
+#endif
+
+template <bool WITH_SUMS>
+__global__ void __launch_bounds__(kStreamThreads, TAC_STREAM_OCC) mrstft_stream_kernel(const StreamArgs a) {
+    extern __shared__ __align__(16) unsigned char stream_smem_raw[];
+    float2* smem = reinterpret_cast<float2*>(stream_smem_raw);
+    int s = 0;
+    while (s + 1 < a.nscales && (int)blockIdx.x >= a.sc[s + 1].cta_begin) ++s;
+    const StreamScale& sc = a.sc[s];
+    const int cta = (int)blockIdx.x - sc.cta_begin;
+    switch (sc.n) {
+        case 2048: stream_cta<Plan2048, WITH_SUMS>(a, sc, cta, smem); break;
+        case 1024: stream_cta<Plan1024, WITH_SUMS>(a, sc, cta, smem); break;
+        case 512: stream_cta<Plan512, WITH_SUMS>(a, sc, cta, smem); break;
+        case 256: stream_cta<Plan256, WITH_SUMS>(a, sc, cta, smem); break;
+        case 128: stream_cta<Plan128, WITH_SUMS>(a, sc, cta, smem); break;
+        default: stream_cta<Plan64, WITH_SUMS>(a, sc, cta, smem); break;
+    }
+}
+
+// grad[row][t] = sum over scales (fixed order) of g_s[t] (+ h_s[t] on the first three hop blocks of runs r >= 1);
+// samples behind the last frame of a scale get nothing from it.
+template <int VEC>
+__global__ void __launch_bounds__(256) mrstft_combine_kernel(const StreamArgs a) {
+    const long long per_row = a.T / VEC;
+    const long long total = a.rows * per_row;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long row = i / per_row;
+        const int t = (int)(i - row * per_row) * VEC;
+        float acc[VEC];
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) acc[v] = 0.0f;
+        for (int s = 0; s < a.nscales; ++s) {
+            const StreamScale& sc = a.sc[s];
+            if (t >= (sc.F - 1) * sc.hop + sc.n) continue;            // behind the last frame (block edges are multiples of VEC)
+            const long long off = row * a.T + t;
+            float v[VEC];
+            if constexpr (VEC == 4) { const float4 q = __ldcs(reinterpret_cast<const float4*>(sc.g + off)); v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w; }
+            else { const float2 q = __ldcs(reinterpret_cast<const float2*>(sc.g + off)); v[0] = q.x; v[1] = q.y; }
+            const int j = t / sc.hop;
+            if (j < sc.F) {
+                int r = (int)(((long long)j * sc.NR) / sc.F);
+                while (r + 1 < sc.NR && run_begin(r + 1, sc.F, sc.NR) <= j) ++r;
+                while (r > 0 && run_begin(r, sc.F, sc.NR) > j) --r;
+                if (r > 0 && j - run_begin(r, sc.F, sc.NR) < 3) {
+                    if constexpr (VEC == 4) { const float4 q = __ldcs(reinterpret_cast<const float4*>(sc.h + off)); v[0] += q.x; v[1] += q.y; v[2] += q.z; v[3] += q.w; }
+                    else { const float2 q = __ldcs(reinterpret_cast<const float2*>(sc.h + off)); v[0] += q.x; v[1] += q.y; }
+                }
+            }
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) acc[e] += v[e];
+        }
+        float* dst = a.grad + row * a.T + t;
+        if constexpr (VEC == 4) *reinterpret_cast<float4*>(dst) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+        else *reinterpret_cast<float2*>(dst) = make_float2(acc[0], acc[1]);
+    }
+}
+
+// sums[2 * orig + i] = sum over the CTAs of that scale (fixed order) of partial[cta][i].  grid = 2 * nscales.
+__global__ void __launch_bounds__(256) mrstft_stream_sums_kernel(const StreamArgs a, double* __restrict__ sums) {
+    __shared__ double sh[256];
+    const int s = blockIdx.x >> 1, i = blockIdx.x & 1;
+    const StreamScale& sc = a.sc[s];
+    const long long c0 = (long long)sc.cta_begin * kStreamWarps;
+    const long long n = ((sc.nwr + kStreamWarps - 1) / kStreamWarps) * kStreamWarps;   // warp slots of this scale (spares hold 0)
+    double v = 0.0;
+    for (long long c = threadIdx.x; c < n; c += 256) v += a.partial[(c0 + c) * 2 + i];
+    sh[threadIdx.x] = v;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) sums[2 * sc.orig + i] = sh[0];
+}
+
+static inline size_t align16(size_t v) { return (v + 15) & ~(size_t)15; }
+
+bool stream_applicable(int64_t T, int n_scales, const int* n_fft, const int* hop, const int* win) {
+    if ((T & 1) != 0 || T >= (1ll << 30)) return false;
+    for (int s = 0; s < n_scales; ++s) {
+        if (!supported_nfft(n_fft[s]) || hop[s] * 4 != n_fft[s]) return false;
+        if (n_fft[s] < 512) return false;      // small plans (4-8 frames per warp task): the chunk/round kernel is faster
+        if (win && win[s] != n_fft[s] && win[s] <= 0) return false;
+        if (num_frames(T, n_fft[s], hop[s], 0) < 1) return false;
+    }
+    return true;
+}
+
+// Workspace: per scale g and h ([rows][T] float each), then [total_ctas][2] float64 partials.
+static void stream_layout(int64_t rows, int64_t T, int n_scales, const int* n_fft, const int* hop, int* order, int* NR, int* cpr,
+                          long long* total_ctas) {
+    // heavy scales first: their CTAs are the longest, the small ones fill the tail
+    for (int s = 0; s < n_scales; ++s) order[s] = s;
+    for (int i = 0; i < n_scales; ++i)
+        for (int j = i + 1; j < n_scales; ++j)
+            if (n_fft[order[j]] > n_fft[order[i]]) { int t = order[i]; order[i] = order[j]; order[j] = t; }
+    long long tot = 0;
+    for (int s = 0; s < n_scales; ++s) {
+        const int F = (int)num_frames(T, n_fft[s], hop[s], 0);
+        int nr = (F + kRunTarget / 2) / kRunTarget;
+        if (nr < 1) nr = 1;
+        const int nfr = n_fft[s] >= 2048 ? 1 : (n_fft[s] >= 512 ? 2 : (n_fft[s] >= 128 ? 4 : 8));
+        NR[s] = nr;
+        cpr[s] = (nr + nfr - 1) / nfr;                                  // warp-runs per row
+        tot += (rows * cpr[s] + kStreamWarps - 1) / kStreamWarps;
+    }
+    *total_ctas = tot;
+}
+
+size_t stream_workspace_bytes(int64_t rows, int64_t T, int n_scales, const int* n_fft, const int* hop) {
+    int order[TAC_MAX_SCALES], NR[TAC_MAX_SCALES], cpr[TAC_MAX_SCALES];
+    long long tot;
+    stream_layout(rows, T, n_scales, n_fft, hop, order, NR, cpr, &tot);
+    return (size_t)n_scales * 2 * align16((size_t)rows * T * sizeof(float)) + (size_t)tot * kStreamWarps * 2 * sizeof(double);
+}
+
+int launch_stream(const float* x, const float* y, int64_t rows, int64_t T, int n_scales, const int* n_fft, const int* hop,
+                  const int* win, float eps, const float* coef, double* sums, float* grad_y, void* workspace,
+                  size_t workspace_bytes, cudaStream_t st) {
+    const size_t need = stream_workspace_bytes(rows, T, n_scales, n_fft, hop);
+    if (!workspace || workspace_bytes < need)
+        return set_error(TAC_EWORKSPACE, "workspace needs %zu bytes, got %zu", need, workspace_bytes);
+    TAC_ALIGNED16(workspace, "workspace");
+    TAC_REQUIRE((((uintptr_t)x | (uintptr_t)y | (uintptr_t)grad_y) & 7u) == 0, "x, y, grad_y must be 8-byte aligned");
+    int order[TAC_MAX_SCALES], NR[TAC_MAX_SCALES], cpr[TAC_MAX_SCALES];
+    long long tot;
+    stream_layout(rows, T, n_scales, n_fft, hop, order, NR, cpr, &tot);
+    TAC_REQUIRE(tot < (1ll << 31), "grid too large");
+    StreamArgs a;
+    a.x = x; a.y = y; a.T = T; a.rows = rows; a.nscales = n_scales; a.total_ctas = (int)tot; a.eps = eps; a.coef = coef;
+    a.grad = grad_y;
+    unsigned char* ws = reinterpret_cast<unsigned char*>(workspace);
+    const size_t buf = align16((size_t)rows * T * sizeof(float));
+    a.partial = sums ? reinterpret_cast<double*>(ws + (size_t)n_scales * 2 * buf) : nullptr;
+    long long begin = 0;
+    for (int i = 0; i < n_scales; ++i) {
+        const int s = order[i];
+        StreamScale& sc = a.sc[i];
+        sc.n = n_fft[s]; sc.hop = hop[s]; sc.F = (int)num_frames(T, sc.n, sc.hop, 0); sc.NR = NR[s];
+        sc.cta_begin = (int)begin; sc.wpr = cpr[s]; sc.nwr = rows * cpr[s]; sc.orig = s;
+        sc.g = reinterpret_cast<float*>(ws + (size_t)(2 * i) * buf);
+        sc.h = reinterpret_cast<float*>(ws + (size_t)(2 * i + 1) * buf);
+        int rc = get_tables(sc.n, win ? win[s] : sc.n, 1, &sc.t);
+        if (rc) return rc;
+        begin += (rows * cpr[s] + kStreamWarps - 1) / kStreamWarps;
+    }
+    const size_t smem = (size_t)kStreamWarps * kStreamWarpFloat2 * sizeof(float2);
+    static bool attr_set = false;
+    if (!attr_set) {
+        TAC_CHECK_CUDA(cudaFuncSetAttribute(mrstft_stream_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        TAC_CHECK_CUDA(cudaFuncSetAttribute(mrstft_stream_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    if (sums) mrstft_stream_kernel<true><<<(unsigned)tot, kStreamThreads, smem, st>>>(a);
+    else mrstft_stream_kernel<false><<<(unsigned)tot, kStreamThreads, smem, st>>>(a);
+    TAC_LAUNCHED(1);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    const bool v4 = (T % 4 == 0) && ((reinterpret_cast<uintptr_t>(grad_y) & 15u) == 0);
+    const long long items = rows * (T / (v4 ? 4 : 2));
+    long long cg = (items + 255) / 256;
+    if (cg > 148 * 16) cg = 148 * 16;
+    if (v4) mrstft_combine_kernel<4><<<(unsigned)cg, 256, 0, st>>>(a);
+    else mrstft_combine_kernel<2><<<(unsigned)cg, 256, 0, st>>>(a);
+    TAC_LAUNCHED(1);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    if (sums) {
+        mrstft_stream_sums_kernel<<<2 * n_scales, 256, 0, st>>>(a, sums); TAC_LAUNCHED(1);
+        TAC_CHECK_CUDA(cudaGetLastError());
+    }
+    return TAC_OK;
+}
+
+}  // namespace tac

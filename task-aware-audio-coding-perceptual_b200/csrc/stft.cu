@@ -60,7 +60,7 @@ __device__ __forceinline__ void planes_task(const ScaleArg& sc, const float* til
     float zr[P::BQ], zi[P::BQ];
     const float2* __restrict__ win2 = sc.t.win2;
     const int hop = sc.hop;
-    auto load = [&](int fr, int m) -> float2 {
+    auto load = [&](auto, int fr, int m) -> float2 {
         int f = f_first + fr;
         f = f < f_end ? f : f_first;                       // invalid frames recompute the first one
         const float2 v = *reinterpret_cast<const float2*>(tile + (f * hop - tile_origin) + 2 * m);
@@ -166,7 +166,7 @@ __global__ void __launch_bounds__(kThreads, 1) stft_tiled_kernel(const TiledArgs
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* tile = reinterpret_cast<float*>(smem_raw);
     float* otile = tile + a.tile_len;                               // [2][K][TF+1]
-    float2* xbuf_all = reinterpret_cast<float2*>(otile + 2 * (size_t)a.K * (a.TF + 1));
+    float2* xbuf_all = reinterpret_cast<float2*>(otile + ((2 * (size_t)a.K * (a.TF + 1) + 3) & ~(size_t)3));   // 16-byte aligned
     __shared__ int s_next;
 
     const int ft = blockIdx.x % a.ntiles;
@@ -193,7 +193,7 @@ __global__ void __launch_bounds__(kThreads, 1) stft_tiled_kernel(const TiledArgs
         const int f_first = f0 + t * P::NFR;
         float zr[P::BQ], zi[P::BQ];
         const float2* __restrict__ win2 = a.t.win2;
-        auto load = [&](int fr, int m) -> float2 {
+        auto load = [&](auto, int fr, int m) -> float2 {
             int f = f_first + fr;
             f = f < f_end ? f : f_first;
             const float2 v = *reinterpret_cast<const float2*>(tile + (f - f0) * a.hop + 2 * m);
@@ -341,7 +341,7 @@ extern "C" int tac_stft_multi(const float* x, int64_t B, int64_t C, int64_t T, i
         a.out = reinterpret_cast<float*>(out[s]);
         int rc = get_tables(a.n, win ? win[s] : a.n, normalized, &a.t);
         if (rc) return rc;
-        const size_t smem = (size_t)a.tile_len * 4 + 2 * (size_t)a.K * (a.TF + 1) * 4 + (size_t)kWarps * kXbufFloat2 * 8;
+        const size_t smem = (size_t)a.tile_len * 4 + ((2 * (size_t)a.K * (a.TF + 1) + 3) & ~(size_t)3) * 4 + (size_t)kWarps * kXbufFloat2 * 8;
         TAC_REQUIRE(rows * a.ntiles < (1ll << 31), "grid too large");
         if (out_mode == TAC_OUT_MAGPHASE) {
             if (f_pad > 0) {

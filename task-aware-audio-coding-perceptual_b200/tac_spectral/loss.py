@@ -62,10 +62,12 @@ class _MRSTFTLoss(torch.autograd.Function):
         coef = grad_sums.to(torch.float32).contiguous()
         grad = torch.empty_like(yr)
         lib = L.lib()
+        nf, hp = L.int_array(n_ffts), L.int_array(hops)
+        ws_bytes = int(lib.tac_mrstft_workspace_bytes(B, T, S, nf, hp))
+        ws = torch.empty(max(ws_bytes, 16), dtype=torch.uint8, device=xr.device)
         with L.device_of(xr):
-            L.check(lib.tac_mrstft_loss_bwd(xr.data_ptr(), yr.data_ptr(), B, T, S, L.int_array(n_ffts),
-                                            L.int_array(hops), L.int_array(wins), eps, coef.data_ptr(),
-                                            grad.data_ptr(), None, 0, L.stream_of(xr)))
+            L.check(lib.tac_mrstft_loss_bwd(xr.data_ptr(), yr.data_ptr(), B, T, S, nf, hp, L.int_array(wins), eps,
+                                            coef.data_ptr(), grad.data_ptr(), ws.data_ptr(), ws_bytes, L.stream_of(xr)))
         return None, grad.reshape(yshape).to(ydtype), None, None, None, None
 
 

@@ -7,3 +7,4 @@ for so in variants/lib_*.so; do
   TAC_SPECTRAL_LIB=$PWD/$so timeout 300 python tools/time_legs.py 2>&1 | tail -7
 done 2>&1 | tee $OUT/ab_time.log
 timeout 300 python tools/check_eig.py 2>&1 | tee $OUT/ab_eig.log | tail -12
+for so in variants/lib_*.so; do TAC_SPECTRAL_LIB=$PWD/$so timeout 300 python tools/time_scales.py 2>&1 | tail -8; done | tee $OUT/ab_scales.log

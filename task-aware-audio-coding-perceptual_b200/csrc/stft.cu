@@ -236,6 +236,136 @@ __global__ void __launch_bounds__(kThreads, 1) stft_tiled_kernel(const TiledArgs
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// Front-end kernel (TAC_OUT_MAGPHASE): 16 warps per CTA, one warp task (NFR frames) per warp, so a CTA covers
+// TF = 16 * NFR consecutive frames of one row.  The per-warp exchange tiles are only needed during the transform and
+// the transposition tile only after it, so both live in the SAME shared memory (178 KiB for n = 2048 instead of
+// 248 KiB): 16 resident warps per SM instead of 8.  Magnitude and phase leave in two passes through a single
+// [K][TF + 1] tile (the transform results stay in registers in between); every (k) row is written as a contiguous run
+// of TF frames.  atan2 is a degree-15 odd minimax polynomial (1.2e-7 abs. error in fp32) instead of the library call.
+constexpr int kFeWarps = 16;
+constexpr int kFeThreads = kFeWarps * 32;
+
+__device__ __forceinline__ float fe_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float fe_rsqrt(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+
+__device__ __forceinline__ float fast_atan2(float y, float x) {
+    const float ax = fabsf(x), ay = fabsf(y);
+    const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
+    const float a = mx > 0.0f ? mn * fe_rcp(mx) : 0.0f;           // in [0, 1]
+    const float s = a * a;
+    float p = -0.004054559860378504f;
+    p = fmaf(p, s, 0.021862933412194252f);
+    p = fmaf(p, s, -0.05591228976845741f);
+    p = fmaf(p, s, 0.09642194956541061f);
+    p = fmaf(p, s, -0.1390862911939621f);
+    p = fmaf(p, s, 0.19946564733982086f);
+    p = fmaf(p, s, -0.33329859375953674f);
+    p = fmaf(p, s, 0.9999993443489075f);
+    float r = p * a;                                              // atan(min / max)
+    r = ay > ax ? 1.57079632679489661923f - r : r;
+    r = x < 0.0f ? 3.14159265358979323846f - r : r;
+    return copysignf(r, y);
+}
+
+template <class P>
+__global__ void __launch_bounds__(kFeThreads, 1) stft_frontend_kernel(const TiledArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float* tile = reinterpret_cast<float*>(smem_raw);
+    unsigned char* shared2 = smem_raw + (size_t)a.tile_len * sizeof(float);      // exchange tiles, then the transposition tile
+    float2* xbuf_all = reinterpret_cast<float2*>(shared2);
+    float* otile = reinterpret_cast<float*>(shared2);                            // [K][TF + 1]
+
+    const int TF = kFeWarps * P::NFR, TS = TF + 1;
+    const int ft = blockIdx.x % a.ntiles;
+    const long long row = blockIdx.x / a.ntiles;
+    const float* xr = a.x + row * a.T;
+    const int f0 = ft * TF;
+    const int f_end = min(a.F, f0 + TF);
+    stage_tile(tile, xr, (long long)f0 * a.hop - a.pad, a.tile_len, a.T, a.pad_mode, a.vec_ok != 0);
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float2* xbuf = xbuf_all + warp * kXbufFloat2;
+    const int f_first = f0 + warp * P::NFR;
+    const bool task = f_first < f_end;                             // warp-uniform
+    float zr[P::BQ], zi[P::BQ];
+    const float2* __restrict__ win2 = a.t.win2;
+    if (task) {
+        auto load = [&](auto, int fr, int m) -> float2 {
+            int f = f_first + fr;
+            f = f < f_end ? f : f_first;
+            const float2 v = *reinterpret_cast<const float2*>(tile + (f - f0) * a.hop + 2 * m);
+            const float2 w = ldg2(win2 + m);
+            return make_float2(__fmul_rn(v.x, w.x), __fmul_rn(v.y, w.y));   // never contracted: X(x) is bit-reproducible
+        };
+        warp_fft_fwd<P>(zr, zi, xbuf, a.t.tw, lane, load);
+    }
+    __syncthreads();                                               // every warp is done with its exchange tile
+    const int myf = f_first + lane / P::A;
+    const bool valid = task && myf < f_end;
+    const int col = myf - f0;
+    const int nf = f_end - f0;
+    float* out0 = a.out + (row * 2) * (long long)a.K * a.f_pad + f0;
+#pragma unroll 1
+    for (int plane = 0; plane < 2; ++plane) {
+        if (task) {
+            warp_fft_post<P>(zr, zi, a.t.pt, lane, [&](int, int k, float vr, float vi, int) {
+                float v;
+                if (plane == 0) {
+                    const float m2 = fmaf(vr, vr, vi * vi);
+                    v = m2 >= 1e-30f ? m2 * fe_rsqrt(m2) : 0.0f;    // |X| (<= 2 ulp); |X| < 1e-15 reads as 0
+                } else {
+                    v = fast_atan2(vi, vr);
+                }
+                if (valid) otile[k * TS + col] = v;
+            });
+        }
+        __syncthreads();
+        float* outp = out0 + (long long)plane * a.K * a.f_pad;
+        const int total = a.K * TF;
+        for (int i = threadIdx.x; i < total; i += kFeThreads) {
+            const int k = i / TF, tt = i % TF;                      // TF is a power of two: shift / mask
+            if (tt < nf) __stcs(outp + (long long)k * a.f_pad + tt, otile[k * TS + tt]);
+        }
+        __syncthreads();
+    }
+}
+
+template <class P>
+static int launch_frontend(TiledArgs a, long long rows, cudaStream_t st, bool* done) {
+    const int TF = kFeWarps * P::NFR;
+    a.TF = TF;
+    a.ntiles = (a.F + TF - 1) / TF;
+    a.tile_len = ((TF - 1) * a.hop + a.n + 3) & ~3;
+    const size_t xb = (size_t)kFeWarps * kXbufFloat2 * sizeof(float2);
+    const size_t ot = (size_t)a.K * (TF + 1) * sizeof(float);
+    const size_t smem = (size_t)a.tile_len * 4 + (xb > ot ? xb : ot);
+    *done = false;
+    if (smem > 200 * 1024 || rows * a.ntiles >= (1ll << 31)) return TAC_OK;      // caller falls back to the generic kernel
+    auto kern = stft_frontend_kernel<P>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        TAC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_set = true;
+    }
+    kern<<<(unsigned)(rows * a.ntiles), kFeThreads, smem, st>>>(a); TAC_LAUNCHED(1);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    *done = true;
+    return TAC_OK;
+}
+
+static int dispatch_frontend(const TiledArgs& a, long long rows, cudaStream_t st, bool* done) {
+    switch (a.n) {
+        case 2048: return launch_frontend<Plan2048>(a, rows, st, done);
+        case 1024: return launch_frontend<Plan1024>(a, rows, st, done);
+        case 512: return launch_frontend<Plan512>(a, rows, st, done);
+        case 256: return launch_frontend<Plan256>(a, rows, st, done);
+        case 128: return launch_frontend<Plan128>(a, rows, st, done);
+        default: return launch_frontend<Plan64>(a, rows, st, done);
+    }
+}
+
 template <class P, int MODE>
 static int launch_tiled(const TiledArgs& a, long long rows, size_t smem, cudaStream_t st) {
     auto kern = stft_tiled_kernel<P, MODE>;
@@ -353,7 +483,12 @@ extern "C" int tac_stft_multi(const float* x, int64_t B, int64_t C, int64_t T, i
                     TAC_CHECK_CUDA(cudaMemsetAsync(a.out, 0, (size_t)rows * 2 * a.K * (size_t)f_pad * sizeof(float), st));
                 }
             }
-            rc = dispatch_tiled<TAC_OUT_MAGPHASE>(a, rows, smem, st);
+            bool done = false;
+#ifndef TAC_NO_FRONTEND16
+            rc = dispatch_frontend(a, rows, st, &done);
+            if (rc) return rc;
+#endif
+            if (!done) rc = dispatch_tiled<TAC_OUT_MAGPHASE>(a, rows, smem, st);
         } else {
             rc = dispatch_tiled<TAC_OUT_COMPLEX>(a, rows, smem, st);
         }

@@ -380,10 +380,10 @@ extern "C" int tac_dpca_eig(const double* stats, int nv, int d, float* s, float*
         if (!workspace || workspace_bytes < need)
             return set_error(TAC_EWORKSPACE, "tac_dpca_eig with d=%d needs %zu workspace bytes", d, need);
         TAC_ALIGNED16(workspace, "workspace");
-        const size_t tsmem = (size_t)d * d * sizeof(double);
+        const size_t tsmem = dpca_eig_tri_smem_bytes(d);
         static bool attr_set = false;
         if (!attr_set) {
-            TAC_CHECK_CUDA(cudaFuncSetAttribute(dpca_eig_tri_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+            TAC_CHECK_CUDA(cudaFuncSetAttribute(dpca_eig_tri_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dpca_eig_tri_smem_bytes(kTriMaxD)));
             attr_set = true;
         }
         dpca_eig_tri_kernel<<<nv, kTriThreads, tsmem, st>>>(stats, d, s, v, mu, rank, reinterpret_cast<double*>(workspace)); TAC_LAUNCHED(1);

@@ -100,6 +100,9 @@ __device__ __forceinline__ int tri_sturm(const double* __restrict__ a, const dou
     return cnt;
 }
 
+// offset of Householder vector k (length d - k - 1) in the packed reflector store
+__host__ __device__ __forceinline__ int tri_refl_off(int k, int d) { return k * (d - 1) - (k * (k - 1)) / 2; }
+
 // phase time stamps (clock64) of view 0, read back by tools through tac_debug_eig_profile()
 __device__ long long g_tri_prof[8];
 #define TRI_STAMP(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) g_tri_prof[i] = clock64(); } while (0)
@@ -108,14 +111,15 @@ __global__ void __launch_bounds__(kTriThreads, 1)
 dpca_eig_tri_kernel(const double* __restrict__ stats, int d, float* __restrict__ s_out, float* __restrict__ v_out,
                     float* __restrict__ mu_out, int* __restrict__ rank_out, double* __restrict__ gws) {
     extern __shared__ __align__(16) unsigned char tri_smem_raw[];
-    double* A = reinterpret_cast<double*>(tri_smem_raw);            // [d][d]; later Z[row][col]
+    double* A = reinterpret_cast<double*>(tri_smem_raw);            // [d][d]; later Z[row][col] with leading dimension d + 1
+    const int ldz = d + 1;                                          // odd stride: a lane-per-row access pattern is conflict free
+    double* refl = A + (size_t)d * (d + 1);                         // packed Householder vectors: v_k at tri_refl_off(k, d), length d-k-1
     __shared__ TriShared sh;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int view = blockIdx.x;
     const size_t stride = 1 + d + (size_t)d * d;
     const double* st = stats + view * stride;
-    double* refl = gws + (size_t)view * 3 * d * d;                  // [k][i]   Householder vectors
-    double* Lp = refl + (size_t)d * d;                              // [i][slot] forward multipliers b_i / D+_i
+    double* Lp = gws + (size_t)view * 2 * d * d;                    // [i][slot] forward multipliers b_i / D+_i
     double* Um = Lp + (size_t)d * d;                                // [i][slot] backward multipliers b_{i-1} / D-_i
     const double n = st[0];
     const double inv_n = n > 0.0 ? 1.0 / n : 0.0;
@@ -192,7 +196,7 @@ dpca_eig_tri_kernel(const double* __restrict__ stats, int d, float* __restrict__
                 vi = x[tid] - (tid == 0 ? alpha : 0.0);
                 pi = beta * (qi - alpha * A[(size_t)(k + 1) * d + (k + 1) + tid]);
                 sh.vec_v[tid] = vi; sh.vec_p[tid] = pi;
-                refl[(size_t)k * d + tid] = beta != 0.0 ? vi : 0.0;
+                refl[tri_refl_off(k, d) + tid] = beta != 0.0 ? vi : 0.0;
             }
             const double pv = tri_warp_sum(vi * pi);
             if (lane == 0) sh.red[8 + warp] = pv;
@@ -271,9 +275,11 @@ dpca_eig_tri_kernel(const double* __restrict__ stats, int d, float* __restrict__
     const double tn = sh.scal[4];
 
     TRI_STAMP(3);
-    // ---- 3. eigenvalues: bisection on the Sturm count, one thread per slot (slot j = (j - s)-th smallest of block [s, e])
-    if (tid < d) {
-        const int slot = tid;
+    // ---- 3. eigenvalues: multisection on the Sturm count.  8 threads per slot (slot j = (j - s)-th smallest eigenvalue
+    // of block [s, e]) evaluate 8 interior points of the bracket per round, so the bracket shrinks 9x per round and all
+    // 1024 threads keep the float64 pipe busy (a Sturm count is one dependent chain of d steps).
+    {
+        const int slot = min(tid >> 3, d - 1), sub = tid & 7;        // spare groups recompute slot d - 1
         const int s = sh.blk_s[slot], e = sh.blk_e[slot], kk = slot - s;
         double gl = 1e300, gu = -1e300;
         for (int i = s; i <= e; ++i) {
@@ -281,17 +287,23 @@ dpca_eig_tri_kernel(const double* __restrict__ stats, int d, float* __restrict__
             gl = fmin(gl, sh.a[i] - r); gu = fmax(gu, sh.a[i] + r);
         }
         double lo = gl - 4.0 * eps, hi = gu + 4.0 * eps;
-        for (int it = 0; it < 56; ++it) {
-            const double x = 0.5 * (lo + hi);
+        const unsigned gshift = (unsigned)(lane & ~7);
+        for (int it = 0; it < 19; ++it) {                            // 9^19 > 2^60
+            const double step = (hi - lo) * (1.0 / 9.0);
+            const double x = fma(step, (double)(sub + 1), lo);
             const int c = tri_sturm(sh.a, sh.b2, s, e, x);
-            if (c <= kk) lo = x; else hi = x;
+            const unsigned below = (__ballot_sync(0xffffffffu, c <= kk) >> gshift) & 0xffu;   // points still left of the eigenvalue
+            const int q = __popc(below);                              // counts are monotone in x: the first q points
+            const double nlo = q > 0 ? fma(step, (double)q, lo) : lo;
+            const double nhi = q < 8 ? fma(step, (double)(q + 1), lo) : hi;
+            lo = nlo; hi = nhi;
         }
-        sh.lam[slot] = 0.5 * (lo + hi);
+        if (sub == 0 && (tid >> 3) < d) sh.lam[slot] = 0.5 * (lo + hi);
     }
     // Z[row][slot] = 0 (the tridiagonalised matrix is no longer needed)
     double* Z = A;
     __syncthreads();
-    for (int e = tid; e < d * d; e += kTriThreads) Z[e] = 0.0;
+    for (int e = tid; e < d * ldz; e += kTriThreads) Z[e] = 0.0;
     __syncthreads();
 
     TRI_STAMP(4);
@@ -325,20 +337,20 @@ dpca_eig_tri_kernel(const double* __restrict__ stats, int d, float* __restrict__
         }
         // z_r = 1; downwards with the forward multipliers, upwards with the backward ones
         double zz = 1.0, nrm = 1.0;
-        Z[(size_t)r * d + slot] = 1.0;
+        Z[(size_t)r * ldz + slot] = 1.0;
         for (int i = r - 1; i >= s; --i) {
             zz = -Lp[(size_t)i * d + slot] * zz;
-            Z[(size_t)i * d + slot] = zz;
+            Z[(size_t)i * ldz + slot] = zz;
             nrm = fma(zz, zz, nrm);
         }
         zz = 1.0;
         for (int i = r + 1; i <= e; ++i) {
             zz = -Um[(size_t)i * d + slot] * zz;
-            Z[(size_t)i * d + slot] = zz;
+            Z[(size_t)i * ldz + slot] = zz;
             nrm = fma(zz, zz, nrm);
         }
         const double inv = tri_rsqrt(nrm);
-        for (int i = s; i <= e; ++i) Z[(size_t)i * d + slot] *= inv;
+        for (int i = s; i <= e; ++i) Z[(size_t)i * ldz + slot] *= inv;
         // cluster detection (ascending inside a block)
         if (slot > s && l - sh.lam[slot - 1] <= 1e-9 * tn) sh.flag = 1;
     }
@@ -350,18 +362,18 @@ dpca_eig_tri_kernel(const double* __restrict__ stats, int d, float* __restrict__
                 bool changed = false;
                 for (int j = k - 1; j >= s && sh.lam[k] - sh.lam[j] <= 1e-9 * tn * (double)(k - j); --j) {
                     double dot = 0.0;
-                    for (int i = lane; i < d; i += 32) dot = fma(Z[(size_t)i * d + j], Z[(size_t)i * d + k], dot);
+                    for (int i = lane; i < d; i += 32) dot = fma(Z[(size_t)i * ldz + j], Z[(size_t)i * ldz + k], dot);
                     dot = tri_warp_sum(dot);
-                    for (int i = lane; i < d; i += 32) Z[(size_t)i * d + k] -= dot * Z[(size_t)i * d + j];
+                    for (int i = lane; i < d; i += 32) Z[(size_t)i * ldz + k] -= dot * Z[(size_t)i * ldz + j];
                     changed = true;
                     __syncwarp();
                 }
                 if (changed) {
                     double nn = 0.0;
-                    for (int i = lane; i < d; i += 32) nn = fma(Z[(size_t)i * d + k], Z[(size_t)i * d + k], nn);
+                    for (int i = lane; i < d; i += 32) nn = fma(Z[(size_t)i * ldz + k], Z[(size_t)i * ldz + k], nn);
                     nn = sqrt(tri_warp_sum(nn));
                     const double sc = nn > 1e-8 ? 1.0 / nn : 0.0;
-                    for (int i = lane; i < d; i += 32) Z[(size_t)i * d + k] *= sc;
+                    for (int i = lane; i < d; i += 32) Z[(size_t)i * ldz + k] *= sc;
                     __syncwarp();
                 }
             }
@@ -370,50 +382,60 @@ dpca_eig_tri_kernel(const double* __restrict__ stats, int d, float* __restrict__
     }
 
     TRI_STAMP(5);
-    // ---- 5. back-transformation  Z <- H_0 H_1 ... H_{d-3} Z  (reverse order; reflector k+... double-buffered in vec_v / vec_p)
+    // ---- 5. back-transformation  Z <- H_0 H_1 ... H_{d-3} Z  (reverse order).  Columns are independent: a warp keeps
+    // four columns of Z in registers (lane <-> rows lane, lane + 32, ...), reads each packed reflector from shared
+    // memory, reduces the four dot products with shuffles and updates in place -- no block barrier inside the loop.
     {
-        int kcur = d - 3;
-        while (kcur >= 0 && sh.beta[kcur] == 0.0) --kcur;
-        int buf = 0;
-        if (kcur >= 0 && tid < d - kcur - 1) sh.vec_v[tid] = refl[(size_t)kcur * d + tid];
-        __syncthreads();
-        while (kcur >= 0) {
-            const int k = kcur, m = d - k - 1;
-            const double beta = sh.beta[k];
-            const double* vv = buf ? sh.vec_p : sh.vec_v;
-            double* vnext = buf ? sh.vec_v : sh.vec_p;
-            int knext = k - 1;
-            while (knext >= 0 && sh.beta[knext] == 0.0) --knext;
-            double* zc = Z + (size_t)(k + 1) * d + ci;
-            if (ci < d) {
-                double a0 = 0.0, a1 = 0.0;
-                int i = cp;
-                for (; i + kTriParts < m; i += 2 * kTriParts) {
-                    a0 = fma(vv[i], zc[(size_t)i * d], a0);
-                    a1 = fma(vv[i + kTriParts], zc[(size_t)(i + kTriParts) * d], a1);
-                }
-                if (i < m) a0 = fma(vv[i], zc[(size_t)i * d], a0);
-                sh.part[cp][ci] = a0 + a1;
-            }
-            if (knext >= 0 && tid < d - knext - 1) vnext[tid] = refl[(size_t)knext * d + tid];   // prefetch the next reflector
-            __syncthreads();
-            if (ci < d) {
-                double t = 0.0;
+        double z[4][4];
+        int colj[4];
 #pragma unroll
-                for (int p = 0; p < kTriParts; ++p) t += sh.part[p][ci];
-                t *= beta;
-                int i = cp;
-                for (; i + kTriParts < m; i += 2 * kTriParts) {
-                    const double z0 = zc[(size_t)i * d], z1 = zc[(size_t)(i + kTriParts) * d];
-                    zc[(size_t)i * d] = fma(-vv[i], t, z0);
-                    zc[(size_t)(i + kTriParts) * d] = fma(-vv[i + kTriParts], t, z1);
-                }
-                if (i < m) zc[(size_t)i * d] = fma(-vv[i], t, zc[(size_t)i * d]);
+        for (int j = 0; j < 4; ++j) {
+            colj[j] = warp + 32 * j;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int r = lane + 32 * i;
+                z[j][i] = (colj[j] < d && r < d) ? Z[(size_t)r * ldz + colj[j]] : 0.0;
             }
-            __syncthreads();
-            kcur = knext; buf ^= 1;
         }
+        for (int k = d - 3; k >= 0; --k) {
+            const double beta = sh.beta[k];
+            if (beta == 0.0) continue;                               // uniform
+            const double* vk = refl + tri_refl_off(k, d) - (k + 1);  // vk[r] = component for row r > k
+            double v[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int r = lane + 32 * i;
+                v[i] = (r > k && r < d) ? vk[r] : 0.0;
+            }
+            double t[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                double acc = 0.0;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) acc = fma(v[i], z[j][i], acc);
+                t[j] = acc;
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) t[j] += __shfl_xor_sync(0xffffffffu, t[j], o);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const double tb = t[j] * beta;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) z[j][i] = fma(-v[i], tb, z[j][i]);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int r = lane + 32 * i;
+                if (colj[j] < d && r < d) Z[(size_t)r * ldz + colj[j]] = z[j][i];
+            }
     }
+    __syncthreads();
 
     TRI_STAMP(6);
     // ---- outputs: descending order by counting, s = sqrt(lambda), null directions -> zero columns
@@ -441,12 +463,13 @@ dpca_eig_tri_kernel(const double* __restrict__ stats, int d, float* __restrict__
         const int row = e / d, rk = e % d;                           // coalesced stores: consecutive threads -> consecutive ranks
         // inverse permutation: column whose rank is rk
         const int col = sh.inv[rk];
-        vo[e] = (float)(sh.lam[col] > null_thr ? Z[(size_t)row * d + col] : 0.0);
+        vo[e] = (float)(sh.lam[col] > null_thr ? Z[(size_t)row * ldz + col] : 0.0);
     }
     if (tid == 0) rank_out[view] = r_eff;
     TRI_STAMP(7);
 }
 
-inline size_t dpca_eig_tri_workspace_bytes(int nv, int d) { return (size_t)nv * 3 * d * d * sizeof(double); }
+inline size_t dpca_eig_tri_workspace_bytes(int nv, int d) { return (size_t)nv * 2 * d * d * sizeof(double); }
+inline size_t dpca_eig_tri_smem_bytes(int d) { return ((size_t)d * (d + 1) + (size_t)tri_refl_off(d - 1 > 0 ? d - 1 : 0, d) + d) * sizeof(double); }
 
 }  // namespace tac

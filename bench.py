@@ -227,6 +227,53 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+# ------------------------------------------------------------------------------------------ stock torch on the same GPU
+def torch_gpu_baseline(x, y, zs, dim_p, iters=10):
+    """The same step through the library calls the reference's call sites make (torch.stft -> cuFFT, autograd,
+    torch.svd -> cuSOLVER, boolean-mask selection, cuBLAS matmuls), on the same B200: BASELINE.md's "kernel to beat".
+    Written out here (not imported from oracle/): msstftd.py:125-127,151 convention for the loss scales, the notebook
+    front end (spectrogram.ipynb cell 10), data_pca + select + project of pkl_file_model_updated.py:37-42,489-511."""
+    import torch
+    dev = x.device
+    wins = {n: torch.hann_window(n, device=dev) for n in set(N_FFTS) | {2048}}
+    norm = {n: wins[n].pow(2).sum().sqrt() for n in N_FFTS}
+
+    def step():
+        D = torch.stft(x, 2048, 512, 2048, wins[2048], center=True, pad_mode="constant", return_complex=True)
+        fe = torch.stack([D.abs(), D.angle()], 1)
+        yr = y.detach().requires_grad_(True)
+        loss = 0.0
+        for n, h in zip(N_FFTS, HOPS):
+            X = torch.stft(x, n, h, n, wins[n], center=False, return_complex=True).abs() / norm[n]
+            Y = torch.stft(yr, n, h, n, wins[n], center=False, return_complex=True).abs() / norm[n]
+            loss = loss + (X - Y).abs().mean() + (X.clamp_min(1e-5).log() - Y.clamp_min(1e-5).log()).abs().mean()
+        (loss / len(N_FFTS)).backward()
+        pcs = []
+        for z in zs:
+            mu = z.mean(0)
+            _, sv, v = torch.svd(z - mu)
+            pcs.append((sv, v, mu))
+        ind = torch.argsort(torch.cat([p[0] for p in pcs]), descending=True)[:dim_p]
+        outs, off = [], 0
+        for z, (sv, v, mu) in zip(zs, pcs):
+            sel = ind[(ind >= off) & (ind < off + sv.numel())] - off
+            off += sv.numel()
+            zp = torch.matmul(z - mu, v[:, sel])
+            outs.append(torch.matmul(zp, v[:, sel].T) + mu)
+        return fe, yr.grad, outs, loss
+
+    for _ in range(2):
+        step()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(iters):
+        step()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / iters
+
+
 # ------------------------------------------------------------------------------------------ native
 def run_native(args):
     import torch
@@ -246,6 +293,7 @@ def run_native(args):
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/nccl_debug.%h.%p.log")   # keep stdout to the one JSON line
+        os.environ["NCCL_DEBUG"] = os.environ.get("TAC_NCCL_DEBUG", "WARN")      # (NCCL_DEBUG=VERSION prints to stdout)
         dist.init_process_group("nccl", device_id=dev)
         group = dist.group.WORLD
     lib = L.lib()
@@ -363,10 +411,20 @@ def run_native(args):
                             for k in legs},
                 "step_bytes": sum(byte_legs.values()), "step_gbs": sum(byte_legs.values()) / (ms_step * 1e-3) / 1e9,
                 "step_frac": sum(byte_legs.values()) / (ms_step * 1e-3) / 1e9 / peak}
+    # per-launch DRAM traffic and warp-instruction count of the dominant kernel, from the committed ncu capture
+    # (profiles/traffic.json: {leg: {"traffic": dram bytes read + written, "inst": smsp__inst_executed.sum, "source": file}})
     prof = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(prof):
         try:
-            roofline["traffic"] = json.load(open(prof)).get(dom)
+            ent = json.load(open(prof)).get(dom) or {}
+            roofline["traffic"] = ent.get("traffic")
+            if ent.get("inst"):
+                sm_hz = (clk.summary().get("sm_mhz") or 1965) * 1e6
+                n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
+                # the kernel is FP32-issue bound, not HBM bound: issued warp-instructions / (4 per SM per clock)
+                roofline["issue_frac"] = ent["inst"] / (leg_ms[dom] * 1e-3 * sm_hz * n_sm * 4)
+                roofline["issue_note"] = "warp instructions per launch (ncu) / (4 schedulers x SMs x SM clock x kernel time)"
+            roofline["traffic_source"] = ent.get("source")
         except Exception:
             pass
 
@@ -442,6 +500,14 @@ def run_native(args):
            "ms_per_step": 1e3 * float(dt.item()) / args.steps, "pipeline": "double-buffered: H2D of step i+1 overlaps compute of step i",
            "loss_last": e2e_vals[-1]}
 
+    tgpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            t_ms = torch_gpu_baseline(dsets[0][0], dsets[0][1], dsets[0][2], dim_p)
+            tgpu = {"value": audio_s_step / (t_ms * 1e-3), "unit": "audio-s/s", "ms_per_step": t_ms,
+                    "what": "same step via torch.stft (cuFFT) + autograd + torch.svd (cuSOLVER) + cuBLAS on this GPU, inputs resident, eager"}
+        except Exception as e:                                           # reported comparator only
+            tgpu = {"error": f"{type(e).__name__}: {e}"}
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
@@ -459,7 +525,7 @@ def run_native(args):
                            "launch": "cuda-graph replay" if graphs is not None else "eager",
                            "overlap": not args.no_overlap,
                            "l2": f"ring of {nsets} input sets ({nsets * set_bytes / 1e6:.0f} MB) > 126 MB L2"},
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
+                "roofline": roofline, "cpu_baseline": cpu, "torch_gpu_baseline": tgpu, "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
                 "launches_per_step": launches_per_step, "clocks": clk.summary(), "loss": loss_val}
         print(json.dumps(line), flush=True)
     sys.stdout.flush()

@@ -164,6 +164,28 @@ TAC_API int tac_dpca_project(const float* const* z, int nv, int64_t B, int d, co
  * indices of the k largest; var [d] float32, top_idx [k] int32 (descending variance). */
 TAC_API int tac_var_topk(const double* stats, int d, int k, float* var, int* top_idx, tac_stream_t stream);
 
+/* dB channel of the notebook front end: librosa.amplitude_to_db(S, ref=np.max) per utterance (spectrogram.ipynb cell 9
+ * L31-63, raw :2894-2913; amin 1e-5, top_db 80 are librosa's defaults).
+ *   mag  row r = magnitude plane [K][ld] float32 at mag + r * row_stride (only the first F columns of a row count: the
+ *        tac_stft_multi TAC_OUT_MAGPHASE output with row_stride = 2*K*f_pad, ld = f_pad is accepted as is)
+ *   out  [rows][K][F] float32;  workspace rows * 4 bytes. */
+TAC_API int tac_amplitude_to_db(const float* mag, int64_t rows, int64_t row_stride, int K, int F, int64_t ld, float amin,
+                        float top_db, float* out, void* workspace, size_t workspace_bytes, tac_stream_t stream);
+
+/* Latent regulariser of pkl_file_models.py:943-947 / pkl_file_model_updated.py:526-532 (z -= mean; z /= |z|_F;
+ * nuc = |z|_* / B) from the singular values tac_dpca_eig already produced: no second SVD.
+ *   out [nv] float32 = sum_i s_i / (sqrt(sum_i s_i^2) * n);  aux [nv][3] float64 = {sum s, |z|_F, n} (may be NULL). */
+TAC_API int tac_nuclear_from_s(const float* s, const int* rank, const double* stats, int nv, int d, float* out, double* aux,
+                       tac_stream_t stream);
+/* Backward helper: gm [nv][d][d] float32 with  d nuc / d z = (z - mean) gm  (V diag(1/s) V^T form of the nuclear-norm
+ * sub-gradient, null directions excluded); apply it with tac_dpca_apply(add_mean = 0). */
+TAC_API int tac_nuclear_grad_matrix(const float* s, const float* v, const int* rank, const double* aux, int nv, int d, float* gm,
+                            tac_stream_t stream);
+/* z_out_v = (z_v - mu_v) P_v (+ mu_v if add_mean) for nv views, P [nv][d][d] float32 row-major: the GEMM of
+ * tac_dpca_project with a caller-supplied matrix. */
+TAC_API int tac_dpca_apply(const float* const* z, int nv, int64_t B, int d, const float* P, const float* mu, int add_mean,
+                   float* const* z_out, tac_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -250,7 +250,7 @@ __global__ void dpca_projector_kernel(const float* __restrict__ vmat, const int*
 
 // z_out = (z - mu) P + mu.  grid (ceil(B/32), ceil(d/32), nv), 256 threads, 32x32 output tile.
 __global__ void __launch_bounds__(256) dpca_apply_kernel(const ViewPtrs vp, long long B, int d, const float* __restrict__ P,
-                                                        const float* __restrict__ mu) {
+                                                        const float* __restrict__ mu, int add_mean) {
     __shared__ float sz[32][33], sp[32][33];
     const int v = blockIdx.z;
     const float* z = vp.z[v];
@@ -281,7 +281,7 @@ __global__ void __launch_bounds__(256) dpca_apply_kernel(const ViewPtrs vp, long
     }
     const int col = c0 + tx;
     if (col < d) {
-        const float mc = __ldg(m + col);
+        const float mc = add_mean ? __ldg(m + col) : 0.0f;
         for (int a = 0; a < 4; ++a) {
             const long long row = r0 + ty * 4 + a;
             if (row < B) out[row * d + col] = acc[a] + mc;
@@ -307,6 +307,54 @@ __global__ void __launch_bounds__(256) var_topk_kernel(const double* __restrict_
         int rk = 0;
         for (int i = 0; i < d; ++i) rk += (sv[i] > me) || (sv[i] == me && i < j);
         if (rk < k) top_idx[rk] = j;
+    }
+}
+
+// ------------------------------------------------------------------------------------------ nuclear-norm regulariser
+// pkl_file_models.py:943-947 / pkl_file_model_updated.py:526-532:  z -= mean; z /= |z|_F; nuc = |z|_* / B.
+// With the singular values s of the centred batch (tac_dpca_eig): |z|_F = sqrt(sum s^2), |z|_* = sum s.
+// out[v] = sum s / (|z|_F * n);  aux[v] = {sum s, |z|_F, n}.  grid (nv), block 256.
+__global__ void __launch_bounds__(256) nuclear_kernel(const float* __restrict__ s, const int* __restrict__ rank, const double* __restrict__ stats,
+                                                     int d, float* __restrict__ out, double* __restrict__ aux) {
+    __shared__ double sh[2][256];
+    const int v = blockIdx.x;
+    const int r = min(rank[v], d);
+    double a = 0.0, q = 0.0;
+    for (int i = threadIdx.x; i < r; i += 256) { const double x = (double)s[(size_t)v * d + i]; a += x; q = fma(x, x, q); }
+    sh[0][threadIdx.x] = a; sh[1][threadIdx.x] = q;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) { sh[0][threadIdx.x] += sh[0][threadIdx.x + o]; sh[1][threadIdx.x] += sh[1][threadIdx.x + o]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        const double n = stats[(size_t)v * (1 + d + (size_t)d * d)];
+        const double fro = sqrt(sh[1][0]);
+        out[v] = (fro > 0.0 && n > 0.0) ? (float)(sh[0][0] / (fro * n)) : 0.0f;
+        if (aux) { aux[3 * v] = sh[0][0]; aux[3 * v + 1] = fro; aux[3 * v + 2] = n; }
+    }
+}
+
+// Gm_v = (V diag(1 / s_i) V^T - (sum s / fro^2) I) / (fro * n):  d nuc / d z = (z - mean) Gm  (null directions carry the zero
+// sub-gradient).  grid (d, nv), block d rounded up to a warp.
+__global__ void nuclear_grad_matrix_kernel(const float* __restrict__ s, const float* __restrict__ vmat, const int* __restrict__ rank,
+                                           const double* __restrict__ aux, int d, float* __restrict__ gm) {
+    __shared__ float rowi[kMaxD];
+    const int v = blockIdx.y, i = blockIdx.x, j = threadIdx.x;
+    const float* V = vmat + (size_t)v * d * d;
+    const int r = min(rank[v], d);
+    const double sum_s = aux[3 * v], fro = aux[3 * v + 1], n = aux[3 * v + 2];
+    const float smax = s[(size_t)v * d];
+    for (int t = threadIdx.x; t < r; t += blockDim.x) {
+        const float sv = s[(size_t)v * d + t];
+        rowi[t] = sv > 1e-6f * smax ? V[(size_t)i * d + t] / sv : 0.0f;
+    }
+    __syncthreads();
+    if (j < d) {
+        float acc = 0.0f;
+        for (int t = 0; t < r; ++t) acc = fmaf(rowi[t], __ldg(V + (size_t)j * d + t), acc);
+        double g = (double)acc - (i == j ? sum_s / (fro * fro) : 0.0);
+        gm[((size_t)v * d + i) * d + j] = (fro > 0.0 && n > 0.0) ? (float)(g / (fro * n)) : 0.0f;
     }
 }
 
@@ -427,7 +475,7 @@ extern "C" int tac_dpca_project(const float* const* z, int nv, int64_t B, int d,
     float* P = reinterpret_cast<float*>(workspace);
     dpca_projector_kernel<<<dim3(d, nv), ((d + 31) / 32) * 32, 0, st>>>(v, idx, cnt, d, P); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
-    dpca_apply_kernel<<<dim3((unsigned)((B + 31) / 32), (d + 31) / 32, nv), 256, 0, st>>>(vp, B, d, P, mu); TAC_LAUNCHED(1);
+    dpca_apply_kernel<<<dim3((unsigned)((B + 31) / 32), (d + 31) / 32, nv), 256, 0, st>>>(vp, B, d, P, mu, 1); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
     return TAC_OK;
 }
@@ -443,5 +491,39 @@ extern "C" int tac_var_topk(const double* stats, int d, int k, float* var, int* 
 // Development aid (not part of the documented ABI): clock64 stamps of the last tac_dpca_eig (d <= 128), view 0.
 extern "C" TAC_API int tac_debug_eig_profile(long long* out8) {
     TAC_CHECK_CUDA(cudaMemcpyFromSymbol(out8, tac::g_tri_prof, 8 * sizeof(long long)));
+    return TAC_OK;
+}
+
+extern "C" int tac_nuclear_from_s(const float* s, const int* rank, const double* stats, int nv, int d, float* out, double* aux,
+                                  tac_stream_t stream) {
+    TAC_REQUIRE(s && rank && stats && out, "null argument");
+    TAC_REQUIRE(nv >= 1 && nv <= kMaxViews && d >= 1 && d <= kMaxD, "bad nv / d");
+    nuclear_kernel<<<nv, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(s, rank, stats, d, out, aux); TAC_LAUNCHED(1);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    return TAC_OK;
+}
+
+extern "C" int tac_nuclear_grad_matrix(const float* s, const float* v, const int* rank, const double* aux, int nv, int d, float* gm,
+                                       tac_stream_t stream) {
+    TAC_REQUIRE(s && v && rank && aux && gm, "null argument");
+    TAC_REQUIRE(nv >= 1 && nv <= kMaxViews && d >= 1 && d <= kMaxD, "bad nv / d");
+    nuclear_grad_matrix_kernel<<<dim3(d, nv), ((d + 31) / 32) * 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(s, v, rank, aux, d, gm);
+    TAC_LAUNCHED(1);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    return TAC_OK;
+}
+
+extern "C" int tac_dpca_apply(const float* const* z, int nv, int64_t B, int d, const float* P, const float* mu, int add_mean,
+                              float* const* z_out, tac_stream_t stream) {
+    TAC_REQUIRE(z && P && mu && z_out, "null argument");
+    TAC_REQUIRE(nv >= 1 && nv <= kMaxViews && d >= 1 && d <= kMaxD && B >= 1, "bad nv / d / B");
+    ViewPtrs vp;
+    for (int i = 0; i < nv; ++i) {
+        TAC_REQUIRE(z[i] && z_out[i], "z[%d] / z_out[%d] is null", i, i);
+        vp.z[i] = z[i]; vp.out[i] = z_out[i];
+    }
+    dpca_apply_kernel<<<dim3((unsigned)((B + 31) / 32), (d + 31) / 32, nv), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        vp, B, d, P, mu, add_mean ? 1 : 0); TAC_LAUNCHED(1);
+    TAC_CHECK_CUDA(cudaGetLastError());
     return TAC_OK;
 }

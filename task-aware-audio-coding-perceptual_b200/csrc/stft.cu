@@ -392,9 +392,65 @@ static int dispatch_tiled(const TiledArgs& a, long long rows, size_t smem, cudaS
     }
 }
 
+// ------------------------------------------------------------------------------------------ dB channel
+// librosa.amplitude_to_db(S, ref=np.max) per utterance (spectrogram.ipynb cell 9 L31-63, raw :2894-2913):
+//   db = 20 log10(max(S, amin)) - 20 log10(max(amin, max S)),  floored at max(db) - top_db.
+// Pass 1: per-row maximum of the magnitude plane (non-negative floats order like their bit patterns: atomicMax on
+// unsigned).  Pass 2: element-wise.  max(db) = 20 log10(max(max S, amin)) - ref = 0 whenever max S >= amin.
+__global__ void __launch_bounds__(256) db_rowmax_kernel(const float* __restrict__ mag, long long row_stride, int K, int F, long long ld,
+                                                       unsigned* __restrict__ rowmax) {
+    const long long row = blockIdx.y;
+    const float* m = mag + row * row_stride;
+    const long long total = (long long)K * F;
+    float v = 0.0f;
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+        const long long k = i / F, t = i - k * F;
+        v = fmaxf(v, __ldg(m + k * ld + t));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(rowmax + row, __float_as_uint(v));
+}
+
+__global__ void __launch_bounds__(256) db_apply_kernel(const float* __restrict__ mag, long long row_stride, int K, int F, long long ld,
+                                                      const unsigned* __restrict__ rowmax, float amin, float top_db,
+                                                      float* __restrict__ out) {
+    const long long row = blockIdx.y;
+    const float* m = mag + row * row_stride;
+    float* o = out + row * (long long)K * F;
+    const float mx = fmaxf(__uint_as_float(rowmax[row]), amin);
+    const float ref = 20.0f * log10f(mx);
+    const float floor_db = -top_db;                                  // max(db) - top_db with max(db) = 0
+    const long long total = (long long)K * F;
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+        const long long k = i / F, t = i - k * F;
+        const float db = 20.0f * log10f(fmaxf(__ldg(m + k * ld + t), amin)) - ref;
+        o[i] = fmaxf(db, floor_db);
+    }
+}
+
 }  // namespace tac
 
 using namespace tac;
+
+extern "C" int tac_amplitude_to_db(const float* mag, int64_t rows, int64_t row_stride, int K, int F, int64_t ld, float amin,
+                                   float top_db, float* out, void* workspace, size_t workspace_bytes, tac_stream_t stream) {
+    TAC_REQUIRE(mag && out && workspace, "null argument");
+    TAC_REQUIRE(rows >= 1 && rows < 65536 && K >= 1 && F >= 1 && ld >= F, "bad shape (rows < 65536, ld >= F)");
+    TAC_REQUIRE(amin > 0.0f && top_db >= 0.0f, "amin must be positive, top_db non-negative");
+    if (workspace_bytes < (size_t)rows * sizeof(unsigned)) return set_error(TAC_EWORKSPACE, "workspace needs %zu bytes", (size_t)rows * sizeof(unsigned));
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    unsigned* rowmax = reinterpret_cast<unsigned*>(workspace);
+    TAC_CHECK_CUDA(cudaMemsetAsync(rowmax, 0, (size_t)rows * sizeof(unsigned), st));
+    long long gx = ((long long)K * F + 255) / 256;
+    gx = gx < 1 ? 1 : (gx > 32 ? 32 : gx);
+    db_rowmax_kernel<<<dim3((unsigned)gx, (unsigned)rows), 256, 0, st>>>(mag, row_stride, K, F, ld, rowmax); TAC_LAUNCHED(1);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    db_apply_kernel<<<dim3((unsigned)gx, (unsigned)rows), 256, 0, st>>>(mag, row_stride, K, F, ld, rowmax, amin, top_db, out); TAC_LAUNCHED(1);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    return TAC_OK;
+}
+
 
 extern "C" int tac_stft_multi(const float* x, int64_t B, int64_t C, int64_t T, int n_scales, const int* n_fft,
                               const int* hop, const int* win, int center, int pad_mode, int normalized,

@@ -13,11 +13,11 @@ There is no CPU or eager-PyTorch fallback: every op raises ``RuntimeError`` when
 ``libtac_spectral.so`` is missing or its input is not on a CUDA device.
 """
 from . import _lib
-from .stft import (Spectrogram, MultiScaleSTFT, stft_multi, complex_spectrogram, create_complex_spectrogram,
+from .stft import (Spectrogram, MultiScaleSTFT, stft_multi, complex_spectrogram, create_complex_spectrogram, amplitude_to_db,
                    num_frames, SUPPORTED_NFFT)
 from .loss import mrstft_loss, mrstft_sums, mrstft_counts, spectral_losses, LOG_FLOOR
-from .dpca import data_pca, dpca_project, dpca_select, dpca_stats, dpca_eig, apply_pca, var_topk
+from .dpca import data_pca, dpca_project, dpca_select, dpca_stats, dpca_eig, apply_pca, var_topk, nuclear_loss
 
-__all__ = ["Spectrogram", "MultiScaleSTFT", "stft_multi", "complex_spectrogram", "create_complex_spectrogram",
+__all__ = ["Spectrogram", "MultiScaleSTFT", "stft_multi", "complex_spectrogram", "create_complex_spectrogram", "amplitude_to_db",
            "num_frames", "SUPPORTED_NFFT", "mrstft_loss", "mrstft_sums", "mrstft_counts", "spectral_losses",
-           "LOG_FLOOR", "data_pca", "dpca_project", "dpca_select", "dpca_stats", "dpca_eig", "apply_pca", "var_topk"]
+           "LOG_FLOOR", "data_pca", "dpca_project", "dpca_select", "dpca_stats", "dpca_eig", "apply_pca", "var_topk", "nuclear_loss"]

@@ -41,6 +41,10 @@ SIGNATURES = {
     "tac_dpca_select": (_I, [_VP, _VP, _I, _I, _I, _VP, _VP, _VP]),
     "tac_dpca_project": (_I, [_VPP, _I, _I64, _I, _VP, _VP, _VP, _VP, _VPP, _VP, _SZ, _VP]),
     "tac_var_topk": (_I, [_VP, _I, _I, _VP, _VP, _VP]),
+    "tac_amplitude_to_db": (_I, [_VP, _I64, _I64, _I, _I, _I64, _F, _F, _VP, _VP, _SZ, _VP]),
+    "tac_nuclear_from_s": (_I, [_VP, _VP, _VP, _I, _I, _VP, _VP, _VP]),
+    "tac_nuclear_grad_matrix": (_I, [_VP, _VP, _VP, _VP, _I, _I, _VP, _VP]),
+    "tac_dpca_apply": (_I, [_VPP, _I, _I64, _I, _VP, _VP, _I, _VPP, _VP]),
 }
 
 PAD_ZERO, PAD_REFLECT = 0, 1

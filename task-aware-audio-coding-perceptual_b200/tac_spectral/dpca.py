@@ -190,3 +190,50 @@ def var_topk(z: torch.Tensor, k: int, group=None):
         L.check(L.lib().tac_var_topk(stats.data_ptr(), d, int(k), var.data_ptr(), top.data_ptr(), L.stream_of(z)))
     idx = top.long()
     return z.index_select(1, idx), idx
+
+
+class _Nuclear(torch.autograd.Function):
+    """``|zc / |zc|_F|_* / B`` with ``zc = z - mean``: forward from the eigen-solve of the Gram matrix, backward
+    ``grad_z = g * (z - mean) Gm`` with ``Gm = (V diag(1/s) V^T - (sum s / |zc|_F^2) I) / (|zc|_F B)``."""
+
+    @staticmethod
+    def forward(ctx, z, algo, group):
+        zc = z.contiguous().float()
+        B, d = zc.shape
+        stats = _allreduce_stats(dpca_stats([zc], algo), group)
+        s, v, mu, rank = dpca_eig(stats, d)
+        out = torch.empty(1, dtype=torch.float32, device=zc.device)
+        aux = torch.empty(3, dtype=torch.float64, device=zc.device)
+        with L.device_of(zc):
+            L.check(L.lib().tac_nuclear_from_s(s.data_ptr(), rank.data_ptr(), stats.data_ptr(), 1, d, out.data_ptr(),
+                                               aux.data_ptr(), L.stream_of(zc)))
+        ctx.save_for_backward(zc, s, v, mu, rank, aux)
+        ctx.meta = (z.shape, z.dtype)
+        return out[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        zc, s, v, mu, rank, aux = ctx.saved_tensors
+        B, d = zc.shape
+        gm = torch.empty((1, d, d), dtype=torch.float32, device=zc.device)
+        grad = torch.empty_like(zc)
+        lib = L.lib()
+        with L.device_of(zc):
+            st = L.stream_of(zc)
+            L.check(lib.tac_nuclear_grad_matrix(s.data_ptr(), v.data_ptr(), rank.data_ptr(), aux.data_ptr(), 1, d, gm.data_ptr(), st))
+            L.check(lib.tac_dpca_apply(L.ptr_array([zc]), 1, B, d, gm.data_ptr(), mu.data_ptr(), 0, L.ptr_array([grad]), st))
+        shape, dtype = ctx.meta
+        return (grad * g.to(grad.dtype)).reshape(shape).to(dtype), None, None
+
+
+def nuclear_loss(z_sample: torch.Tensor, algo: Optional[str] = None, group=None) -> torch.Tensor:
+    """The reference's latent regulariser (``pkl_file_model_updated.py:526-532``, ``pkl_file_models.py:943-947``):
+    centre, divide by the Frobenius norm, nuclear norm / batch size -- from the Gram eigen-solve that DPCA already
+    runs (``sum sqrt(eig) / sqrt(sum eig) / B``) instead of a second SVD.  ``z_sample`` is ``[B, d]``, ``d <= 256``
+    (the concatenated views of ``torch.cat((z1, z2), dim=1)``); with ``group`` the batch of all ranks is used."""
+    L.require_cuda(z_sample, "z_sample")
+    if z_sample.dim() != 2:
+        raise ValueError(f"expected z_sample of shape [B, d], got {tuple(z_sample.shape)}")
+    if z_sample.shape[1] > 256:
+        raise ValueError("nuclear_loss supports d <= 256")
+    return _Nuclear.apply(z_sample, algo, group)

@@ -172,3 +172,29 @@ def create_complex_spectrogram(y: torch.Tensor, sr: int, n_fft: int = 2048, hop_
         mag, ph = mag[0], ph[0]
     return {"magnitude": mag, "phase": ph,
             "params": {"sr": sr, "n_fft": n_fft, "hop_length": hop_length, "win_length": win_length, "window": "hann"}}
+
+
+def amplitude_to_db(spec: torch.Tensor, n_frames: Optional[int] = None, amin: float = 1e-5, top_db: float = 80.0) -> torch.Tensor:
+    """``librosa.amplitude_to_db(magnitude, ref=np.max)`` per utterance (notebook cell 9 L31-63): ``spec`` is the
+    ``[B, 2, K, f_pad]`` output of :func:`complex_spectrogram` (its magnitude plane is used in place) or a plain
+    magnitude ``[B, K, F]``; ``n_frames`` = number of real (unpadded) frames.  Returns ``[B, K, n_frames]``."""
+    L.require_cuda(spec, "spec")
+    if spec.dim() == 4 and spec.shape[1] == 2:
+        B, _, K, ld = spec.shape
+        row_stride = 2 * K * ld
+    elif spec.dim() == 3:
+        B, K, ld = spec.shape
+        row_stride = K * ld
+    else:
+        raise ValueError(f"expected [B, 2, K, F] or [B, K, F], got {tuple(spec.shape)}")
+    if spec.dtype != torch.float32 or not spec.is_contiguous():
+        raise ValueError("spec must be contiguous float32")
+    F = int(n_frames) if n_frames is not None else ld
+    if not 1 <= F <= ld:
+        raise ValueError(f"n_frames must be in [1, {ld}]")
+    out = torch.empty((B, K, F), dtype=torch.float32, device=spec.device)
+    ws = torch.empty(max(4 * B, 16), dtype=torch.uint8, device=spec.device)
+    with L.device_of(spec):
+        L.check(L.lib().tac_amplitude_to_db(spec.data_ptr(), B, row_stride, K, F, ld, float(amin), float(top_db), out.data_ptr(),
+                                            ws.data_ptr(), 4 * B, L.stream_of(spec)))
+    return out

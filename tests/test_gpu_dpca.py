@@ -150,3 +150,21 @@ def test_dpca_errors(ts):
         ts.dpca_project([torch.randn(8, 300, device="cuda")], 4)
     with pytest.raises(RuntimeError):
         ts.dpca_project([torch.randn(8, 200, device="cuda")], 4, algo="tf32x3")     # tensor-core Gram needs d <= 128
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("B,d", [(256, 128), (64, 32), (300, 256), (16, 64)])
+def test_nuclear_loss_forward_backward(ts, B, d):
+    """Next row 8f-1: |zc/|zc|_F|_* / B (pkl_file_model_updated.py:526-532) from the Gram eigenvalues; fp32 rtol 1e-4
+    on the value, gradient against torch autograd of the float64 oracle (rtol 1e-3 of the largest entry: 1/s amplifies
+    the fp32 rounding of the small singular values)."""
+    z = O.synth_latents(B, d, 1, seed=91)[0]
+    ref_in = z.double().requires_grad_(True)
+    ref = O.nuclear_loss_ref(ref_in)
+    ref.backward()
+    zg = z.cuda().requires_grad_(True)
+    got = ts.nuclear_loss(zg)
+    assert abs(float(got.detach()) - float(ref.detach())) <= 1e-4 * abs(float(ref.detach())), (float(got.detach()), float(ref.detach()))
+    got.backward()
+    err = (zg.grad.cpu().double() - ref_in.grad).abs().max()
+    assert float(err) <= 1e-3 * float(ref_in.grad.abs().max()), float(err / ref_in.grad.abs().max())

@@ -148,3 +148,22 @@ def test_errors(ts):
         ts.stft_multi(torch.randn(1, 1, 4000), [512], [128])  # CPU tensor: no fallback
     with pytest.raises(ValueError):
         ts.Spectrogram(n_fft=512, window_fn=torch.hamming_window, power=None)
+
+
+@pytest.mark.gpu
+def test_amplitude_to_db(ts):
+    """dB channel of the notebook front end (cell 9): librosa.amplitude_to_db(|D|, ref=np.max), per utterance; absolute
+    tolerance 1e-3 dB (20*log10 amplifies the 1e-7 relative error of |D| by 8.7)."""
+    (y,), _ = O.synth_audio(3, 16000, 1, seed=17)
+    y[1] *= 1e-3                                              # a quiet utterance: its own reference level
+    mag, _ = O.frontend_ref(y)
+    ref = O.amplitude_to_db_ref(mag)
+    spec = ts.complex_spectrogram(y.cuda(), f_pad=40)         # padded layout, 32 real frames
+    got = ts.amplitude_to_db(spec, n_frames=32)
+    assert got.shape == (3, 1025, 32)
+    assert float((got.cpu() - ref).abs().max()) < 1e-3
+    assert float(got.max()) == 0.0 and float(got.min()) >= -80.0
+    plain = ts.amplitude_to_db(mag.cuda().contiguous())
+    assert float((plain.cpu() - ref).abs().max()) < 1e-3
+    with pytest.raises(ValueError):
+        ts.amplitude_to_db(spec, n_frames=41)

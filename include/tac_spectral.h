@@ -186,6 +186,42 @@ TAC_API int tac_nuclear_grad_matrix(const float* s, const float* v, const int* r
 TAC_API int tac_dpca_apply(const float* const* z, int nv, int64_t B, int d, const float* P, const float* mu, int add_mean,
                    float* const* z_out, tac_stream_t stream);
 
+/* ---- next row: batched inverse STFT ------------------------------------------------------------
+ * Replaces batch_reconstruct_waveform, train_pkl_file_task_aware.py:174-208 (magnitude * exp(1j * phase), then a Python
+ * list comprehension of torch.istft(n_fft=2048, hop_length=512, win_length=2048, hann) per item, then torch.stack), and
+ * reconstruct_waveform (:210-236).  One launch for the whole batch: polar -> complex, one-sided inverse real FFT,
+ * synthesis window, overlap-add and division by the window envelope fused; semantics of torch.istft(center, normalized,
+ * onesided=True, length).
+ *   in_mode  TAC_IN_POLAR    a = magnitude, b = phase   (float32 planes)
+ *            TAC_IN_PLANES   a = real,      b = imaginary
+ *            TAC_IN_COMPLEX  a = interleaved complex64, b ignored (strides in complex elements)
+ *   element (row r, bin k, frame f) lives at a[r * row_stride + k * ld + f]; K = n_fft/2 + 1 bins, F frames -- the two
+ *   planes of the [B, 2, 1025, 600] decoder output are passed as a = base, b = base + K*ld, row_stride = 2*K*ld, ld = 600
+ *   out      [rows][out_len] float32; tac_istft_length() samples are produced per row (hop*(F-1) when centred),
+ *            cropped to out_len; a larger out_len continues into the padded tail of the overlap-added signal and is
+ *            zero-filled behind it, exactly like torch.istft(length=)
+ * hop must lie in [n_fft/8, n_fft]; the call fails with TAC_EINVAL (as torch.istft raises) when the overlap-added squared
+ * window vanishes inside the kept range.  No workspace. */
+#define TAC_IN_POLAR 0
+#define TAC_IN_PLANES 1
+#define TAC_IN_COMPLEX 2
+TAC_API int64_t tac_istft_length(int64_t F, int n_fft, int hop, int center);
+TAC_API int tac_istft(const float* a, const float* b, int in_mode, int64_t rows, int64_t row_stride, int64_t ld, int64_t F,
+              int n_fft, int hop, int win, int center, int normalized, float* out, int64_t out_len, tac_stream_t stream);
+
+/* ---- next row (second half): pairwise cosine loss of the view latents --------------------------
+ * Replaces  cos_sim = torch.nn.CosineSimilarity(); cos_loss = torch.mean(cos_sim(z1, z2) [+ ... all six pairs])
+ * at pkl_file_models.py:390-391, 761-763 and pkl_file_model_updated.py:429-430, 513-514.
+ *   z      host array of nv (2, 3 or 4) device pointers, each [B][d] float32 row-major
+ *   sum    [1] float64 (device) = sum_b sum_{i<j} cos(z_i[b], z_j[b]) -- SUM-reducible across batch shards; the caller
+ *          divides by the global batch.  eps: torch's clamp on each norm (1e-8).
+ *   bwd    grad_z[i] [B][d] = scale * (*gscale if gscale else 1) * d(sum)/dz_i  (scale = 1 / global batch). */
+TAC_API size_t tac_cosine_pairs_workspace_bytes(int64_t B);
+TAC_API int tac_cosine_pairs_fwd(const float* const* z, int nv, int64_t B, int d, float eps, double* sum, void* workspace,
+                         size_t workspace_bytes, tac_stream_t stream);
+TAC_API int tac_cosine_pairs_bwd(const float* const* z, int nv, int64_t B, int d, float eps, const float* gscale, float scale,
+                         float* const* grad_z, tac_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

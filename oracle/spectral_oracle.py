@@ -278,6 +278,44 @@ def nuclear_loss_ref(z_sample: torch.Tensor) -> torch.Tensor:
     return torch.linalg.svdvals(zc).sum() / z_sample.shape[0]
 
 
+def pairwise_cosine_loss_ref(zs: Sequence[torch.Tensor]) -> torch.Tensor:
+    """``cos_sim = torch.nn.CosineSimilarity(); cos_loss = torch.mean(cos_sim(z1, z2) + cos_sim(z1, z3) + ...)`` over all
+    view pairs (``pkl_file_models.py:390-391, 761-763``; ``pkl_file_model_updated.py:429-430, 513-514``)."""
+    cos_sim = torch.nn.CosineSimilarity()
+    total = None
+    for i in range(len(zs)):
+        for j in range(i + 1, len(zs)):
+            c = cos_sim(zs[i], zs[j])
+            total = c if total is None else total + c
+    return torch.mean(total)
+
+
+# --------------------------------------------------------------------------------------------
+# Inverse STFT (SURVEY.md section 8f rank 2)
+# --------------------------------------------------------------------------------------------
+
+def istft_ref(spec: torch.Tensor, n_fft: int, hop: int, win: int | None = None, *, center: bool = True,
+              normalized: bool = False, length: int | None = None) -> torch.Tensor:
+    """``torch.istft`` with the periodic Hann window the reference builds (``torch.hann_window(win_length)``,
+    ``train_pkl_file_task_aware.py:189``); ``spec`` complex ``[B, K, F]``."""
+    win = n_fft if win is None else win
+    return torch.istft(spec, n_fft=n_fft, hop_length=hop, win_length=win, window=hann_periodic(win), center=center,
+                       normalized=normalized, length=length, return_complex=False)
+
+
+def batch_reconstruct_waveform_ref(magnitude_batch: torch.Tensor, phase_batch: torch.Tensor, n_fft: int = 2048,
+                                   hop_length: int = 512, win_length: int = 2048) -> torch.Tensor:
+    """``batch_reconstruct_waveform`` (``train_pkl_file_task_aware.py:174-208``): ``mag * exp(1j * phase)``, then
+    ``torch.istft`` item by item (list comprehension of ``:195-205``), then ``torch.stack`` (``:208``)."""
+    if magnitude_batch.shape != phase_batch.shape:
+        raise ValueError("The shapes of magnitude and phase must match for batched processing.")
+    spec = magnitude_batch * torch.exp(1j * phase_batch)
+    w = hann_periodic(win_length)
+    items = [torch.istft(spec[i], n_fft=n_fft, hop_length=hop_length, win_length=win_length, window=w, return_complex=False)
+             for i in range(magnitude_batch.shape[0])]
+    return torch.stack(items, dim=0)
+
+
 def subspace_angle(Va: torch.Tensor, Vb: torch.Tensor) -> float:
     """Largest principal angle (rad) between column spaces, float64 sine formulation
     ``asin ||(I - Qa Qa^T) Qb||_2`` after QR (SURVEY.md section 7 hard part 5)."""

@@ -1,0 +1,333 @@
+// K4 -- batched inverse STFT (polar -> complex, one-sided inverse real FFT, synthesis window, overlap-add and
+// window-envelope normalisation fused), the step in front of the discriminator front end:
+// batch_reconstruct_waveform, train_pkl_file_task_aware.py:174-208 (mag * exp(1j * phase) -> per-item torch.istft(n_fft=2048,
+// hop=512, hann) in a Python list comprehension -> stack).
+//
+// The spectrogram arrives TIME-innermost ([K][F] planes of the [B, 2, 1025, 600] decoder output), a frame needs one
+// column of it.  A CTA therefore walks a run of consecutive frames of one row in tiles of TFR = 8 * NFR frames:
+//   phase 1  all threads read the [K][TFR] tile with the frame index fastest (contiguous TFR * 4 bytes per bin), turn
+//            (magnitude, phase) into (re, im), apply the one-sided weights and store it transposed, [frame][k];
+//   phase 2  every warp runs the adjoint network of fft_core.cuh (== n * irfft for these weights) on its NFR frames and
+//            leaves the windowed frames in a private tile;
+//   phase 3  all threads overlap-add the TFR frames (+ the carry of the frames before them) in ascending frame order
+//            -- a fixed order, no atomics: the waveform is bit-stable --, divide by the window envelope of the frames that
+//            exist and write the hop blocks that are now complete with coalesced stores; the n - hop samples behind them
+//            become the next carry.
+// Runs of one row are independent: a run starts R - 1 = ceil(n / hop) - 1 frames early and discards what it does not own.
+// Algorithmic bytes per row: read 8 * K * F, write 4 * out_len.
+#include "tac_common.cuh"
+
+#include <math.h>
+#include <vector>
+
+namespace tac {
+
+constexpr int kIWarps = 8;
+constexpr int kIThreads = kIWarps * 32;
+
+struct IstftArgs {
+    const float* a;
+    const float* b;
+    int in_mode;
+    long long row_stride, ld;       // elements between rows / between bins (complex elements for TAC_IN_COMPLEX)
+    int F, n, hop, K, R;
+    int start;                      // first padded position that is kept (n / 2 when centred)
+    long long nat_len, out_len;     // samples available behind `start`; samples written per row (zero-filled beyond)
+    int run_blocks, runs_per_row, nblk;
+    int vec_ok;                     // strides and base pointers allow 16-byte copies of 4 consecutive frames
+    float scale;                    // 2 / n (* sqrt(n) when normalized): the window table holds w / 2
+    FftTables t;
+    float* out;
+};
+
+__device__ __forceinline__ void cp_async4(void* smem, const void* g) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(s), "l"(g) : "memory");
+}
+// 16-byte copy of which only the first `bytes` (0, 4, 8, 12 or 16) are read from global memory; the rest is zero-filled
+__device__ __forceinline__ void cp_async16_zfill(void* smem, const void* g, int bytes) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(s), "l"(g), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// sin / cos of a decoder phase: two-constant Cody-Waite reduction to [-pi, pi], then the MUFU approximations
+// (absolute error < 5e-7 there; the parity tolerance is 1e-4 of the largest sample).  Huge arguments take the library path.
+__device__ __forceinline__ void phase_sincos(float x, float* sn, float* cs) {
+    if (fabsf(x) > 30000.0f) { sincosf(x, sn, cs); return; }
+    const float k = rintf(x * 0.15915494309189535f);
+    float r = fmaf(-k, 6.28125f, x);
+    r = fmaf(-k, 1.9353071795864769e-3f, r);
+    *sn = __sinf(r);
+    *cs = __cosf(r);
+}
+
+template <class P>
+__global__ void __launch_bounds__(kIThreads, 1) istft_kernel(const IstftArgs a) {
+    constexpr int M = P::M, NFR = P::NFR, TFR = kIWarps * NFR, KP = M + 2, N = P::N, K = M + 1;
+    constexpr int RAWF = ((2 * K * TFR + 3) / 4) * 4;                  // floats of the raw tile, 16-byte multiple
+    extern __shared__ __align__(16) unsigned char istft_smem_raw[];
+    float* raw = reinterpret_cast<float*>(istft_smem_raw);             // [2 planes][K][TFR] as in HBM (or [K][TFR] complex)
+    float2* tile = reinterpret_cast<float2*>(raw + RAWF);              // [TFR][KP] (re, im) frame-major; a warp's rows
+                                                                       // become its windowed frames (in place)
+    float2* xbuf_all = tile + TFR * KP;                                // [warps][kXbufFloat2]
+    float* carry = reinterpret_cast<float*>(xbuf_all + kIWarps * kXbufFloat2);   // [2][n - hop]
+    const int hop = a.hop, F = a.F;
+    const int clen = N - hop;
+    float* inv_env = carry + 2 * clen;                                 // [hop] 1 / sum w^2 where every covering frame exists
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int run = blockIdx.x % a.runs_per_row;
+    const long long row = blockIdx.x / a.runs_per_row;
+    const int ja = run * a.run_blocks;                                 // owned hop blocks [ja, jb)
+    const int jb = min(a.nblk, ja + a.run_blocks);
+    const int q = N / hop, r = N % hop;
+    const float* __restrict__ wf = reinterpret_cast<const float*>(a.t.win2);     // w[i] / 2
+    const float2* __restrict__ win2 = a.t.win2;
+    const float scale = a.scale;
+    const long long lim = a.nat_len < a.out_len ? a.nat_len : a.out_len;
+    float* orow = a.out + row * a.out_len;
+    const long long in_row = row * a.row_stride;
+    const int in_mode = a.in_mode;
+    const bool vec = a.vec_ok != 0;
+
+    // phase 1 (asynchronous): the [K][TFR] tile exactly as it lies in HBM, 16 bytes (4 frames of one bin) per copy when the
+    // strides allow it; frames outside [0, F) are zero-filled by the copy itself
+    auto issue = [&](int ft) {
+        if (in_mode == TAC_IN_COMPLEX) {
+            const float2* pc = reinterpret_cast<const float2*>(a.a) + in_row;
+            if (vec) {
+                for (int c = tid; c < K * (TFR / 2); c += kIThreads) {
+                    const int k = c / (TFR / 2), f0 = ft + 2 * (c % (TFR / 2));
+                    const int nv = f0 < 0 ? 0 : min(max(F - f0, 0), 2);
+                    cp_async16_zfill(raw + 4 * c, nv ? (const void*)(pc + (long long)k * a.ld + f0) : (const void*)pc, 8 * nv);
+                }
+            } else {
+                for (int e = tid; e < 2 * K * TFR; e += kIThreads) {
+                    const int k = e / (2 * TFR), f = ft + (e % (2 * TFR)) / 2;
+                    if (f >= 0 && f < F) cp_async4(raw + e, reinterpret_cast<const float*>(pc + (long long)k * a.ld + f) + (e & 1));
+                    else raw[e] = 0.0f;
+                }
+            }
+        } else {
+            if (vec) {
+                for (int c = tid; c < 2 * K * (TFR / 4); c += kIThreads) {
+                    const int pl = c / (K * (TFR / 4)), cc = c - pl * (K * (TFR / 4));
+                    const int k = cc / (TFR / 4), f0 = ft + 4 * (cc % (TFR / 4));
+                    const float* src = (pl ? a.b : a.a) + in_row;
+                    const int nv = f0 < 0 ? 0 : min(max(F - f0, 0), 4);
+                    cp_async16_zfill(raw + 4 * c, nv ? (const void*)(src + (long long)k * a.ld + f0) : (const void*)src, 4 * nv);
+                }
+            } else {
+                for (int e = tid; e < 2 * K * TFR; e += kIThreads) {
+                    const int pl = e / (K * TFR), ee = e - pl * (K * TFR);
+                    const int k = ee / TFR, f = ft + ee % TFR;
+                    if (f >= 0 && f < F) cp_async4(raw + e, (pl ? a.b : a.a) + in_row + (long long)k * a.ld + f);
+                    else raw[e] = 0.0f;
+                }
+            }
+        }
+        cp_async_commit();
+    };
+
+    // tiles start on a multiple of 4 frames (16-byte copies); at most 3 more warm-up frames
+    const int fs = ((ja - (a.R - 1)) >> 2) << 2;
+    const int ntiles = (jb - fs + TFR - 1) / TFR;
+    issue(fs);
+    for (int i = tid; i < clen; i += kIThreads) carry[i] = 0.0f;
+    for (int o = tid; o < hop; o += kIThreads) {
+        float e = 0.0f;
+        for (int i = o; i < N; i += hop) { const float w = wf[i]; e = fmaf(w, w, e); }
+        inv_env[o] = 1.0f / (4.0f * e);
+    }
+
+    for (int it = 0; it < ntiles; ++it) {
+        const int ft = fs + it * TFR;
+        cp_async_wait_all();
+        __syncthreads();                                   // raw tile `it` has landed; phase 3 of tile it - 1 is over
+
+        // ---- conversion: raw [k][frame] -> tile[frame][k] as (re, im) with the one-sided weights
+        for (int e = tid; e < K * TFR; e += kIThreads) {
+            const int k = e / TFR, fl = e % TFR;
+            float2 v;
+            if (in_mode == TAC_IN_COMPLEX) {
+                v = reinterpret_cast<const float2*>(raw)[e];
+            } else {
+                v = make_float2(raw[e], raw[K * TFR + e]);
+                if (in_mode == TAC_IN_POLAR) {
+                    float sn, cs;
+                    phase_sincos(v.y, &sn, &cs);
+                    v = make_float2(v.x * cs, v.x * sn);
+                }
+            }
+            if (k == 0 || k == M) { v.x *= 0.5f; v.y = 0.0f; }         // X[0], X[n/2] count once and are real
+            tile[fl * KP + k] = v;
+        }
+        __syncthreads();
+        if (it + 1 < ntiles) issue(ft + TFR);              // the next raw tile streams in behind phases 2 and 3
+
+        // ---- phase 2: n * irfft of NFR frames per warp, windowed, in place over the warp's own tile rows
+        {
+            float2* xbuf = xbuf_all + warp * kXbufFloat2;
+            float2* tw = tile + (warp * NFR) * KP;
+            warp_fft_adj<P>(xbuf, a.t.tw, a.t.pt, lane,
+                [&](int fr, int k, int) -> float2 { return tw[fr * KP + k]; },
+                [&](auto, int f2, auto ac, int b, float2 g) {
+                    const int m = P::BQ * decltype(ac)::value + b;
+                    const float2 w = ldg2(win2 + m);
+                    tw[f2 * KP + m] = make_float2(g.x * w.x * scale, g.y * w.y * scale);
+                });
+        }
+        __syncthreads();
+
+        // ---- phase 3: overlap-add in ascending frame order, envelope, write-out, next carry (no divisions: hop block
+        //      jl of the tile region, offset o inside it; frames lo .. jl cover the position)
+        {
+            const float* cin = carry + (it & 1) * clen;
+            float* cout = carry + ((it + 1) & 1) * clen;
+            const float* pf = reinterpret_cast<const float*>(tile);     // frame fl at pf + fl * 2 * KP
+            const int region = TFR * hop + clen;
+            for (int jl = 0; jl * hop < region; ++jl) {
+                const int jg = ft + jl;                                  // global hop block
+                if (jl < TFR && (jg < ja || jg >= jb)) continue;         // not this run's block: never written
+                const bool inner = jg - q >= 0 && jg < F;                // every covering frame exists
+                for (int o = tid; o < hop; o += kIThreads) {
+                    const int i = jl * hop + o;
+                    if (i >= region) break;
+                    const int lo = jl - q + (o >= r ? 1 : 0);
+                    float v = i < clen ? cin[i] : 0.0f;
+                    const int fhi = min(jl, TFR - 1);
+                    for (int fl = max(lo, 0); fl <= fhi; ++fl) v += pf[fl * (2 * KP) + (i - fl * hop)];
+                    if (jl >= TFR) { cout[i - TFR * hop] = v; continue; }
+                    const long long t = (long long)jg * hop + o - a.start;
+                    if (t < 0 || t >= lim) continue;
+                    float ie;
+                    if (inner) {
+                        ie = inv_env[o];
+                    } else {
+                        float env = 0.0f;                                // sum of (w / 2)^2 over the frames that exist
+                        for (int fl = lo; fl <= jl; ++fl) {
+                            const int fg = ft + fl;
+                            if (fg >= 0 && fg < F) { const float w = wf[i - fl * hop]; env = fmaf(w, w, env); }
+                        }
+                        ie = 1.0f / (4.0f * env);
+                    }
+                    orow[t] = v * ie;
+                }
+            }
+        }
+    }
+    if (run == a.runs_per_row - 1)
+        for (long long t = lim + tid; t < a.out_len; t += kIThreads) orow[t] = 0.0f;      // behind the padded signal: zeros
+}
+
+template <class P>
+static int launch_istft(const IstftArgs& a, long long rows, cudaStream_t st) {
+    constexpr int TFR = kIWarps * P::NFR;
+    const size_t rawf = ((2 * (size_t)(P::M + 1) * TFR + 3) / 4) * 4;
+    const size_t base = rawf * sizeof(float) + ((size_t)TFR * (P::M + 2) + (size_t)kIWarps * kXbufFloat2) * sizeof(float2);
+    const size_t smem = base + (2 * (size_t)(a.n - a.hop) + (size_t)a.hop) * sizeof(float);
+    static bool attr_set = false;
+    if (!attr_set) {                                   // the smallest admissible hop (n / 8) has the largest carry
+        const size_t smem_max = base + (2 * (size_t)(P::N - P::N / 8) + (size_t)P::N) * sizeof(float);
+        TAC_CHECK_CUDA(cudaFuncSetAttribute(istft_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max));
+        attr_set = true;
+    }
+    const long long grid = rows * a.runs_per_row;
+    TAC_REQUIRE(grid < (1ll << 31), "grid too large");
+    istft_kernel<P><<<(unsigned)grid, kIThreads, smem, st>>>(a);
+    TAC_LAUNCHED(1);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    return TAC_OK;
+}
+
+}  // namespace tac
+
+using namespace tac;
+
+extern "C" int64_t tac_istft_length(int64_t F, int n_fft, int hop, int center) {
+    if (F < 1 || hop <= 0 || n_fft <= 0) return 0;
+    const int64_t full = (int64_t)n_fft + (int64_t)hop * (F - 1);
+    return center ? full - 2 * (int64_t)(n_fft / 2) : full;
+}
+
+extern "C" int tac_istft(const float* a, const float* b, int in_mode, int64_t rows, int64_t row_stride, int64_t ld, int64_t F,
+                         int n_fft, int hop, int win, int center, int normalized, float* out, int64_t out_len,
+                         tac_stream_t stream) {
+    TAC_REQUIRE(in_mode == TAC_IN_POLAR || in_mode == TAC_IN_PLANES || in_mode == TAC_IN_COMPLEX, "unknown in_mode %d", in_mode);
+    TAC_REQUIRE(a && out && (in_mode == TAC_IN_COMPLEX || b), "null pointer");
+    TAC_REQUIRE(supported_nfft(n_fft), "unsupported n_fft %d (64..2048, power of two)", n_fft);
+    TAC_REQUIRE(rows >= 0 && F >= 1 && F < (1ll << 30) / n_fft, "bad shape: rows %lld, frames %lld", (long long)rows, (long long)F);
+    TAC_REQUIRE(hop >= 1 && hop <= n_fft && hop * 8 >= n_fft, "hop %d must lie in [n_fft / 8, n_fft]", hop);
+    TAC_REQUIRE(ld >= F && row_stride >= (int64_t)(n_fft / 2) * ld + F, "strides do not cover [K][F]");
+    TAC_REQUIRE(((uintptr_t)a & 3u) == 0 && (in_mode != TAC_IN_COMPLEX || ((uintptr_t)a & 7u) == 0), "input not aligned");
+    const int64_t nat = tac_istft_length(F, n_fft, hop, center);
+    TAC_REQUIRE(nat >= 1 && out_len >= 1, "empty output (frames %lld)", (long long)F);
+    // like torch.istft(length=): a length beyond the natural one keeps reading the (centre-)padded tail of the
+    // overlap-added signal -- envelope check included -- and is zero-filled only behind n_fft + hop * (F - 1)
+    const int64_t avail = (int64_t)n_fft + (int64_t)hop * (F - 1) - (center ? n_fft / 2 : 0);
+    if (rows == 0) return TAC_OK;
+    if (win <= 0) win = n_fft;
+
+    IstftArgs k;
+    int rc = get_tables(n_fft, win, 0, &k.t);
+    if (rc) return rc;
+
+    // torch.istft refuses a window whose overlap-added square vanishes inside the kept range (NOLA); same check here,
+    // on the host in float64 (the envelope is periodic in hop away from the two edges, so the edges + one period suffice)
+    {
+        std::vector<double> w(n_fft, 0.0);
+        const int left = (n_fft - win) / 2;
+        for (int i = 0; i < win; ++i) w[left + i] = 0.5 - 0.5 * cos(2.0 * M_PI * (double)i / (double)win);
+        const int64_t start = center ? n_fft / 2 : 0;
+        const int64_t lim = avail < out_len ? avail : out_len;
+        const int64_t edge = 2 * (int64_t)n_fft;
+        double mn = 1e300;
+        for (int pass = 0; pass < 2; ++pass) {
+            int64_t t0 = pass == 0 ? 0 : (lim > edge ? lim - edge : 0);
+            int64_t t1 = pass == 0 ? (lim < edge ? lim : edge) : lim;
+            for (int64_t t = t0; t < t1; ++t) {
+                const int64_t p = t + start;
+                int64_t f_hi = p / hop, f_lo = p >= n_fft ? (p - n_fft + hop) / hop : 0;
+                if (f_hi > F - 1) f_hi = F - 1;
+                double e = 0.0;
+                for (int64_t f = f_lo; f <= f_hi; ++f) e += w[p - f * hop] * w[p - f * hop];
+                if (e < mn) mn = e;
+            }
+        }
+        TAC_REQUIRE(mn > 1e-11, "window overlap-add envelope vanishes (min %.3g): istft needs a NOLA-compliant window/hop", mn);
+    }
+
+    k.a = a; k.b = b; k.in_mode = in_mode; k.row_stride = row_stride; k.ld = ld;
+    k.F = (int)F; k.n = n_fft; k.hop = hop; k.K = n_fft / 2 + 1; k.R = (n_fft + hop - 1) / hop;
+    k.start = center ? n_fft / 2 : 0;
+    k.nat_len = avail; k.out_len = out_len;
+    k.nblk = (int)(((int64_t)n_fft + (int64_t)hop * (F - 1) + hop - 1) / hop);
+    const int nfr = n_fft >= 2048 ? 1 : (n_fft >= 512 ? 2 : (n_fft >= 128 ? 4 : 8));
+    const int tfr = kIWarps * nfr;
+    // enough runs to fill the GPU twice over, but never shorter than four tiles (the R - 1 warm-up frames are recomputed)
+    long long want = (2 * kNumSMs + rows - 1) / rows;
+    int rb = (int)((k.nblk + want - 1) / want);
+    if (rb < 4 * tfr) rb = 4 * tfr;
+    if (rb > k.nblk) rb = k.nblk;
+    k.run_blocks = rb;
+    k.runs_per_row = (k.nblk + rb - 1) / rb;
+    k.scale = (float)((2.0 / (double)n_fft) * (normalized ? sqrt((double)n_fft) : 1.0));
+    k.out = out;
+    {   // 16-byte asynchronous copies need 16-byte aligned frame quads in every row of every plane
+        const int per = in_mode == TAC_IN_COMPLEX ? 2 : 4;
+        bool ok = (ld % per == 0) && (row_stride % per == 0) && ((uintptr_t)a & 15u) == 0;
+        if (in_mode != TAC_IN_COMPLEX) ok = ok && ((uintptr_t)b & 15u) == 0;
+        k.vec_ok = ok ? 1 : 0;
+    }
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    switch (n_fft) {
+        case 2048: return launch_istft<Plan2048>(k, rows, st);
+        case 1024: return launch_istft<Plan1024>(k, rows, st);
+        case 512: return launch_istft<Plan512>(k, rows, st);
+        case 256: return launch_istft<Plan256>(k, rows, st);
+        case 128: return launch_istft<Plan128>(k, rows, st);
+        default: return launch_istft<Plan64>(k, rows, st);
+    }
+}

@@ -14,10 +14,11 @@ There is no CPU or eager-PyTorch fallback: every op raises ``RuntimeError`` when
 """
 from . import _lib
 from .stft import (Spectrogram, MultiScaleSTFT, stft_multi, complex_spectrogram, create_complex_spectrogram, amplitude_to_db,
-                   num_frames, SUPPORTED_NFFT)
+                   num_frames, SUPPORTED_NFFT, istft, batch_reconstruct_waveform, reconstruct_waveform)
 from .loss import mrstft_loss, mrstft_sums, mrstft_counts, spectral_losses, LOG_FLOOR
-from .dpca import data_pca, dpca_project, dpca_select, dpca_stats, dpca_eig, apply_pca, var_topk, nuclear_loss
+from .dpca import data_pca, dpca_project, dpca_select, dpca_stats, dpca_eig, apply_pca, var_topk, nuclear_loss, pairwise_cosine_loss
 
 __all__ = ["Spectrogram", "MultiScaleSTFT", "stft_multi", "complex_spectrogram", "create_complex_spectrogram", "amplitude_to_db",
            "num_frames", "SUPPORTED_NFFT", "mrstft_loss", "mrstft_sums", "mrstft_counts", "spectral_losses",
-           "LOG_FLOOR", "data_pca", "dpca_project", "dpca_select", "dpca_stats", "dpca_eig", "apply_pca", "var_topk", "nuclear_loss"]
+           "LOG_FLOOR", "data_pca", "dpca_project", "dpca_select", "dpca_stats", "dpca_eig", "apply_pca", "var_topk", "nuclear_loss",
+           "pairwise_cosine_loss", "istft", "batch_reconstruct_waveform", "reconstruct_waveform"]

@@ -45,11 +45,17 @@ SIGNATURES = {
     "tac_nuclear_from_s": (_I, [_VP, _VP, _VP, _I, _I, _VP, _VP, _VP]),
     "tac_nuclear_grad_matrix": (_I, [_VP, _VP, _VP, _VP, _I, _I, _VP, _VP]),
     "tac_dpca_apply": (_I, [_VPP, _I, _I64, _I, _VP, _VP, _I, _VPP, _VP]),
+    "tac_cosine_pairs_workspace_bytes": (_SZ, [_I64]),
+    "tac_cosine_pairs_fwd": (_I, [_VPP, _I, _I64, _I, _F, _VP, _VP, _SZ, _VP]),
+    "tac_cosine_pairs_bwd": (_I, [_VPP, _I, _I64, _I, _F, _VP, _F, _VPP, _VP]),
+    "tac_istft_length": (_I64, [_I64, _I, _I, _I]),
+    "tac_istft": (_I, [_VP, _VP, _I, _I64, _I64, _I64, _I64, _I, _I, _I, _I, _I, _VP, _I64, _VP]),
 }
 
 PAD_ZERO, PAD_REFLECT = 0, 1
 OUT_COMPLEX, OUT_PLANES, OUT_MAGPHASE = 0, 1, 2
 GRAM_TF32X3, GRAM_FP64 = 0, 1
+IN_POLAR, IN_PLANES, IN_COMPLEX = 0, 1, 2
 
 _lib = None
 

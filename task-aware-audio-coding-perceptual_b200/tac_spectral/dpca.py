@@ -237,3 +237,48 @@ def nuclear_loss(z_sample: torch.Tensor, algo: Optional[str] = None, group=None)
     if z_sample.shape[1] > 256:
         raise ValueError("nuclear_loss supports d <= 256")
     return _Nuclear.apply(z_sample, algo, group)
+
+
+class _CosinePairs(torch.autograd.Function):
+    """``mean_b sum_{i<j} cos(z_i[b], z_j[b])``: one pass over the views forward, one pass backward."""
+
+    @staticmethod
+    def forward(ctx, eps, group, *zs):
+        zc = [z.contiguous().float() for z in zs]
+        nv, B, d = _check_views(zc)
+        dev = zc[0].device
+        lib = L.lib()
+        ws_bytes = int(lib.tac_cosine_pairs_workspace_bytes(B))
+        ws = torch.empty(max(ws_bytes, 16), dtype=torch.uint8, device=dev)
+        acc = torch.zeros(2, dtype=torch.float64, device=dev)             # [sum of cosines, local batch]
+        acc[1] = float(B)
+        with L.device_of(zc[0]):
+            L.check(lib.tac_cosine_pairs_fwd(L.ptr_array(zc), nv, B, d, float(eps), acc.data_ptr(), ws.data_ptr(), ws_bytes,
+                                             L.stream_of(zc[0])))
+        acc = _allreduce_stats(acc, group)                                 # batch shards: both entries are sums
+        ctx.save_for_backward(acc, *zc)
+        ctx.eps = float(eps)
+        ctx.meta = [(z.shape, z.dtype) for z in zs]
+        return (acc[0] / acc[1]).float()
+
+    @staticmethod
+    def backward(ctx, g):
+        acc, *zc = ctx.saved_tensors
+        nv, B, d = len(zc), zc[0].shape[0], zc[0].shape[1]
+        grads = [torch.empty_like(z) for z in zc]
+        gs = (g.float() / acc[1].float()).reshape(1).contiguous()          # g / global batch, stays on the device
+        with L.device_of(zc[0]):
+            L.check(L.lib().tac_cosine_pairs_bwd(L.ptr_array(zc), nv, B, d, ctx.eps, gs.data_ptr(), 1.0, L.ptr_array(grads),
+                                                 L.stream_of(zc[0])))
+        return (None, None) + tuple(gr.reshape(sh).to(dt) for gr, (sh, dt) in zip(grads, ctx.meta))
+
+
+def pairwise_cosine_loss(zs: Sequence[torch.Tensor], eps: float = 1e-8, group=None) -> torch.Tensor:
+    """``torch.mean(cos_sim(z1, z2) + cos_sim(z1, z3) + ...)`` over all view pairs with ``cos_sim =
+    torch.nn.CosineSimilarity()`` (``pkl_file_models.py:390-391,761-763``; ``pkl_file_model_updated.py:429-430,513-514``)
+    for 2, 3 or 4 views ``[B, d]``; with ``group`` the mean runs over the batch of all ranks."""
+    for i, z in enumerate(zs):
+        L.require_cuda(z, f"zs[{i}]")
+    if len(zs) not in (2, 3, 4):
+        raise ValueError(f"pairwise_cosine_loss takes 2, 3 or 4 views, got {len(zs)}")
+    return _CosinePairs.apply(eps, group, *zs)

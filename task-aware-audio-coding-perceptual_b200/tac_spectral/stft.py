@@ -198,3 +198,160 @@ def amplitude_to_db(spec: torch.Tensor, n_frames: Optional[int] = None, amin: fl
         L.check(L.lib().tac_amplitude_to_db(spec.data_ptr(), B, row_stride, K, F, ld, float(amin), float(top_db), out.data_ptr(),
                                             ws.data_ptr(), 4 * B, L.stream_of(spec)))
     return out
+
+
+# ------------------------------------------------------------------------------------------------
+# inverse STFT: batch_reconstruct_waveform, train_pkl_file_task_aware.py:174-208
+# ------------------------------------------------------------------------------------------------
+_ENV_CACHE: Dict[tuple, torch.Tensor] = {}
+
+
+def _istft_envelope(n_fft: int, hop: int, win: int, F: int, center: bool, length: int, device) -> torch.Tensor:
+    """Overlap-added squared synthesis window over the kept range (what torch.istft divides by); cached per shape."""
+    key = (n_fft, hop, win, F, bool(center), int(length), str(device))
+    env = _ENV_CACHE.get(key)
+    if env is None:
+        w = torch.zeros(n_fft, dtype=torch.float64)
+        left = (n_fft - win) // 2
+        w[left:left + win] = torch.hann_window(win, periodic=True, dtype=torch.float64)
+        full = torch.zeros(n_fft + hop * (F - 1), dtype=torch.float64)
+        for f in range(F):
+            full[f * hop:f * hop + n_fft] += w * w
+        start = n_fft // 2 if center else 0
+        nat = full.numel() - start                      # torch.istft(length=) reads on into the padded tail
+        env = torch.ones(length, dtype=torch.float64)
+        m = min(nat, length)
+        env[:m] = full[start:start + m]
+        env = env.to(torch.float32).to(device)
+        _ENV_CACHE[key] = env
+    return env
+
+
+def _istft_call(a: torch.Tensor, b: Optional[torch.Tensor], in_mode: int, rows: int, row_stride: int, ld: int, F: int,
+                n_fft: int, hop: int, win: int, center: bool, normalized: bool, length: int) -> torch.Tensor:
+    out = torch.empty((rows, length), dtype=torch.float32, device=a.device)
+    with L.device_of(a):
+        L.check(L.lib().tac_istft(a.data_ptr(), b.data_ptr() if b is not None else None, in_mode, rows, row_stride, ld, F,
+                                  n_fft, hop, win, int(center), int(normalized), out.data_ptr(), length, L.stream_of(a)))
+    return out
+
+
+class _ISTFTPolar(torch.autograd.Function):
+    """waveform = istft(mag * exp(1j * phase)).  Backward: the adjoint of the overlap-add synthesis is an analysis STFT
+    of grad / envelope (K1 kernel, ``center=False`` on the re-padded signal), scaled by the one-sided weights c_k / n,
+    followed by the polar chain rule."""
+
+    @staticmethod
+    def forward(ctx, mag, phase, n_fft, hop, win, center, normalized, length):
+        B, K, F = mag.shape
+        mag_c, ph_c = mag.contiguous().float(), phase.contiguous().float()
+        ctx.save_for_backward(mag_c, ph_c)
+        ctx.cfg = (n_fft, hop, win, center, normalized, length)
+        return _istft_call(mag_c, ph_c, L.IN_POLAR, B, K * F, F, F, n_fft, hop, win, center, normalized, length)
+
+    @staticmethod
+    def backward(ctx, g):
+        mag, ph = ctx.saved_tensors
+        n_fft, hop, win, center, normalized, length = ctx.cfg
+        G = _istft_adjoint(g.contiguous().float(), mag.shape[2], n_fft, hop, win, center, normalized, length)   # [B, K, F] complex
+        c, s = torch.cos(ph), torch.sin(ph)
+        gm = G.real * c + G.imag * s
+        gp = mag * (G.imag * c - G.real * s)
+        return gm, gp, None, None, None, None, None, None
+
+
+class _ISTFTComplex(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, spec, n_fft, hop, win, center, normalized, length):
+        B, K, F = spec.shape
+        spec_c = spec.contiguous()
+        ctx.cfg = (n_fft, hop, win, center, normalized, length, F)
+        return _istft_call(torch.view_as_real(spec_c), None, L.IN_COMPLEX, B, K * F, F, F, n_fft, hop, win, center,
+                           normalized, length)
+
+    @staticmethod
+    def backward(ctx, g):
+        n_fft, hop, win, center, normalized, length, F = ctx.cfg
+        return _istft_adjoint(g.contiguous().float(), F, n_fft, hop, win, center, normalized, length), None, None, None, None, None, None
+
+
+def _istft_adjoint(g: torch.Tensor, F: int, n_fft: int, hop: int, win: int, center: bool, normalized: bool,
+                   length: int) -> torch.Tensor:
+    """dL/dX [B, K, F] (complex64) from dL/dwaveform [B, length]."""
+    B = g.shape[0]
+    env = _istft_envelope(n_fft, hop, win, F, center, length, g.device)
+    start = n_fft // 2 if center else 0
+    full = n_fft + hop * (F - 1)
+    nat = min(full - start, length)
+    gp = torch.zeros((B, 1, full), dtype=torch.float32, device=g.device)
+    gp[:, 0, start:start + nat] = g[:, :nat] / env[:nat]
+    G = stft_multi(gp, [n_fft], [hop], [win], center=False, normalized=False, out_mode=L.OUT_COMPLEX)[0][:, 0]   # [B, K, F]
+    ck = torch.full((n_fft // 2 + 1, 1), 2.0 / n_fft, dtype=torch.float32, device=g.device)
+    ck[0] = ck[-1] = 1.0 / n_fft
+    if normalized:
+        ck = ck * float(n_fft) ** 0.5
+    G = G * ck
+    # the imaginary parts of X[0] and X[n/2] do not reach the waveform
+    G.imag[:, 0] = 0.0
+    G.imag[:, -1] = 0.0
+    return G
+
+
+def istft(spec: torch.Tensor, n_fft: int, hop_length: Optional[int] = None, win_length: Optional[int] = None,
+          window: Optional[torch.Tensor] = None, center: bool = True, normalized: bool = False, onesided: Optional[bool] = None,
+          length: Optional[int] = None, return_complex: bool = False) -> torch.Tensor:
+    """``torch.istft`` for a batch: ``spec`` complex64 ``[B, n_fft/2+1, F]`` (or ``[K, F]``) -> ``[B, length]`` in ONE
+    launch of ``tac_istft``.  Same keyword arguments as ``torch.istft``; implemented: periodic Hann window (``window``
+    must be ``None`` or equal ``torch.hann_window(win_length)``), ``onesided`` in (None, True), real output."""
+    L.require_cuda(spec, "spec")
+    if not spec.is_complex():
+        raise RuntimeError("istft requires a complex-valued input tensor")          # torch.istft's own error class
+    if onesided is False or return_complex:
+        raise ValueError("only onesided=True, return_complex=False is implemented")
+    single = spec.dim() == 2
+    if single:
+        spec = spec[None]
+    if spec.dim() != 3 or spec.shape[1] != n_fft // 2 + 1:
+        raise ValueError(f"expected spec of shape [B, {n_fft // 2 + 1}, F], got {tuple(spec.shape)}")
+    hop = int(hop_length) if hop_length is not None else n_fft // 4
+    win = int(win_length) if win_length is not None else n_fft
+    if window is not None:
+        ref_w = torch.hann_window(win, periodic=True, dtype=torch.float32, device=window.device)
+        if window.numel() != win or not torch.allclose(window.float(), ref_w, atol=1e-6):
+            raise ValueError("Unsupported window: only the periodic torch.hann_window is implemented")
+    F = spec.shape[2]
+    nat = int(L.lib().tac_istft_length(F, n_fft, hop, int(center)))
+    out_len = int(length) if length is not None else nat
+    y = _ISTFTComplex.apply(spec.to(torch.complex64), n_fft, hop, win, bool(center), bool(normalized), out_len)
+    return y[0] if single else y
+
+
+def batch_reconstruct_waveform(magnitude_batch: torch.Tensor, phase_batch: torch.Tensor, sample_rate: int, n_fft: int = 2048,
+                               hop_length: int = 512, win_length: int = 2048, window: str = "hann") -> torch.Tensor:
+    """Same name, arguments and errors as ``train_pkl_file_task_aware.py:174-208``: ``[B, K, F]`` magnitude and phase
+    -> ``[B, hop*(F-1)]`` waveforms; the complex product, the per-item ``torch.istft`` loop and the stack are one kernel.
+    Strided views (e.g. the two channels of the ``[B, 2, 1025, 600]`` decoder output) are used in place."""
+    if magnitude_batch.shape != phase_batch.shape:
+        raise ValueError("The shapes of magnitude and phase must match for batched processing.")
+    if window != "hann":
+        raise ValueError(f"Window type '{window}' is not supported. Use 'hann'.")
+    L.require_cuda(magnitude_batch, "magnitude_batch")
+    L.require_cuda(phase_batch, "phase_batch")
+    if magnitude_batch.dim() != 3 or magnitude_batch.shape[1] != n_fft // 2 + 1:
+        raise ValueError(f"expected [B, {n_fft // 2 + 1}, F], got {tuple(magnitude_batch.shape)}")
+    B, K, F = magnitude_batch.shape
+    nat = int(L.lib().tac_istft_length(F, n_fft, hop_length, 1))
+    needs_grad = torch.is_grad_enabled() and (magnitude_batch.requires_grad or phase_batch.requires_grad)
+    m, p = magnitude_batch, phase_batch
+    in_place = (not needs_grad and m.dtype == torch.float32 and p.dtype == torch.float32 and m.stride() == p.stride()
+                and m.stride(2) == 1 and m.stride(1) >= F and m.stride(0) >= K * m.stride(1))
+    if in_place:
+        return _istft_call(m, p, L.IN_POLAR, B, m.stride(0), m.stride(1), F, n_fft, hop_length, win_length, True, False, nat)
+    return _ISTFTPolar.apply(m, p, n_fft, hop_length, win_length, True, False, nat)
+
+
+def reconstruct_waveform(magnitude: torch.Tensor, phase: torch.Tensor, sample_rate: int, n_fft: int = 2048,
+                         hop_length: int = 512, win_length: int = 2048, window: str = "hann") -> torch.Tensor:
+    """Single-utterance form (``train_pkl_file_task_aware.py:210-226``): ``[K, F]`` -> ``[1, hop*(F-1)]`` (the reference
+    returns ``y.unsqueeze(0)``)."""
+    return batch_reconstruct_waveform(magnitude[None], phase[None], sample_rate, n_fft, hop_length, win_length, window)

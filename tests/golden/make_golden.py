@@ -167,11 +167,66 @@ def gen_var_topk():
                         z_sel=m.dec.seen.numpy())
 
 
+def _reference_function(path, name, patches=()):
+    """Compile ONE function of a reference script that cannot be imported as a module (``train_pkl_file_task_aware.py``
+    imports librosa / speechbrain and downloads checkpoints at import time): its source is read from the reference
+    checkout at generation time, never stored in this repository.  ``patches`` are (old, new) string replacements applied
+    to that source -- only used to turn the hard-coded ``"cuda:0"`` of ``:189`` into ``"cpu"`` (no GPU in this container)."""
+    import ast
+    src = open(os.path.join(REF, path)).read()
+    node = next(n for n in ast.parse(src).body if isinstance(n, ast.FunctionDef) and n.name == name)
+    text = ast.get_source_segment(src, node)
+    for old, new in patches:
+        assert old in text
+        text = text.replace(old, new)
+    ns = {"torch": torch, "np": np}
+    exec(compile(text, f"{path}:{name}", "exec"), ns)
+    return ns[name]
+
+
+def gen_istft():
+    """``batch_reconstruct_waveform`` / ``reconstruct_waveform`` of ``train_pkl_file_task_aware.py:174-226`` on a seeded
+    magnitude / phase batch shaped like the decoder output (K = 1025)."""
+    brw = _reference_function("train_pkl_file_task_aware.py", "batch_reconstruct_waveform", [('"cuda:0"', '"cpu"')])
+    rw = _reference_function("train_pkl_file_task_aware.py", "reconstruct_waveform", [('"cuda:0"', '"cpu"')])
+    g = torch.Generator().manual_seed(909)
+    B, K, F = 3, 1025, 14
+    mag = torch.rand(B, K, F, generator=g) * torch.linspace(2.0, 0.05, K)[None, :, None]
+    phase = (torch.rand(B, K, F, generator=g) - 0.5) * 2.0 * np.pi * 1.2          # a little beyond [-pi, pi] like a raw decoder
+    wav = brw(mag, phase, 16000)
+    one = rw(mag[0], phase[0], 16000)
+    np.savez_compressed(os.path.join(HERE, "istft.npz"), mag=mag.numpy(), phase=phase.numpy(), wav=wav.numpy(),
+                        one=one.numpy())
+
+
+def gen_cosine():
+    """``cos_loss`` of ``ResE4D1.forward`` (``pkl_file_model_updated.py:429-430``) and ``ResE2D1.forward`` (``:513-514``),
+    evaluation branch (no DPCA), encoders / decoder stubbed as in ``gen_dpca``."""
+    B, d = 40, 24
+    out = {}
+    zs = [_latents(B, d, 51 + i) - 0.3 for i in range(4)]
+    m4 = _bare(pmu.ResE4D1)
+    m4.enc1, m4.enc2, m4.enc3, m4.enc4 = _Enc(), _Enc(), _Enc(), _Enc()
+    m4.dec = _Dec(lambda z: torch.zeros(z.shape[0], 2, 2, d))
+    r4 = m4.forward(*[z.reshape(B, 2, 1, d // 2) for z in zs], False)
+    for i, z in enumerate(zs):
+        out[f"c4_z{i + 1}"] = z.numpy()
+    out["c4_cos"] = r4[4].detach().numpy()
+    m2 = _bare(pmu.ResE2D1)
+    m2.enc1, m2.enc2 = _Enc(), _Enc()
+    m2.dec = _Dec(lambda z: torch.zeros(z.shape[0], 2, 1, d))
+    r2 = m2.forward(zs[0].reshape(B, 1, 1, d), zs[1].reshape(B, 1, 1, d), False)
+    out["c2_cos"] = r2[4].detach().numpy()
+    np.savez_compressed(os.path.join(HERE, "cosine.npz"), **out)
+
+
 if __name__ == "__main__":
     gen_stft()
     gen_dpca()
     gen_spec_losses()
     gen_var_topk()
+    gen_istft()
+    gen_cosine()
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)))

@@ -133,3 +133,36 @@ def test_subspace_angle_and_synth():
     s, v, mu = O.data_pca_ref(zs[0])
     assert O.subspace_angle(v[:, :4], v[:, :4] @ torch.linalg.qr(torch.randn(4, 4))[0]) < 1e-6
     assert abs(O.subspace_angle(v[:, :1], v[:, 1:2]) - np.pi / 2) < 1e-6
+
+
+def test_istft_matches_reference(golden_dir):
+    """batch_reconstruct_waveform / reconstruct_waveform of train_pkl_file_task_aware.py:174-226 (tests/golden/istft.npz,
+    produced by the reference's own functions) and an independent float64 inverse DFT + overlap-add."""
+    g = np.load(os.path.join(golden_dir, "istft.npz"))
+    mag, ph = torch.from_numpy(g["mag"]), torch.from_numpy(g["phase"])
+    wav = O.batch_reconstruct_waveform_ref(mag, ph)
+    assert wav.shape == (3, 512 * (14 - 1))                       # hop * (F - 1), cf. 512*(600-1) = 306688 in the reference
+    assert torch.allclose(wav, torch.from_numpy(g["wav"]), rtol=1e-6, atol=1e-7)
+    assert torch.allclose(wav[:1], torch.from_numpy(g["one"]), rtol=1e-6, atol=1e-7)
+    spec = (mag * torch.exp(1j * ph)).to(torch.complex64)
+    assert torch.allclose(O.istft_ref(spec, 2048, 512), wav, rtol=1e-6, atol=1e-7)
+    # float64 direct synthesis of item 0
+    X = spec[0].to(torch.complex128).numpy()
+    n, hop, F = 2048, 512, X.shape[1]
+    w = O.hann_periodic(n, torch.float64).numpy()
+    ola, env = np.zeros(n + hop * (F - 1)), np.zeros(n + hop * (F - 1))
+    for f in range(F):
+        ola[f * hop:f * hop + n] += np.fft.irfft(X[:, f], n) * w
+        env[f * hop:f * hop + n] += w * w
+    ref = (ola / np.maximum(env, 1e-30))[n // 2:n // 2 + hop * (F - 1)]
+    assert np.abs(wav[0].numpy() - ref).max() <= 2e-6 * np.abs(ref).max()
+    with pytest.raises(ValueError):
+        O.batch_reconstruct_waveform_ref(mag, ph[:, :-1])
+
+
+def test_cosine_loss_matches_reference(golden_dir):
+    """cos_loss of ResE4D1.forward / ResE2D1.forward (pkl_file_model_updated.py:429-430, 513-514)."""
+    g = np.load(os.path.join(golden_dir, "cosine.npz"))
+    zs = [torch.from_numpy(g[f"c4_z{i + 1}"]) for i in range(4)]
+    assert torch.allclose(O.pairwise_cosine_loss_ref(zs), torch.from_numpy(g["c4_cos"]), rtol=1e-6, atol=1e-7)
+    assert torch.allclose(O.pairwise_cosine_loss_ref(zs[:2]), torch.from_numpy(g["c2_cos"]), rtol=1e-6, atol=1e-7)

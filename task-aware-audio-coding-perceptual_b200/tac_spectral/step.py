@@ -157,8 +157,9 @@ class SpectralStep:
         """Enqueue one step; returns the (device, float64) loss scalar of the global batch.  Results:
         ``self.loss``, ``self.grad_y``, ``self.fe_out``, ``self.z_out``, ``self.cnt`` / ``self.idx``.
 
-        Schedule: statistics (+ all-reduce) run first on an otherwise idle GPU; then the eigen-solve chain
-        (high-priority stream, 1 CTA per view) runs NEXT TO the loss / front-end kernels that fill the other SMs."""
+        Schedule: statistics (+ all-reduce) run first, on the high-priority side stream, with the short-CTA front-end
+        kernel underneath; then the eigen-solve chain (1 CTA per view) runs NEXT TO the loss kernel that fills the
+        other SMs."""
         self._check(x, y, zs)
         with torch.cuda.device(self.device):
             main = torch.cuda.current_stream(self.device)
@@ -170,17 +171,22 @@ class SpectralStep:
                     self._ev_stats.record(self.side)
                     self.leg_dpca_solve()
                     self.leg_dpca_project(zs)
-                main.wait_event(self._ev_stats)          # do not flood the SMs before the statistics / collective have run
-                self._spectral_chain(x, y)
+                # the front end's CTAs are short (~12 us): it runs UNDER the statistics + collective, whose kernels get the
+                # next free SMs through the side stream's priority; the long-CTA loss kernel must not flood the SMs before
+                # the collective has run
+                if self.frontend:
+                    self.leg_frontend(x)
+                main.wait_event(self._ev_stats)
+                self._spectral_chain(x, y, frontend=False)
                 main.wait_stream(self.side)
             else:
                 self._dpca_chain(zs)
                 self._spectral_chain(x, y)
         return self.loss
 
-    def _spectral_chain(self, x, y):
+    def _spectral_chain(self, x, y, frontend=True):
         self.leg_loss_fused(x, y)
-        if self.frontend:
+        if self.frontend and frontend:
             self.leg_frontend(x)
         self.leg_allreduce("sums")
         self.leg_loss_value()

@@ -15,6 +15,7 @@
 // therefore written once per scale with plain stores, in a fixed order: the gradient is bit-stable run to run.
 #include "tac_common.cuh"
 #include "loss_common.cuh"
+#include "fft_core_pk.cuh"
 
 namespace tac {
 
@@ -203,6 +204,149 @@ __device__ __forceinline__ void stream_cta(const StreamArgs& a, const StreamScal
     }
 }
 
+
+// The same walk on the packed-complex core (fft_core_pk.cuh): every complex value is one aligned register pair and the
+// butterflies, twiddles, window products and overlap-adds are two-wide FP32 instructions -- about half the instruction
+// stream of stream_cta for the same arithmetic.  Only the per-bin loss terms (|.|, log, sign) stay scalar.
+template <class P, bool WITH_SUMS>
+__device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamScale& sc, int cta, float2* smem) {
+    constexpr int A = P::A, BQ = P::BQ, M = P::M, NFR = P::NFR, NS1 = P::NS1, QA = A / 4;
+    static_assert(A % 4 == 0 && NFR * M <= kOlaFloat2, "plan does not fit the streaming overlap-add ring");
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float2* xbuf = smem + warp * kStreamWarpFloat2;
+    cf* ola = reinterpret_cast<cf*>(xbuf + kXbufFloat2);  // [NFR][4 quarters][QA][BQ]
+    const long long wr = (long long)cta * kStreamWarps + warp;
+    if (wr >= sc.nwr) {
+        if (WITH_SUMS && lane < 2) a.partial[((long long)blockIdx.x * kStreamWarps + warp) * 2 + lane] = 0.0;
+        return;
+    }
+    const long long row = wr / sc.wpr;
+    const int run0 = (int)(wr % sc.wpr) * NFR;
+    const int F = sc.F, NR = sc.NR, hop = sc.hop;
+    const float* xr = a.x + row * a.T;
+    const float* yr = a.y + row * a.T;
+    float* grow = sc.g + row * a.T;
+    float* hrow = sc.h + row * a.T;
+    const float2* __restrict__ win2 = sc.t.win2;
+
+    auto run_lo = [&](int g) { const int r = run0 + g; return r < NR ? run_begin(r, F, NR) : 0; };
+    auto run_len = [&](int g) { const int r = run0 + g; return r < NR ? run_begin(r + 1, F, NR) - run_begin(r, F, NR) : 0; };
+    int maxlen = 0;
+#pragma unroll
+    for (int g = 0; g < NFR; ++g) maxlen = max(maxlen, run_len(g));
+    const int len_post = run_len(lane / A);
+    int lo_s[NS1], len_s[NS1], f2_s[NS1];
+#pragma unroll
+    for (int s = 0; s < NS1; ++s) {
+        f2_s[s] = (lane + 32 * s) / BQ;
+        lo_s[s] = run_lo(f2_s[s]);
+        len_s[s] = run_len(f2_s[s]);
+    }
+    const int b_lane = lane % BQ;
+    {
+        float4* o4 = reinterpret_cast<float4*>(ola);
+        for (int i = lane; i < NFR * M / 2; i += 32) o4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    __syncwarp();
+
+    const float c_l1 = __ldg(a.coef + 2 * sc.orig), c_log = __ldg(a.coef + 2 * sc.orig + 1);
+    const float eps = a.eps;
+    float l1 = 0.0f, ll = 0.0f;
+    for (int t = 0; t < maxlen; ++t) {
+        cf z[BQ];
+        cf G[BQ + 1];
+        float mx[BQ + 1];
+        const float* fx[NS1];
+        const float* fy[NS1];
+#pragma unroll
+        for (int s = 0; s < NS1; ++s) {
+            const int f = lo_s[s] + min(t, max(len_s[s] - 1, 0));
+            fx[s] = xr + (long long)f * hop;
+            fy[s] = yr + (long long)f * hop;
+        }
+        auto load_x = [&](auto scn, int, int m) -> cf {
+            return mul2(__ldg(reinterpret_cast<const cf*>(fx[decltype(scn)::value] + 2 * m)), ldg_cf(win2 + m));
+        };
+        auto load_y = [&](auto scn, int, int m) -> cf {
+            return mul2(__ldg(reinterpret_cast<const cf*>(fy[decltype(scn)::value] + 2 * m)), ldg_cf(win2 + m));
+        };
+        warp_fft_fwd_pk<P>(z, xbuf, sc.t.tw, lane, load_x);
+        warp_fft_post_pk<P>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
+            const float vr = lo(v), vi = hi(v);
+            mx[slot] = fast_mag(fmaf(vr, vr, vi * vi));                   // |X|
+        });
+        warp_fft_fwd_pk<P>(z, xbuf, sc.t.tw, lane, load_y);
+        float tl1 = 0.0f, tll = 0.0f;
+        warp_fft_post_pk<P>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
+            const float vr = lo(v), vi = hi(v);
+            const float m2 = fmaf(vr, vr, vi * vi);
+            const float inv = m2 >= kTinyMag2 ? fast_rsqrt(m2) : 0.0f;
+            const float my = m2 * inv;                                    // |Y|
+            const float xv = mx[slot];                                    // |X|
+            const float d = my - xv;
+            const float dl = fast_lg2(fmaxf(my, eps)) - fast_lg2(fmaxf(xv, eps));
+            if (WITH_SUMS) { tl1 += fabsf(d); tll += fabsf(dl); }
+            const float invm = my >= eps ? inv : 0.0f;
+            float g = fmaf(signed_coef(dl, c_log), invm, signed_coef(d, c_l1));
+            g *= inv;
+            G[slot] = mul2(v, bc(g));                                     // dL/dY[k]  (odd slots: its conjugate)
+        });
+        if (WITH_SUMS && t < len_post) { l1 += tl1; ll += tll; }
+        warp_fft_adj_pk<P>(xbuf, sc.t.tw, sc.t.pt, lane,
+            [&](int, int, int slot) -> cf { return G[slot]; },
+            [&](auto scn, int f2, auto ac, int b, cf gv) {
+                constexpr int s = decltype(scn)::value, av = decltype(ac)::value;
+                constexpr int q = av / QA, ap = av % QA;
+                const bool active = t < len_s[s];
+                const int f = lo_s[s] + t;
+                const cf w = ldg_cf(win2 + BQ * av + b);
+                const int p = (q + f) & 3;
+                cf* slot = ola + ((f2 * 4 + p) * QA + ap) * BQ + b;
+                if (q == 3) {
+                    if (active) *slot = mul2(gv, w);
+                } else if (q == 0) {
+                    const cf o = *slot;
+                    float* dst = (t < 3 && run0 + f2 > 0) ? hrow : grow;
+                    if (active) *reinterpret_cast<cf*>(dst + (long long)f * hop + 2 * (BQ * ap + b)) = fma2(gv, w, o);
+                } else {
+                    const cf o = fma2(gv, w, *slot);
+                    if (active) *slot = o;
+                }
+            });
+    }
+#pragma unroll
+    for (int s = 0; s < NS1; ++s) {
+        if (len_s[s] > 0) {
+            const int f = lo_s[s] + len_s[s] - 1;
+#pragma unroll
+            for (int q = 1; q < 4; ++q) {
+                const int p = (q + f) & 3;
+#pragma unroll
+                for (int ap = 0; ap < QA; ++ap) {
+                    const cf o = ola[((f2_s[s] * 4 + p) * QA + ap) * BQ + b_lane];
+                    *reinterpret_cast<cf*>(grow + (long long)(f + q) * hop + 2 * (BQ * ap + b_lane)) = o;
+                }
+            }
+        }
+    }
+    if (WITH_SUMS) {
+        l1 = warp_sum(l1); ll = warp_sum(ll);
+        if (lane == 0) {
+            double* pp = a.partial + ((long long)blockIdx.x * kStreamWarps + warp) * 2;
+            pp[0] = (double)l1; pp[1] = (double)ll * 0.69314718055994530942;
+        }
+    }
+}
+
+#ifndef TAC_STREAM_PK
+#define TAC_STREAM_PK 1       // packed-complex core (FFMA2); 0 = the scalar core of fft_core.cuh
+#endif
+#if TAC_STREAM_PK
+#define TAC_STREAM_CTA stream_cta_pk
+#else
+#define TAC_STREAM_CTA stream_cta
+#endif
+
 #ifndef TAC_STREAM_OCC
 #define TAC_STREAM_OCC 2      // 255 registers, no spills; 3 (168 registers) spills ~1 KB per thread and measured slower
 #endif
@@ -216,12 +360,9 @@ __global__ void __launch_bounds__(kStreamThreads, TAC_STREAM_OCC) mrstft_stream_
     const StreamScale& sc = a.sc[s];
     const int cta = (int)blockIdx.x - sc.cta_begin;
     switch (sc.n) {
-        case 2048: stream_cta<Plan2048, WITH_SUMS>(a, sc, cta, smem); break;
-        case 1024: stream_cta<Plan1024, WITH_SUMS>(a, sc, cta, smem); break;
-        case 512: stream_cta<Plan512, WITH_SUMS>(a, sc, cta, smem); break;
-        case 256: stream_cta<Plan256, WITH_SUMS>(a, sc, cta, smem); break;
-        case 128: stream_cta<Plan128, WITH_SUMS>(a, sc, cta, smem); break;
-        default: stream_cta<Plan64, WITH_SUMS>(a, sc, cta, smem); break;
+        case 2048: TAC_STREAM_CTA<Plan2048, WITH_SUMS>(a, sc, cta, smem); break;
+        case 1024: TAC_STREAM_CTA<Plan1024, WITH_SUMS>(a, sc, cta, smem); break;
+        default: TAC_STREAM_CTA<Plan512, WITH_SUMS>(a, sc, cta, smem); break;      // stream_applicable: n >= 512
     }
 }
 

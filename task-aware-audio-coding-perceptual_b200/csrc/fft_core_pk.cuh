@@ -142,8 +142,9 @@ __device__ __forceinline__ cf post_twiddle_pk(const cf base) {
 }
 
 // One-sided real spectrum from the packed transform.  emit(fr, k, v, slot) is called once for every k in [0, M]:
-// EVEN slots 2j carry X[k], k = k1 + A j; ODD slots 2j + 1 carry conj(X[M - k]); slot BQ (k1 == 0 lanes) carries X[M/2].
-template <class P, class Emit>
+// EVEN slots 2j carry X[k], k = k1 + A j; ODD slots 2j + 1 carry conj(X[M - k]) (TRUE_ODD: X[M - k] itself, for callers
+// that write the spectrum out); slot BQ (k1 == 0 lanes) carries X[M/2].
+template <class P, bool TRUE_ODD = false, class Emit>
 __device__ __forceinline__ void warp_fft_post_pk(const cf (&z)[P::BQ], const float2* __restrict__ pt, int lane, Emit emit) {
     constexpr int A = P::A, BQ = P::BQ, M = P::M;
     const int k1 = lane % A, fr = lane / A;
@@ -161,7 +162,8 @@ __device__ __forceinline__ void warp_fft_post_pk(const cf (&z)[P::BQ], const flo
         const cf T = fma2(rotm(D), bc(lo(cs)), mul2(D, bc(-hi(cs))));
         const int k = k1 + A * j;
         emit(fr, k, add2(S, T), 2 * j);
-        emit(fr, M - k, sub2(S, T), 2 * j + 1);
+        if constexpr (TRUE_ODD) emit(fr, M - k, sub2(cnj(S), cnj(T)), 2 * j + 1);
+        else emit(fr, M - k, sub2(S, T), 2 * j + 1);
     });
     if (k1 == 0) emit(fr, M / 2, mul2(cnj(z[BQ / 2]), bc(2.0f)), BQ);
 }

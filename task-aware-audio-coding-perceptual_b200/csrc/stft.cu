@@ -10,6 +10,7 @@
 //    end).  Results are transposed through a padded shared-memory tile so that each (k) row is
 //    written as a contiguous run of TF frames.
 #include "tac_common.cuh"
+#include "fft_core_pk.cuh"
 
 namespace tac {
 
@@ -57,17 +58,16 @@ template <class P>
 __device__ __forceinline__ void planes_task(const ScaleArg& sc, const float* tile, float2* xbuf, int lane,
                                             int f_first, int f_end, int tile_origin /* f*hop coordinate of tile[0] */,
                                             float* out_re_row, long long im_off) {
-    float zr[P::BQ], zi[P::BQ];
+    cf z[P::BQ];
     const float2* __restrict__ win2 = sc.t.win2;
     const int hop = sc.hop;
-    auto load = [&](auto, int fr, int m) -> float2 {
+    auto load = [&](auto, int fr, int m) -> cf {
         int f = f_first + fr;
         f = f < f_end ? f : f_first;                       // invalid frames recompute the first one
-        const float2 v = *reinterpret_cast<const float2*>(tile + (f * hop - tile_origin) + 2 * m);
-        const float2 w = ldg2(win2 + m);
-        return make_float2(__fmul_rn(v.x, w.x), __fmul_rn(v.y, w.y));   // never contracted: X(x) is bit-reproducible
+        // a plain product (mul.rn, never contracted): X(x) is bit-reproducible
+        return mul2(*reinterpret_cast<const cf*>(tile + (f * hop - tile_origin) + 2 * m), ldg_cf(win2 + m));
     };
-    warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load);
+    warp_fft_fwd_pk<P>(z, xbuf, sc.t.tw, lane, load);
     const int myf = f_first + lane / P::A;
     const bool valid = myf < f_end;
     // per-lane base pointers so that every store address is base + compile-time offset
@@ -76,7 +76,8 @@ __device__ __forceinline__ void planes_task(const ScaleArg& sc, const float* til
     float* re_hi = out_re_row + (long long)myf * sc.K + (P::M - k1);
     float* im_lo = re_lo + im_off;
     float* im_hi = re_hi + im_off;
-    warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
+    warp_fft_post_pk<P, true>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
+        const float vr = lo(v), vi = hi(v);
         if (valid) {
             if (slot == P::BQ) {                       // k = M/2 (k1 == 0 lanes only)
                 __stcs(re_lo + P::M / 2, vr); __stcs(im_lo + P::M / 2, vi);
@@ -191,20 +192,19 @@ __global__ void __launch_bounds__(kThreads, 1) stft_tiled_kernel(const TiledArgs
         t = __shfl_sync(0xffffffffu, t, 0);
         if (t >= ntasks) break;
         const int f_first = f0 + t * P::NFR;
-        float zr[P::BQ], zi[P::BQ];
+        cf z[P::BQ];
         const float2* __restrict__ win2 = a.t.win2;
-        auto load = [&](auto, int fr, int m) -> float2 {
+        auto load = [&](auto, int fr, int m) -> cf {
             int f = f_first + fr;
             f = f < f_end ? f : f_first;
-            const float2 v = *reinterpret_cast<const float2*>(tile + (f - f0) * a.hop + 2 * m);
-            const float2 w = ldg2(win2 + m);
-            return make_float2(__fmul_rn(v.x, w.x), __fmul_rn(v.y, w.y));   // never contracted: X(x) is bit-reproducible
+            return mul2(*reinterpret_cast<const cf*>(tile + (f - f0) * a.hop + 2 * m), ldg_cf(win2 + m));   // plain product
         };
-        warp_fft_fwd<P>(zr, zi, xbuf, a.t.tw, lane, load);
+        warp_fft_fwd_pk<P>(z, xbuf, a.t.tw, lane, load);
         const int myf = f_first + lane / P::A;
         const bool valid = myf < f_end;
         const int col = myf - f0;
-        warp_fft_post<P>(zr, zi, a.t.pt, lane, [&](int, int k, float vr, float vi, int) {
+        warp_fft_post_pk<P, true>(z, a.t.pt, lane, [&](int, int k, cf v, int) {
+            const float vr = lo(v), vi = hi(v);
             if (valid) {
                 if (MODE == TAC_OUT_MAGPHASE) {
                     o0[k * TS + col] = sqrtf(fmaf(vr, vr, vi * vi));
@@ -289,17 +289,15 @@ __global__ void __launch_bounds__(kFeThreads, 1) stft_frontend_kernel(const Tile
     float2* xbuf = xbuf_all + warp * kXbufFloat2;
     const int f_first = f0 + warp * P::NFR;
     const bool task = f_first < f_end;                             // warp-uniform
-    float zr[P::BQ], zi[P::BQ];
+    cf z[P::BQ];
     const float2* __restrict__ win2 = a.t.win2;
     if (task) {
-        auto load = [&](auto, int fr, int m) -> float2 {
+        auto load = [&](auto, int fr, int m) -> cf {
             int f = f_first + fr;
             f = f < f_end ? f : f_first;
-            const float2 v = *reinterpret_cast<const float2*>(tile + (f - f0) * a.hop + 2 * m);
-            const float2 w = ldg2(win2 + m);
-            return make_float2(__fmul_rn(v.x, w.x), __fmul_rn(v.y, w.y));   // never contracted: X(x) is bit-reproducible
+            return mul2(*reinterpret_cast<const cf*>(tile + (f - f0) * a.hop + 2 * m), ldg_cf(win2 + m));   // plain product
         };
-        warp_fft_fwd<P>(zr, zi, xbuf, a.t.tw, lane, load);
+        warp_fft_fwd_pk<P>(z, xbuf, a.t.tw, lane, load);
     }
     __syncthreads();                                               // every warp is done with its exchange tile
     const int myf = f_first + lane / P::A;
@@ -310,7 +308,8 @@ __global__ void __launch_bounds__(kFeThreads, 1) stft_frontend_kernel(const Tile
 #pragma unroll 1
     for (int plane = 0; plane < 2; ++plane) {
         if (task) {
-            warp_fft_post<P>(zr, zi, a.t.pt, lane, [&](int, int k, float vr, float vi, int) {
+            warp_fft_post_pk<P, true>(z, a.t.pt, lane, [&](int, int k, cf c, int) {
+                const float vr = lo(c), vi = hi(c);
                 float v;
                 if (plane == 0) {
                     const float m2 = fmaf(vr, vr, vi * vi);

@@ -84,7 +84,8 @@ struct Dit {
 };
 
 // ------------------------------------------------------------------ forward transform
-// load(integral_constant s, fr, m) returns the windowed packed sample pair z_fr[m] = (x[2m], x[2m+1]).  On return lane
+// load(integral_constant s, fr, m, integral_constant quarter) returns the windowed packed sample pair z_fr[m] =
+// (x[2m], x[2m+1]); quarter = 4 m / M tells a hop = n/4 caller which loads are the last use of their data.  On return lane
 // (fr = lane / A, k1 = lane % A) holds Z_fr[k1 + A*k2] in slot k2 of z.
 template <class P, class Load>
 __device__ __forceinline__ void warp_fft_fwd_pk(cf (&z)[P::BQ], float2* xbuf, const float2* __restrict__ tw, int lane,
@@ -97,7 +98,7 @@ __device__ __forceinline__ void warp_fft_fwd_pk(cf (&z)[P::BQ], float2* xbuf, co
         cf a[A];
         static_for<0, A>([&](auto ac) {
             constexpr int av = decltype(ac)::value;
-            a[brev(av, A)] = load(sc, fr, BQ * av + b);
+            a[brev(av, A)] = load(sc, fr, BQ * av + b, std::integral_constant<int, (4 * av) / A>{});   // + quarter of the frame
         });
         Dit<A, false>::run(a);
         cf* row = reinterpret_cast<cf*>(xbuf) + (fr * A) * RS + b;

@@ -16,6 +16,7 @@
 // Runs of one row are independent: a run starts R - 1 = ceil(n / hop) - 1 frames early and discards what it does not own.
 // Algorithmic bytes per row: read 8 * K * F, write 4 * out_len.
 #include "tac_common.cuh"
+#include "fft_core_pk.cuh"
 
 #include <math.h>
 #include <vector>
@@ -171,12 +172,15 @@ __global__ void __launch_bounds__(kIThreads, 1) istft_kernel(const IstftArgs a) 
         {
             float2* xbuf = xbuf_all + warp * kXbufFloat2;
             float2* tw = tile + (warp * NFR) * KP;
-            warp_fft_adj<P>(xbuf, a.t.tw, a.t.pt, lane,
-                [&](int fr, int k, int) -> float2 { return tw[fr * KP + k]; },
-                [&](auto, int f2, auto ac, int b, float2 g) {
+            cf* twc = reinterpret_cast<cf*>(tw);
+            warp_fft_adj_pk<P>(xbuf, a.t.tw, a.t.pt, lane,
+                [&](int fr, int k, int slot) -> cf {           // odd slots: conj(X[M - k]) (fft_core_pk.cuh convention)
+                    const cf v = twc[fr * KP + k];
+                    return (slot & 1) ? cnj(v) : v;
+                },
+                [&](auto, int f2, auto ac, int b, cf g) {
                     const int m = P::BQ * decltype(ac)::value + b;
-                    const float2 w = ldg2(win2 + m);
-                    tw[f2 * KP + m] = make_float2(g.x * w.x * scale, g.y * w.y * scale);
+                    twc[f2 * KP + m] = mul2(mul2(g, ldg_cf(win2 + m)), bc(scale));
                 });
         }
         __syncthreads();

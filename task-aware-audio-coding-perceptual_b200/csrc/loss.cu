@@ -8,6 +8,7 @@
 // f + 2R ... with R = ceil(n/hop) never overlap), so the result is deterministic too.
 #include "tac_common.cuh"
 #include "loss_common.cuh"
+#include "fft_core_pk.cuh"
 
 namespace tac {
 
@@ -49,27 +50,27 @@ template <class P>
 __device__ __forceinline__ void loss_fwd_task(const LossScale& sc, const float* tx, const float* ty, float2* xbuf,
                                               int lane, int f_first, int f_end, int origin, float eps,
                                               float& acc_l1, float& acc_log) {
-    float zr[P::BQ], zi[P::BQ];
+    cf z[P::BQ];
     float mx[P::BQ + 1];
     const float2* __restrict__ win2 = sc.t.win2;
     const int hop = sc.hop;
     const float* cur = tx;
-    auto load = [&](auto, int fr, int m) -> float2 {
+    auto load = [&](auto, int fr, int m, auto) -> cf {
         int f = f_first + fr;
         f = f < f_end ? f : f_first;
-        const float2 v = *reinterpret_cast<const float2*>(cur + (f * hop - origin) + 2 * m);
-        const float2 w = ldg2(win2 + m);
-        return make_float2(__fmul_rn(v.x, w.x), __fmul_rn(v.y, w.y));   // never contracted: X(x) is bit-reproducible
+        return mul2(*reinterpret_cast<const cf*>(cur + (f * hop - origin) + 2 * m), ldg_cf(win2 + m));   // plain product
     };
-    warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load);
-    warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
+    warp_fft_fwd_pk<P>(z, xbuf, sc.t.tw, lane, load);
+    warp_fft_post_pk<P>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
+        const float vr = lo(v), vi = hi(v);
         mx[slot] = fast_mag(fmaf(vr, vr, vi * vi));
     });
     cur = ty;
-    warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load);
+    warp_fft_fwd_pk<P>(z, xbuf, sc.t.tw, lane, load);
     const bool valid = (f_first + lane / P::A) < f_end;
     float l1 = 0.0f, ll = 0.0f;
-    warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
+    warp_fft_post_pk<P>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
+        const float vr = lo(v), vi = hi(v);
         const float m2 = fmaf(vr, vr, vi * vi);
         const float my = fast_mag(m2);                                  // same arithmetic as the fused kernel
         const float xv = mx[slot];
@@ -170,31 +171,32 @@ template <class P, bool WITH_SUMS>
 __device__ __forceinline__ void loss_bwd_task(const LossScale& sc, const float* __restrict__ xr, const float* __restrict__ yr,
                                               float* acc, float2* xbuf, int lane, int f_base, int f_stride, int f_end,
                                               long long c0, float eps, float c_l1, float c_log, float& acc_l1, float& acc_log) {
-    float zr[P::BQ], zi[P::BQ];
-    float gr[P::BQ + 1], gi[P::BQ + 1];
+    cf z[P::BQ];
+    cf G[P::BQ + 1];
+    float mx[P::BQ + 1];
     const float2* __restrict__ win2 = sc.t.win2;
     const int hop = sc.hop;
     const float* cur = xr;
     // frames of this task: f_base + i * f_stride, i in [0, NFR)
-    auto load = [&](auto, int fr, int m) -> float2 {
+    auto load = [&](auto, int fr, int m, auto) -> cf {
         int f = f_base + fr * f_stride;
         f = f < f_end ? f : f_base;
-        const float2 v = __ldg(reinterpret_cast<const float2*>(cur + (long long)f * hop) + m);
-        const float2 w = ldg2(win2 + m);
-        return make_float2(__fmul_rn(v.x, w.x), __fmul_rn(v.y, w.y));   // never contracted: X(x) is bit-reproducible
+        return mul2(__ldg(reinterpret_cast<const cf*>(cur + (long long)f * hop) + m), ldg_cf(win2 + m));   // plain product
     };
-    warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load);
-    warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
-        gr[slot] = fast_mag(fmaf(vr, vr, vi * vi));                  // |X|
+    warp_fft_fwd_pk<P>(z, xbuf, sc.t.tw, lane, load);
+    warp_fft_post_pk<P>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
+        const float vr = lo(v), vi = hi(v);
+        mx[slot] = fast_mag(fmaf(vr, vr, vi * vi));                  // |X|
     });
     cur = yr;
-    warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load);
+    warp_fft_fwd_pk<P>(z, xbuf, sc.t.tw, lane, load);
     float l1 = 0.0f, ll = 0.0f;
-    warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
+    warp_fft_post_pk<P>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
+        const float vr = lo(v), vi = hi(v);
         const float m2 = fmaf(vr, vr, vi * vi);
         const float inv = m2 >= kTinyMag2 ? fast_rsqrt(m2) : 0.0f;
         const float my = m2 * inv;                                    // |Y|
-        const float xv = gr[slot];                                    // |X|
+        const float xv = mx[slot];                                    // |X|
         const float d = my - xv;
         const float dl = fast_lg2(fmaxf(my, eps)) - fast_lg2(fmaxf(xv, eps));
         if (WITH_SUMS) { l1 += fabsf(d); ll += fabsf(dl); }           // same arithmetic as the forward-only kernel
@@ -202,20 +204,17 @@ __device__ __forceinline__ void loss_bwd_task(const LossScale& sc, const float* 
         const float invm = my >= eps ? inv : 0.0f;
         float g = fmaf(signed_coef(dl, c_log), invm, signed_coef(d, c_l1));
         g *= inv;                                                     // dY / dYc = Yc / |Y|
-        gr[slot] = g * vr; gi[slot] = g * vi;
+        G[slot] = mul2(v, bc(g));                                     // odd slots: conj(dL/dY[M-k]), as the adjoint expects
     });
     if (WITH_SUMS && (f_base + (lane / P::A) * f_stride) < f_end) { acc_l1 += l1; acc_log += ll * 0.69314718055994530942f; }
-    warp_fft_adj<P>(xbuf, sc.t.tw, sc.t.pt, lane,
-        [&](int, int, int slot) -> float2 { return make_float2(gr[slot], gi[slot]); },
-        [&](auto, int fr, auto ac, int b, float2 g) {
+    warp_fft_adj_pk<P>(xbuf, sc.t.tw, sc.t.pt, lane,
+        [&](int, int, int slot) -> cf { return G[slot]; },
+        [&](auto, int fr, auto ac, int b, cf g) {
             const int m = P::BQ * decltype(ac)::value + b;
             const int f = f_base + fr * f_stride;
             if (f < f_end) {
-                const float2 w = ldg2(win2 + m);
-                float2* p = reinterpret_cast<float2*>(acc + ((long long)f * hop - c0)) + m;
-                float2 o = *p;
-                o.x = fmaf(g.x, w.x, o.x); o.y = fmaf(g.y, w.y, o.y);
-                *p = o;
+                cf* p = reinterpret_cast<cf*>(acc + ((long long)f * hop - c0)) + m;
+                *p = fma2(g, ldg_cf(win2 + m), *p);
             }
         });
 }

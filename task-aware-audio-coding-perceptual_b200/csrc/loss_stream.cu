@@ -205,6 +205,43 @@ __device__ __forceinline__ void stream_cta(const StreamArgs& a, const StreamScal
 }
 
 
+// Cache policy of the packed kernel.  A sample is read by the four consecutive frames that cover it: the first quarter
+// of a frame is the LAST use of its data (evict first), everything else is wanted again one step later.  The gradient
+// blocks are written once and read by the combine kernel only: streaming stores keep them out of the way of the frames.
+#ifndef TAC_LD_HINT
+#define TAC_LD_HINT 2         // 0: plain read-only loads; 1: frame hints; 2: + tables evict-last (A/B on B200: 0.570 -> 0.559 ms with 2 + streaming stores)
+#endif
+#ifndef TAC_ST_CS
+#define TAC_ST_CS 1
+#endif
+template <int QUARTER>
+__device__ __forceinline__ cf ld_frame(const float* p) {
+#if TAC_LD_HINT >= 1
+    cf v;
+    if constexpr (QUARTER == 0) asm("ld.global.nc.L1::evict_first.b64 %0, [%1];" : "=l"(v) : "l"(p));
+    else asm("ld.global.nc.L1::evict_last.b64 %0, [%1];" : "=l"(v) : "l"(p));
+    return v;
+#else
+    return __ldg(reinterpret_cast<const cf*>(p));
+#endif
+}
+__device__ __forceinline__ cf ld_table(const float2* p) {
+#if TAC_LD_HINT >= 2
+    cf v;
+    asm("ld.global.nc.L1::evict_last.b64 %0, [%1];" : "=l"(v) : "l"(p));
+    return v;
+#else
+    return ldg_cf(p);
+#endif
+}
+__device__ __forceinline__ void st_grad(float* p, cf v) {
+#if TAC_ST_CS
+    asm volatile("st.global.cs.b64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+#else
+    *reinterpret_cast<cf*>(p) = v;
+#endif
+}
+
 // The same walk on the packed-complex core (fft_core_pk.cuh): every complex value is one aligned register pair and the
 // butterflies, twiddles, window products and overlap-adds are two-wide FP32 instructions -- about half the instruction
 // stream of stream_cta for the same arithmetic.  Only the per-bin loss terms (|.|, log, sign) stay scalar.
@@ -264,11 +301,11 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
             fx[s] = xr + (long long)f * hop;
             fy[s] = yr + (long long)f * hop;
         }
-        auto load_x = [&](auto scn, int, int m) -> cf {
-            return mul2(__ldg(reinterpret_cast<const cf*>(fx[decltype(scn)::value] + 2 * m)), ldg_cf(win2 + m));
+        auto load_x = [&](auto scn, int, int m, auto qc) -> cf {
+            return mul2(ld_frame<decltype(qc)::value>(fx[decltype(scn)::value] + 2 * m), ld_table(win2 + m));
         };
-        auto load_y = [&](auto scn, int, int m) -> cf {
-            return mul2(__ldg(reinterpret_cast<const cf*>(fy[decltype(scn)::value] + 2 * m)), ldg_cf(win2 + m));
+        auto load_y = [&](auto scn, int, int m, auto qc) -> cf {
+            return mul2(ld_frame<decltype(qc)::value>(fy[decltype(scn)::value] + 2 * m), ld_table(win2 + m));
         };
         warp_fft_fwd_pk<P>(z, xbuf, sc.t.tw, lane, load_x);
         warp_fft_post_pk<P>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
@@ -299,7 +336,7 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
                 constexpr int q = av / QA, ap = av % QA;
                 const bool active = t < len_s[s];
                 const int f = lo_s[s] + t;
-                const cf w = ldg_cf(win2 + BQ * av + b);
+                const cf w = ld_table(win2 + BQ * av + b);
                 const int p = (q + f) & 3;
                 cf* slot = ola + ((f2 * 4 + p) * QA + ap) * BQ + b;
                 if (q == 3) {
@@ -307,7 +344,7 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
                 } else if (q == 0) {
                     const cf o = *slot;
                     float* dst = (t < 3 && run0 + f2 > 0) ? hrow : grow;
-                    if (active) *reinterpret_cast<cf*>(dst + (long long)f * hop + 2 * (BQ * ap + b)) = fma2(gv, w, o);
+                    if (active) st_grad(dst + (long long)f * hop + 2 * (BQ * ap + b), fma2(gv, w, o));
                 } else {
                     const cf o = fma2(gv, w, *slot);
                     if (active) *slot = o;
@@ -324,7 +361,7 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
 #pragma unroll
                 for (int ap = 0; ap < QA; ++ap) {
                     const cf o = ola[((f2_s[s] * 4 + p) * QA + ap) * BQ + b_lane];
-                    *reinterpret_cast<cf*>(grow + (long long)(f + q) * hop + 2 * (BQ * ap + b_lane)) = o;
+                    st_grad(grow + (long long)(f + q) * hop + 2 * (BQ * ap + b_lane), o);
                 }
             }
         }

@@ -61,7 +61,7 @@ __device__ __forceinline__ void planes_task(const ScaleArg& sc, const float* til
     cf z[P::BQ];
     const float2* __restrict__ win2 = sc.t.win2;
     const int hop = sc.hop;
-    auto load = [&](auto, int fr, int m) -> cf {
+    auto load = [&](auto, int fr, int m, auto) -> cf {
         int f = f_first + fr;
         f = f < f_end ? f : f_first;                       // invalid frames recompute the first one
         // a plain product (mul.rn, never contracted): X(x) is bit-reproducible
@@ -194,7 +194,7 @@ __global__ void __launch_bounds__(kThreads, 1) stft_tiled_kernel(const TiledArgs
         const int f_first = f0 + t * P::NFR;
         cf z[P::BQ];
         const float2* __restrict__ win2 = a.t.win2;
-        auto load = [&](auto, int fr, int m) -> cf {
+        auto load = [&](auto, int fr, int m, auto) -> cf {
             int f = f_first + fr;
             f = f < f_end ? f : f_first;
             return mul2(*reinterpret_cast<const cf*>(tile + (f - f0) * a.hop + 2 * m), ldg_cf(win2 + m));   // plain product
@@ -292,7 +292,7 @@ __global__ void __launch_bounds__(kFeThreads, 1) stft_frontend_kernel(const Tile
     cf z[P::BQ];
     const float2* __restrict__ win2 = a.t.win2;
     if (task) {
-        auto load = [&](auto, int fr, int m) -> cf {
+        auto load = [&](auto, int fr, int m, auto) -> cf {
             int f = f_first + fr;
             f = f < f_end ? f : f_first;
             return mul2(*reinterpret_cast<const cf*>(tile + (f - f0) * a.hop + 2 * m), ldg_cf(win2 + m));   // plain product

@@ -431,10 +431,22 @@ extern "C" int tac_dpca_eig(const double* stats, int nv, int d, float* s, float*
         const size_t tsmem = dpca_eig_tri_smem_bytes(d);
         static bool attr_set = false;
         if (!attr_set) {
-            TAC_CHECK_CUDA(cudaFuncSetAttribute(dpca_eig_tri_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dpca_eig_tri_smem_bytes(kTriMaxD)));
+            TAC_CHECK_CUDA(cudaFuncSetAttribute(dpca_eig_tri_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dpca_eig_tri_smem_bytes(kTriMaxD)));
+            TAC_CHECK_CUDA(cudaFuncSetAttribute(dpca_eig_tri_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dpca_eig_tri_smem_bytes(kTriMaxD)));
+            TAC_CHECK_CUDA(cudaFuncSetAttribute(dpca_tri_vectors_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dpca_tri_vectors_smem_bytes()));
             attr_set = true;
         }
-        dpca_eig_tri_kernel<<<nv, kTriThreads, tsmem, st>>>(stats, d, s, v, mu, rank, reinterpret_cast<double*>(workspace)); TAC_LAUNCHED(1);
+        double* gws = reinterpret_cast<double*>(workspace);
+#if TAC_EIG_SPLIT
+        // 1. tridiagonalise (one CTA per view)  2. one warp per eigenpair on d/8 CTAs per view  3. order + outputs
+        dpca_eig_tri_kernel<true><<<nv, kTriThreads, tsmem, st>>>(stats, d, s, v, mu, rank, gws); TAC_LAUNCHED(1);
+        TAC_CHECK_CUDA(cudaGetLastError());
+        dpca_tri_vectors_kernel<<<dim3((d + kVecWarps - 1) / kVecWarps, nv), kVecThreads, dpca_tri_vectors_smem_bytes(), st>>>(d, gws); TAC_LAUNCHED(1);
+        TAC_CHECK_CUDA(cudaGetLastError());
+        dpca_tri_finish_kernel<<<nv, kTriThreads, 0, st>>>(stats, d, s, v, rank, gws); TAC_LAUNCHED(1);
+#else
+        dpca_eig_tri_kernel<false><<<nv, kTriThreads, tsmem, st>>>(stats, d, s, v, mu, rank, gws); TAC_LAUNCHED(1);
+#endif
         TAC_CHECK_CUDA(cudaGetLastError());
         return TAC_OK;
     }

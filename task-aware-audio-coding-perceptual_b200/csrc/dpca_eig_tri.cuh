@@ -107,6 +107,16 @@ __host__ __device__ __forceinline__ int tri_refl_off(int k, int d) { return k * 
 __device__ long long g_tri_prof[8];
 #define TRI_STAMP(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) g_tri_prof[i] = clock64(); } while (0)
 
+// Workspace of the split solve, per view, in doubles (fixed offsets, d <= 128).
+constexpr int kTriWsRefl = 0;                    // packed reflectors, d (d - 1) / 2 <= 8128
+constexpr int kTriWsA = 8192;                    // a, b, b2, beta: 4 x 128
+constexpr int kTriWsLam = kTriWsA + 512;         // eigenvalues of the scaled T, slot order
+constexpr int kTriWsScal = kTriWsLam + 128;      // scal[8]
+constexpr int kTriWsBlk = kTriWsScal + 8;        // blk_s[128], blk_e[128] (ints)
+constexpr int kTriWsVec = 9216;                  // eigenvectors of C, [slot][row] float64
+constexpr int kTriWsDoubles = kTriWsVec + kTriMaxD * kTriMaxD;
+
+template <bool SPLIT>
 __global__ void __launch_bounds__(kTriThreads, 1)
 dpca_eig_tri_kernel(const double* __restrict__ stats, int d, float* __restrict__ s_out, float* __restrict__ v_out,
                     float* __restrict__ mu_out, int* __restrict__ rank_out, double* __restrict__ gws) {
@@ -119,7 +129,7 @@ dpca_eig_tri_kernel(const double* __restrict__ stats, int d, float* __restrict__
     const int view = blockIdx.x;
     const size_t stride = 1 + d + (size_t)d * d;
     const double* st = stats + view * stride;
-    double* Lp = gws + (size_t)view * 2 * d * d;                    // [i][slot] forward multipliers b_i / D+_i
+    double* Lp = gws + (size_t)view * (SPLIT ? kTriWsDoubles : 2 * d * d);   // [i][slot] forward multipliers b_i / D+_i
     double* Um = Lp + (size_t)d * d;                                // [i][slot] backward multipliers b_{i-1} / D-_i
     const double n = st[0];
     const double inv_n = n > 0.0 ? 1.0 / n : 0.0;
@@ -272,6 +282,22 @@ dpca_eig_tri_kernel(const double* __restrict__ stats, int d, float* __restrict__
         }
     }
     __syncthreads();
+    if constexpr (SPLIT) {       // hand T, the block structure and the reflectors to dpca_tri_vectors_kernel
+        double* w = Lp;
+        const int nrefl = tri_refl_off(d - 1 > 0 ? d - 1 : 0, d);
+        for (int i = tid; i < nrefl; i += kTriThreads) w[kTriWsRefl + i] = refl[i];
+        if (tid < d) {
+            w[kTriWsA + tid] = sh.a[tid];
+            w[kTriWsA + kTriMaxD + tid] = sh.b[tid];
+            w[kTriWsA + 2 * kTriMaxD + tid] = sh.b2[tid];
+            w[kTriWsA + 3 * kTriMaxD + tid] = sh.beta[tid];
+            int* blk = reinterpret_cast<int*>(w + kTriWsBlk);
+            blk[tid] = sh.blk_s[tid]; blk[kTriMaxD + tid] = sh.blk_e[tid];
+        }
+        if (tid < 8) w[kTriWsScal + tid] = sh.scal[tid];
+        TRI_STAMP(3);
+        return;
+    }
     const double tn = sh.scal[4];
 
     TRI_STAMP(3);
@@ -469,7 +495,244 @@ dpca_eig_tri_kernel(const double* __restrict__ stats, int d, float* __restrict__
     TRI_STAMP(7);
 }
 
-inline size_t dpca_eig_tri_workspace_bytes(int nv, int d) { return (size_t)nv * 2 * d * d * sizeof(double); }
+// ------------------------------------------------------------------------------------------ split solve, stages 2 and 3
+// Eigenpairs are independent once T is known, and every stage below is a dependent float64 chain, so one SM is the wrong
+// place for 128 of them: dpca_tri_vectors_kernel gives each eigenpair its own WARP, eight warps per CTA, d / 8 CTAs per
+// view.  Measured on B200 (d = 128): multisection + twisted factorisation + back-transformation 725 k cycles on one SM
+// -> under 100 k cycles spread over 16 SMs.
+constexpr int kVecWarps = 8;
+constexpr int kVecThreads = kVecWarps * 32;
+
+struct VecShared {
+    double a[kTriMaxD], b[kTriMaxD], b2[kTriMaxD], beta[kTriMaxD];
+    double scal[8];
+    int blk_s[kTriMaxD], blk_e[kTriMaxD];
+};
+
+__global__ void __launch_bounds__(kVecThreads, 1)
+dpca_tri_vectors_kernel(int d, double* __restrict__ gws) {
+    extern __shared__ __align__(16) unsigned char vec_smem_raw[];
+    double* refl = reinterpret_cast<double*>(vec_smem_raw);                       // packed reflectors (<= 8128)
+    double* scratch = refl + 8192;                                                // per warp: Dp | Dm | Lp | Um, 128 each
+    __shared__ VecShared sh;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int view = blockIdx.y;
+    double* w = gws + (size_t)view * kTriWsDoubles;
+    const int nrefl = tri_refl_off(d - 1 > 0 ? d - 1 : 0, d);
+    for (int i = tid; i < nrefl; i += kVecThreads) refl[i] = w[kTriWsRefl + i];
+    if (tid < d) {
+        sh.a[tid] = w[kTriWsA + tid];
+        sh.b[tid] = w[kTriWsA + kTriMaxD + tid];
+        sh.b2[tid] = w[kTriWsA + 2 * kTriMaxD + tid];
+        sh.beta[tid] = w[kTriWsA + 3 * kTriMaxD + tid];
+        const int* blk = reinterpret_cast<const int*>(w + kTriWsBlk);
+        sh.blk_s[tid] = blk[tid]; sh.blk_e[tid] = blk[kTriMaxD + tid];
+    }
+    if (tid < 8) sh.scal[tid] = w[kTriWsScal + tid];
+    __syncthreads();
+    const int slot = blockIdx.x * kVecWarps + warp;
+    if (slot >= d) return;                                   // no block barrier below
+    const double eps = 2.220446049250313e-16;
+    const int s = sh.blk_s[slot], e = sh.blk_e[slot], kk = slot - s;
+
+    // ---- eigenvalue: multisection, the 32 lanes evaluate 32 interior points of the bracket per round (33^12 > 2^60)
+    double gl = 1e300, gu = -1e300;
+    for (int i = s + lane; i <= e; i += 32) {
+        const double r = (i > s ? fabs(sh.b[i - 1]) : 0.0) + (i < e ? fabs(sh.b[i]) : 0.0);
+        gl = fmin(gl, sh.a[i] - r); gu = fmax(gu, sh.a[i] + r);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        gl = fmin(gl, __shfl_xor_sync(0xffffffffu, gl, o));
+        gu = fmax(gu, __shfl_xor_sync(0xffffffffu, gu, o));
+    }
+    double lo = gl - 4.0 * eps, hi = gu + 4.0 * eps;
+    for (int it = 0; it < 12; ++it) {
+        const double step = (hi - lo) * (1.0 / 33.0);
+        const double x = fma(step, (double)(lane + 1), lo);
+        const int c = tri_sturm(sh.a, sh.b2, s, e, x);
+        const int q = __popc(__ballot_sync(0xffffffffu, c <= kk));    // counts are monotone in x: the first q points
+        const double nlo = q > 0 ? fma(step, (double)q, lo) : lo;
+        const double nhi = q < 32 ? fma(step, (double)(q + 1), lo) : hi;
+        lo = nlo; hi = nhi;
+    }
+    const double l = 0.5 * (lo + hi);
+
+    // ---- eigenvector of T: twisted factorisation.  Lane 0 runs the backward sweep, lane 1 the forward sweep (they are
+    // independent), all lanes pick the twist index, lanes 0 / 1 run the two substitutions.
+    double* Dp = scratch + (size_t)warp * 4 * kTriMaxD;
+    double* Dm = Dp + kTriMaxD;
+    double* Lp = Dm + kTriMaxD;
+    double* Um = Lp + kTriMaxD;
+    const double pivmin = 1e-290;
+    if (lane == 0) {
+        double dm = sh.a[e] - l;
+        for (int i = e; i > s; --i) {
+            if (fabs(dm) < pivmin) dm = -pivmin;
+            const double r = tri_rcp(dm);
+            Dm[i] = dm;
+            Um[i] = sh.b[i - 1] * r;
+            dm = fma(-sh.b2[i - 1], r, sh.a[i - 1] - l);
+        }
+        Dm[s] = dm;
+    } else if (lane == 1) {
+        double dp = sh.a[s] - l;
+        Dp[s] = dp;
+        for (int i = s; i < e; ++i) {
+            if (fabs(dp) < pivmin) dp = -pivmin;
+            const double rc = tri_rcp(dp);
+            Lp[i] = sh.b[i] * rc;
+            dp = fma(-sh.b2[i], rc, sh.a[i + 1] - l);
+            Dp[i + 1] = dp;
+        }
+    }
+    __syncwarp();
+    double best = 1e300;
+    int r = e;
+    for (int i = s + lane; i <= e; i += 32) {               // gamma_i = D+_i + D-_i - (a_i - l); first minimum wins
+        const double g = fabs(Dp[i] + Dm[i] - (sh.a[i] - l));
+        if (g < best) { best = g; r = i; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int orr = __shfl_xor_sync(0xffffffffu, r, o);
+        if (ob < best || (ob == best && orr < r)) { best = ob; r = orr; }
+    }
+    __syncwarp();
+    double* zc = Dp;                                         // the column of Z, rows s..e (D+ is no longer needed)
+    if (lane == 0) {
+        double zz = 1.0;
+        zc[r] = 1.0;
+        for (int i = r - 1; i >= s; --i) { zz = -Lp[i] * zz; zc[i] = zz; }
+    } else if (lane == 1) {
+        double zz = 1.0;
+        for (int i = r + 1; i <= e; ++i) { zz = -Um[i] * zz; zc[i] = zz; }
+    }
+    __syncwarp();
+    double z[4];
+    double nrm = 0.0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int row = lane + 32 * i;
+        z[i] = (row >= s && row <= e) ? zc[row] : 0.0;
+        nrm = fma(z[i], z[i], nrm);
+    }
+    nrm = tri_warp_sum(nrm);
+    const double inv = tri_rsqrt(nrm);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) z[i] *= inv;
+
+    // ---- back-transformation  z <- H_0 H_1 ... H_{d-3} z
+    for (int k = d - 3; k >= 0; --k) {
+        const double beta = sh.beta[k];
+        if (beta == 0.0) continue;                           // uniform
+        const double* vk = refl + tri_refl_off(k, d) - (k + 1);
+        double v[4];
+        double acc = 0.0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int row = lane + 32 * i;
+            v[i] = (row > k && row < d) ? vk[row] : 0.0;
+            acc = fma(v[i], z[i], acc);
+        }
+        acc = tri_warp_sum(acc);
+        const double tb = acc * beta;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) z[i] = fma(-v[i], tb, z[i]);
+    }
+    double* vec = w + kTriWsVec + (size_t)slot * kTriMaxD;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int row = lane + 32 * i;
+        if (row < d) vec[row] = z[i];
+    }
+    if (lane == 0) w[kTriWsLam + slot] = l;
+}
+
+// Stage 3 (one CTA per view): Gram-Schmidt inside clusters closer than 1e-9 |T| (rare; on the back-transformed vectors,
+// which is the same thing because Q is orthogonal), descending order by counting, s = sqrt(lambda), float32 outputs.
+__global__ void __launch_bounds__(kTriThreads, 1)
+dpca_tri_finish_kernel(const double* __restrict__ stats, int d, float* __restrict__ s_out, float* __restrict__ v_out,
+                       int* __restrict__ rank_out, double* __restrict__ gws) {
+    __shared__ double lam[kTriMaxD];
+    __shared__ int blk_s[kTriMaxD], ord[kTriMaxD], inv[kTriMaxD];
+    __shared__ double scal[8];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int view = blockIdx.x;
+    double* w = gws + (size_t)view * kTriWsDoubles;
+    double* V = w + kTriWsVec;                               // [slot][row]
+    const double n = stats[(size_t)view * (1 + d + (size_t)d * d)];
+    if (tid < d) {
+        lam[tid] = w[kTriWsLam + tid];
+        blk_s[tid] = reinterpret_cast<const int*>(w + kTriWsBlk)[tid];
+    }
+    if (tid < 8) scal[tid] = w[kTriWsScal + tid];
+    __syncthreads();
+    const double tn = scal[4];
+    const int clustered = __syncthreads_or(tid < d && tid > blk_s[tid] && lam[tid] - lam[tid - 1] <= 1e-9 * tn);
+    if (clustered) {
+        if (warp == 0) {
+            for (int k = 1; k < d; ++k) {
+                const int s = blk_s[k];
+                bool changed = false;
+                for (int j = k - 1; j >= s && lam[k] - lam[j] <= 1e-9 * tn * (double)(k - j); --j) {
+                    double dot = 0.0;
+                    for (int i = lane; i < d; i += 32) dot = fma(V[(size_t)j * kTriMaxD + i], V[(size_t)k * kTriMaxD + i], dot);
+                    dot = tri_warp_sum(dot);
+                    for (int i = lane; i < d; i += 32) V[(size_t)k * kTriMaxD + i] -= dot * V[(size_t)j * kTriMaxD + i];
+                    changed = true;
+                    __syncwarp();
+                }
+                if (changed) {
+                    double nn = 0.0;
+                    for (int i = lane; i < d; i += 32) nn = fma(V[(size_t)k * kTriMaxD + i], V[(size_t)k * kTriMaxD + i], nn);
+                    nn = sqrt(tri_warp_sum(nn));
+                    const double sc = nn > 1e-8 ? 1.0 / nn : 0.0;
+                    for (int i = lane; i < d; i += 32) V[(size_t)k * kTriMaxD + i] *= sc;
+                    __syncwarp();
+                }
+            }
+        }
+        __syncthreads();
+    }
+    const double fro = scal[3];
+    const double null_thr = 1e-14 * fro;
+    if (tid < d) lam[tid] *= scal[5];
+    __syncthreads();
+    if (tid < d) {
+        const double lj = lam[tid];
+        int rk = 0;
+        for (int i = 0; i < d; ++i) { const double li = lam[i]; rk += (li > lj) || (li == lj && i < tid); }
+        ord[tid] = rk;
+        inv[rk] = tid;
+    }
+    __syncthreads();
+    const int r_eff = (int)(n < (double)d ? n : (double)d);          // torch.svd(some=True): min(B, d) values
+    float* so = s_out + (size_t)view * d;
+    float* vo = v_out + (size_t)view * d * d;
+    if (tid < d) {
+        const int rk = ord[tid];
+        const double l = lam[tid];
+        so[rk] = (rk < r_eff && l > 0.0) ? (float)sqrt(l) : 0.0f;
+    }
+    for (int e = tid; e < d * d; e += kTriThreads) {
+        const int rk = e / d, row = e % d;                           // coalesced reads of one eigenvector per d threads
+        const int col = inv[rk];
+        vo[(size_t)row * d + rk] = (float)(lam[col] > null_thr ? V[(size_t)col * kTriMaxD + row] : 0.0);
+    }
+    if (tid == 0) rank_out[view] = r_eff;
+}
+
+inline size_t dpca_tri_vectors_smem_bytes() { return (size_t)(8192 + kVecWarps * 4 * kTriMaxD) * sizeof(double); }
+
+#ifndef TAC_EIG_SPLIT
+#define TAC_EIG_SPLIT 1        // 1: tridiagonalise (1 CTA / view) -> eigenpairs on d/8 CTAs per view -> order + outputs;  0: one CTA per view
+#endif
+inline size_t dpca_eig_tri_workspace_bytes(int nv, int d) {
+    const size_t per = TAC_EIG_SPLIT ? (size_t)kTriWsDoubles : (size_t)2 * d * d;
+    return (size_t)nv * per * sizeof(double);
+}
 inline size_t dpca_eig_tri_smem_bytes(int d) { return ((size_t)d * (d + 1) + (size_t)tri_refl_off(d - 1 > 0 ? d - 1 : 0, d) + d) * sizeof(double); }
 
 }  // namespace tac

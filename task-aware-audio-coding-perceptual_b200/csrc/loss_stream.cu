@@ -24,8 +24,18 @@ namespace tac {
 #endif
 constexpr int kStreamWarps = TAC_STREAM_WARPS;
 constexpr int kStreamThreads = kStreamWarps * 32;
-constexpr int kRunTarget = 7;                       // frames per run (work unit of one lane group)
-constexpr int kOlaFloat2 = 1024;                    // per-warp overlap-add ring: NFR * M float2 <= 1024 (8 KiB)
+#ifndef TAC_STREAM_PK
+#define TAC_STREAM_PK 1       // packed-complex core (FFMA2); 0 = the scalar core of fft_core.cuh
+#endif
+#ifndef TAC_RUN_TARGET
+#define TAC_RUN_TARGET 7
+#endif
+constexpr int kRunTarget = TAC_RUN_TARGET;          // frames per run (work unit of one lane group)
+// per-warp overlap-add ring.  Scalar kernel: four hop blocks, NFR * M float2 <= 1024 (8 KiB).  Packed kernel: THREE --
+// the block that completes in a frame (q == 0) and the one that opens in it (q == 3) belong to the same lane and share a
+// slot -- so a CTA needs 58 KiB instead of 66, two CTAs fit the 132 KiB shared-memory configuration and the L1 that
+// serves the 3/4-overlapping frame reads grows from 64 to 96 KiB.
+constexpr int kOlaFloat2 = TAC_STREAM_PK ? 768 : 1024;
 constexpr int kStreamWarpFloat2 = kXbufFloat2 + kOlaFloat2;
 
 struct StreamScale {
@@ -69,7 +79,7 @@ __device__ __forceinline__ float2 ld_stream2(const float* p) {
 template <class P, bool WITH_SUMS>
 __device__ __forceinline__ void stream_cta(const StreamArgs& a, const StreamScale& sc, int cta, float2* smem) {
     constexpr int A = P::A, BQ = P::BQ, M = P::M, NFR = P::NFR, NS1 = P::NS1, QA = A / 4;
-    static_assert(A % 4 == 0 && NFR * M <= kOlaFloat2, "plan does not fit the streaming overlap-add ring");
+    static_assert(A % 4 == 0 && (TAC_STREAM_PK || NFR * M <= kOlaFloat2), "plan does not fit the streaming overlap-add ring");
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float2* xbuf = smem + warp * kStreamWarpFloat2;
     float2* ola = xbuf + kXbufFloat2;                      // [NFR][4 quarters][QA][BQ]
@@ -248,10 +258,10 @@ __device__ __forceinline__ void st_grad(float* p, cf v) {
 template <class P, bool WITH_SUMS>
 __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamScale& sc, int cta, float2* smem) {
     constexpr int A = P::A, BQ = P::BQ, M = P::M, NFR = P::NFR, NS1 = P::NS1, QA = A / 4;
-    static_assert(A % 4 == 0 && NFR * M <= kOlaFloat2, "plan does not fit the streaming overlap-add ring");
+    static_assert(A % 4 == 0 && NFR * M * 3 / 4 <= kOlaFloat2, "plan does not fit the streaming overlap-add ring");
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float2* xbuf = smem + warp * kStreamWarpFloat2;
-    cf* ola = reinterpret_cast<cf*>(xbuf + kXbufFloat2);  // [NFR][4 quarters][QA][BQ]
+    cf* ola = reinterpret_cast<cf*>(xbuf + kXbufFloat2);  // [NFR][3 slots][QA][BQ]: hop block j of a frame group lives in slot j % 3
     const long long wr = (long long)cta * kStreamWarps + warp;
     if (wr >= sc.nwr) {
         if (WITH_SUMS && lane < 2) a.partial[((long long)blockIdx.x * kStreamWarps + warp) * 2 + lane] = 0.0;
@@ -272,17 +282,18 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
 #pragma unroll
     for (int g = 0; g < NFR; ++g) maxlen = max(maxlen, run_len(g));
     const int len_post = run_len(lane / A);
-    int lo_s[NS1], len_s[NS1], f2_s[NS1];
+    int lo_s[NS1], len_s[NS1], f2_s[NS1], fm_s[NS1];       // fm_s: (current frame) % 3
 #pragma unroll
     for (int s = 0; s < NS1; ++s) {
         f2_s[s] = (lane + 32 * s) / BQ;
         lo_s[s] = run_lo(f2_s[s]);
         len_s[s] = run_len(f2_s[s]);
+        fm_s[s] = lo_s[s] % 3;
     }
     const int b_lane = lane % BQ;
     {
         float4* o4 = reinterpret_cast<float4*>(ola);
-        for (int i = lane; i < NFR * M / 2; i += 32) o4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int i = lane; i < NFR * M * 3 / 8; i += 32) o4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     __syncwarp();
 
@@ -337,8 +348,9 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
                 const bool active = t < len_s[s];
                 const int f = lo_s[s] + t;
                 const cf w = ld_table(win2 + BQ * av + b);
-                const int p = (q + f) & 3;
-                cf* slot = ola + ((f2 * 4 + p) * QA + ap) * BQ + b;
+                int p = fm_s[s] + (q == 3 ? 0 : q);                  // slot of hop block f + q; q == 3 reuses the slot q == 0 just left
+                p = p >= 3 ? p - 3 : p;
+                cf* slot = ola + ((f2 * 3 + p) * QA + ap) * BQ + b;
                 if (q == 3) {
                     if (active) *slot = mul2(gv, w);
                 } else if (q == 0) {
@@ -350,6 +362,8 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
                     if (active) *slot = o;
                 }
             });
+#pragma unroll
+        for (int s = 0; s < NS1; ++s) fm_s[s] = fm_s[s] == 2 ? 0 : fm_s[s] + 1;
     }
 #pragma unroll
     for (int s = 0; s < NS1; ++s) {
@@ -357,10 +371,10 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
             const int f = lo_s[s] + len_s[s] - 1;
 #pragma unroll
             for (int q = 1; q < 4; ++q) {
-                const int p = (q + f) & 3;
+                const int p = (q + f) % 3;
 #pragma unroll
                 for (int ap = 0; ap < QA; ++ap) {
-                    const cf o = ola[((f2_s[s] * 4 + p) * QA + ap) * BQ + b_lane];
+                    const cf o = ola[((f2_s[s] * 3 + p) * QA + ap) * BQ + b_lane];
                     st_grad(grow + (long long)(f + q) * hop + 2 * (BQ * ap + b_lane), o);
                 }
             }
@@ -375,9 +389,6 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
     }
 }
 
-#ifndef TAC_STREAM_PK
-#define TAC_STREAM_PK 1       // packed-complex core (FFMA2); 0 = the scalar core of fft_core.cuh
-#endif
 #if TAC_STREAM_PK
 #define TAC_STREAM_CTA stream_cta_pk
 #else

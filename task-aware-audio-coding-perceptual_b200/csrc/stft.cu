@@ -240,9 +240,8 @@ __global__ void __launch_bounds__(kThreads, 1) stft_tiled_kernel(const TiledArgs
 // Front-end kernel (TAC_OUT_MAGPHASE): 16 warps per CTA, one warp task (NFR frames) per warp, so a CTA covers
 // TF = 16 * NFR consecutive frames of one row.  The per-warp exchange tiles are only needed during the transform and
 // the transposition tile only after it, so both live in the SAME shared memory (178 KiB for n = 2048 instead of
-// 248 KiB): 16 resident warps per SM instead of 8.  Magnitude and phase leave in two passes through a single
-// [K][TF + 1] tile (the transform results stay in registers in between); every (k) row is written as a contiguous run
-// of TF frames.  atan2 is a degree-15 odd minimax polynomial (1.2e-7 abs. error in fp32) instead of the library call.
+// 248 KiB): 16 resident warps per SM instead of 8.  Magnitude and phase leave together through two [K][TF + 1] tiles
+// (they fit the space of the exchange tiles); every (k) row is written as a contiguous run of TF frames.  atan2 is a degree-15 odd minimax polynomial (1.2e-7 abs. error in fp32) instead of the library call.
 constexpr int kFeWarps = 16;
 constexpr int kFeThreads = kFeWarps * 32;
 
@@ -305,29 +304,25 @@ __global__ void __launch_bounds__(kFeThreads, 1) stft_frontend_kernel(const Tile
     const int col = myf - f0;
     const int nf = f_end - f0;
     float* out0 = a.out + (row * 2) * (long long)a.K * a.f_pad + f0;
-#pragma unroll 1
-    for (int plane = 0; plane < 2; ++plane) {
-        if (task) {
-            warp_fft_post_pk<P, true>(z, a.t.pt, lane, [&](int, int k, cf c, int) {
-                const float vr = lo(c), vi = hi(c);
-                float v;
-                if (plane == 0) {
-                    const float m2 = fmaf(vr, vr, vi * vi);
-                    v = m2 >= 1e-30f ? m2 * fe_rsqrt(m2) : 0.0f;    // |X| (<= 2 ulp); |X| < 1e-15 reads as 0
-                } else {
-                    v = fast_atan2(vi, vr);
-                }
-                if (valid) otile[k * TS + col] = v;
-            });
+    float* otile1 = otile + (size_t)a.K * TS;                      // phase plane next to the magnitude plane
+    if (task) {
+        warp_fft_post_pk<P, true>(z, a.t.pt, lane, [&](int, int k, cf c, int) {
+            const float vr = lo(c), vi = hi(c);
+            const float m2 = fmaf(vr, vr, vi * vi);
+            const float mag = m2 >= 1e-30f ? m2 * fe_rsqrt(m2) : 0.0f;   // |X| (<= 2 ulp); |X| < 1e-15 reads as 0
+            const float ph = fast_atan2(vi, vr);
+            if (valid) { otile[k * TS + col] = mag; otile1[k * TS + col] = ph; }
+        });
+    }
+    __syncthreads();
+    float* out1 = out0 + (long long)a.K * a.f_pad;
+    const int total = a.K * TF;
+    for (int i = threadIdx.x; i < total; i += kFeThreads) {
+        const int k = i / TF, tt = i % TF;                          // TF is a power of two: shift / mask
+        if (tt < nf) {
+            __stcs(out0 + (long long)k * a.f_pad + tt, otile[k * TS + tt]);
+            __stcs(out1 + (long long)k * a.f_pad + tt, otile1[k * TS + tt]);
         }
-        __syncthreads();
-        float* outp = out0 + (long long)plane * a.K * a.f_pad;
-        const int total = a.K * TF;
-        for (int i = threadIdx.x; i < total; i += kFeThreads) {
-            const int k = i / TF, tt = i % TF;                      // TF is a power of two: shift / mask
-            if (tt < nf) __stcs(outp + (long long)k * a.f_pad + tt, otile[k * TS + tt]);
-        }
-        __syncthreads();
     }
 }
 
@@ -339,7 +334,7 @@ static int launch_frontend(TiledArgs a, long long rows, cudaStream_t st, bool* d
     a.tile_len = ((TF - 1) * a.hop + a.n + 3) & ~3;
     const size_t xb = (size_t)kFeWarps * kXbufFloat2 * sizeof(float2);
     const size_t ot = (size_t)a.K * (TF + 1) * sizeof(float);
-    const size_t smem = (size_t)a.tile_len * 4 + (xb > ot ? xb : ot);
+    const size_t smem = (size_t)a.tile_len * 4 + (xb > 2 * ot ? xb : 2 * ot);     // both planes leave through one pass
     *done = false;
     if (smem > 200 * 1024 || rows * a.ntiles >= (1ll << 31)) return TAC_OK;      // caller falls back to the generic kernel
     auto kern = stft_frontend_kernel<P>;

@@ -21,6 +21,10 @@
 #pragma once
 #include "fft_core.cuh"
 
+#ifndef TAC_TW_EARLY
+#define TAC_TW_EARLY 0
+#endif
+
 namespace tac {
 
 typedef unsigned long long cf;          // packed complex: re in the low half, im in the high half of a register pair
@@ -100,13 +104,24 @@ __device__ __forceinline__ void warp_fft_fwd_pk(cf (&z)[P::BQ], float2* xbuf, co
             constexpr int av = decltype(ac)::value;
             a[brev(av, A)] = load(sc, fr, BQ * av + b, std::integral_constant<int, (4 * av) / A>{});   // + quarter of the frame
         });
+#if TAC_TW_EARLY
+        float2 wt[A];                                               // twiddles requested BEFORE the butterflies: the table
+        static_for<1, A>([&](auto kc) {                             // latency hides under Dit<A> instead of stalling the tail
+            constexpr int k1 = decltype(kc)::value;
+            wt[k1] = ldg2(tw + k1 * BQ + b);
+        });
+#endif
         Dit<A, false>::run(a);
         cf* row = reinterpret_cast<cf*>(xbuf) + (fr * A) * RS + b;
         static_for<0, A>([&](auto kc) {
             constexpr int k1 = decltype(kc)::value;
             cf v = a[k1];
             if constexpr (k1 > 0) {
+#if TAC_TW_EARLY
+                const float2 w = wt[k1];
+#else
                 const float2 w = ldg2(tw + k1 * BQ + b);            // W_M^(b*k1) = w.x - j w.y
+#endif
                 v = fma2(rotm(v), bc(w.y), mul2(v, bc(w.x)));
             }
             row[k1 * RS] = v;
@@ -213,12 +228,23 @@ __device__ __forceinline__ void warp_fft_adj_pk(float2* xbuf, const float2* __re
         constexpr int k2 = decltype(kc)::value;
         y[brev(k2, BQ)] = z[k2];
     });
+#if TAC_TW_EARLY
+    float2 wt[BQ];
+    static_for<1, BQ>([&](auto bc_) {
+        constexpr int b = decltype(bc_)::value;
+        wt[b] = ldg2(tw + k1 * BQ + b);
+    });
+#endif
     Dit<BQ, true>::run(y);
     cf* wr = reinterpret_cast<cf*>(xbuf) + lane * RS;
     static_for<0, BQ>([&](auto bc_) {
         constexpr int b = decltype(bc_)::value;
         if constexpr (b > 0) {
+#if TAC_TW_EARLY
+            const float2 w = wt[b];
+#else
             const float2 w = ldg2(tw + k1 * BQ + b);        // conj(W_M^(b*k1)) = w.x + j w.y
+#endif
             y[b] = fma2(rotp(y[b]), bc(w.y), mul2(y[b], bc(w.x)));
         }
         if constexpr (P::kVec4) {

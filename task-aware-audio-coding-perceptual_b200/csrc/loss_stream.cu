@@ -224,6 +224,9 @@ __device__ __forceinline__ void stream_cta(const StreamArgs& a, const StreamScal
 #ifndef TAC_ST_CS
 #define TAC_ST_CS 1
 #endif
+#ifndef TAC_PREFETCH
+#define TAC_PREFETCH 0
+#endif
 template <int QUARTER>
 __device__ __forceinline__ cf ld_frame(const float* p) {
 #if TAC_LD_HINT >= 1
@@ -312,6 +315,24 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
             fx[s] = xr + (long long)f * hop;
             fy[s] = yr + (long long)f * hop;
         }
+#if TAC_PREFETCH
+        // the quarter of the NEXT frame that no frame has touched yet comes from HBM: ask for it one step ahead (one lane
+        // per 128-byte line; no registers are tied up while it travels)
+        if (t + 1 < maxlen) {
+            static_for<0, NS1>([&](auto scn) {
+                constexpr int s = decltype(scn)::value;
+                const int b = (lane + 32 * s) % BQ;
+                if ((b & 15) == 0 && t + 1 < len_s[s]) {
+                    const long long off = (long long)(lo_s[s] + t + 1) * hop + 2 * b;
+                    static_for<3 * A / 4, A>([&](auto ac) {
+                        constexpr int av = decltype(ac)::value;
+                        asm volatile("prefetch.global.L1 [%0];" :: "l"(xr + off + 2 * BQ * av));
+                        asm volatile("prefetch.global.L1 [%0];" :: "l"(yr + off + 2 * BQ * av));
+                    });
+                }
+            });
+        }
+#endif
         auto load_x = [&](auto scn, int, int m, auto qc) -> cf {
             return mul2(ld_frame<decltype(qc)::value>(fx[decltype(scn)::value] + 2 * m), ld_table(win2 + m));
         };

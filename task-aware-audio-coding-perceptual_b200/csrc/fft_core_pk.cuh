@@ -21,10 +21,6 @@
 #pragma once
 #include "fft_core.cuh"
 
-#ifndef TAC_TW_EARLY
-#define TAC_TW_EARLY 0
-#endif
-
 namespace tac {
 
 typedef unsigned long long cf;          // packed complex: re in the low half, im in the high half of a register pair
@@ -104,26 +100,20 @@ __device__ __forceinline__ void warp_fft_fwd_pk(cf (&z)[P::BQ], float2* xbuf, co
             constexpr int av = decltype(ac)::value;
             a[brev(av, A)] = load(sc, fr, BQ * av + b, std::integral_constant<int, (4 * av) / A>{});   // + quarter of the frame
         });
-#if TAC_TW_EARLY
-        float2 wt[A];                                               // twiddles requested BEFORE the butterflies: the table
-        static_for<1, A>([&](auto kc) {                             // latency hides under Dit<A> instead of stalling the tail
-            constexpr int k1 = decltype(kc)::value;
-            wt[k1] = ldg2(tw + k1 * BQ + b);
-        });
-#endif
+        // Inter-pass twiddles W_M^(b k1), k1 = 8 q + r, as W^(b r) W^(8 b q): 7 + A/8 - 1 table reads per sub-transform instead
+        // of A - 1 (the loss kernel is bound by the L1TEX data pipe, and the tables were 38 % of its bytes), at two more
+        // packed instructions for the elements that need both factors.
+        float2 wr_[8], wq_[A / 8 > 0 ? A / 8 : 1];
+        static_for<1, (A < 8 ? A : 8)>([&](auto rc) { constexpr int r = decltype(rc)::value; wr_[r] = ldg2(tw + r * BQ + b); });
+        static_for<1, A / 8>([&](auto qc) { constexpr int q = decltype(qc)::value; wq_[q] = ldg2(tw + 8 * q * BQ + b); });
         Dit<A, false>::run(a);
         cf* row = reinterpret_cast<cf*>(xbuf) + (fr * A) * RS + b;
         static_for<0, A>([&](auto kc) {
             constexpr int k1 = decltype(kc)::value;
+            constexpr int r = k1 % 8, q = k1 / 8;
             cf v = a[k1];
-            if constexpr (k1 > 0) {
-#if TAC_TW_EARLY
-                const float2 w = wt[k1];
-#else
-                const float2 w = ldg2(tw + k1 * BQ + b);            // W_M^(b*k1) = w.x - j w.y
-#endif
-                v = fma2(rotm(v), bc(w.y), mul2(v, bc(w.x)));
-            }
+            if constexpr (r > 0) v = fma2(rotm(v), bc(wr_[r].y), mul2(v, bc(wr_[r].x)));     // W = w.x - j w.y
+            if constexpr (q > 0) v = fma2(rotm(v), bc(wq_[q].y), mul2(v, bc(wq_[q].x)));
             row[k1 * RS] = v;
         });
     });
@@ -228,25 +218,16 @@ __device__ __forceinline__ void warp_fft_adj_pk(float2* xbuf, const float2* __re
         constexpr int k2 = decltype(kc)::value;
         y[brev(k2, BQ)] = z[k2];
     });
-#if TAC_TW_EARLY
-    float2 wt[BQ];
-    static_for<1, BQ>([&](auto bc_) {
-        constexpr int b = decltype(bc_)::value;
-        wt[b] = ldg2(tw + k1 * BQ + b);
-    });
-#endif
+    float2 wr_[8], wq_[BQ / 8];                             // conj(W_M^(b k1)) = conj(W^(r k1)) conj(W^(8 q k1)), b = 8 q + r
+    static_for<1, 8>([&](auto rc) { constexpr int r = decltype(rc)::value; wr_[r] = ldg2(tw + k1 * BQ + r); });
+    static_for<1, BQ / 8>([&](auto qc) { constexpr int q = decltype(qc)::value; wq_[q] = ldg2(tw + k1 * BQ + 8 * q); });
     Dit<BQ, true>::run(y);
     cf* wr = reinterpret_cast<cf*>(xbuf) + lane * RS;
     static_for<0, BQ>([&](auto bc_) {
         constexpr int b = decltype(bc_)::value;
-        if constexpr (b > 0) {
-#if TAC_TW_EARLY
-            const float2 w = wt[b];
-#else
-            const float2 w = ldg2(tw + k1 * BQ + b);        // conj(W_M^(b*k1)) = w.x + j w.y
-#endif
-            y[b] = fma2(rotp(y[b]), bc(w.y), mul2(y[b], bc(w.x)));
-        }
+        constexpr int r = b % 8, q = b / 8;
+        if constexpr (r > 0) y[b] = fma2(rotp(y[b]), bc(wr_[r].y), mul2(y[b], bc(wr_[r].x)));   // conj(W) = w.x + j w.y
+        if constexpr (q > 0) y[b] = fma2(rotp(y[b]), bc(wq_[q].y), mul2(y[b], bc(wq_[q].x)));
         if constexpr (P::kVec4) {
             if constexpr (b & 1) reinterpret_cast<ulonglong2*>(wr)[b >> 1] = make_ulonglong2(y[b - 1], y[b]);
         } else {

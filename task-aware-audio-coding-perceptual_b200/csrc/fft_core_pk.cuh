@@ -40,6 +40,14 @@ __device__ __forceinline__ cf cnj(cf v) { return pk(lo(v), -hi(v)); }           
 
 __device__ __forceinline__ cf ldg_cf(const float2* p) { return __ldg(reinterpret_cast<const cf*>(p)); }
 
+// Periodic Hann pair (w[2m], w[2m+1]) * wh-scale for m = BQ a + b from the lane's phase registers (FftTables::wphase).
+template <int A, int a>
+__device__ __forceinline__ cf hann_pair(cf Hh, cf Cw, cf Sw) {
+    constexpr double ca = 2 * a <= A ? cx_cos2pi(a, A) : cx_cos2pi(A - a, A);
+    constexpr double sa = 2 * a <= A ? cx_sin2pi(a, A) : -cx_sin2pi(A - a, A);
+    return fma2(Sw, bc((float)sa), fma2(Cw, bc((float)-ca), Hh));
+}
+
 // ------------------------------------------------------------------ radix-2 DIT network
 // a' = a + W b, b' = a - W b,  W = exp(-+ 2 pi j K / N) (upper sign: forward), 0 <= K < N/2.
 template <int N, int K, bool INV>
@@ -84,8 +92,9 @@ struct Dit {
 };
 
 // ------------------------------------------------------------------ forward transform
-// load(integral_constant s, fr, m, integral_constant quarter) returns the windowed packed sample pair z_fr[m] =
-// (x[2m], x[2m+1]); quarter = 4 m / M tells a hop = n/4 caller which loads are the last use of their data.  On return lane
+// load(integral_constant s, fr, m, integral_constant a) returns the windowed packed sample pair z_fr[m] = (x[2m], x[2m+1]),
+// m = BQ a + b; the compile-time a lets a caller form the window analytically and know which quarter of the frame it reads.
+// On return lane
 // (fr = lane / A, k1 = lane % A) holds Z_fr[k1 + A*k2] in slot k2 of z.
 template <class P, class Load>
 __device__ __forceinline__ void warp_fft_fwd_pk(cf (&z)[P::BQ], float2* xbuf, const float2* __restrict__ tw, int lane,
@@ -98,7 +107,7 @@ __device__ __forceinline__ void warp_fft_fwd_pk(cf (&z)[P::BQ], float2* xbuf, co
         cf a[A];
         static_for<0, A>([&](auto ac) {
             constexpr int av = decltype(ac)::value;
-            a[brev(av, A)] = load(sc, fr, BQ * av + b, std::integral_constant<int, (4 * av) / A>{});   // + quarter of the frame
+            a[brev(av, A)] = load(sc, fr, BQ * av + b, ac);
         });
         // Inter-pass twiddles W_M^(b k1), k1 = 8 q + r, as W^(b r) W^(8 b q): 7 + A/8 - 1 table reads per sub-transform instead
         // of A - 1 (the loss kernel is bound by the L1TEX data pipe, and the tables were 38 % of its bytes), at two more

@@ -227,6 +227,9 @@ __device__ __forceinline__ void stream_cta(const StreamArgs& a, const StreamScal
 #ifndef TAC_PREFETCH
 #define TAC_PREFETCH 0
 #endif
+#ifndef TAC_AWIN
+#define TAC_AWIN 0
+#endif
 template <int QUARTER>
 __device__ __forceinline__ cf ld_frame(const float* p) {
 #if TAC_LD_HINT >= 1
@@ -258,7 +261,7 @@ __device__ __forceinline__ void st_grad(float* p, cf v) {
 // The same walk on the packed-complex core (fft_core_pk.cuh): every complex value is one aligned register pair and the
 // butterflies, twiddles, window products and overlap-adds are two-wide FP32 instructions -- about half the instruction
 // stream of stream_cta for the same arithmetic.  Only the per-bin loss terms (|.|, log, sign) stay scalar.
-template <class P, bool WITH_SUMS>
+template <class P, bool WITH_SUMS, bool AWIN>
 __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamScale& sc, int cta, float2* smem) {
     constexpr int A = P::A, BQ = P::BQ, M = P::M, NFR = P::NFR, NS1 = P::NS1, QA = A / 4;
     static_assert(A % 4 == 0 && NFR * M * 3 / 4 <= kOlaFloat2, "plan does not fit the streaming overlap-add ring");
@@ -300,6 +303,20 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
     }
     __syncwarp();
 
+    // analytic window (AWIN: every scale has win == n_fft): per-lane phase registers instead of 3 * A table reads per frame
+    cf wC[NS1], wS[NS1];
+    const cf wH = bc(sc.t.wh);
+    if constexpr (AWIN) {
+#pragma unroll
+        for (int s = 0; s < NS1; ++s) {
+            const float4 ph = __ldg(sc.t.wphase + (lane + 32 * s) % BQ);
+            wC[s] = pk(ph.x, ph.y); wS[s] = pk(ph.z, ph.w);
+        }
+    }
+    auto window = [&](auto scn, auto ac, int m) -> cf {
+        if constexpr (AWIN) return hann_pair<A, decltype(ac)::value>(wH, wC[decltype(scn)::value], wS[decltype(scn)::value]);
+        else return ld_table(win2 + m);
+    };
     const float c_l1 = __ldg(a.coef + 2 * sc.orig), c_log = __ldg(a.coef + 2 * sc.orig + 1);
     const float eps = a.eps;
     float l1 = 0.0f, ll = 0.0f;
@@ -333,11 +350,11 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
             });
         }
 #endif
-        auto load_x = [&](auto scn, int, int m, auto qc) -> cf {
-            return mul2(ld_frame<decltype(qc)::value>(fx[decltype(scn)::value] + 2 * m), ld_table(win2 + m));
+        auto load_x = [&](auto scn, int, int m, auto ac) -> cf {
+            return mul2(ld_frame<(4 * decltype(ac)::value) / A>(fx[decltype(scn)::value] + 2 * m), window(scn, ac, m));
         };
-        auto load_y = [&](auto scn, int, int m, auto qc) -> cf {
-            return mul2(ld_frame<decltype(qc)::value>(fy[decltype(scn)::value] + 2 * m), ld_table(win2 + m));
+        auto load_y = [&](auto scn, int, int m, auto ac) -> cf {
+            return mul2(ld_frame<(4 * decltype(ac)::value) / A>(fy[decltype(scn)::value] + 2 * m), window(scn, ac, m));
         };
         warp_fft_fwd_pk<P>(z, xbuf, sc.t.tw, lane, load_x);
         warp_fft_post_pk<P>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
@@ -368,7 +385,7 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
                 constexpr int q = av / QA, ap = av % QA;
                 const bool active = t < len_s[s];
                 const int f = lo_s[s] + t;
-                const cf w = ld_table(win2 + BQ * av + b);
+                const cf w = window(scn, ac, BQ * av + b);
                 int p = fm_s[s] + (q == 3 ? 0 : q);                  // slot of hop block f + q; q == 3 reuses the slot q == 0 just left
                 p = p >= 3 ? p - 3 : p;
                 cf* slot = ola + ((f2 * 3 + p) * QA + ap) * BQ + b;
@@ -410,17 +427,11 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
     }
 }
 
-#if TAC_STREAM_PK
-#define TAC_STREAM_CTA stream_cta_pk
-#else
-#define TAC_STREAM_CTA stream_cta
-#endif
-
 #ifndef TAC_STREAM_OCC
-#define TAC_STREAM_OCC 2      // 255 registers, no spills; 3 (168 registers) spills ~1 KB per thread and measured slower
+#define TAC_STREAM_OCC 2      // 255 registers; 3 (168 registers) spills and measured no faster
 #endif
 
-template <bool WITH_SUMS>
+template <bool WITH_SUMS, bool AWIN>
 __global__ void __launch_bounds__(kStreamThreads, TAC_STREAM_OCC) mrstft_stream_kernel(const StreamArgs a) {
     extern __shared__ __align__(16) unsigned char stream_smem_raw[];
     float2* smem = reinterpret_cast<float2*>(stream_smem_raw);
@@ -428,11 +439,19 @@ __global__ void __launch_bounds__(kStreamThreads, TAC_STREAM_OCC) mrstft_stream_
     while (s + 1 < a.nscales && (int)blockIdx.x >= a.sc[s + 1].cta_begin) ++s;
     const StreamScale& sc = a.sc[s];
     const int cta = (int)blockIdx.x - sc.cta_begin;
-    switch (sc.n) {
-        case 2048: TAC_STREAM_CTA<Plan2048, WITH_SUMS>(a, sc, cta, smem); break;
-        case 1024: TAC_STREAM_CTA<Plan1024, WITH_SUMS>(a, sc, cta, smem); break;
-        default: TAC_STREAM_CTA<Plan512, WITH_SUMS>(a, sc, cta, smem); break;      // stream_applicable: n >= 512
+#if TAC_STREAM_PK
+    switch (sc.n) {                                                                // stream_applicable: n >= 512
+        case 2048: stream_cta_pk<Plan2048, WITH_SUMS, AWIN>(a, sc, cta, smem); break;
+        case 1024: stream_cta_pk<Plan1024, WITH_SUMS, AWIN>(a, sc, cta, smem); break;
+        default: stream_cta_pk<Plan512, WITH_SUMS, AWIN>(a, sc, cta, smem); break;
     }
+#else
+    switch (sc.n) {
+        case 2048: stream_cta<Plan2048, WITH_SUMS>(a, sc, cta, smem); break;
+        case 1024: stream_cta<Plan1024, WITH_SUMS>(a, sc, cta, smem); break;
+        default: stream_cta<Plan512, WITH_SUMS>(a, sc, cta, smem); break;
+    }
+#endif
 }
 
 // grad[row][t] = sum over scales (fixed order) of g_s[t] (+ h_s[t] on the first three hop blocks of runs r >= 1);
@@ -563,14 +582,19 @@ int launch_stream(const float* x, const float* y, int64_t rows, int64_t T, int n
         begin += (rows * cpr[s] + kStreamWarps - 1) / kStreamWarps;
     }
     const size_t smem = (size_t)kStreamWarps * kStreamWarpFloat2 * sizeof(float2);
-    static bool attr_set = false;
-    if (!attr_set) {
-        TAC_CHECK_CUDA(cudaFuncSetAttribute(mrstft_stream_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        TAC_CHECK_CUDA(cudaFuncSetAttribute(mrstft_stream_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set = true;
+    // analytic Hann (needs win == n_fft on every scale) measured 0.457 ms against 0.451 ms with the table on cfg 2 once the
+    // twiddle reads were factorised: the window reads hit L1 and the two extra packed FMAs per pair cost more.  Off.
+    bool awin = TAC_STREAM_PK != 0 && TAC_AWIN != 0;
+    for (int i = 0; i < n_scales; ++i) awin = awin && a.sc[i].t.wphase != nullptr;
+    void (*kern)(const StreamArgs) = sums ? (awin ? mrstft_stream_kernel<true, true> : mrstft_stream_kernel<true, false>)
+                                          : (awin ? mrstft_stream_kernel<false, true> : mrstft_stream_kernel<false, false>);
+    static bool attr_set[4] = {false, false, false, false};
+    const int variant = (sums ? 2 : 0) + (awin ? 1 : 0);
+    if (!attr_set[variant]) {
+        TAC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set[variant] = true;
     }
-    if (sums) mrstft_stream_kernel<true><<<(unsigned)tot, kStreamThreads, smem, st>>>(a);
-    else mrstft_stream_kernel<false><<<(unsigned)tot, kStreamThreads, smem, st>>>(a);
+    kern<<<(unsigned)tot, kStreamThreads, smem, st>>>(a);
     TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
     const bool v4 = (T % 4 == 0) && ((reinterpret_cast<uintptr_t>(grad_y) & 15u) == 0);

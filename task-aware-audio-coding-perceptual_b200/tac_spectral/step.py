@@ -21,6 +21,8 @@ from __future__ import annotations
 
 from typing import List, Optional, Sequence
 
+import os
+
 import torch
 
 from . import _lib as L
@@ -88,7 +90,12 @@ class SpectralStep:
                 L.check(lib.tac_prepare_fft(self.fe_n_fft, self.fe_n_fft, 0))
             # the DPCA chain is a string of small, latency-bound kernels: it gets a HIGH-PRIORITY stream so that its CTAs
             # are placed ahead of the thousands of pending loss-kernel CTAs whenever an SM slot frees up
-            self.side = torch.cuda.Stream(device=dev, priority=-1) if self.overlap else None
+            self.side = torch.cuda.Stream(device=dev, priority=-2) if self.overlap else None
+            # the loss chain gets its own stream one priority level above the caller's: the front end (caller's stream) starts
+            # first, under the statistics + collective; once the loss kernel is launched its CTAs take every SM slot that
+            # frees up, and the rest of the short-CTA front end fills the loss kernel's last, partial wave
+            self.fill = self.overlap and self.frontend and os.environ.get("TAC_STEP_FILL", "1") != "0"
+            self.mid = torch.cuda.Stream(device=dev, priority=-1) if self.fill else None
             self._ev_stats = torch.cuda.Event()
 
     # ------------------------------------------------------------------ individual legs (current stream)
@@ -174,10 +181,18 @@ class SpectralStep:
                 # the front end's CTAs are short (~12 us): it runs UNDER the statistics + collective, whose kernels get the
                 # next free SMs through the side stream's priority; the long-CTA loss kernel must not flood the SMs before
                 # the collective has run
-                if self.frontend:
+                if self.fill:
+                    self.mid.wait_stream(main)
                     self.leg_frontend(x)
-                main.wait_event(self._ev_stats)
-                self._spectral_chain(x, y, frontend=False)
+                    with torch.cuda.stream(self.mid):
+                        self.mid.wait_event(self._ev_stats)
+                        self._spectral_chain(x, y, frontend=False)
+                    main.wait_stream(self.mid)
+                else:
+                    if self.frontend:
+                        self.leg_frontend(x)
+                    main.wait_event(self._ev_stats)
+                    self._spectral_chain(x, y, frontend=False)
                 main.wait_stream(self.side)
             else:
                 self._dpca_chain(zs)

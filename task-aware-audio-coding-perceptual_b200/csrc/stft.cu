@@ -237,12 +237,17 @@ __global__ void __launch_bounds__(kThreads, 1) stft_tiled_kernel(const TiledArgs
 }
 
 // ------------------------------------------------------------------------------------------
-// Front-end kernel (TAC_OUT_MAGPHASE): 16 warps per CTA, one warp task (NFR frames) per warp, so a CTA covers
-// TF = 16 * NFR consecutive frames of one row.  The per-warp exchange tiles are only needed during the transform and
-// the transposition tile only after it, so both live in the SAME shared memory (178 KiB for n = 2048 instead of
-// 248 KiB): 16 resident warps per SM instead of 8.  Magnitude and phase leave together through two [K][TF + 1] tiles
-// (they fit the space of the exchange tiles); every (k) row is written as a contiguous run of TF frames.  atan2 is a degree-15 odd minimax polynomial (1.2e-7 abs. error in fp32) instead of the library call.
-constexpr int kFeWarps = 16;
+// Front-end kernel (TAC_OUT_MAGPHASE): kFeWarps warps per CTA, one warp task (NFR frames) per warp, so a CTA covers
+// TF = kFeWarps * NFR consecutive frames of one row.  The per-warp exchange tiles are only needed during the transform and
+// the two [K][TF + 1] transposition tiles (magnitude, phase) only after it, so they live in the SAME shared memory; both
+// planes leave in one pass, every (k) row as a contiguous run of TF frames.  With 8 warps a CTA needs 96 KiB and two are
+// resident per SM: one computes while the other stages its samples or writes out.  atan2 is a degree-15 odd minimax
+// polynomial (1.2e-7 abs. error in fp32) instead of the library call.
+#ifndef TAC_FE_WARPS
+#define TAC_FE_WARPS 8          // 8-warp CTAs (96 KiB, two per SM): one CTA computes while the other stages / writes out -- 0.136 -> 0.109 ms on cfg 2 against 16-warp CTAs
+#endif
+constexpr int kFeWarps = TAC_FE_WARPS;
+constexpr int kFeOcc = kFeWarps <= 8 ? 2 : 1;        // 8-warp CTAs: 96 KiB each, two per SM
 constexpr int kFeThreads = kFeWarps * 32;
 
 __device__ __forceinline__ float fe_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
@@ -268,7 +273,7 @@ __device__ __forceinline__ float fast_atan2(float y, float x) {
 }
 
 template <class P>
-__global__ void __launch_bounds__(kFeThreads, 1) stft_frontend_kernel(const TiledArgs a) {
+__global__ void __launch_bounds__(kFeThreads, kFeOcc) stft_frontend_kernel(const TiledArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* tile = reinterpret_cast<float*>(smem_raw);
     unsigned char* shared2 = smem_raw + (size_t)a.tile_len * sizeof(float);      // exchange tiles, then the transposition tile

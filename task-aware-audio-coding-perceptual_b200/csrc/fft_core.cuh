@@ -148,11 +148,6 @@ struct FftTables {                          // device pointers, one set per (n_f
     const float2* win2;                     // [M]   (w[2m], w[2m+1]) * 0.5 * norm
     const float2* tw;                       // [A][BQ] (cos, sin)(2*pi*b*k1/M) at k1*BQ + b
     const float2* pt;                       // [M]   (cos, sin)(2*pi*k/n)
-    // Analytic Hann window (win == n_fft only, else null): win2[BQ a + b] = wh - ca wphase[b].xy + sa wphase[b].zw with
-    // (ca, sa) = (cos, sin)(2 pi a / A) compile-time and wphase[b] = wh (cos phi_0, cos phi_1, sin phi_0, sin phi_1),
-    // phi_e = 2 pi (2 b + e) / n: two packed FMAs from per-lane registers instead of an 8-byte table read per sample pair.
-    const float4* wphase;                   // [BQ]
-    float wh;                               // 0.25 * norm  (0.5 real-FFT post-process * 0.5 Hann)
 };
 
 __device__ __forceinline__ float2 ldg2(const float2* p) { return __ldg(p); }

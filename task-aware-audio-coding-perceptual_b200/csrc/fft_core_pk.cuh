@@ -40,14 +40,6 @@ __device__ __forceinline__ cf cnj(cf v) { return pk(lo(v), -hi(v)); }           
 
 __device__ __forceinline__ cf ldg_cf(const float2* p) { return __ldg(reinterpret_cast<const cf*>(p)); }
 
-// Periodic Hann pair (w[2m], w[2m+1]) * wh-scale for m = BQ a + b from the lane's phase registers (FftTables::wphase).
-template <int A, int a>
-__device__ __forceinline__ cf hann_pair(cf Hh, cf Cw, cf Sw) {
-    constexpr double ca = 2 * a <= A ? cx_cos2pi(a, A) : cx_cos2pi(A - a, A);
-    constexpr double sa = 2 * a <= A ? cx_sin2pi(a, A) : -cx_sin2pi(A - a, A);
-    return fma2(Sw, bc((float)sa), fma2(Cw, bc((float)-ca), Hh));
-}
-
 // ------------------------------------------------------------------ radix-2 DIT network
 // a' = a + W b, b' = a - W b,  W = exp(-+ 2 pi j K / N) (upper sign: forward), 0 <= K < N/2.
 template <int N, int K, bool INV>
@@ -93,7 +85,7 @@ struct Dit {
 
 // ------------------------------------------------------------------ forward transform
 // load(integral_constant s, fr, m, integral_constant a) returns the windowed packed sample pair z_fr[m] = (x[2m], x[2m+1]),
-// m = BQ a + b; the compile-time a lets a caller form the window analytically and know which quarter of the frame it reads.
+// m = BQ a + b; the compile-time a tells a hop = n/4 caller which quarter of the frame it reads (cache policy).
 // On return lane
 // (fr = lane / A, k1 = lane % A) holds Z_fr[k1 + A*k2] in slot k2 of z.
 template <class P, class Load>

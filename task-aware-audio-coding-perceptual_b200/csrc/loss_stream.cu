@@ -225,12 +225,6 @@ __device__ __forceinline__ void stream_cta(const StreamArgs& a, const StreamScal
 #ifndef TAC_ST_CS
 #define TAC_ST_CS 1
 #endif
-#ifndef TAC_PREFETCH
-#define TAC_PREFETCH 0
-#endif
-#ifndef TAC_AWIN
-#define TAC_AWIN 0
-#endif
 template <int QUARTER>
 __device__ __forceinline__ cf ld_frame(const float* p) {
 #if TAC_LD_HINT >= 1
@@ -262,7 +256,7 @@ __device__ __forceinline__ void st_grad(float* p, cf v) {
 // The same walk on the packed-complex core (fft_core_pk.cuh): every complex value is one aligned register pair and the
 // butterflies, twiddles, window products and overlap-adds are two-wide FP32 instructions -- about half the instruction
 // stream of stream_cta for the same arithmetic.  Only the per-bin loss terms (|.|, log, sign) stay scalar.
-template <class P, bool WITH_SUMS, bool AWIN>
+template <class P, bool WITH_SUMS>
 __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamScale& sc, int cta, float2* smem) {
     constexpr int A = P::A, BQ = P::BQ, M = P::M, NFR = P::NFR, NS1 = P::NS1, QA = A / 4;
     static_assert(A % 4 == 0 && NFR * M * 3 / 4 <= kOlaFloat2, "plan does not fit the streaming overlap-add ring");
@@ -304,20 +298,7 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
     }
     __syncwarp();
 
-    // analytic window (AWIN: every scale has win == n_fft): per-lane phase registers instead of 3 * A table reads per frame
-    cf wC[NS1], wS[NS1];
-    const cf wH = bc(sc.t.wh);
-    if constexpr (AWIN) {
-#pragma unroll
-        for (int s = 0; s < NS1; ++s) {
-            const float4 ph = __ldg(sc.t.wphase + (lane + 32 * s) % BQ);
-            wC[s] = pk(ph.x, ph.y); wS[s] = pk(ph.z, ph.w);
-        }
-    }
-    auto window = [&](auto scn, auto ac, int m) -> cf {
-        if constexpr (AWIN) return hann_pair<A, decltype(ac)::value>(wH, wC[decltype(scn)::value], wS[decltype(scn)::value]);
-        else return ld_table(win2 + m);
-    };
+    auto window = [&](auto, auto, int m) -> cf { return ld_table(win2 + m); };
     const float c_l1 = __ldg(a.coef + 2 * sc.orig), c_log = __ldg(a.coef + 2 * sc.orig + 1);
     const float eps = a.eps;
     float l1 = 0.0f, ll = 0.0f;
@@ -333,24 +314,6 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
             fx[s] = xr + (long long)f * hop;
             fy[s] = yr + (long long)f * hop;
         }
-#if TAC_PREFETCH
-        // the quarter of the NEXT frame that no frame has touched yet comes from HBM: ask for it one step ahead (one lane
-        // per 128-byte line; no registers are tied up while it travels)
-        if (t + 1 < maxlen) {
-            static_for<0, NS1>([&](auto scn) {
-                constexpr int s = decltype(scn)::value;
-                const int b = (lane + 32 * s) % BQ;
-                if ((b & 15) == 0 && t + 1 < len_s[s]) {
-                    const long long off = (long long)(lo_s[s] + t + 1) * hop + 2 * b;
-                    static_for<3 * A / 4, A>([&](auto ac) {
-                        constexpr int av = decltype(ac)::value;
-                        asm volatile("prefetch.global.L1 [%0];" :: "l"(xr + off + 2 * BQ * av));
-                        asm volatile("prefetch.global.L1 [%0];" :: "l"(yr + off + 2 * BQ * av));
-                    });
-                }
-            });
-        }
-#endif
         auto load_x = [&](auto scn, int, int m, auto ac) -> cf {
             return mul2(ld_frame<(4 * decltype(ac)::value) / A>(fx[decltype(scn)::value] + 2 * m), window(scn, ac, m));
         };
@@ -432,7 +395,7 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
 #define TAC_STREAM_OCC 2      // 255 registers; 3 (168 registers) spills and measured no faster
 #endif
 
-template <bool WITH_SUMS, bool AWIN>
+template <bool WITH_SUMS>
 __global__ void __launch_bounds__(kStreamThreads, TAC_STREAM_OCC) mrstft_stream_kernel(const StreamArgs a) {
     extern __shared__ __align__(16) unsigned char stream_smem_raw[];
     float2* smem = reinterpret_cast<float2*>(stream_smem_raw);
@@ -442,9 +405,9 @@ __global__ void __launch_bounds__(kStreamThreads, TAC_STREAM_OCC) mrstft_stream_
     const int cta = (int)blockIdx.x - sc.cta_begin;
 #if TAC_STREAM_PK
     switch (sc.n) {                                                                // stream_applicable: n >= 512
-        case 2048: stream_cta_pk<Plan2048, WITH_SUMS, AWIN>(a, sc, cta, smem); break;
-        case 1024: stream_cta_pk<Plan1024, WITH_SUMS, AWIN>(a, sc, cta, smem); break;
-        default: stream_cta_pk<Plan512, WITH_SUMS, AWIN>(a, sc, cta, smem); break;
+        case 2048: stream_cta_pk<Plan2048, WITH_SUMS>(a, sc, cta, smem); break;
+        case 1024: stream_cta_pk<Plan1024, WITH_SUMS>(a, sc, cta, smem); break;
+        default: stream_cta_pk<Plan512, WITH_SUMS>(a, sc, cta, smem); break;
     }
 #else
     switch (sc.n) {
@@ -598,14 +561,9 @@ int launch_stream(const float* x, const float* y, int64_t rows, int64_t T, int n
         begin += (rows * cpr[s] + kStreamWarps - 1) / kStreamWarps;
     }
     const size_t smem = (size_t)kStreamWarps * kStreamWarpFloat2 * sizeof(float2);
-    // analytic Hann (needs win == n_fft on every scale) measured 0.457 ms against 0.451 ms with the table on cfg 2 once the
-    // twiddle reads were factorised: the window reads hit L1 and the two extra packed FMAs per pair cost more.  Off.
-    bool awin = TAC_STREAM_PK != 0 && TAC_AWIN != 0;
-    for (int i = 0; i < n_scales; ++i) awin = awin && a.sc[i].t.wphase != nullptr;
-    void (*kern)(const StreamArgs) = sums ? (awin ? mrstft_stream_kernel<true, true> : mrstft_stream_kernel<true, false>)
-                                          : (awin ? mrstft_stream_kernel<false, true> : mrstft_stream_kernel<false, false>);
-    static bool attr_set[4] = {false, false, false, false};
-    const int variant = (sums ? 2 : 0) + (awin ? 1 : 0);
+    void (*kern)(const StreamArgs) = sums ? mrstft_stream_kernel<true> : mrstft_stream_kernel<false>;
+    static bool attr_set[2] = {false, false};
+    const int variant = sums ? 1 : 0;
     if (!attr_set[variant]) {
         TAC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set[variant] = true;

@@ -79,15 +79,6 @@ int get_tables(int n, int win, int normalized, FftTables* out) {
         double ang = 2.0 * M_PI * (double)k / (double)n;
         pt[k] = make_float2((float)cos(ang), (float)sin(ang));
     }
-    // analytic-window phase table (float4 [BQ]) behind the three float2 tables
-    const double wh = 0.5 * scale;
-    const size_t wp_off = host.size();
-    host.resize(wp_off + 2 * (size_t)BQ);
-    for (int b = 0; b < BQ; ++b) {
-        const double p0 = 2.0 * M_PI * (double)(2 * b) / (double)n, p1 = 2.0 * M_PI * (double)(2 * b + 1) / (double)n;
-        host[wp_off + 2 * b] = make_float2((float)(wh * cos(p0)), (float)(wh * cos(p1)));
-        host[wp_off + 2 * b + 1] = make_float2((float)(wh * sin(p0)), (float)(wh * sin(p1)));
-    }
     void* base = nullptr;
     TAC_CHECK_CUDA(cudaMalloc(&base, host.size() * sizeof(float2)));
     cudaError_t e = cudaMemcpy(base, host.data(), host.size() * sizeof(float2), cudaMemcpyHostToDevice);
@@ -100,8 +91,6 @@ int get_tables(int n, int win, int normalized, FftTables* out) {
     en.t.win2 = reinterpret_cast<const float2*>(base);
     en.t.tw = en.t.win2 + M;
     en.t.pt = en.t.win2 + 2 * (size_t)M;
-    en.t.wphase = win == n ? reinterpret_cast<const float4*>(en.t.win2 + wp_off) : nullptr;
-    en.t.wh = (float)wh;
     g_cache[key] = en;
     *out = en.t;
     return TAC_OK;

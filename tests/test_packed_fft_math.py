@@ -119,3 +119,16 @@ def test_real_fft_from_packed_transform(A, BQ):
     zp = 0.5 * (x[0::2] + 1j * x[1::2])                      # the 0.5 lives in win2 (tables.cu)
     X = post(two_pass_fft(zp, A, BQ), n)
     assert np.allclose(X, np.fft.rfft(x), rtol=1e-11, atol=1e-11)
+
+
+def test_three_pass_partner_chunks():
+    """DESIGN.md 'what comes after' (1): with k = k1 + 32 k2 + 128 k3 (lane k1, chunk k2, radix-8 over k3) the real-FFT partner
+    M - k of every bin of a chunk lies in ONE chunk of ONE lane: lane (32 - k1) % 32, chunk 3 - k2 (k1 != 0) or (4 - k2) % 4."""
+    M = 1024
+    for k1 in range(32):
+        for k2 in range(4):
+            ks = [k1 + 32 * k2 + 128 * k3 for k3 in range(8)]
+            partners = {(M - k) % M for k in ks}
+            p1 = (32 - k1) % 32
+            p2 = (3 - k2) if k1 else (4 - k2) % 4
+            assert partners == {p1 + 32 * p2 + 128 * k3 for k3 in range(8)}

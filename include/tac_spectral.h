@@ -212,6 +212,16 @@ TAC_API int64_t tac_istft_length(int64_t F, int n_fft, int hop, int center);
 TAC_API int tac_istft(const float* a, const float* b, int in_mode, int64_t rows, int64_t row_stride, int64_t ld, int64_t F,
               int n_fft, int hop, int win, int center, int normalized, float* out, int64_t out_len, tac_stream_t stream);
 
+/* Adjoint of the analysis STFT of tac_stft_multi (center = 0 framing): the backward of the Spectrogram module the
+ * reference instantiates at msstftd.py:125-127 -- torchaudio's transform is differentiable and adversarial / feature
+ * losses are back-propagated through the discriminator input to the generated waveform.
+ *   out[r][t] = scale * sum_f w[t - f*hop] * sum_{k=0}^{n/2} Re((a + i b)[r][k][f] * e^{+2 pi i k (t - f*hop) / n})
+ * for t in [0, out_len) (zero behind n_fft + hop*(F-1)); a, b = dL/dRe X, dL/dIm X in the layouts of tac_istft
+ * (TAC_IN_PLANES or TAC_IN_COMPLEX); scale = 1 / sqrt(sum w^2) for normalized spectrograms, else 1.  Same kernel as
+ * tac_istft without the one-sided weights and without the envelope division. */
+TAC_API int tac_stft_adjoint(const float* a, const float* b, int in_mode, int64_t rows, int64_t row_stride, int64_t ld, int64_t F,
+                     int n_fft, int hop, int win, float scale, float* out, int64_t out_len, tac_stream_t stream);
+
 /* ---- next row (second half): pairwise cosine loss of the view latents --------------------------
  * Replaces  cos_sim = torch.nn.CosineSimilarity(); cos_loss = torch.mean(cos_sim(z1, z2) [+ ... all six pairs])
  * at pkl_file_models.py:390-391, 761-763 and pkl_file_model_updated.py:429-430, 513-514.
@@ -224,6 +234,46 @@ TAC_API int tac_cosine_pairs_fwd(const float* const* z, int nv, int64_t B, int d
                          size_t workspace_bytes, tac_stream_t stream);
 TAC_API int tac_cosine_pairs_bwd(const float* const* z, int nv, int64_t B, int d, float eps, const float* gscale, float scale,
                          float* const* grad_z, tac_stream_t stream);
+
+/* ---- multi-GPU exchange: one-shot sum over NVLink peer memory ------------------------------------------
+ * Replaces the packed ncclAllReduce(sum) of [loss sums | per view n, sum z, sum z z^T] that SURVEY.md 8e prescribes for
+ * the batch-sharded form of train_pkl_file_task_aware.py:597-629 / pkl_file_model_updated.py:489-511 (the reference
+ * itself computes both over the whole batch on one device).  Every rank owns ONE buffer of tac_xchg_bytes() in
+ * peer-mappable memory (torch.distributed._symmetric_memory, or tac_ipc_alloc below) that every process of the node has
+ * mapped; `peer[r]` is rank r's buffer as mapped in THIS process (peer[rank] = the local one).  A push peer-stores the
+ * local payload into slot[rank] of every rank and raises a flag there; a pop spins on the local flags and adds the slots
+ * in RANK ORDER (bit-identical float64 sums on all ranks).  Sequence counters live in the buffer, so push / pop pairs are
+ * CUDA-graph replayable; every rank must execute the same sequence of pushes and pops.  The buffer must be zero-filled
+ * (and the ranks synchronised) once before first use.  A pop whose peers do not arrive within ~10 s traps. */
+#define TAC_XCHG_MAX_WORLD 8
+typedef struct tac_xchg {
+    int world, rank;
+    int64_t payload;                    /* float64 values per rank slot */
+    void* peer[TAC_XCHG_MAX_WORLD];
+} tac_xchg;
+TAC_API size_t tac_xchg_bytes(int world, int64_t payload);
+/* src [payload] float64 (device) -> slot[rank] on all ranks, then the flags. */
+TAC_API int tac_xchg_push(const tac_xchg* x, const double* src, tac_stream_t stream);
+/* dst [payload] float64 = sum over ranks (rank order) of the slots of the matching push. */
+TAC_API int tac_xchg_pop(const tac_xchg* x, double* dst, tac_stream_t stream);
+/* tac_dpca_stats whose last kernel pushes the statistics (x->payload = nv * (1 + d + d*d)); x NULL / world 1: plain. */
+TAC_API int tac_dpca_stats_push(const float* const* z, int nv, int64_t B, int d, int algo, double* stats, void* workspace,
+                        size_t workspace_bytes, const tac_xchg* x, tac_stream_t stream);
+/* tac_dpca_eig (d <= 128) whose first kernel pops: the one-CTA-per-view tridiagonalisation waits for the peers' flags
+ * itself, adds the slots into `stats` (overwritten with the GLOBAL statistics) and goes on -- no kernel in between. */
+TAC_API int tac_dpca_eig_pop(double* stats, int nv, int d, float* s, float* v, float* mu, int* rank, void* workspace,
+                     size_t workspace_bytes, const tac_xchg* x, tac_stream_t stream);
+/* Tail of the loss chain in one single-CTA kernel: push sums[n] (n <= 64), pop the global sums back into `sums`, and
+ * loss[0] = sum_j sums[j] * inv[j] (float64; inv = 1 / (S * global count), the constant d loss / d sums).  x NULL / world
+ * 1: the dot product alone.  Replaces the second all-reduce + torch.dot of the step. */
+TAC_API int tac_loss_finalize(double* sums, int n, const double* inv, const tac_xchg* x, double* loss, tac_stream_t stream);
+/* Peer-mappable device memory through CUDA IPC for callers without a symmetric-memory allocator: the ONE place the
+ * library allocates on behalf of the caller (memory from a caching allocator cannot be exported).  handle64: 64 bytes
+ * (cudaIpcMemHandle_t) to hand to the other processes of the node, which map it with tac_ipc_open. */
+TAC_API int tac_ipc_alloc(size_t bytes, void** ptr, unsigned char* handle64);
+TAC_API int tac_ipc_open(const unsigned char* handle64, void** ptr);
+TAC_API int tac_ipc_close(void* ptr);
+TAC_API int tac_ipc_free(void* ptr);
 
 #ifdef __cplusplus
 }

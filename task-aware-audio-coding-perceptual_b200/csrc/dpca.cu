@@ -361,7 +361,7 @@ __global__ void nuclear_grad_matrix_kernel(const float* __restrict__ s, const fl
 static size_t eig_smem_bytes(int d) { return (size_t)d * d * sizeof(double); }
 
 static int dpca_tc_stats(const float* const* z, int nv, long long B, int d, double* stats, void* ws, size_t ws_bytes,
-                         cudaStream_t st) {
+                         const XchgDev& xd, cudaStream_t st) {
     TAC_REQUIRE(d <= kTcFeat, "TAC_GRAM_TF32X3 supports d <= %d (got %d); use TAC_GRAM_FP64", kTcFeat, d);
     const size_t need = dpca_tc_workspace_bytes(nv, B, d);
     if (!ws || ws_bytes < need) return set_error(TAC_EWORKSPACE, "tac_dpca_stats needs %zu workspace bytes", need);
@@ -376,7 +376,7 @@ static int dpca_tc_stats(const float* const* z, int nv, long long B, int d, doub
     dpca_gram_tc_kernel<<<dim3(nsplit, nv), kTcThreads, kTcSmemBytes, st>>>(p[0], p[1], p[2], p[3], p[4], p[5], p[6], p[7], B, d,
                                                                            stats, partial); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
-    dpca_gram_finish_kernel<<<dim3(d, nv), kTcFeat, 0, st>>>(partial, nsplit, d, stats); TAC_LAUNCHED(1);
+    dpca_gram_finish_kernel<<<dim3(d, nv), kTcFeat, 0, st>>>(partial, nsplit, d, stats, xd); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
     return TAC_OK;
 }
@@ -396,9 +396,28 @@ extern "C" size_t tac_dpca_workspace_bytes(int nv, int64_t B, int d) {
     return (m + 255) & ~(size_t)255;
 }
 
+static int check_stats_xchg(const tac_xchg* x, int nv, int d) {
+    if (!x || x->world <= 1) return TAC_OK;
+    TAC_REQUIRE(x->world <= kXchgMaxWorld && x->rank >= 0 && x->rank < x->world, "bad exchange world / rank");
+    TAC_REQUIRE(x->payload == (int64_t)nv * (1 + d + (int64_t)d * d), "exchange payload %lld != nv * (1 + d + d*d) = %lld",
+                (long long)x->payload, (long long)nv * (1 + d + (long long)d * d));
+    for (int r = 0; r < x->world; ++r) TAC_REQUIRE(x->peer[r] != nullptr, "peer[%d] is null", r);
+    return TAC_OK;
+}
+
 extern "C" int tac_dpca_stats(const float* const* z, int nv, int64_t B, int d, int algo, double* stats, void* workspace,
                               size_t workspace_bytes, tac_stream_t stream) {
+    return tac_dpca_stats_push(z, nv, B, d, algo, stats, workspace, workspace_bytes, nullptr, stream);
+}
+
+extern "C" int tac_dpca_stats_push(const float* const* z, int nv, int64_t B, int d, int algo, double* stats, void* workspace,
+                                   size_t workspace_bytes, const tac_xchg* x, tac_stream_t stream) {
     TAC_REQUIRE(z && stats, "null argument");
+    {
+        int rc = check_stats_xchg(x, nv, d);
+        if (rc) return rc;
+    }
+    const XchgDev xd = xchg_dev(x);
     TAC_REQUIRE(nv >= 1 && nv <= kMaxViews, "nv must be in [1, %d]", kMaxViews);
     TAC_REQUIRE(B >= 1 && d >= 1 && d <= kMaxD, "need B >= 1 and 1 <= d <= %d", kMaxD);
     TAC_REQUIRE(algo == TAC_GRAM_TF32X3 || algo == TAC_GRAM_FP64, "unknown algo %d", algo);
@@ -409,17 +428,29 @@ extern "C" int tac_dpca_stats(const float* const* z, int nv, int64_t B, int d, i
     }
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     if (algo == TAC_GRAM_TF32X3) {
-        return dpca_tc_stats(vp.z, nv, B, d, stats, workspace, workspace_bytes, st);
+        return dpca_tc_stats(vp.z, nv, B, d, stats, workspace, workspace_bytes, xd, st);
     }
     const int nt = (d + 31) / 32;
     dpca_gram_fp64_kernel<<<dim3(nt * nt, nv), 256, 0, st>>>(vp, B, d, stats); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
+    if (xd.world > 1) return tac_xchg_push(x, stats, stream);       // float64 SIMT Gram: the generic push kernel follows
     return TAC_OK;
 }
 
 extern "C" int tac_dpca_eig(const double* stats, int nv, int d, float* s, float* v, float* mu, int* rank, void* workspace,
                             size_t workspace_bytes, tac_stream_t stream) {
+    // without an exchange the statistics are only read
+    return tac_dpca_eig_pop(const_cast<double*>(stats), nv, d, s, v, mu, rank, workspace, workspace_bytes, nullptr, stream);
+}
+
+extern "C" int tac_dpca_eig_pop(double* stats, int nv, int d, float* s, float* v, float* mu, int* rank, void* workspace,
+                                size_t workspace_bytes, const tac_xchg* x, tac_stream_t stream) {
     TAC_REQUIRE(stats && s && v && mu && rank, "null argument");
+    {
+        int rc = check_stats_xchg(x, nv, d);
+        if (rc) return rc;
+    }
+    const XchgDev xd = xchg_dev(x);
     TAC_REQUIRE(nv >= 1 && nv <= kMaxViews, "nv must be in [1, %d]", kMaxViews);
     TAC_REQUIRE(d >= 1 && d <= kMaxD, "need 1 <= d <= %d", kMaxD);
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
@@ -429,26 +460,26 @@ extern "C" int tac_dpca_eig(const double* stats, int nv, int d, float* s, float*
             return set_error(TAC_EWORKSPACE, "tac_dpca_eig with d=%d needs %zu workspace bytes", d, need);
         TAC_ALIGNED16(workspace, "workspace");
         const size_t tsmem = dpca_eig_tri_smem_bytes(d);
-        static bool attr_set = false;
-        if (!attr_set) {
-            TAC_CHECK_CUDA(cudaFuncSetAttribute(dpca_eig_tri_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dpca_eig_tri_smem_bytes(kTriMaxD)));
-            TAC_CHECK_CUDA(cudaFuncSetAttribute(dpca_eig_tri_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dpca_eig_tri_smem_bytes(kTriMaxD)));
-            TAC_CHECK_CUDA(cudaFuncSetAttribute(dpca_tri_vectors_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dpca_tri_vectors_smem_bytes()));
-            attr_set = true;
-        }
+        TAC_SMEM_OPT_IN(dpca_eig_tri_kernel<false>, dpca_eig_tri_smem_bytes(kTriMaxD));
+        TAC_SMEM_OPT_IN(dpca_eig_tri_kernel<true>, dpca_eig_tri_smem_bytes(kTriMaxD));
+        TAC_SMEM_OPT_IN(dpca_tri_vectors_kernel, dpca_tri_vectors_smem_bytes());
         double* gws = reinterpret_cast<double*>(workspace);
 #if TAC_EIG_SPLIT
         // 1. tridiagonalise (one CTA per view)  2. one warp per eigenpair on d/8 CTAs per view  3. order + outputs
-        dpca_eig_tri_kernel<true><<<nv, kTriThreads, tsmem, st>>>(stats, d, s, v, mu, rank, gws); TAC_LAUNCHED(1);
+        dpca_eig_tri_kernel<true><<<nv, kTriThreads, tsmem, st>>>(stats, d, s, v, mu, rank, gws, xd); TAC_LAUNCHED(1);
         TAC_CHECK_CUDA(cudaGetLastError());
         dpca_tri_vectors_kernel<<<dim3((d + kVecWarps - 1) / kVecWarps, nv), kVecThreads, dpca_tri_vectors_smem_bytes(), st>>>(d, gws); TAC_LAUNCHED(1);
         TAC_CHECK_CUDA(cudaGetLastError());
         dpca_tri_finish_kernel<<<nv, kTriThreads, 0, st>>>(stats, d, s, v, rank, gws); TAC_LAUNCHED(1);
 #else
-        dpca_eig_tri_kernel<false><<<nv, kTriThreads, tsmem, st>>>(stats, d, s, v, mu, rank, gws); TAC_LAUNCHED(1);
+        dpca_eig_tri_kernel<false><<<nv, kTriThreads, tsmem, st>>>(stats, d, s, v, mu, rank, gws, xd); TAC_LAUNCHED(1);
 #endif
         TAC_CHECK_CUDA(cudaGetLastError());
         return TAC_OK;
+    }
+    if (xd.world > 1) {                                             // Jacobi path (d > 128): generic pop kernel in front
+        int rc = tac_xchg_pop(x, stats, stream);
+        if (rc) return rc;
     }
     const size_t smem = eig_smem_bytes(d);
     const int use_gws = smem > 160 * 1024;

@@ -17,6 +17,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "xchg.cuh"
+
 namespace tac {
 
 constexpr int kTriThreads = 1024;
@@ -118,8 +120,8 @@ constexpr int kTriWsDoubles = kTriWsVec + kTriMaxD * kTriMaxD;
 
 template <bool SPLIT>
 __global__ void __launch_bounds__(kTriThreads, 1)
-dpca_eig_tri_kernel(const double* __restrict__ stats, int d, float* __restrict__ s_out, float* __restrict__ v_out,
-                    float* __restrict__ mu_out, int* __restrict__ rank_out, double* __restrict__ gws) {
+dpca_eig_tri_kernel(double* stats, int d, float* __restrict__ s_out, float* __restrict__ v_out,
+                    float* __restrict__ mu_out, int* __restrict__ rank_out, double* __restrict__ gws, const XchgDev xd) {
     extern __shared__ __align__(16) unsigned char tri_smem_raw[];
     double* A = reinterpret_cast<double*>(tri_smem_raw);            // [d][d]; later Z[row][col] with leading dimension d + 1
     const int ldz = d + 1;                                          // odd stride: a lane-per-row access pattern is conflict free
@@ -128,7 +130,18 @@ dpca_eig_tri_kernel(const double* __restrict__ stats, int d, float* __restrict__
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int view = blockIdx.x;
     const size_t stride = 1 + d + (size_t)d * d;
-    const double* st = stats + view * stride;
+    double* st = stats + view * stride;
+    if (xd.world > 1) {
+        // The pop of the step's exchange happens HERE: this CTA is resident from the start of the step (high-priority
+        // stream), waits for the peers' flags itself and adds the world's slots of ITS view in rank order into `stats`,
+        // so no reduction kernel has to find an SM between the loss kernel's CTAs and nothing else waits for the peers.
+        const unsigned seq = xchg_pop_seq(xd);
+        xchg_wait(xd, seq);
+        __syncthreads();
+        for (size_t e = tid; e < stride; e += kTriThreads) st[e] = xchg_sum(xd, seq, (size_t)view * stride + e);
+        __syncthreads();
+        if (tid == 0) xchg_pop_commit(xd, seq, gridDim.x);
+    }
     double* Lp = gws + (size_t)view * (SPLIT ? kTriWsDoubles : 2 * d * d);   // [i][slot] forward multipliers b_i / D+_i
     double* Um = Lp + (size_t)d * d;                                // [i][slot] backward multipliers b_{i-1} / D-_i
     const double n = st[0];

@@ -20,6 +20,8 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include "xchg.cuh"
+
 namespace tac {
 
 constexpr int kTcFeat = 128;                 // padded feature count = UMMA M = UMMA N
@@ -229,20 +231,36 @@ dpca_colsum_kernel(const float* z0, const float* z1, const float* z2, const floa
 }
 
 // stats S = sum_split partial + n * mean mean^T   (float64).  grid (d, nv), block 128.
+// With an exchange (xd.world > 1) the kernel that completes the statistics also SENDS them: every value is peer-stored
+// into this rank's slot on all ranks as it is formed, and the last CTA raises the flags (xchg.cuh) -- compute and
+// collective are one kernel, the transfer overlaps the re-assembly row by row.
 __global__ void __launch_bounds__(kTcFeat)
-dpca_gram_finish_kernel(const float* __restrict__ partial, int nsplit, int d, double* __restrict__ stats) {
+dpca_gram_finish_kernel(const float* __restrict__ partial, int nsplit, int d, double* __restrict__ stats, const XchgDev xd) {
     const int v = blockIdx.y, i = blockIdx.x, j = threadIdx.x;
-    double* st = stats + (size_t)v * (1 + (size_t)d + (size_t)d * d);
-    if (j >= d) return;
-    const double n = st[0];
-    double acc = 0.0;
-    for (int s = 0; s < nsplit; ++s) {
-        // symmetrise: (i, j) and (j, i) were accumulated by different instruction orders
-        const float* p = partial + ((size_t)v * nsplit + s) * kTcFeat * kTcFeat;
-        acc += 0.5 * ((double)p[(size_t)i * kTcFeat + j] + (double)p[(size_t)j * kTcFeat + i]);
+    const size_t stride = 1 + (size_t)d + (size_t)d * d;
+    double* st = stats + (size_t)v * stride;
+    const bool push = xd.world > 1;
+    const unsigned seq = push ? xchg_push_seq(xd) : 0u;
+    if (j < d) {
+        const double n = st[0];
+        double acc = 0.0;
+        for (int s = 0; s < nsplit; ++s) {
+            // symmetrise: (i, j) and (j, i) were accumulated by different instruction orders
+            const float* p = partial + ((size_t)v * nsplit + s) * kTcFeat * kTcFeat;
+            acc += 0.5 * ((double)p[(size_t)i * kTcFeat + j] + (double)p[(size_t)j * kTcFeat + i]);
+        }
+        const double mi = st[1 + i] / n, mj = st[1 + j] / n;
+        const double val = acc + n * mi * mj;
+        st[1 + d + (size_t)i * d + j] = val;
+        if (push) {
+            xchg_store(xd, seq, (size_t)v * stride + 1 + d + (size_t)i * d + j, val);
+            if (i == 0) {                                   // n and the column sums (dpca_colsum_kernel) ride along
+                xchg_store(xd, seq, (size_t)v * stride + 1 + j, st[1 + j]);
+                if (j == 0) xchg_store(xd, seq, (size_t)v * stride, n);
+            }
+        }
     }
-    const double mi = st[1 + i] / n, mj = st[1 + j] / n;
-    st[1 + d + (size_t)i * d + j] = acc + n * mi * mj;
+    if (push) xchg_push_commit(xd, seq, gridDim.x * gridDim.y);
 }
 
 inline size_t dpca_tc_workspace_bytes(int nv, long long B, int d) {

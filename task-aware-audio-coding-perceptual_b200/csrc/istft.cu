@@ -37,6 +37,7 @@ struct IstftArgs {
     int run_blocks, runs_per_row, nblk;
     int vec_ok;                     // strides and base pointers allow 16-byte copies of 4 consecutive frames
     float scale;                    // 2 / n (* sqrt(n) when normalized): the window table holds w / 2
+    int adjoint;                    // 1: adjoint of the analysis STFT (no one-sided edge weights, no envelope division)
     FftTables t;
     float* out;
 };
@@ -162,7 +163,8 @@ __global__ void __launch_bounds__(kIThreads, 1) istft_kernel(const IstftArgs a) 
                     v = make_float2(v.x * cs, v.x * sn);
                 }
             }
-            if (k == 0 || k == M) { v.x *= 0.5f; v.y = 0.0f; }         // X[0], X[n/2] count once and are real
+            // X[0], X[n/2] count once and are real (adjoint mode: every bin's real part counts once -> edges at full weight)
+            if (k == 0 || k == M) { v.x *= a.adjoint ? 1.0f : 0.5f; v.y = 0.0f; }
             tile[fl * KP + k] = v;
         }
         __syncthreads();
@@ -207,7 +209,9 @@ __global__ void __launch_bounds__(kIThreads, 1) istft_kernel(const IstftArgs a) 
                     const long long t = (long long)jg * hop + o - a.start;
                     if (t < 0 || t >= lim) continue;
                     float ie;
-                    if (inner) {
+                    if (a.adjoint) {
+                        ie = 1.0f;
+                    } else if (inner) {
                         ie = inv_env[o];
                     } else {
                         float env = 0.0f;                                // sum of (w / 2)^2 over the frames that exist
@@ -232,12 +236,9 @@ static int launch_istft(const IstftArgs& a, long long rows, cudaStream_t st) {
     const size_t rawf = ((2 * (size_t)(P::M + 1) * TFR + 3) / 4) * 4;
     const size_t base = rawf * sizeof(float) + ((size_t)TFR * (P::M + 2) + (size_t)kIWarps * kXbufFloat2) * sizeof(float2);
     const size_t smem = base + (2 * (size_t)(a.n - a.hop) + (size_t)a.hop) * sizeof(float);
-    static bool attr_set = false;
-    if (!attr_set) {                                   // the smallest admissible hop (n / 8) has the largest carry
-        const size_t smem_max = base + (2 * (size_t)(P::N - P::N / 8) + (size_t)P::N) * sizeof(float);
-        TAC_CHECK_CUDA(cudaFuncSetAttribute(istft_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max));
-        attr_set = true;
-    }
+    // the smallest admissible hop (n / 8) has the largest carry
+    const size_t smem_max = base + (2 * (size_t)(P::N - P::N / 8) + (size_t)P::N) * sizeof(float);
+    TAC_SMEM_OPT_IN(istft_kernel<P>, smem_max);
     const long long grid = rows * a.runs_per_row;
     TAC_REQUIRE(grid < (1ll << 31), "grid too large");
     istft_kernel<P><<<(unsigned)grid, kIThreads, smem, st>>>(a);
@@ -256,9 +257,9 @@ extern "C" int64_t tac_istft_length(int64_t F, int n_fft, int hop, int center) {
     return center ? full - 2 * (int64_t)(n_fft / 2) : full;
 }
 
-extern "C" int tac_istft(const float* a, const float* b, int in_mode, int64_t rows, int64_t row_stride, int64_t ld, int64_t F,
-                         int n_fft, int hop, int win, int center, int normalized, float* out, int64_t out_len,
-                         tac_stream_t stream) {
+static int istft_impl(const float* a, const float* b, int in_mode, int64_t rows, int64_t row_stride, int64_t ld, int64_t F,
+                      int n_fft, int hop, int win, int center, int normalized, float* out, int64_t out_len,
+                      tac_stream_t stream, int adjoint, float adj_scale) {
     TAC_REQUIRE(in_mode == TAC_IN_POLAR || in_mode == TAC_IN_PLANES || in_mode == TAC_IN_COMPLEX, "unknown in_mode %d", in_mode);
     TAC_REQUIRE(a && out && (in_mode == TAC_IN_COMPLEX || b), "null pointer");
     TAC_REQUIRE(supported_nfft(n_fft), "unsupported n_fft %d (64..2048, power of two)", n_fft);
@@ -280,7 +281,7 @@ extern "C" int tac_istft(const float* a, const float* b, int in_mode, int64_t ro
 
     // torch.istft refuses a window whose overlap-added square vanishes inside the kept range (NOLA); same check here,
     // on the host in float64 (the envelope is periodic in hop away from the two edges, so the edges + one period suffice)
-    {
+    if (!adjoint) {
         std::vector<double> w(n_fft, 0.0);
         const int left = (n_fft - win) / 2;
         for (int i = 0; i < win; ++i) w[left + i] = 0.5 - 0.5 * cos(2.0 * M_PI * (double)i / (double)win);
@@ -318,6 +319,8 @@ extern "C" int tac_istft(const float* a, const float* b, int in_mode, int64_t ro
     k.run_blocks = rb;
     k.runs_per_row = (k.nblk + rb - 1) / rb;
     k.scale = (float)((2.0 / (double)n_fft) * (normalized ? sqrt((double)n_fft) : 1.0));
+    k.adjoint = adjoint ? 1 : 0;
+    if (adjoint) k.scale = adj_scale;   // out = scale * w[m] * sum_k Re(G_k e^{+i theta}): the network gives 2 * sum, the table w / 2
     k.out = out;
     {   // 16-byte asynchronous copies need 16-byte aligned frame quads in every row of every plane
         const int per = in_mode == TAC_IN_COMPLEX ? 2 : 4;
@@ -334,4 +337,16 @@ extern "C" int tac_istft(const float* a, const float* b, int in_mode, int64_t ro
         case 128: return launch_istft<Plan128>(k, rows, st);
         default: return launch_istft<Plan64>(k, rows, st);
     }
+}
+
+extern "C" int tac_istft(const float* a, const float* b, int in_mode, int64_t rows, int64_t row_stride, int64_t ld, int64_t F,
+                         int n_fft, int hop, int win, int center, int normalized, float* out, int64_t out_len,
+                         tac_stream_t stream) {
+    return istft_impl(a, b, in_mode, rows, row_stride, ld, F, n_fft, hop, win, center, normalized, out, out_len, stream, 0, 1.0f);
+}
+
+extern "C" int tac_stft_adjoint(const float* a, const float* b, int in_mode, int64_t rows, int64_t row_stride, int64_t ld, int64_t F,
+                                int n_fft, int hop, int win, float scale, float* out, int64_t out_len, tac_stream_t stream) {
+    TAC_REQUIRE(in_mode == TAC_IN_PLANES || in_mode == TAC_IN_COMPLEX, "tac_stft_adjoint takes TAC_IN_PLANES or TAC_IN_COMPLEX");
+    return istft_impl(a, b, in_mode, rows, row_stride, ld, F, n_fft, hop, win, 0, 0, out, out_len, stream, 1, scale);
 }

@@ -521,12 +521,8 @@ static int launch_bwd(const float* x, const float* y, int64_t B, int64_t T, int 
     }
     if (a.nchunks > 1) TAC_CHECK_CUDA(cudaMemsetAsync(grad_y, 0, (size_t)B * T * sizeof(float), st));
     const size_t smem = (size_t)a.tile_len * sizeof(float) + (size_t)kBwdWarps * kXbufFloat2 * sizeof(float2);
-    static bool attr_set = false;
-    if (!attr_set) {
-        TAC_CHECK_CUDA(cudaFuncSetAttribute(mrstft_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 75 * 1024));
-        TAC_CHECK_CUDA(cudaFuncSetAttribute(mrstft_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 75 * 1024));
-        attr_set = true;
-    }
+    TAC_SMEM_OPT_IN(mrstft_bwd_kernel<false>, 75 * 1024);
+    TAC_SMEM_OPT_IN(mrstft_bwd_kernel<true>, 75 * 1024);
     if (sums) {
         mrstft_bwd_kernel<true><<<(unsigned)grid, kBwdThreads, smem, st>>>(a); TAC_LAUNCHED(1);
         TAC_CHECK_CUDA(cudaGetLastError());

@@ -562,12 +562,8 @@ int launch_stream(const float* x, const float* y, int64_t rows, int64_t T, int n
     }
     const size_t smem = (size_t)kStreamWarps * kStreamWarpFloat2 * sizeof(float2);
     void (*kern)(const StreamArgs) = sums ? mrstft_stream_kernel<true> : mrstft_stream_kernel<false>;
-    static bool attr_set[2] = {false, false};
-    const int variant = sums ? 1 : 0;
-    if (!attr_set[variant]) {
-        TAC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set[variant] = true;
-    }
+    if (sums) TAC_SMEM_OPT_IN(mrstft_stream_kernel<true>, smem);
+    else TAC_SMEM_OPT_IN(mrstft_stream_kernel<false>, smem);
     kern<<<(unsigned)tot, kStreamThreads, smem, st>>>(a);
     TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());

@@ -343,11 +343,7 @@ static int launch_frontend(TiledArgs a, long long rows, cudaStream_t st, bool* d
     *done = false;
     if (smem > 200 * 1024 || rows * a.ntiles >= (1ll << 31)) return TAC_OK;      // caller falls back to the generic kernel
     auto kern = stft_frontend_kernel<P>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        TAC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set = true;
-    }
+    TAC_SMEM_OPT_IN(kern, 200 * 1024);
     kern<<<(unsigned)(rows * a.ntiles), kFeThreads, smem, st>>>(a); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
     *done = true;
@@ -368,11 +364,7 @@ static int dispatch_frontend(const TiledArgs& a, long long rows, cudaStream_t st
 template <class P, int MODE>
 static int launch_tiled(const TiledArgs& a, long long rows, size_t smem, cudaStream_t st) {
     auto kern = stft_tiled_kernel<P, MODE>;
-    static bool attr_set = false;      // per instantiation; idempotent
-    if (!attr_set) {
-        TAC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set = true;
-    }
+    TAC_SMEM_OPT_IN(kern, 200 * 1024);                 // per instantiation and device
     const long long grid = rows * a.ntiles;
     kern<<<(unsigned)grid, kThreads, smem, st>>>(a); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
@@ -499,11 +491,7 @@ extern "C" int tac_stft_multi(const float* x, int64_t B, int64_t C, int64_t T, i
         a.nchunks = (int)(last_start / a.chunk) + 1;
         a.tile_len = a.chunk + nmax;
         const size_t smem = (size_t)a.tile_len * sizeof(float) + (size_t)kWarps * kXbufFloat2 * sizeof(float2);
-        static bool attr_set = false;
-        if (!attr_set) {
-            TAC_CHECK_CUDA(cudaFuncSetAttribute(stft_planes_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
-            attr_set = true;
-        }
+        TAC_SMEM_OPT_IN(stft_planes_kernel, 110 * 1024);
         const long long grid = rows * a.nchunks;
         TAC_REQUIRE(grid < (1ll << 31), "grid too large");
         stft_planes_kernel<<<(unsigned)grid, kThreads, smem, st>>>(a); TAC_LAUNCHED(1);

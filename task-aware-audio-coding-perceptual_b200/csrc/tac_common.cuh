@@ -4,6 +4,8 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <stdarg.h>
+#include <string.h>
+#include <atomic>
 
 #include "../../include/tac_spectral.h"
 #include "fft_core.cuh"
@@ -23,6 +25,19 @@ int set_error(int code, const char* fmt, ...);   // stores the message thread-lo
 #define TAC_REQUIRE(cond, ...)                                                                \
     do {                                                                                      \
         if (!(cond)) return tac::set_error(TAC_EINVAL, __VA_ARGS__);                          \
+    } while (0)
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a PER-DEVICE property of a kernel: the opt-in is remembered per
+// (call site, device), thread-safely, so that a second GPU used from the same process gets it too.
+#define TAC_SMEM_OPT_IN(kern, bytes)                                                          \
+    do {                                                                                      \
+        static std::atomic<unsigned long long> _tac_done{0ull};                               \
+        int _tac_dev = 0;                                                                     \
+        TAC_CHECK_CUDA(cudaGetDevice(&_tac_dev));                                             \
+        if (!((_tac_done.load(std::memory_order_acquire) >> (_tac_dev & 63)) & 1ull)) {       \
+            TAC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes))); \
+            _tac_done.fetch_or(1ull << (_tac_dev & 63), std::memory_order_release);           \
+        }                                                                                     \
     } while (0)
 
 #define TAC_ALIGNED16(p, name)                                                                \

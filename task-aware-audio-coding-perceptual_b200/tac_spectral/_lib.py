@@ -20,6 +20,16 @@ LIB_PATH = os.environ.get("TAC_SPECTRAL_LIB") or os.path.join(_HERE, "libtac_spe
 _I, _I64, _SZ, _VP, _F = C.c_int, C.c_int64, C.c_size_t, C.c_void_p, C.c_float
 _IP = C.POINTER(C.c_int)
 _VPP = C.POINTER(C.c_void_p)
+XCHG_MAX_WORLD = 8
+
+
+class XchgStruct(C.Structure):
+    """``tac_xchg`` of include/tac_spectral.h (host struct, passed by pointer; NULL = no exchange)."""
+    _fields_ = [("world", C.c_int), ("rank", C.c_int), ("payload", C.c_int64), ("peer", C.c_void_p * XCHG_MAX_WORLD)]
+
+
+_XP = C.POINTER(XchgStruct)
+_UBP = C.POINTER(C.c_ubyte)
 SIGNATURES = {
     "tac_last_error": (C.c_char_p, []),
     "tac_version": (_I, []),
@@ -50,6 +60,17 @@ SIGNATURES = {
     "tac_cosine_pairs_bwd": (_I, [_VPP, _I, _I64, _I, _F, _VP, _F, _VPP, _VP]),
     "tac_istft_length": (_I64, [_I64, _I, _I, _I]),
     "tac_istft": (_I, [_VP, _VP, _I, _I64, _I64, _I64, _I64, _I, _I, _I, _I, _I, _VP, _I64, _VP]),
+    "tac_stft_adjoint": (_I, [_VP, _VP, _I, _I64, _I64, _I64, _I64, _I, _I, _I, _F, _VP, _I64, _VP]),
+    "tac_xchg_bytes": (_SZ, [_I, _I64]),
+    "tac_xchg_push": (_I, [_XP, _VP, _VP]),
+    "tac_xchg_pop": (_I, [_XP, _VP, _VP]),
+    "tac_dpca_stats_push": (_I, [_VPP, _I, _I64, _I, _I, _VP, _VP, _SZ, _XP, _VP]),
+    "tac_dpca_eig_pop": (_I, [_VP, _I, _I, _VP, _VP, _VP, _VP, _VP, _SZ, _XP, _VP]),
+    "tac_loss_finalize": (_I, [_VP, _I, _VP, _XP, _VP, _VP]),
+    "tac_ipc_alloc": (_I, [_SZ, _VPP, _UBP]),
+    "tac_ipc_open": (_I, [_UBP, _VPP]),
+    "tac_ipc_close": (_I, [_VP]),
+    "tac_ipc_free": (_I, [_VP]),
 }
 
 PAD_ZERO, PAD_REFLECT = 0, 1

@@ -91,25 +91,62 @@ def _allreduce_stats(stats: torch.Tensor, group) -> torch.Tensor:
 
 
 def data_pca(z: torch.Tensor, algo: Optional[str] = None, group=None):
-    """Drop-in for the reference's ``data_pca(z)``: ``(s, v, mean)``."""
+    """Drop-in for the reference's ``data_pca(z)``: ``(s, v, mean)``.
+
+    The returned triple is DETACHED (the reference's is differentiable through ``torch.svd``): use :func:`dpca_project`
+    / :func:`apply_pca`, whose backward carries the basis term, when gradients must reach ``z``.  A ``z`` that requires
+    grad therefore raises a warning here instead of silently cutting the graph."""
     _, B, d = _check_views([z])
+    if torch.is_grad_enabled() and z.requires_grad:
+        import warnings
+        warnings.warn("tac_spectral.data_pca returns detached (s, v, mean); gradients through the PCA basis are "
+                      "implemented in dpca_project / apply_pca (basis_grad=True)", stacklevel=2)
     stats = _allreduce_stats(dpca_stats([z], algo), group)
     s, v, mu, _ = dpca_eig(stats, d)
-    world = 1
+    n = B
     if group is not None:
-        import torch.distributed as dist
-        world = dist.get_world_size(group)
-    r = min(B * world, d)                               # torch.svd(some=True) returns min(B, d) columns
+        n = int(stats[0, 0].item())                     # global batch (shards need not be equal); one host read
+    r = min(n, d)                                       # torch.svd(some=True) returns min(B, d) columns
     return s[0, :r], v[0, :, :r], mu[0]
 
 
+def basis_grad_term(zc: torch.Tensor, A: torch.Tensor, V: torch.Tensor, s: torch.Tensor, sel: torch.Tensor) -> torch.Tensor:
+    """The part of ``d loss / d z`` that flows through the PCA BASIS (the reference back-propagates through
+    ``torch.svd`` in ``data_pca``, ``pkl_file_model_updated.py:37-42,503-511``): with ``C = zc^T zc = V diag(s^2) V^T``
+    and the spectral projector ``P = sum_{i in sel} v_i v_i^T``,
+
+        dP = V (K o (V^T dC V)) V^T,   K_ij = (m_i - m_j) / (s_i^2 - s_j^2)  (m = selection mask; 0 where m_i == m_j)
+
+    so for ``A = zc^T g`` (``g`` = upstream gradient; summed over ranks when the batch is sharded) ``Cbar = V (K o V^T A V)
+    V^T`` and the term is ``zc (Cbar + Cbar^T)``.  Null directions of a rank-deficient batch (zero columns of ``V``, as
+    ``tac_dpca_eig`` emits them) enter through their projector ``N = I - V V^T``: ``Cbar += W A N + N A W`` with
+    ``W = V_sel diag(1 / s^2) V_sel^T``.  Plain torch algebra on ``d x d`` matrices (autograd glue, float64)."""
+    dt = torch.float64
+    Vd, Ad, zd = V.to(dt), A.to(dt), zc.to(dt)
+    lam = s.to(dt) ** 2
+    m = sel.to(dt)
+    valid = (Vd * Vd).sum(0) > 0.25                                   # real eigenvectors (null columns are zero)
+    dm = m[:, None] - m[None, :]
+    diff = lam[:, None] - lam[None, :]
+    pair = (dm != 0) & valid[:, None] & valid[None, :]
+    K = torch.where(pair, dm / torch.where(pair, diff, torch.ones_like(diff)), torch.zeros_like(diff))
+    M = Vd.T @ Ad @ Vd
+    Cbar = Vd @ (K * M) @ Vd.T
+    Vv = Vd * valid.to(dt)
+    N = torch.eye(Vd.shape[0], dtype=dt, device=V.device) - Vv @ Vv.T
+    w = torch.where((m > 0) & valid & (lam > 0), 1.0 / lam.clamp_min(1e-300), torch.zeros_like(lam))
+    W = (Vd * w) @ Vd.T
+    Cbar = Cbar + W @ Ad @ N + N @ Ad @ W
+    return (zd @ (Cbar + Cbar.T)).to(zc.dtype)
+
+
 class _Project(torch.autograd.Function):
-    """``z_out_i = (z_i - mu_i) P_i + mu_i`` for all views in one launch chain.  The backward treats the
-    projector ``P_i = V_sel V_sel^T`` as a constant of the step (the dependence of the mean on ``z`` is
-    kept): ``grad_z = (g - mean g) P + mean g``, computed by the same kernel."""
+    """``z_out_i = (z_i - mu_i) P_i + mu_i`` for all views in one launch chain.  Backward:
+    ``grad_z = (g - mean g) P + mean g`` (same kernel; the dependence of the mean on ``z`` is kept) plus, with
+    ``basis_grad`` (default, the reference's semantics), the term through the eigenvectors (:func:`basis_grad_term`)."""
 
     @staticmethod
-    def forward(ctx, v, mu, idx, cnt, group, *zs):
+    def forward(ctx, s, v, mu, idx, cnt, group, basis_grad, *zs):
         nv, B, d = len(zs), zs[0].shape[0], zs[0].shape[1]
         zc = [z.contiguous().float() for z in zs]
         outs = [torch.empty_like(z) for z in zc]
@@ -117,14 +154,15 @@ class _Project(torch.autograd.Function):
         with L.device_of(zc[0]):
             L.check(L.lib().tac_dpca_project(L.ptr_array(zc), nv, B, d, v.data_ptr(), mu.data_ptr(), idx.data_ptr(),
                                              cnt.data_ptr(), L.ptr_array(outs), ws.data_ptr(), n, L.stream_of(zc[0])))
-        ctx.save_for_backward(v, idx, cnt)
+        ctx.basis_grad = bool(basis_grad)
+        ctx.save_for_backward(s, v, mu, idx, cnt, *(zc if basis_grad else ()))
         ctx.group = group
         ctx.dtypes = [z.dtype for z in zs]
         return tuple(outs)
 
     @staticmethod
     def backward(ctx, *gs):
-        v, idx, cnt = ctx.saved_tensors
+        s, v, mu, idx, cnt, *zsaved = ctx.saved_tensors
         nv = len(gs)
         gc = [g.contiguous().float() for g in gs]
         B, d = gc[0].shape
@@ -140,7 +178,17 @@ class _Project(torch.autograd.Function):
         with L.device_of(gc[0]):
             L.check(L.lib().tac_dpca_project(L.ptr_array(gc), nv, B, d, v.data_ptr(), gmean.data_ptr(), idx.data_ptr(),
                                              cnt.data_ptr(), L.ptr_array(outs), ws.data_ptr(), nb, L.stream_of(gc[0])))
-        return (None, None, None, None, None) + tuple(o.to(dt) for o, dt in zip(outs, ctx.dtypes))
+        if ctx.basis_grad:
+            A = torch.stack([(z - mu[i]).T @ g for i, (z, g) in enumerate(zip(zsaved, gc))])      # [nv, d, d]
+            if ctx.group is not None:
+                import torch.distributed as dist
+                dist.all_reduce(A, group=ctx.group)
+            ar = torch.arange(d, device=idx.device)
+            for i in range(nv):
+                sel = torch.zeros(d, dtype=torch.float32, device=idx.device)
+                sel.scatter_add_(0, idx[i].long(), (ar < cnt[i]).float())              # selection mask, no host sync
+                outs[i] = outs[i] + basis_grad_term(zsaved[i] - mu[i], A[i], v[i], s[i], sel)
+        return (None, None, None, None, None, None, None) + tuple(o.to(dt) for o, dt in zip(outs, ctx.dtypes))
 
 
 def dpca_select(s: torch.Tensor, rank: torch.Tensor, dim_p: int):
@@ -155,26 +203,28 @@ def dpca_select(s: torch.Tensor, rank: torch.Tensor, dim_p: int):
 
 
 def dpca_project(zs: Sequence[torch.Tensor], dim_p: int, algo: Optional[str] = None, group=None,
-                 return_info: bool = False):
+                 return_info: bool = False, basis_grad: bool = True):
     """The DPCA block: per-view PCA, global top-``dim_p`` selection over all views' singular values,
     per-view projection onto the selected components and back (``pkl_file_model_updated.py:489-511``).
 
-    With ``group`` the statistics are all-reduced so that all ranks use the PCA of the global batch."""
+    With ``group`` the statistics are all-reduced so that all ranks use the PCA of the global batch.
+    ``basis_grad`` (default True): gradients flow through the PCA basis as in the reference, which back-propagates
+    through ``torch.svd``; ``False`` = stop-gradient on the projector (cheaper; only the centring is differentiated)."""
     nv, B, d = _check_views(zs)
     if dim_p < 0:
         raise ValueError("dim_p must be >= 0")
     stats = _allreduce_stats(dpca_stats(zs, algo), group)
     s, v, mu, rank = dpca_eig(stats, d)
     idx, cnt = dpca_select(s, rank, dim_p)
-    outs = list(_Project.apply(v, mu, idx, cnt, group, *zs))
+    outs = list(_Project.apply(s, v, mu, idx, cnt, group, basis_grad, *zs))
     if return_info:
         return outs, {"s": s, "v": v, "mu": mu, "rank": rank, "idx": idx, "cnt": cnt, "stats": stats}
     return outs
 
 
-def apply_pca(z: torch.Tensor, dim_p: int, algo: Optional[str] = None, group=None) -> torch.Tensor:
+def apply_pca(z: torch.Tensor, dim_p: int, algo: Optional[str] = None, group=None, basis_grad: bool = True) -> torch.Tensor:
     """``apply_pca`` (``pkl_file_models.py:224-228``): rank-``dim_p`` reconstruction of one view."""
-    return dpca_project([z], dim_p, algo, group)[0]
+    return dpca_project([z], dim_p, algo, group, basis_grad=basis_grad)[0]
 
 
 def var_topk(z: torch.Tensor, k: int, group=None):

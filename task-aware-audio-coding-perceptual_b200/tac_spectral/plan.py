@@ -42,6 +42,7 @@ class StepPlan:
     n_views: int
     d: int
     world: int = 1
+    global_rows: int = 0  # clips on ALL ranks; 0 = equal shards (rows * world).  Uneven shards (shard_bounds) pass the true sum
 
     def __post_init__(self):
         self.n_ffts, self.hops = list(self.n_ffts), list(self.hops)
@@ -51,6 +52,12 @@ class StepPlan:
         self.counts = [self.rows * (n // 2 + 1) * num_frames(self.T, n, h, False) for n, h in zip(self.n_ffts, self.hops)]
         if min(self.counts) <= 0:
             raise ValueError(f"signal of {self.T} samples is shorter than the largest n_fft")
+        if self.global_rows <= 0:
+            self.global_rows = self.rows * self.world
+        if self.global_rows < self.rows:
+            raise ValueError(f"global_rows {self.global_rows} < local rows {self.rows}")
+        self.global_counts = [self.global_rows * (n // 2 + 1) * num_frames(self.T, n, h, False)
+                              for n, h in zip(self.n_ffts, self.hops)]
 
     # ---- packed buffer layout
     @property
@@ -69,10 +76,10 @@ class StepPlan:
             raise ValueError(f"packed buffer must be float64 [{self.packed_len}]")
         return packed[self.sums_slice()], packed[self.stats_slice()].view(self.n_views, self.stat_stride)
 
-    # ---- normalisers (equal shards: every rank holds `rows` clips)
+    # ---- normalisers (GLOBAL element counts: rows of all ranks, equal shards or not)
     def inv_counts(self) -> List[float]:
         """d loss / d sums: loss = sum_j sums[j] * inv[j] with the GLOBAL element counts."""
-        return [1.0 / (self.S * c * self.world) for c in self.counts for _ in (0, 1)]
+        return [1.0 / (self.S * c) for c in self.global_counts for _ in (0, 1)]
 
     def loss_from_sums(self, sums: torch.Tensor) -> torch.Tensor:
         return torch.dot(sums.double().cpu(), torch.tensor(self.inv_counts(), dtype=torch.float64))

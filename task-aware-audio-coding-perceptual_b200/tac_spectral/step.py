@@ -9,10 +9,17 @@
 
 launched through the C ABI on the caller's current stream, so that the whole step can be captured
 in a CUDA graph (``torch.cuda.graph``) and replayed.  Multi-GPU (``group``): the per-scale loss sums
-and the DPCA sufficient statistics live in ONE packed float64 buffer that is all-reduced once per
-step; everything after it (eigen-solve, selection, projection) runs redundantly on
-every rank on the global statistics, and the input gradient needs no collective because the global
-normaliser is known from shapes.
+and the DPCA sufficient statistics are the step's only exchange; everything after it
+(eigen-solve, selection, projection) runs redundantly on every rank on the global statistics, and the
+input gradient needs no collective because the global normaliser is known from shapes.
+
+``exchange="p2p"`` (default at world > 1): the exchange is ONE-SHOT over NVLink peer memory and fused into the
+kernels on either side of it (``exchange.py``, ``csrc/xchg.cuh``): the kernel that completes the statistics
+peer-stores them into every rank's slot and raises a flag, the one-CTA-per-view tridiagonalisation spins on the
+flags itself and adds the slots in rank order; the loss sums travel the same way inside the single-CTA kernel
+that forms the loss scalar.  No kernel of the step waits for another rank except those two consumers, so rank
+skew and collective latency stay off the spectral chain.  ``exchange="nccl"``: the packed float64 buffer is
+all-reduced by NCCL in two slices (round-1 form, kept for A/B and as the fallback without peer access).
 
 The loss backward and the front end do not depend on the all-reduce; with ``overlap=True`` they run
 on a side stream next to the latency-bound DPCA chain (one CTA per view in the eigen-solve).
@@ -35,7 +42,8 @@ class SpectralStep:
     def __init__(self, rows: int, T: int, n_views: int, batch: int, d: int, dim_p: int,
                  n_ffts: Sequence[int] = (1024, 2048, 512), hops: Optional[Sequence[int]] = None,
                  eps: float = LOG_FLOOR, frontend: bool = True, fe_n_fft: int = 2048, fe_hop: int = 512,
-                 f_pad: int = 0, device="cuda", group=None, gram_algo: Optional[str] = None, overlap: bool = True):
+                 f_pad: int = 0, device="cuda", group=None, gram_algo: Optional[str] = None, overlap: bool = True,
+                 exchange: Optional[str] = None):
         self.rows, self.T, self.nv, self.B, self.d, self.dim_p = int(rows), int(T), int(n_views), int(batch), int(d), int(dim_p)
         self.n_ffts = list(n_ffts)
         self.hops = [n // 4 for n in self.n_ffts] if hops is None else list(hops)
@@ -48,6 +56,11 @@ class SpectralStep:
         if group is not None:
             import torch.distributed as dist
             self.world = dist.get_world_size(group)
+        exchange = exchange or os.environ.get("TAC_STEP_EXCHANGE", "p2p")
+        if exchange not in ("p2p", "nccl"):
+            raise ValueError(f"unknown exchange {exchange!r} (p2p | nccl)")
+        self.exchange = exchange if self.world > 1 else "none"
+        self.xchg = None
         from .dpca import _algo_code
         self.algo = _algo_code(gram_algo, self.d)
         lib = L.lib()
@@ -55,12 +68,19 @@ class SpectralStep:
         S, nv, d = self.S, self.nv, self.d
         self._nf, self._hp = L.int_array(self.n_ffts), L.int_array(self.hops)
         # ---- packed all-reduce payload: [2S loss sums | nv * (1 + d + d*d) DPCA statistics], float64 (plan.py)
-        self.plan = StepPlan(self.rows, self.T, self.n_ffts, self.hops, nv, d, self.world)
+        global_rows = self.rows * self.world
+        if self.world > 1:
+            # shards need not be equal (plan.shard_bounds hands out uneven ones): the loss normaliser uses the TRUE global
+            # clip count, gathered once here; the DPCA count n travels in the statistics themselves
+            t = torch.tensor([self.rows], dtype=torch.int64, device=dev)
+            dist.all_reduce(t, group=group)
+            global_rows = int(t.item())
+        self.plan = StepPlan(self.rows, self.T, self.n_ffts, self.hops, nv, d, self.world, global_rows)
         self.stat_stride = self.plan.stat_stride
         self.packed = torch.zeros(self.plan.packed_len, dtype=torch.float64, device=dev)
         self.sums, self.stats = self.plan.views(self.packed)
         inv = self.plan.inv_counts()
-        self.inv64 = torch.tensor(inv, dtype=torch.float64, device=dev)        # loss = dot(sums, inv64)
+        self.inv64 = torch.tensor(inv, dtype=torch.float64, device=dev)        # loss = dot(sums, inv64) (tac_loss_finalize)
         self.coef = torch.tensor(inv, dtype=torch.float32, device=dev)         # d loss / d sums (constant)
         self.loss = torch.zeros((), dtype=torch.float64, device=dev)
         # ---- workspaces and outputs
@@ -97,6 +117,16 @@ class SpectralStep:
             self.fill = self.overlap and self.frontend and os.environ.get("TAC_STEP_FILL", "1") != "0"
             self.mid = torch.cuda.Stream(device=dev, priority=-1) if self.fill else None
             self._ev_stats = torch.cuda.Event()
+        if self.exchange == "p2p":
+            # last in the constructor: the rendezvous synchronises the ranks, so the first step's pops find peers that
+            # have finished building their tables
+            from .exchange import Exchange
+            self.xchg = Exchange({"stats": nv * self.stat_stride, "sums": 2 * S}, group, dev)
+
+    def close(self):
+        if self.xchg is not None:
+            self.xchg.close()
+            self.xchg = None
 
     # ------------------------------------------------------------------ individual legs (current stream)
     def _check(self, x, y, zs):
@@ -131,22 +161,27 @@ class SpectralStep:
                                                 self.eps, self.coef.data_ptr(), self.sums.data_ptr(), self.grad_y.data_ptr(),
                                                 self.ws_loss.data_ptr(), self.ws_loss_bytes, st))
 
-    def leg_dpca_stats(self, zs):
+    def _x(self, name, on):
+        return self.xchg.desc(name) if (on and self.xchg is not None) else None
+
+    def leg_dpca_stats(self, zs, push=False):
+        """Local statistics; ``push``: the finishing kernel also peer-stores them to every rank (p2p exchange)."""
         st = torch.cuda.current_stream(self.device).cuda_stream
-        L.check(L.lib().tac_dpca_stats(L.ptr_array(zs), self.nv, self.B, self.d, self.algo, self.stats.data_ptr(),
-                                       self.ws_dpca.data_ptr(), self.ws_dpca_bytes, st))
+        L.check(L.lib().tac_dpca_stats_push(L.ptr_array(zs), self.nv, self.B, self.d, self.algo, self.stats.data_ptr(),
+                                            self.ws_dpca.data_ptr(), self.ws_dpca_bytes, self._x("stats", push), st))
 
     def leg_allreduce(self, what="all"):
         """The step's exchange: the packed float64 buffer [loss sums | DPCA statistics].  It is reduced in two
         slices so that the eigen-solve (needs the statistics only) overlaps the loss kernel."""
-        if self.group is not None:
+        if self.group is not None and self.world > 1:
             self.plan.allreduce(self.packed, self.group, what)
 
-    def leg_dpca_solve(self):
+    def leg_dpca_solve(self, pop=False):
+        """Eigen-solve + selection; ``pop``: the tridiagonalisation kernel first waits for and sums the world's pushes."""
         st = torch.cuda.current_stream(self.device).cuda_stream
         lib = L.lib()
-        L.check(lib.tac_dpca_eig(self.stats.data_ptr(), self.nv, self.d, self.s.data_ptr(), self.v.data_ptr(), self.mu.data_ptr(),
-                                 self.rank.data_ptr(), self.ws_dpca.data_ptr(), self.ws_dpca_bytes, st))
+        L.check(lib.tac_dpca_eig_pop(self.stats.data_ptr(), self.nv, self.d, self.s.data_ptr(), self.v.data_ptr(), self.mu.data_ptr(),
+                                     self.rank.data_ptr(), self.ws_dpca.data_ptr(), self.ws_dpca_bytes, self._x("stats", pop), st))
         L.check(lib.tac_dpca_select(self.s.data_ptr(), self.rank.data_ptr(), self.nv, self.d, self.dim_p, self.idx.data_ptr(),
                                     self.cnt.data_ptr(), st))
 
@@ -156,27 +191,33 @@ class SpectralStep:
                                          self.idx.data_ptr(), self.cnt.data_ptr(), self._zout_ptrs, self.ws_dpca.data_ptr(),
                                          self.ws_dpca_bytes, st))
 
-    def leg_loss_value(self):
-        torch.dot(self.sums, self.inv64, out=self.loss)
+    def leg_loss_value(self, exchange=False):
+        """loss = sums . inv in one single-CTA kernel; ``exchange``: the sums of all ranks are exchanged in it first."""
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        L.check(L.lib().tac_loss_finalize(self.sums.data_ptr(), 2 * self.S, self.inv64.data_ptr(), self._x("sums", exchange),
+                                          self.loss.data_ptr(), st))
 
     # ------------------------------------------------------------------ the step
     def run(self, x: torch.Tensor, y: torch.Tensor, zs: List[torch.Tensor]) -> torch.Tensor:
         """Enqueue one step; returns the (device, float64) loss scalar of the global batch.  Results:
         ``self.loss``, ``self.grad_y``, ``self.fe_out``, ``self.z_out``, ``self.cnt`` / ``self.idx``.
 
-        Schedule: statistics (+ all-reduce) run first, on the high-priority side stream, with the short-CTA front-end
+        Schedule: statistics (+ push) run first, on the high-priority side stream, with the short-CTA front-end
         kernel underneath; then the eigen-solve chain (1 CTA per view) runs NEXT TO the loss kernel that fills the
-        other SMs."""
+        other SMs.  With the p2p exchange the loss kernel waits for the LOCAL statistics only: the tridiagonalisation
+        CTAs are resident by then and do the waiting for the peers themselves."""
         self._check(x, y, zs)
+        p2p = self.exchange == "p2p"
         with torch.cuda.device(self.device):
             main = torch.cuda.current_stream(self.device)
             if self.overlap:
                 self.side.wait_stream(main)
                 with torch.cuda.stream(self.side):
-                    self.leg_dpca_stats(zs)
-                    self.leg_allreduce("stats")
+                    self.leg_dpca_stats(zs, push=p2p)
+                    if not p2p:
+                        self.leg_allreduce("stats")
                     self._ev_stats.record(self.side)
-                    self.leg_dpca_solve()
+                    self.leg_dpca_solve(pop=p2p)
                     self.leg_dpca_project(zs)
                 # the front end's CTAs are short (~12 us): it runs UNDER the statistics + collective, whose kernels get the
                 # next free SMs through the side stream's priority; the long-CTA loss kernel must not flood the SMs before
@@ -205,13 +246,17 @@ class SpectralStep:
         self.leg_loss_fused(x, y)
         if self.frontend and frontend:
             self.leg_frontend(x)
-        self.leg_allreduce("sums")
-        self.leg_loss_value()
+        p2p = self.exchange == "p2p"
+        if not p2p:
+            self.leg_allreduce("sums")
+        self.leg_loss_value(exchange=p2p)
 
     def _dpca_chain(self, zs):
-        self.leg_dpca_stats(zs)
-        self.leg_allreduce("stats")
-        self.leg_dpca_solve()
+        p2p = self.exchange == "p2p"
+        self.leg_dpca_stats(zs, push=p2p)
+        if not p2p:
+            self.leg_allreduce("stats")
+        self.leg_dpca_solve(pop=p2p)
         self.leg_dpca_project(zs)
 
     def algorithmic_bytes(self) -> dict:

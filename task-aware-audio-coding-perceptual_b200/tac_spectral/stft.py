@@ -44,12 +44,23 @@ def _check_window(window_fn: Callable, wkwargs) -> None:
 def stft_multi(x: torch.Tensor, n_ffts: Sequence[int], hops: Sequence[int], wins: Optional[Sequence[int]] = None, *,
                center: bool = False, pad_mode: Optional[str] = "reflect", normalized: bool = True,
                out_mode: int = L.OUT_PLANES, f_pad: int = 0) -> List[torch.Tensor]:
-    """All scales of ``x [B, C, T]`` in one call of ``tac_stft_multi``; see ``include/tac_spectral.h``."""
+    """All scales of ``x [B, C, T]`` in one call of ``tac_stft_multi``; see ``include/tac_spectral.h``.
+
+    Differentiable like the ``torchaudio.transforms.Spectrogram`` it replaces (``msstftd.py:125-127``): when ``x``
+    requires grad the call goes through :class:`_STFTMulti`, whose backward is the adjoint transform
+    (``tac_stft_adjoint``), so adversarial / feature-matching losses reach the generated waveform."""
     L.require_cuda(x, "x")
     if x.dim() != 3:
         raise ValueError(f"expected x of shape [B, C, T], got {tuple(x.shape)}")
     wins = list(n_ffts) if wins is None else list(wins)
     assert len(n_ffts) == len(hops) == len(wins)                       # msstftd.py:177
+    if torch.is_grad_enabled() and x.requires_grad:
+        cfg = (tuple(n_ffts), tuple(hops), tuple(wins), bool(center), pad_mode, bool(normalized), int(out_mode), int(f_pad))
+        return list(_STFTMulti.apply(x, cfg))
+    return _stft_multi_raw(x, n_ffts, hops, wins, center, pad_mode, normalized, out_mode, f_pad)
+
+
+def _stft_multi_raw(x, n_ffts, hops, wins, center, pad_mode, normalized, out_mode, f_pad) -> List[torch.Tensor]:
     x = x.contiguous().float()
     B, Cc, T = x.shape
     outs = []
@@ -69,6 +80,81 @@ def stft_multi(x: torch.Tensor, n_ffts: Sequence[int], hops: Sequence[int], wins
                                        L.int_array(wins), int(bool(center)), _pad_mode_code(pad_mode),
                                        int(bool(normalized)), out_mode, int(f_pad), L.ptr_array(outs), L.stream_of(x)))
     return outs
+
+
+def _window_norm(win: int) -> float:
+    """``1 / sqrt(sum w^2)`` of the periodic Hann window (torchaudio's ``normalized=True`` / 'window')."""
+    w = torch.hann_window(win, periodic=True, dtype=torch.float64)
+    return float(1.0 / torch.sqrt((w * w).sum()))
+
+
+def _stft_adjoint(a: torch.Tensor, b: Optional[torch.Tensor], in_mode: int, rows: int, K: int, F: int, n_fft: int, hop: int,
+                  win: int, scale: float, out_len: int) -> torch.Tensor:
+    """``[rows, out_len]`` = adjoint of the ``center=False`` analysis STFT applied to ``a + i b`` ([rows, K, F])."""
+    if n_fft not in SUPPORTED_NFFT or hop * 8 < n_fft or hop > n_fft:
+        raise NotImplementedError(f"STFT backward needs n_fft in {SUPPORTED_NFFT} and hop in [n_fft/8, n_fft] "
+                                  f"(got n_fft={n_fft}, hop={hop})")
+    out = torch.empty((rows, out_len), dtype=torch.float32, device=a.device)
+    with L.device_of(a):
+        L.check(L.lib().tac_stft_adjoint(a.data_ptr(), b.data_ptr() if b is not None else None, in_mode, rows, K * F, F, F,
+                                         n_fft, hop, win, float(scale), out.data_ptr(), out_len, L.stream_of(a)))
+    return out
+
+
+class _STFTMulti(torch.autograd.Function):
+    """``tac_stft_multi`` with the backward torchaudio's Spectrogram has: per scale the adjoint of framing + window +
+    one-sided DFT (``tac_stft_adjoint``, the inverse-STFT kernel without edge weights and envelope), then the adjoint of
+    the centre padding (crop for zeros, fold-back for reflect); magnitude / phase outputs add the polar chain rule."""
+
+    @staticmethod
+    def forward(ctx, x, cfg):
+        n_ffts, hops, wins, center, pad_mode, normalized, out_mode, f_pad = cfg
+        outs = _stft_multi_raw(x.detach(), n_ffts, hops, wins, center, pad_mode, normalized, out_mode, f_pad)
+        ctx.cfg, ctx.xshape, ctx.xdtype = cfg, tuple(x.shape), x.dtype
+        if out_mode == L.OUT_MAGPHASE:
+            ctx.save_for_backward(*outs)
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, *gs):
+        n_ffts, hops, wins, center, pad_mode, normalized, out_mode, f_pad = ctx.cfg
+        B, Cc, T = ctx.xshape
+        rows = B * Cc
+        total = None
+        for i, (n, h, w) in enumerate(zip(n_ffts, hops, wins)):
+            g = gs[i]
+            if g is None:
+                continue
+            K, pad = n // 2 + 1, (n // 2 if center else 0)
+            F = num_frames(T, n, h, center)
+            if out_mode == L.OUT_COMPLEX:                                   # [B, C, K, F] complex64
+                a, b, mode = torch.view_as_real(g.contiguous().to(torch.complex64)), None, L.IN_COMPLEX
+            elif out_mode == L.OUT_PLANES:                                  # [B, 2C, F, K] -> two [B, C, K, F] planes
+                g = g.float()
+                a = g[:, :Cc].permute(0, 1, 3, 2).contiguous()
+                b = g[:, Cc:].permute(0, 1, 3, 2).contiguous()
+                mode = L.IN_PLANES
+            else:                                                           # [rows, 2, K, f_pad]: polar chain rule
+                out = ctx.saved_tensors[i]
+                Fv = min(F, out.shape[-1])
+                mag, ph = out[:, 0, :, :Fv], out[:, 1, :, :Fv]
+                gm, gp = g[:, 0, :, :Fv].float(), g[:, 1, :, :Fv].float()
+                c, sn = torch.cos(ph), torch.sin(ph)
+                gpm = torch.where(mag > 0, gp / mag.clamp_min(1e-30), torch.zeros_like(gp))
+                a = (gm * c - gpm * sn).contiguous()
+                b = (gm * sn + gpm * c).contiguous()
+                mode, F = L.IN_PLANES, Fv
+            scale = _window_norm(w) if normalized else 1.0
+            gp_sig = _stft_adjoint(a, b, mode, rows, K, F, n, h, w, scale, T + 2 * pad)   # grad w.r.t. the padded signal
+            gx = gp_sig[:, pad:pad + T]
+            if pad and _pad_mode_code(pad_mode) == L.PAD_REFLECT:
+                gx = gx.clone()
+                gx[:, 1:pad + 1] += gp_sig[:, :pad].flip(-1)                 # xp[i] = x[pad - i],          i < pad
+                gx[:, T - 1 - pad:T - 1] += gp_sig[:, pad + T:].flip(-1)     # xp[pad + T + j] = x[T - 2 - j]
+            total = gx if total is None else total + gx
+        if total is None:
+            return None, None
+        return total.reshape(B, Cc, T).to(ctx.xdtype), None
 
 
 class Spectrogram(nn.Module):

@@ -57,6 +57,7 @@ def parse():
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of CUDA-graph replay")
     ap.add_argument("--no-overlap", action="store_true", help="run every leg on one stream")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the cfg 3 / cfg 4 / cfg 5 extra block")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU-baseline budget (bounded sample)")
     return ap.parse_args()
 
@@ -274,6 +275,171 @@ def torch_gpu_baseline(x, y, zs, dim_p, iters=10):
     return a.elapsed_time(b) / iters
 
 
+# ------------------------------------------------------------------------------------------ host placement
+def bind_to_gpu_numa(index):
+    """Pin this process to the CPUs of its GPU's NUMA node (NVML affinity mask) BEFORE pinned host buffers are
+    allocated, so that the e2e H2D copies do not cross sockets.  Best effort; returns what was done."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * i + b for i, wd in enumerate(mask) for b in range(64) if (int(wd) >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        cpus &= allowed
+        if not cpus:
+            return {"bound": False, "why": "NVML affinity mask empty inside this cpuset"}
+        os.sched_setaffinity(0, cpus)
+        return {"bound": True, "cpus": len(cpus), "of": len(allowed)}
+    except Exception as e:
+        return {"bound": False, "why": f"{type(e).__name__}: {e}"}
+
+
+# ------------------------------------------------------------------------------------------ N-rank parity on hardware
+def check_parity_n(step, dset, w, dev, rank, world, rerun=True):
+    """The sharded step (p2p exchange or NCCL, as benchmarked) against the SAME kernels run on the whole batch by one
+    GPU: every rank runs its shard once more, the shards are all-gathered, rank 0 runs the 1-rank step on the
+    concatenation (the reference's semantics: loss means and PCA over the whole batch on one device,
+    train_pkl_file_task_aware.py:597-629, pkl_file_model_updated.py:489-511) and compares loss, the per-view selection
+    (cnt / idx), the projected latents and the loss gradient.  Tolerances: loss 1e-9 relative (float64 sums in a
+    different order), latents 1e-4 of their largest entry (north star), gradient 1e-6 of its largest entry."""
+    import torch
+    import torch.distributed as dist
+    from tac_spectral.step import SpectralStep
+    x, y, zs = dset
+    if rerun:                                                           # False: judge the results already in `step` (graph replay)
+        step.run(x, y, zs)
+    torch.cuda.synchronize()
+
+    def gather(t):
+        out = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(out, t.contiguous())
+        return torch.cat(out, 0)
+
+    X, Y = gather(x), gather(y)
+    Zs = [gather(z) for z in zs]
+    G = gather(step.grad_y)
+    Zo = [gather(z) for z in step.z_out]
+    cnts = gather(step.cnt[None])                                       # [world, nv]: must agree across ranks
+    losses = gather(step.loss.reshape(1))
+    if rank != 0:
+        return None
+    one = SpectralStep(X.shape[0], X.shape[1], len(Zs), Zs[0].shape[0], Zs[0].shape[1], w["dim_p"], N_FFTS, HOPS, device=dev)
+    one.run(X, Y, Zs)
+    torch.cuda.synchronize()
+    res = {"loss_rel": abs(float(losses[0]) - float(one.loss)) / abs(float(one.loss)),
+           "loss_rank_spread": float((losses - losses[0]).abs().max()),
+           "cnt_equal": bool((cnts == one.cnt[None]).all()),
+           "idx_equal": bool(all(torch.equal(step.idx[v, :int(one.cnt[v])], one.idx[v, :int(one.cnt[v])]) for v in range(len(Zs)))),
+           "z_out_rel": max(float((a - b).abs().max() / b.abs().max()) for a, b in zip(Zo, one.z_out)),
+           "grad_rel": float((G - one.grad_y).abs().max() / one.grad_y.abs().max())}
+    ok = (res["loss_rel"] <= 1e-9 and res["loss_rank_spread"] == 0.0 and res["cnt_equal"] and res["idx_equal"]
+          and res["z_out_rel"] <= 1e-4 and res["grad_rel"] <= 1e-6)
+    res["verdict"] = "ok" if ok else "MISMATCH"
+    return res
+
+
+# ------------------------------------------------------------------------------------------ cfg 3 / cfg 4 / cfg 5
+def _time_ms(fn, iters, warm=2):
+    import torch
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(iters):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / iters
+
+
+def run_extras(args, dev, rank, world, group, peak, barrier):
+    """The other BASELINE.json configs, measured in the same run so that they are driver-visible:
+    cfg 4 (K1 discriminator inputs, 5 scales, 512 x 10 s -- the one genuinely HBM-bound config), cfg 5 (60 s clips,
+    dim_p sweep 8..256 over 4 views of d = 128) and, at 8 ranks, the cfg 3 step (4 views, batch 1024 global,
+    dim_p = 128).  Device-timed with CUDA events; every rank runs them (the exchange needs all ranks), rank 0 reports."""
+    import torch
+    import torch.distributed as dist
+    import tac_spectral as ts
+    from tac_spectral.step import SpectralStep
+    out = {}
+    g = torch.Generator(device="cpu").manual_seed(4321 + rank)
+
+    # ---- cfg 4: msstftd front end, n_fft 2048..128, hop n/4, 512 clips x 160 000 samples -> [512, 2, F_s, K_s] planes
+    try:
+        n4, h4 = [2048, 1024, 512, 256, 128], [512, 256, 128, 64, 32]
+        B4, T4 = 512, 160000
+        x4 = (0.1 * torch.randn(B4, 1, T4, generator=g)).to(dev)
+        ms4 = ts.MultiScaleSTFT(n4, h4, n4)
+        outs = None
+
+        def k1():
+            nonlocal outs
+            outs = None                                                  # 6.6 GB of planes: one set alive at a time
+            outs = ms4(x4)
+        t4 = _time_ms(k1, iters=5, warm=2)
+        bytes4 = 4 * B4 * T4 + 8 * B4 * sum((1 + (T4 - n) // h) * (n // 2 + 1) for n, h in zip(n4, h4))
+        out["cfg4_k1_planes"] = {"workload": "msstftd front end, 5 scales 2048..128 hop n/4, 512 x 10 s, planes [B,2,F,K]",
+                                 "ms": t4, "bytes": bytes4, "gbs": bytes4 / (t4 * 1e-3) / 1e9, "frac": bytes4 / (t4 * 1e-3) / 1e9 / peak,
+                                 "audio_s_per_s": B4 * T4 / SR / (t4 * 1e-3), "includes": "output allocation by the caching allocator"}
+        del outs, x4
+        outs = None
+        torch.cuda.empty_cache()
+    except Exception as e:
+        out["cfg4_k1_planes"] = {"error": f"{type(e).__name__}: {e}"}
+
+    # ---- cfg 5: E4D1 latent=256 sweep: 16 items x 4 views x 60 s per GPU, DPCA d = 128 x 4, dim_p 8..256
+    try:
+        b5, v5, T5, d5 = 16, 4, 960000, 128
+        x5 = (0.1 * torch.randn(b5 * v5, T5, generator=g)).to(dev)
+        y5 = x5 + 0.02 * torch.randn(b5 * v5, T5, generator=g).to(dev)
+        z5 = [z.to(dev) for z in synth_host(b5, v5, 64, d5, seed=555 + rank)[2]]
+        sweep = {}
+        for dim_p in (8, 16, 32, 64, 128, 256):
+            st5 = SpectralStep(b5 * v5, T5, v5, b5, d5, dim_p, N_FFTS, HOPS, device=dev, group=group)
+            t_step = _time_ms(lambda: st5.run(x5, y5, z5), iters=3, warm=1)
+            t_dpca = _time_ms(lambda: (st5.leg_dpca_stats(z5), st5.leg_dpca_solve(), st5.leg_dpca_project(z5)), iters=5, warm=1)
+            sweep[str(dim_p)] = {"step_ms": t_step, "dpca_chain_ms_local": t_dpca, "cnt": st5.cnt.tolist(),
+                                 "audio_s_per_s": world * b5 * v5 * T5 / SR / (t_step * 1e-3)}
+            st5.close()
+            st5 = None
+        out["cfg5_dim_p_sweep"] = {"workload": f"{b5} items x {v5} views x 60 s per GPU, 3-scale loss fwd+bwd + front end + DPCA "
+                                               f"d={d5} x {v5} views (global batch {b5 * world})", "per_dim_p": sweep}
+        del x5, y5, z5
+        torch.cuda.empty_cache()
+    except Exception as e:
+        out["cfg5_dim_p_sweep"] = {"error": f"{type(e).__name__}: {e}"}
+        if world > 1:
+            raise                                                        # ranks must not diverge inside an exchange
+
+    # ---- cfg 3 (the north star's 8-GPU config): 4 views, batch 128 per GPU (1024 global at 8), dim_p = 128
+    if world == 8 or os.environ.get("TAC_BENCH_CFG3"):
+        w3 = WORKLOADS["cfg3"]
+        hx, hy, hz = synth_host(w3["batch"], w3["views"], w3["T"], w3["d"], seed=3000 + rank)
+        x3, y3, z3 = hx.to(dev), hy.to(dev), [z.to(dev) for z in hz]
+        st3 = SpectralStep(w3["batch"] * w3["views"], w3["T"], w3["views"], w3["batch"], w3["d"], w3["dim_p"], N_FFTS, HOPS,
+                           device=dev, group=group)
+        st3.run(x3, y3, z3)
+        torch.cuda.synchronize()
+        g3 = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g3):
+            st3.run(x3, y3, z3)
+        barrier()
+        t3 = _time_ms(g3.replay, iters=max(10, args.steps), warm=3)
+        tt = torch.tensor([t3], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        t3 = float(tt.item())
+        out["cfg3_step"] = {"workload": w3["desc"], "n_gpus": world, "ms_per_step": t3, "loss": float(st3.loss.item()),
+                            "audio_s_per_s": world * w3["batch"] * w3["views"] * w3["T"] / SR / (t3 * 1e-3), "cnt": st3.cnt.tolist(),
+                            "note": "inputs L2-resident (one input set); device time, max over ranks"}
+        g3 = None
+        st3.close()
+    return out
+
+
 # ------------------------------------------------------------------------------------------ native
 def run_native(args):
     import torch
@@ -292,10 +458,8 @@ def run_native(args):
     group = None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/nccl_debug.%h.%p.log")   # keep stdout to the one JSON line
-        os.environ["NCCL_DEBUG"] = os.environ.get("TAC_NCCL_DEBUG", "WARN")      # (NCCL_DEBUG=VERSION prints to stdout)
-        # the two collectives of a step are tiny and sit on its critical path: their kernels run on a HIGH-PRIORITY NCCL
-        # stream so that they take the next free SM slot ahead of the pending front-end / loss CTAs
+        # NCCL carries the rendezvous, the barriers and the max-over-ranks of the timing (and the step's exchange only
+        # with TAC_STEP_EXCHANGE=nccl); NCCL_DEBUG is left as the caller set it
         opts = None
         if os.environ.get("TAC_NCCL_HIPRI", "1") != "0":
             try:
@@ -305,12 +469,16 @@ def run_native(args):
         dist.init_process_group("nccl", device_id=dev, pg_options=opts)
         group = dist.group.WORLD
     lib = L.lib()
+    numa = bind_to_gpu_numa(local)                    # before any pinned allocation: e2e copies stay on the GPU's socket
 
     w = WORKLOADS[args.workload]
     batch, views, T, d, dim_p = w["batch"], w["views"], w["T"], w["d"], w["dim_p"]
     rows = batch * views
     step = SpectralStep(rows, T, views, batch, d, dim_p, N_FFTS, HOPS, device=dev, group=group, overlap=not args.no_overlap)
     alg = step.algorithmic_bytes()
+    exch_desc = {"none": "none (1 GPU)", "nccl": "NCCL all-reduce of one packed float64 buffer, two slices",
+                 "p2p": f"one-shot NVLink peer stores + flags fused into the producing / consuming kernels "
+                        f"({step.xchg.backend if step.xchg else '-'} peer memory), rank-ordered float64 sums"}[step.exchange]
 
     # ---- inputs resident in HBM: a ring of input sets larger than L2 (126 MB) so no step finds its inputs cached
     set_bytes = 2 * rows * T * 4 + views * batch * d * 4
@@ -367,10 +535,12 @@ def run_native(args):
         do_step(i)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    step_evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     with ClockSampler(local) as clk:
         e0.record()
         for i in range(args.steps):
             do_step(args.warmup + i)
+            step_evs[i].record()                      # per-step spread (p50 / p95 below); the headline stays total / steps
         e1.record()
         torch.cuda.synchronize()
         if world > 1:
@@ -381,6 +551,9 @@ def run_native(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_step = float(t.item()) / args.steps
+    per_step = sorted(a.elapsed_time(b) for a, b in zip([e0] + step_evs[:-1], step_evs))
+    pct = lambda q: per_step[min(len(per_step) - 1, int(q * len(per_step)))]
+    spread = {"ms_per_step_p50": pct(0.50), "ms_per_step_p95": pct(0.95), "ms_per_step_max": per_step[-1]}
     audio_s_step = world * rows * T / SR
     value = audio_s_step / (ms_step * 1e-3)
     loss_val = float(step.loss.item())
@@ -397,9 +570,7 @@ def run_native(args):
                          ("dpca_solve", step.leg_dpca_solve), ("dpca_project", lambda: step.leg_dpca_project(zs))):
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record(); fn(); b.record()
-            rec[name] = (a, b)
-            if name == "dpca_stats":
-                step.leg_allreduce("all")
+            rec[name] = (a, b)                         # rank-local legs: no push / pop, no collective
         evs.append(rec)
     torch.cuda.synchronize()
     for rec in evs:
@@ -435,6 +606,11 @@ def run_native(args):
             roofline["traffic_source"] = ent.get("source")
         except Exception:
             pass
+
+    # ---- N > 1: the sharded, exchanged step against the whole batch on ONE GPU (rank 0), on hardware
+    parity_n = None
+    if world > 1:
+        parity_n = check_parity_n(step, dsets[0], w, dev, rank, world)
 
     # ---- e2e: public API, pinned HOST buffers; every step's inputs cross PCIe (H2D) and its loss is read back (D2H).
     # Two device input sets + two graphs: the copy of step i+1 (copy stream) overlaps the compute of step i, as a
@@ -522,6 +698,14 @@ def run_native(args):
         v, t_step, sample = cpu_baseline(w, args.cpu_seconds, threads)
         cpu = {"value": v, "unit": "audio-s/s", "cores": threads, "kind": "port", "sample": sample, "ms_per_step": 1e3 * t_step}
 
+    extra = None
+    if not args.no_extra:
+        graphs = g_e2e = None                                            # free the main workload's buffers first
+        step.close()
+        step = dsets = dbuf = None
+        torch.cuda.empty_cache()
+        extra = run_extras(args, dev, rank, world, group, peak, barrier)
+
     if rank == 0:
         line = {"metric": "audio-seconds/sec through STFT-loss+DPCA step", "value": value, "unit": "audio-s/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
@@ -529,12 +713,13 @@ def run_native(args):
                 "config": {"workload": f"{args.workload}: {w['desc']}", "clips_per_gpu": rows, "samples_per_clip": T,
                            "loss_scales": list(N_FFTS), "loss_kernel": "fused fwd+bwd (tac_mrstft_loss_fwd_bwd): reads x, y; writes grad_y", "front_end": "n_fft 2048 hop 512 centred, mag+phase [rows,2,1025,32] (unpadded)",
                            "dpca": {"views": views, "batch": batch, "d": d, "dim_p": dim_p, "gram": "tcgen05 3xTF32"},
-                           "parallelism": f"dp{world} (batch shards; one packed NCCL all-reduce of loss sums + DPCA statistics)",
+                           "parallelism": f"dp{world} (batch shards; exchange of loss sums + DPCA statistics: {exch_desc})",
                            "launch": "cuda-graph replay" if graphs is not None else "eager",
                            "overlap": not args.no_overlap,
                            "l2": f"ring of {nsets} input sets ({nsets * set_bytes / 1e6:.0f} MB) > 126 MB L2"},
                 "roofline": roofline, "cpu_baseline": cpu, "torch_gpu_baseline": tgpu, "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
-                "launches_per_step": launches_per_step, "clocks": clk.summary(), "loss": loss_val}
+                "launches_per_step": launches_per_step, "clocks": clk.summary(), "loss": loss_val, **spread,
+                "parity_n": parity_n, "numa": numa, "extra": extra}
         print(json.dumps(line), flush=True)
     sys.stdout.flush()
     if world > 1:

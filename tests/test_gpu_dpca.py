@@ -123,11 +123,40 @@ def test_sharded_stats_equal_full_batch(ts):
     assert cnt.cpu().tolist() == [len(i) for i in ref_idx]
 
 
+@pytest.mark.parametrize("shape", [(256, 128, 2, 32), (64, 32, 2, 16), (24, 32, 2, 10)])
+def test_project_backward_matches_reference_autograd(ts, shape):
+    """The reference back-propagates through torch.svd inside data_pca (pkl_file_model_updated.py:37-42, 489-511):
+    d loss / d z of dpca_project (basis_grad=True, the default) against torch autograd of the oracle's restatement,
+    float64 on the CPU.  Includes a rank-deficient batch (B < d).  Tolerance: 1e-3 of the largest gradient entry
+    (float32 eigenvectors and singular values enter 1 / (s_i^2 - s_j^2))."""
+    B, d, nv, dim_p = shape
+    zs = O.synth_latents(B, d, nv)
+    torch.manual_seed(2)
+    gs = [torch.randn(B, d, dtype=torch.float64) for _ in zs]
+    zr = [z.double().requires_grad_(True) for z in zs]
+    ref_out, ref_idx = O.dpca_project_ref(zr, dim_p)
+    torch.autograd.backward(ref_out, gs)
+    zg = [z.cuda().requires_grad_(True) for z in zs]
+    outs, info = ts.dpca_project(zg, dim_p, algo="fp64", return_info=True)
+    assert info["cnt"].cpu().tolist() == [len(i) for i in ref_idx]
+    torch.autograd.backward(outs, [g.float().cuda() for g in gs])
+    for v in range(nv):
+        ref = zr[v].grad
+        err = float((zg[v].grad.cpu().double() - ref).abs().max())
+        assert err <= 1e-3 * float(ref.abs().max()), f"view {v}: {err:.3e} vs scale {float(ref.abs().max()):.3e}"
+
+
+def test_data_pca_warns_when_graph_is_cut(ts):
+    z = torch.randn(32, 16, device="cuda", requires_grad=True)
+    with pytest.warns(UserWarning, match="detached"):
+        ts.data_pca(z)
+
+
 def test_project_backward(ts):
-    """grad_z = (g - mean g) P + mean g with the projector held constant."""
+    """basis_grad=False: grad_z = (g - mean g) P + mean g with the projector held constant (stop-gradient form)."""
     zs = O.synth_latents(64, 32, 2)
     zg = [z.cuda().requires_grad_(True) for z in zs]
-    outs, info = ts.dpca_project(zg, 16, algo="fp64", return_info=True)
+    outs, info = ts.dpca_project(zg, 16, algo="fp64", return_info=True, basis_grad=False)
     torch.manual_seed(1)
     gs = [torch.randn(64, 32) for _ in zs]
     torch.autograd.backward(outs, [g.cuda() for g in gs])

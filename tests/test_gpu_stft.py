@@ -167,3 +167,65 @@ def test_amplitude_to_db(ts):
     assert float((plain.cpu() - ref).abs().max()) < 1e-3
     with pytest.raises(ValueError):
         ts.amplitude_to_db(spec, n_frames=41)
+
+
+# ------------------------------------------------------------------------------------------------ backward (autograd)
+def _torch_stft(x, n, h, win, center, pad_mode, normalized):
+    w = torch.hann_window(win, dtype=x.dtype)
+    X = torch.stft(x, n, h, win, w, center=center, pad_mode=pad_mode if center else "reflect", return_complex=True)
+    return X / w.pow(2).sum().sqrt() if normalized else X
+
+
+@pytest.mark.parametrize("cfg", [(1024, 256, 1024, False, "reflect", True), (2048, 512, 2048, True, "constant", False),
+                                 (512, 128, 512, True, "reflect", True), (256, 64, 200, False, "reflect", True)])
+def test_stft_backward_matches_torch(ts, cfg):
+    """torchaudio's Spectrogram (msstftd.py:125-127) is differentiable: d loss / d waveform through the complex
+    layout [B, C, K, F] and through the discriminator planes [B, 2C, F, K] against torch.stft autograd (float64, CPU).
+    Tolerance: 1e-4 of the largest gradient entry."""
+    n, h, win, center, pad_mode, normalized = cfg
+    torch.manual_seed(3)
+    x = 0.3 * torch.randn(3, 2, 6000)
+    xr = x.double().requires_grad_(True)
+    Xr = _torch_stft(xr.reshape(6, -1), n, h, win, center, pad_mode, normalized).reshape(3, 2, n // 2 + 1, -1)
+    G = torch.randn(Xr.shape, dtype=torch.float64) + 1j * torch.randn(Xr.shape, dtype=torch.float64)
+    (Xr.real * G.real + Xr.imag * G.imag).sum().backward()
+    ref = xr.grad
+    # complex layout
+    from tac_spectral import _lib as L
+    xg = x.cuda().requires_grad_(True)
+    Xc = ts.stft_multi(xg, [n], [h], [win], center=center, pad_mode=pad_mode, normalized=normalized, out_mode=L.OUT_COMPLEX)[0]
+    Gc = G.to(torch.complex64).cuda()
+    (Xc.real * Gc.real + Xc.imag * Gc.imag).sum().backward()
+    err = float((xg.grad.cpu().double() - ref).abs().max())
+    assert err <= 1e-4 * float(ref.abs().max()), f"complex: {err:.3e} vs {float(ref.abs().max()):.3e}"
+    # planes layout (cat(real, imag) + rearrange b c w t -> b c t w)
+    xg2 = x.cuda().requires_grad_(True)
+    Pl = ts.stft_multi(xg2, [n], [h], [win], center=center, pad_mode=pad_mode, normalized=normalized, out_mode=L.OUT_PLANES)[0]
+    Gp = torch.cat([G.real, G.imag], 1).permute(0, 1, 3, 2).float().cuda()
+    (Pl * Gp).sum().backward()
+    err = float((xg2.grad.cpu().double() - ref).abs().max())
+    assert err <= 1e-4 * float(ref.abs().max()), f"planes: {err:.3e} vs {float(ref.abs().max()):.3e}"
+
+
+def test_frontend_backward_matches_torch(ts):
+    """Magnitude / phase front end (spectrogram.ipynb cell 10): polar chain rule on top of the adjoint transform."""
+    torch.manual_seed(4)
+    x = 0.3 * torch.randn(2, 8000)
+    xr = x.double().requires_grad_(True)
+    D = torch.stft(xr, 2048, 512, 2048, torch.hann_window(2048, dtype=torch.float64), center=True, pad_mode="constant",
+                   return_complex=True)
+    gm, gp = torch.randn(D.shape, dtype=torch.float64), 0.01 * torch.randn(D.shape, dtype=torch.float64)
+    (D.abs() * gm + D.angle() * gp).sum().backward()
+    xg = x.cuda().requires_grad_(True)
+    out = ts.complex_spectrogram(xg)
+    (out[:, 0] * gm.float().cuda() + out[:, 1] * gp.float().cuda()).sum().backward()
+    ref = xr.grad
+    err = float((xg.grad.cpu().double() - ref).abs().max())
+    assert err <= 2e-4 * float(ref.abs().max()), f"{err:.3e} vs {float(ref.abs().max()):.3e}"
+
+
+def test_multiscale_module_is_differentiable(ts):
+    x = (0.1 * torch.randn(2, 1, 16000)).cuda().requires_grad_(True)
+    outs = ts.MultiScaleSTFT()(x)
+    sum(o.square().sum() for o in outs).backward()
+    assert x.grad is not None and float(x.grad.abs().max()) > 0

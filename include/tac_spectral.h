@@ -85,6 +85,46 @@ TAC_API int tac_stft_multi(const float* x, int64_t B, int64_t C, int64_t T, int 
                    const int* hop, const int* win, int center, int pad_mode, int normalized,
                    int out_mode, int64_t f_pad, void* const* out, tac_stream_t stream);
 
+/* K1x -- single-scale STFT for ANY frame length (8 <= n_fft, n_fft + n_fft/2 <= 4096), output epilogue fused into the
+ * write-out.  Frame lengths of the list above run on the warp FFT core, every other one on a Bluestein (chirp-z)
+ * transform in shared memory.  Replaces:
+ *   - librosa.stft(n_fft=2046, hop 512, win 2046) + np.abs + np.angle + librosa.amplitude_to_db of spectrogram.ipynb
+ *     cell 9 (raw :2894-2913)                                  -> TAC_EPI_MAGPHASE (+ rowmax, tac_db_from_rowmax) / TAC_EPI_MAGDB
+ *   - torch.stft(n_fft=510, hop 128, hann, center=True) + spec_fwd (abs(z)^0.5 * exp(1j angle z) * 0.15) + pad_spec of
+ *     sgmse/sgmse/data_module.py:109-116,162-169,212-214 and sgmse/sgmse/util/other.py:76-90   -> TAC_EPI_COMPRESS, f_pad
+ *   - torchaudio.transforms.Spectrogram() (n_fft=400, hop 200, power=2) and 10*log10(S + 1e-10) of
+ *     testing_scripts.ipynb:246-249                            -> TAC_EPI_POWER / TAC_EPI_LOGPOWER
+ *   - the north star's mel alternative (melscale_fbanks(K, 0, 8000, 80, 16000, None, 'htk')) -> TAC_EPI_MEL
+ * Every output is time-innermost with f_pad >= F entries per row (f_pad = 0: f_pad = F); frames [F, f_pad) are
+ * zero-filled, f_pad < F crops. */
+#define TAC_EPI_COMPLEX 0   /* complex64 [rows, K, f_pad]      z                                                    */
+#define TAC_EPI_COMPRESS 1  /* complex64 [rows, K, f_pad]      |z|^p0 * exp(j angle z) * p1                         */
+#define TAC_EPI_MAGPHASE 2  /* float32   [rows, 2, K, f_pad]   |z|, angle z                                         */
+#define TAC_EPI_MAGDB 3     /* float32   [rows, 2, K, f_pad]   |z|, max(20 log10(max(|z|, p0)) - p1, p2)            */
+#define TAC_EPI_POWER 4     /* float32   [rows, K, f_pad]      |z|^p0                                               */
+#define TAC_EPI_LOGPOWER 5  /* float32   [rows, K, f_pad]      p1 * log10(|z|^p0 + p2)                              */
+#define TAC_EPI_DB 6        /* float32   [rows, K, f_pad]      max(20 log10(max(|z|, p0)) - p1, p2)   (p0 = amin,
+                                                               p1 = 20 log10(max(amin, ref)), p2 = floor in dB)     */
+#define TAC_EPI_MEL 7       /* float32   [rows, n_mels, f_pad] sum_k fb[k][m] |z_k|^p0 ; p1 != 0: p1 * log10(. + p2) */
+typedef struct tac_epilogue {
+    int kind;
+    float p0, p1, p2;
+    int n_mels;             /* TAC_EPI_MEL */
+    const float* mel_fb;    /* device [K][n_mels] float32 -- the layout of torchaudio.functional.melscale_fbanks */
+    const int* mel_range;   /* device [n_mels][2]: first and one-past-last frequency row of each filter that is non-zero */
+    unsigned* rowmax;       /* optional device [rows]: running maximum of |z| per row as float bits (atomicMax); the caller
+                               zero-fills it.  Kinds that form |z|: MAGPHASE, MAGDB, DB, POWER with p0 = 1. */
+} tac_epilogue;
+/*   x       [rows, T] float32;  window: 0 periodic Hann, 1 its square root (data_module.py:13-17), centred in n_fft when
+ *           win < n_fft;  center / pad_mode / normalized as for tac_stft_multi. */
+TAC_API int tac_stft_ex_supported(int n_fft);
+TAC_API int tac_stft_ex(const float* x, int64_t rows, int64_t T, int n_fft, int hop, int win, int window, int center,
+                        int pad_mode, int normalized, const tac_epilogue* epi, int64_t f_pad, void* out, tac_stream_t stream);
+/* out[rows, K, F] = max(20 log10(max(mag, amin)) - 20 log10(max(rowmax, amin)), -top_db): the second phase of
+ * librosa.amplitude_to_db(S, ref=np.max) when the row maxima came out of the STFT epilogue (tac_epilogue.rowmax). */
+TAC_API int tac_db_from_rowmax(const float* mag, int64_t rows, int64_t row_stride, int K, int F, int64_t ld, const unsigned* rowmax,
+                               float amin, float top_db, float* out, tac_stream_t stream);
+
 /* K2 -- fused multi-resolution STFT loss (no spectrogram is written to memory).
  * Definition of record (the reference holds no such function): per scale s, on the
  * msstftd.py:125-127 STFT convention, X = |STFT_s(x)|, Y = |STFT_s(y)|,

@@ -119,6 +119,7 @@ int tac_shutdown(void) {
     }
     tac::g_cache.clear();
     cudaSetDevice(cur);
+    tac::free_blu_tables();
     return TAC_OK;
 }
 

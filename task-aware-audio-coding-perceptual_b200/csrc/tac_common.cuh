@@ -52,6 +52,7 @@ inline bool supported_nfft(int n) {
 
 // Looks up (building on first use) the device tables of one FFT configuration on the current device.
 int get_tables(int n_fft, int win, int normalized, FftTables* out);
+void free_blu_tables();      // chirp-z tables of stft_ex.cu (tac_shutdown)
 
 inline int64_t num_frames(int64_t T, int n, int hop, int center) {
     int64_t Tp = T + (center ? 2 * (int64_t)(n / 2) : 0);

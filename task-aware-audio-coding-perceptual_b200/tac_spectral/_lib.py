@@ -28,7 +28,14 @@ class XchgStruct(C.Structure):
     _fields_ = [("world", C.c_int), ("rank", C.c_int), ("payload", C.c_int64), ("peer", C.c_void_p * XCHG_MAX_WORLD)]
 
 
+class EpilogueStruct(C.Structure):
+    """``tac_epilogue`` of include/tac_spectral.h (host struct, passed by pointer)."""
+    _fields_ = [("kind", C.c_int), ("p0", C.c_float), ("p1", C.c_float), ("p2", C.c_float), ("n_mels", C.c_int),
+                ("mel_fb", C.c_void_p), ("mel_range", C.c_void_p), ("rowmax", C.c_void_p)]
+
+
 _XP = C.POINTER(XchgStruct)
+_EP = C.POINTER(EpilogueStruct)
 _UBP = C.POINTER(C.c_ubyte)
 SIGNATURES = {
     "tac_last_error": (C.c_char_p, []),
@@ -38,6 +45,9 @@ SIGNATURES = {
     "tac_shutdown": (_I, []),
     "tac_stft_num_frames": (_I64, [_I64, _I, _I, _I]),
     "tac_stft_multi": (_I, [_VP, _I64, _I64, _I64, _I, _IP, _IP, _IP, _I, _I, _I, _I, _I64, _VPP, _VP]),
+    "tac_stft_ex_supported": (_I, [_I]),
+    "tac_stft_ex": (_I, [_VP, _I64, _I64, _I, _I, _I, _I, _I, _I, _I, _EP, _I64, _VP, _VP]),
+    "tac_db_from_rowmax": (_I, [_VP, _I64, _I64, _I, _I, _I64, _VP, _F, _F, _VP, _VP]),
     "tac_mrstft_workspace_bytes": (_SZ, [_I64, _I64, _I, _IP, _IP]),
     "tac_mrstft_loss_fwd": (_I, [_VP, _VP, _I64, _I64, _I, _IP, _IP, _IP, _F, _VP, _VP, _SZ, _VP]),
     "tac_mrstft_loss_bwd": (_I, [_VP, _VP, _I64, _I64, _I, _IP, _IP, _IP, _F, _VP, _VP, _VP, _SZ, _VP]),
@@ -75,6 +85,8 @@ SIGNATURES = {
 
 PAD_ZERO, PAD_REFLECT = 0, 1
 OUT_COMPLEX, OUT_PLANES, OUT_MAGPHASE = 0, 1, 2
+EPI_COMPLEX, EPI_COMPRESS, EPI_MAGPHASE, EPI_MAGDB, EPI_POWER, EPI_LOGPOWER, EPI_DB, EPI_MEL = range(8)
+WINDOW_HANN, WINDOW_SQRT_HANN = 0, 1
 GRAM_TF32X3, GRAM_FP64 = 0, 1
 IN_POLAR, IN_PLANES, IN_COMPLEX = 0, 1, 2
 

@@ -13,6 +13,8 @@
 """
 from __future__ import annotations
 
+import ctypes as C
+import math
 from typing import Callable, Dict, List, Optional, Sequence
 
 import torch
@@ -39,6 +41,95 @@ def _check_window(window_fn: Callable, wkwargs) -> None:
     # same error class the reference raises for an unsupported window (train_pkl_file_task_aware.py:190-191)
     if window_fn is not torch.hann_window or (wkwargs and wkwargs.get("periodic", True) is not True):
         raise ValueError("Unsupported window: only the periodic torch.hann_window is implemented")
+
+
+def ex_supported(n_fft: int) -> bool:
+    """Frame lengths ``tac_stft_ex`` accepts (warp FFT core or chirp-z)."""
+    n = int(n_fft)
+    return n >= 8 and n + n // 2 <= 4096
+
+
+_EX_PLANES = {L.EPI_COMPLEX: None, L.EPI_COMPRESS: None, L.EPI_MAGPHASE: 2, L.EPI_MAGDB: 2, L.EPI_POWER: 1,
+              L.EPI_LOGPOWER: 1, L.EPI_DB: 1}
+
+
+def stft_ex(x: torch.Tensor, n_fft: int, hop: int, win: Optional[int] = None, *, window: str = "hann", center: bool = True,
+            pad_mode: Optional[str] = "reflect", normalized: bool = False, kind: int = L.EPI_COMPLEX, p0: float = 0.0,
+            p1: float = 0.0, p2: float = 0.0, f_pad: int = 0, mel: Optional["MelBank"] = None,
+            rowmax: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """One scale of ``x [rows, T]`` through ``tac_stft_ex`` (any ``n_fft``; epilogue ``kind`` of include/tac_spectral.h).
+    Returns complex64 ``[rows, K, f_pad]``, float32 ``[rows, 2, K, f_pad]`` / ``[rows, K, f_pad]`` or ``[rows, n_mels, f_pad]``."""
+    L.require_cuda(x, "x")
+    if x.dim() != 2:
+        raise ValueError(f"expected x of shape [rows, T], got {tuple(x.shape)}")
+    if window not in ("hann", "sqrthann"):
+        raise NotImplementedError(f"Window type {window} not implemented!")           # data_module.py:19
+    x = x.contiguous().float()
+    rows, T = x.shape
+    n_fft, hop = int(n_fft), int(hop)
+    win = n_fft if win is None else int(win)
+    F = (T + (2 * (n_fft // 2) if center else 0) - n_fft) // hop + 1 if T + (2 * (n_fft // 2) if center else 0) >= n_fft else 0
+    if F < 1:
+        raise ValueError(f"signal of {T} samples is shorter than n_fft={n_fft}")
+    K, Fp = n_fft // 2 + 1, int(f_pad) if f_pad else F
+    ep = L.EpilogueStruct()
+    ep.kind, ep.p0, ep.p1, ep.p2 = int(kind), float(p0), float(p1), float(p2)
+    if kind == L.EPI_MEL:
+        if mel is None or mel.n_freqs != K:
+            raise ValueError(f"the mel epilogue needs a MelBank with n_freqs={K}")
+        fb, rng = mel.on(x.device)
+        ep.n_mels, ep.mel_fb, ep.mel_range = mel.n_mels, fb.data_ptr(), rng.data_ptr()
+        out = torch.empty((rows, mel.n_mels, Fp), dtype=torch.float32, device=x.device)
+    elif _EX_PLANES[kind] is None:
+        out = torch.empty((rows, K, Fp), dtype=torch.complex64, device=x.device)
+    elif _EX_PLANES[kind] == 2:
+        out = torch.empty((rows, 2, K, Fp), dtype=torch.float32, device=x.device)
+    else:
+        out = torch.empty((rows, K, Fp), dtype=torch.float32, device=x.device)
+    if rowmax is not None:
+        if rowmax.dtype != torch.int32 or rowmax.numel() != rows or not rowmax.is_cuda:
+            raise ValueError("rowmax must be a zero-filled CUDA int32 tensor of `rows` elements")
+        ep.rowmax = rowmax.data_ptr()
+    with L.device_of(x):
+        L.check(L.lib().tac_stft_ex(x.data_ptr(), rows, T, n_fft, hop, win, L.WINDOW_SQRT_HANN if window == "sqrthann" else L.WINDOW_HANN,
+                                    int(bool(center)), _pad_mode_code(pad_mode), int(bool(normalized)), C.byref(ep), Fp,
+                                    out.data_ptr(), L.stream_of(x)))
+    return out
+
+
+def _hz_to_mel(f: float) -> float:
+    return 2595.0 * math.log10(1.0 + f / 700.0)
+
+
+class MelBank:
+    """Triangular HTK mel filter bank ``[n_freqs, n_mels]`` -- the matrix ``torchaudio.functional.melscale_fbanks(n_freqs,
+    f_min, f_max, n_mels, sample_rate, norm=None, mel_scale='htk')`` defines -- generated on the host in
+    float64, plus each filter's non-zero row range for the kernel."""
+
+    def __init__(self, n_freqs: int, f_min: float = 0.0, f_max: float = 8000.0, n_mels: int = 80, sample_rate: int = 16000):
+        self.n_freqs, self.n_mels = int(n_freqs), int(n_mels)
+        freqs = [i * (sample_rate // 2) / (self.n_freqs - 1) for i in range(self.n_freqs)]
+        m_lo, m_hi = _hz_to_mel(f_min), _hz_to_mel(f_max)
+        pts = [700.0 * (10.0 ** ((m_lo + (m_hi - m_lo) * i / (self.n_mels + 1)) / 2595.0) - 1.0) for i in range(self.n_mels + 2)]
+        fb = torch.zeros((self.n_freqs, self.n_mels), dtype=torch.float64)
+        rng = torch.zeros((self.n_mels, 2), dtype=torch.int32)
+        for m in range(self.n_mels):
+            lo, ce, hi = pts[m], pts[m + 1], pts[m + 2]
+            first, last = self.n_freqs, 0
+            for k, f in enumerate(freqs):
+                v = max(0.0, min((f - lo) / (ce - lo), (hi - f) / (hi - ce)))
+                if v > 0.0:
+                    fb[k, m] = v
+                    first, last = min(first, k), max(last, k + 1)
+            rng[m, 0], rng[m, 1] = (first, last) if last > first else (0, 0)
+        self.fb, self.range = fb.to(torch.float32), rng
+        self._dev = {}
+
+    def on(self, device):
+        key = str(device)
+        if key not in self._dev:
+            self._dev[key] = (self.fb.to(device).contiguous(), self.range.to(device).contiguous())
+        return self._dev[key]
 
 
 def stft_multi(x: torch.Tensor, n_ffts: Sequence[int], hops: Sequence[int], wins: Optional[Sequence[int]] = None, *,
@@ -174,10 +265,10 @@ class Spectrogram(nn.Module):
         self.win_length = int(win_length) if win_length is not None else self.n_fft
         self.hop_length = int(hop_length) if hop_length is not None else self.win_length // 2
         _check_window(window_fn, wkwargs)
-        if self.n_fft not in SUPPORTED_NFFT:
-            raise ValueError(f"n_fft={n_fft} unsupported; choose one of {SUPPORTED_NFFT}")
-        if power is not None:
-            raise NotImplementedError("only power=None (complex spectrogram, msstftd.py:127) is implemented")
+        if not ex_supported(self.n_fft):
+            raise ValueError(f"n_fft={n_fft} unsupported (8 <= n_fft, n_fft + n_fft // 2 <= 4096)")
+        if power is not None and not power > 0:
+            raise ValueError("power must be None (complex) or positive")
         if pad != 0 or not onesided:
             raise NotImplementedError("pad != 0 and onesided=False are not implemented")
         if normalized not in (False, True, "window"):
@@ -185,10 +276,11 @@ class Spectrogram(nn.Module):
         self.normalized = bool(normalized)
         self.center = bool(center)
         self.pad_mode = pad_mode
-        self.power = None
+        self.power = None if power is None else float(power)
         # torchaudio keeps the window as a buffer; kept so that state_dict()s stay interchangeable
         self.register_buffer("window", torch.hann_window(self.win_length), persistent=False)
-        if torch.cuda.is_available():
+        self._core = self.n_fft in SUPPORTED_NFFT and self.hop_length % 2 == 0      # the warp FFT core has a plan for it
+        if torch.cuda.is_available() and self._core:
             L.check(L.lib().tac_prepare_fft(self.n_fft, self.win_length, int(self.normalized)))
 
     def _run(self, x: torch.Tensor, out_mode: int) -> torch.Tensor:
@@ -198,10 +290,33 @@ class Spectrogram(nn.Module):
                          pad_mode=self.pad_mode, normalized=self.normalized, out_mode=out_mode)[0]
         return out, lead
 
-    def forward(self, waveform: torch.Tensor) -> torch.Tensor:
-        """``[..., T]`` -> complex64 ``[..., K, F]`` (what ``msstftd.py:151`` receives)."""
-        out, lead = self._run(waveform, L.OUT_COMPLEX)
+    def _ex(self, waveform: torch.Tensor, kind: int, p0: float = 0.0, p1: float = 0.0, p2: float = 0.0) -> torch.Tensor:
+        lead = waveform.shape[:-1]
+        out = stft_ex(waveform.reshape(-1, waveform.shape[-1]), self.n_fft, self.hop_length, self.win_length,
+                      center=self.center, pad_mode=self.pad_mode, normalized=self.normalized, kind=kind, p0=p0, p1=p1, p2=p2)
         return out.reshape(*lead, out.shape[-2], out.shape[-1])
+
+    def forward(self, waveform: torch.Tensor) -> torch.Tensor:
+        """``[..., T]`` -> complex64 ``[..., K, F]`` for ``power=None`` (what ``msstftd.py:151`` receives), else the
+        real ``|X|^power`` (``torchaudio.transforms.Spectrogram()`` of ``testing_scripts.ipynb:246``: n_fft 400, power 2)."""
+        needs_grad = torch.is_grad_enabled() and waveform.requires_grad
+        if self.power is None:
+            if self._core:
+                out, lead = self._run(waveform, L.OUT_COMPLEX)
+                return out.reshape(*lead, out.shape[-2], out.shape[-1])
+            if needs_grad:
+                raise NotImplementedError(f"the STFT backward is implemented for n_fft in {SUPPORTED_NFFT} only")
+            return self._ex(waveform, L.EPI_COMPLEX)
+        if needs_grad:                                   # differentiable like torchaudio's: |.|^p of the complex result
+            if not self._core:
+                raise NotImplementedError(f"the STFT backward is implemented for n_fft in {SUPPORTED_NFFT} only")
+            out, lead = self._run(waveform, L.OUT_COMPLEX)
+            return out.reshape(*lead, out.shape[-2], out.shape[-1]).abs().pow(self.power)
+        return self._ex(waveform, L.EPI_POWER, self.power)
+
+    def log_power(self, waveform: torch.Tensor, multiplier: float = 10.0, eps: float = 1e-10) -> torch.Tensor:
+        """``multiplier * log10(Spectrogram(power)(x) + eps)`` in the same kernel (``testing_scripts.ipynb:246-249``)."""
+        return self._ex(waveform, L.EPI_LOGPOWER, 2.0 if self.power is None else self.power, float(multiplier), float(eps))
 
     def planes(self, x: torch.Tensor) -> torch.Tensor:
         """``[B, C, T]`` -> float32 ``[B, 2C, F, K]``: ``msstftd.py:151-153`` fused (no complex
@@ -243,21 +358,116 @@ def complex_spectrogram(y: torch.Tensor, n_fft: int = 2048, hop_length: int = 51
     L.require_cuda(y, "y")
     if y.dim() != 2:
         raise ValueError(f"expected y of shape [B, T], got {tuple(y.shape)}")
+    if n_fft not in SUPPORTED_NFFT or hop_length % 2:
+        # the dB-channel variant of the notebook frames with n_fft = win_length = 2046 (cell 9, raw :2897-2901): chirp-z path
+        if torch.is_grad_enabled() and y.requires_grad:
+            raise NotImplementedError(f"the STFT backward is implemented for n_fft in {SUPPORTED_NFFT} only")
+        return stft_ex(y, n_fft, hop_length, win_length, center=True, pad_mode=pad_mode, normalized=False,
+                       kind=L.EPI_MAGPHASE, f_pad=int(f_pad or 0))
     return stft_multi(y[:, None, :], [n_fft], [hop_length], [win_length], center=True, pad_mode=pad_mode,
                       normalized=False, out_mode=L.OUT_MAGPHASE, f_pad=int(f_pad or 0))[0]
 
 
 def create_complex_spectrogram(y: torch.Tensor, sr: int, n_fft: int = 2048, hop_length: int = 512,
-                               win_length: int = 2048) -> Dict[str, object]:
+                               win_length: int = 2048, db_scale: bool = False) -> Dict[str, object]:
     """Same name, argument meaning and result keys as the notebook function (cell 10 L26-52):
-    ``{'magnitude', 'phase', 'params'}`` for one utterance ``y [T]`` (or a batch ``[B, T]``)."""
+    ``{'magnitude', 'phase', 'params'}`` for one utterance ``y [T]`` (or a batch ``[B, T]``).  ``db_scale=True`` is the
+    cell 9 variant (raw ``:2894-2913``; it frames with ``n_fft = win_length = 2046``) and adds
+    ``'db_scale' = librosa.amplitude_to_db(magnitude, ref=np.max)``: the per-utterance maximum leaves the STFT kernel with
+    the magnitude plane, so the dB pass reads that plane once."""
     single = y.dim() == 1
-    out = complex_spectrogram(y[None] if single else y, n_fft, hop_length, win_length)
+    yb = y[None] if single else y
+    out_d = {}
+    if db_scale:
+        L.require_cuda(yb, "y")
+        rowmax = torch.zeros(yb.shape[0], dtype=torch.int32, device=yb.device)
+        out = stft_ex(yb, n_fft, hop_length, win_length, center=True, pad_mode="constant", normalized=False,
+                      kind=L.EPI_MAGPHASE, rowmax=rowmax)
+        B, _, K, F = out.shape
+        db = torch.empty((B, K, F), dtype=torch.float32, device=out.device)
+        with L.device_of(out):
+            L.check(L.lib().tac_db_from_rowmax(out.data_ptr(), B, 2 * K * F, K, F, F, rowmax.data_ptr(), 1e-5, 80.0,
+                                               db.data_ptr(), L.stream_of(out)))
+        out_d["db_scale"] = db[0] if single else db
+    else:
+        out = complex_spectrogram(yb, n_fft, hop_length, win_length)
     mag, ph = out[:, 0], out[:, 1]
     if single:
         mag, ph = mag[0], ph[0]
-    return {"magnitude": mag, "phase": ph,
+    return {"magnitude": mag, "phase": ph, **out_d,
             "params": {"sr": sr, "n_fft": n_fft, "hop_length": hop_length, "win_length": win_length, "window": "hann"}}
+
+
+class MelSpectrogram(nn.Module):
+    """``torchaudio.transforms.MelSpectrogram``-shaped module for the north star's mel alternative (SURVEY.md 8c item 5;
+    the reference itself has no mel path): framing, window, FFT, ``|X|^power`` and the HTK filter bank in ONE kernel,
+    ``[..., T]`` -> ``[..., n_mels, F]``.  ``log_mel`` adds ``multiplier * log10(mel + eps)`` in the same pass."""
+
+    def __init__(self, sample_rate: int = 16000, n_fft: int = 400, win_length: Optional[int] = None,
+                 hop_length: Optional[int] = None, f_min: float = 0.0, f_max: Optional[float] = None, pad: int = 0,
+                 n_mels: int = 128, window_fn: Callable = torch.hann_window, power: float = 2.0, normalized: bool = False,
+                 wkwargs: Optional[dict] = None, center: bool = True, pad_mode: str = "reflect", onesided: Optional[bool] = None,
+                 norm: Optional[str] = None, mel_scale: str = "htk"):
+        super().__init__()
+        _check_window(window_fn, wkwargs)
+        if norm is not None or mel_scale != "htk" or pad != 0:
+            raise NotImplementedError("only norm=None, mel_scale='htk', pad=0 are implemented")
+        if not ex_supported(n_fft):
+            raise ValueError(f"n_fft={n_fft} unsupported (8 <= n_fft, n_fft + n_fft // 2 <= 4096)")
+        self.n_fft = int(n_fft)
+        self.win_length = int(win_length) if win_length is not None else self.n_fft
+        self.hop_length = int(hop_length) if hop_length is not None else self.win_length // 2
+        self.power, self.normalized, self.center, self.pad_mode = float(power), bool(normalized), bool(center), pad_mode
+        self.bank = MelBank(self.n_fft // 2 + 1, f_min, float(f_max if f_max is not None else sample_rate // 2), n_mels, sample_rate)
+
+    def _run(self, waveform, p1, p2):
+        lead = waveform.shape[:-1]
+        out = stft_ex(waveform.reshape(-1, waveform.shape[-1]), self.n_fft, self.hop_length, self.win_length, center=self.center,
+                      pad_mode=self.pad_mode, normalized=self.normalized, kind=L.EPI_MEL, p0=self.power, p1=p1, p2=p2, mel=self.bank)
+        return out.reshape(*lead, out.shape[-2], out.shape[-1])
+
+    def forward(self, waveform: torch.Tensor) -> torch.Tensor:
+        return self._run(waveform, 0.0, 0.0)
+
+    def log_mel(self, waveform: torch.Tensor, multiplier: float = 10.0, eps: float = 1e-10) -> torch.Tensor:
+        return self._run(waveform, float(multiplier), float(eps))
+
+
+class SpecsFrontEnd(nn.Module):
+    """The SGMSE+ enhancer's spectrogram front end: ``SpecsDataModule.stft`` + ``spec_fwd``
+    (``sgmse/sgmse/data_module.py:162-175,212-214``; defaults ``:109-118``: n_fft 510, hop 128, periodic Hann,
+    ``abs(z)**0.5 * exp(1j * angle(z)) * 0.15``) and ``pad_spec`` (``sgmse/sgmse/util/other.py:76-90``, frames zero-padded to a
+    multiple of 64) as ONE kernel.  Same constructor keywords as the data module."""
+
+    def __init__(self, n_fft: int = 510, hop_length: int = 128, window: str = "hann", spec_factor: float = 0.15,
+                 spec_abs_exponent: float = 0.5, transform_type: str = "exponent", **ignored):
+        super().__init__()
+        if window not in ("hann", "sqrthann"):
+            raise NotImplementedError(f"Window type {window} not implemented!")       # data_module.py:19
+        if transform_type not in ("exponent", "none"):
+            raise NotImplementedError(f"transform_type {transform_type!r}: only 'exponent' and 'none' are implemented")
+        self.n_fft, self.hop_length, self.window = int(n_fft), int(hop_length), window
+        self.spec_factor, self.spec_abs_exponent, self.transform_type = float(spec_factor), float(spec_abs_exponent), transform_type
+
+    def stft(self, sig: torch.Tensor) -> torch.Tensor:
+        """``torch.stft(sig, n_fft, hop, window, center=True, return_complex=True)`` (data_module.py:212-214)."""
+        lead = sig.shape[:-1]
+        out = stft_ex(sig.reshape(-1, sig.shape[-1]), self.n_fft, self.hop_length, self.n_fft, window=self.window, center=True,
+                      pad_mode="reflect", kind=L.EPI_COMPLEX)
+        return out.reshape(*lead, out.shape[-2], out.shape[-1])
+
+    def forward(self, sig: torch.Tensor, pad64: bool = True) -> torch.Tensor:
+        """``pad_spec(spec_fwd(stft(sig)))``: ``[..., T]`` -> complex64 ``[..., n_fft/2+1, ceil64(F)]``."""
+        lead, T = sig.shape[:-1], sig.shape[-1]
+        F = T // self.hop_length + 1
+        f_pad = (F + 63) // 64 * 64 if pad64 else F
+        if self.transform_type == "none":
+            kind, p0, p1 = L.EPI_COMPLEX, 0.0, 0.0
+        else:
+            kind, p0, p1 = L.EPI_COMPRESS, self.spec_abs_exponent, self.spec_factor
+        out = stft_ex(sig.reshape(-1, T), self.n_fft, self.hop_length, self.n_fft, window=self.window, center=True,
+                      pad_mode="reflect", kind=kind, p0=p0, p1=p1, f_pad=f_pad)
+        return out.reshape(*lead, out.shape[-2], out.shape[-1])
 
 
 def amplitude_to_db(spec: torch.Tensor, n_frames: Optional[int] = None, amin: float = 1e-5, top_db: float = 80.0) -> torch.Tensor:

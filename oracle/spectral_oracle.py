@@ -164,6 +164,65 @@ def amplitude_to_db_ref(mag: torch.Tensor, amin: float = 1e-5, top_db: float = 8
     return torch.maximum(db, db.amax(dim=(-2, -1), keepdim=True) - top_db)
 
 
+def torch_stft_ref(x: torch.Tensor, n_fft: int, hop: int, win: int | None = None, *, window: str = "hann", center: bool = True,
+                   pad_mode: str = "reflect", normalized: bool = False) -> torch.Tensor:
+    """``torch.stft`` for ANY ``n_fft`` -- the library call behind ``librosa.stft(n_fft=2046, ...)`` (``spectrogram.ipynb`` cell 9,
+    raw ``:2897-2906``), ``SpecsDataModule.stft`` (``sgmse/sgmse/data_module.py:212-214``; window per ``:13-17``) and
+    ``torchaudio.transforms.Spectrogram()`` (``testing_scripts.ipynb:246``).  ``normalized`` is torchaudio's 'window' form."""
+    win = n_fft if win is None else win
+    w = hann_periodic(win)
+    if window == "sqrthann":
+        w = torch.sqrt(w)
+    lead = x.shape[:-1]
+    out = torch.stft(x.reshape(-1, x.shape[-1]).float(), n_fft, hop, win, w, center=center, pad_mode=pad_mode, normalized=False,
+                     onesided=True, return_complex=True)
+    if normalized:
+        out = out / w.pow(2).sum().sqrt()
+    return out.reshape(*lead, out.shape[-2], out.shape[-1])
+
+
+def sgmse_spec_ref(sig: torch.Tensor, n_fft: int = 510, hop: int = 128, window: str = "hann", spec_factor: float = 0.15,
+                   spec_abs_exponent: float = 0.5, pad64: bool = True) -> torch.Tensor:
+    """``pad_spec(spec_fwd(stft(sig)))`` of the SGMSE+ enhancer: ``sgmse/sgmse/data_module.py:212-214`` (centred reflect-padded
+    ``torch.stft``), ``:162-169`` (``spec.abs()**e * exp(1j * spec.angle())`` then ``* spec_factor``; defaults ``:109-118``) and
+    ``sgmse/sgmse/util/other.py:76-90`` (zero-pad the frame axis to a multiple of 64)."""
+    spec = torch_stft_ref(sig, n_fft, hop, n_fft, window=window, center=True, pad_mode="reflect")
+    if spec_abs_exponent != 1:
+        spec = spec.abs() ** spec_abs_exponent * torch.exp(1j * spec.angle())
+    spec = spec * spec_factor
+    if pad64:
+        F = spec.shape[-1]
+        if F % 64 != 0:
+            spec = torch.nn.functional.pad(spec, (0, 64 - F % 64))
+    return spec
+
+
+def power_spectrogram_ref(x: torch.Tensor, log: bool = False, **kwargs) -> torch.Tensor:
+    """``torchaudio.transforms.Spectrogram(**kwargs)(x)`` (``testing_scripts.ipynb:246``: all defaults -- n_fft 400, hop 200,
+    power 2, centred, reflect); ``log``: ``10 * torch.log10(S + 1e-10)`` (``:249``)."""
+    import torchaudio
+    S = torchaudio.transforms.Spectrogram(**kwargs)(x.float())
+    return 10.0 * torch.log10(S + 1e-10) if log else S
+
+
+def mel_spectrogram_ref(x: torch.Tensor, n_fft: int, hop: int, n_mels: int = 80, f_min: float = 0.0, f_max: float = 8000.0,
+                        sample_rate: int = 16000, power: float = 1.0, center: bool = False, normalized: bool = True) -> torch.Tensor:
+    """SURVEY.md 8c item 5 (no mel path exists in the reference; definition of record): the magnitude spectrogram of the
+    ``msstftd.py:125-127`` convention times ``torchaudio.functional.melscale_fbanks(K, f_min, f_max, n_mels, sample_rate,
+    norm=None, mel_scale='htk')``."""
+    import torchaudio
+    S = torch_stft_ref(x, n_fft, hop, n_fft, center=center, normalized=normalized).abs() ** power          # [..., K, F]
+    fb = torchaudio.functional.melscale_fbanks(n_fft // 2 + 1, f_min, f_max, n_mels, sample_rate, norm=None, mel_scale="htk")
+    return torch.matmul(S.transpose(-1, -2), fb).transpose(-1, -2)
+
+
+def amplitude_to_db_fixed_ref(mag: torch.Tensor, ref: float = 1.0, amin: float = 1e-5, floor_db: float = -80.0) -> torch.Tensor:
+    """``20 log10(max(S, amin)) - 20 log10(max(amin, ref))`` floored at ``floor_db`` (``librosa.amplitude_to_db`` with a
+    fixed reference; with ``ref`` = the array maximum this is the ``ref=np.max`` form of the notebook)."""
+    db = 20.0 * torch.log10(torch.clamp(mag, min=amin)) - 20.0 * math.log10(max(amin, ref))
+    return torch.clamp(db, min=floor_db)
+
+
 # --------------------------------------------------------------------------------------------
 # Losses
 # --------------------------------------------------------------------------------------------

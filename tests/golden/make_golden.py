@@ -16,6 +16,8 @@ feeds them seeded inputs and stores inputs + outputs:
   decoder replaced by pass-through stubs (so the latents are the seeded inputs and the tensor handed
   to the decoder is captured).
 * ``spec_losses.npz`` -- the loss dictionary / spectral SNR of ``ResE2D1.forward`` (``:520-540``).
+* ``sgmse_spec.npz``  -- the SGMSE+ front end ``pad_spec(spec_fwd(stft(sig)))`` (``sgmse/sgmse/data_module.py:162-175,212-214``,
+  ``sgmse/sgmse/util/other.py:76-90``), the three functions compiled from the reference source with ``ast``.
 * ``var_topk.npz``    -- variance top-k of ``pkl_file_models.py:901-907`` through
   ``SpectralResE1D1.forward`` with stubbed encoder / decoder.
 """
@@ -220,6 +222,41 @@ def gen_cosine():
     np.savez_compressed(os.path.join(HERE, "cosine.npz"), **out)
 
 
+def _reference_method(path, cls, name):
+    """Like ``_reference_function`` for ONE method of a class in a module that cannot be imported (``sgmse.data_module``
+    needs pytorch_lightning): the method's source is read from the reference at generation time and compiled as a plain
+    function taking ``self``."""
+    import ast
+    import textwrap
+    src = open(os.path.join(REF, path)).read()
+    cnode = next(n for n in ast.parse(src).body if isinstance(n, ast.ClassDef) and n.name == cls)
+    node = next(n for n in cnode.body if isinstance(n, ast.FunctionDef) and n.name == name)
+    text = textwrap.dedent(ast.get_source_segment(src, node, padded=True))
+    ns = {"torch": torch, "np": np}
+    exec(compile(text, f"{path}:{cls}.{name}", "exec"), ns)
+    return ns[name]
+
+
+def gen_sgmse():
+    """The SGMSE+ front end: ``SpecsDataModule.stft`` / ``spec_fwd`` (``sgmse/sgmse/data_module.py:162-175,212-214``) with the
+    module's default hyper-parameters (``:109-118,123-125``), the window of ``get_window`` (``:13-17``), then ``pad_spec``
+    (``sgmse/sgmse/util/other.py:76-90``) on the ``[B, 1, K, F]`` tensor as ``sgmse/test_single.py:148-149`` does."""
+    import types
+    dm = "sgmse/sgmse/data_module.py"
+    get_window = _reference_function(dm, "get_window")
+    self = types.SimpleNamespace(n_fft=510, hop_length=128, window=get_window("hann", 510), windows={}, spec_factor=0.15,
+                                 spec_abs_exponent=0.5, transform_type="exponent")
+    for name in ("spec_fwd", "_get_window", "stft"):
+        setattr(self, name, types.MethodType(_reference_method(dm, "SpecsDataModule", name), self))
+    self.stft_kwargs = {"n_fft": 510, "hop_length": 128, "window": self.window, "center": True, "return_complex": True}   # :192-199
+    pad_spec = _reference_function("sgmse/sgmse/util/other.py", "pad_spec")
+    g = torch.Generator().manual_seed(510)
+    sig = torch.randn(2, 6000, generator=g) * 0.1 + 0.05 * torch.sin(torch.arange(6000) * 0.05)[None]
+    Y = self.spec_fwd(self.stft(sig))                                  # [2, 256, 47]
+    Yp = pad_spec(Y.unsqueeze(1))                                      # [2, 1, 256, 64]
+    np.savez_compressed(os.path.join(HERE, "sgmse_spec.npz"), sig=sig.numpy(), F=np.array(Y.shape[-1]), Yp=Yp.squeeze(1).numpy())
+
+
 if __name__ == "__main__":
     gen_stft()
     gen_dpca()
@@ -227,6 +264,7 @@ if __name__ == "__main__":
     gen_var_topk()
     gen_istft()
     gen_cosine()
+    gen_sgmse()
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)))

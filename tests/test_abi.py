@@ -59,11 +59,18 @@ def test_no_cpu_fallback(ts):
 
 def test_constructor_validation(ts):
     with pytest.raises(ValueError):
-        ts.Spectrogram(n_fft=1000, power=None)
+        ts.Spectrogram(n_fft=4000, power=None)                      # beyond the chirp-z path (n + n/2 <= 4096)
     with pytest.raises(ValueError):
         ts.Spectrogram(n_fft=512, window_fn=torch.hamming_window, power=None)
+    with pytest.raises(ValueError):
+        ts.Spectrogram(n_fft=512, power=-1.0)
+    sp = ts.Spectrogram()                                            # testing_scripts.ipynb:246: torchaudio's defaults
+    assert (sp.n_fft, sp.hop_length, sp.win_length, sp.power, sp.center) == (400, 200, 400, 2.0, True)
+    assert ts.ex_supported(2046) and ts.ex_supported(510) and ts.ex_supported(400) and not ts.ex_supported(4096)
     with pytest.raises(NotImplementedError):
-        ts.Spectrogram(n_fft=512, power=2.0)
+        ts.SpecsFrontEnd(window="hamming")                           # data_module.py:19
+    fe = ts.SpecsFrontEnd()                                          # data_module.py:109-118 defaults
+    assert (fe.n_fft, fe.hop_length, fe.spec_factor, fe.spec_abs_exponent) == (510, 128, 0.15, 0.5)
     with pytest.raises(AssertionError):
         ts.MultiScaleSTFT([512, 1024], [128], [512, 1024])          # msstftd.py:177
     sp = ts.Spectrogram(n_fft=1024, hop_length=256, win_length=1024, window_fn=torch.hann_window, normalized=True,

@@ -166,3 +166,31 @@ def test_cosine_loss_matches_reference(golden_dir):
     zs = [torch.from_numpy(g[f"c4_z{i + 1}"]) for i in range(4)]
     assert torch.allclose(O.pairwise_cosine_loss_ref(zs), torch.from_numpy(g["c4_cos"]), rtol=1e-6, atol=1e-7)
     assert torch.allclose(O.pairwise_cosine_loss_ref(zs[:2]), torch.from_numpy(g["c2_cos"]), rtol=1e-6, atol=1e-7)
+
+
+def test_sgmse_front_end_matches_reference(golden_dir):
+    # sgmse/sgmse/data_module.py:162-175,212-214 + util/other.py:76-90, compiled from the reference by make_golden.gen_sgmse
+    g = _load(golden_dir, "sgmse_spec.npz")
+    got = O.sgmse_spec_ref(torch.from_numpy(g["sig"]))
+    assert got.shape == g["Yp"].shape == (2, 256, 64) and int(g["F"]) == 6000 // 128 + 1
+    assert np.array_equal(got.numpy(), g["Yp"])                       # same torch calls -> bit-equal
+    assert np.all(g["Yp"][..., int(g["F"]):] == 0)
+
+
+@pytest.mark.parametrize("n,h", [(2046, 512), (510, 128), (400, 200)])
+def test_any_nfft_stft_against_direct_dft(n, h):
+    # the non-power-of-two frame lengths of spectrogram.ipynb:2897-2901, data_module.py:109-110 and torchaudio's default
+    torch.manual_seed(5)
+    x = torch.randn(2, 2 * n + 123)
+    z = O.torch_stft_ref(x, n, h, n, center=False).numpy()
+    ref = O.dft_frames_f64(x.numpy(), n, h, normalized=False)
+    assert np.abs(z - ref).max() <= 2e-6 * np.abs(ref).max()
+
+
+def test_power_and_mel_refs_shapes():
+    x = torch.randn(2, 4000)
+    S = O.power_spectrogram_ref(x)
+    assert S.shape == (2, 201, 21) and float(S.min()) >= 0.0          # torchaudio defaults: n_fft 400, hop 200, centred
+    assert torch.allclose(O.power_spectrogram_ref(x, log=True), 10 * torch.log10(S + 1e-10))
+    M = O.mel_spectrogram_ref(x, 1024, 256)
+    assert M.shape == (2, 80, 1 + (4000 - 1024) // 256)

@@ -275,6 +275,37 @@ TAC_API int tac_cosine_pairs_fwd(const float* const* z, int nv, int64_t B, int d
 TAC_API int tac_cosine_pairs_bwd(const float* const* z, int nv, int64_t B, int d, float eps, const float* gscale, float scale,
                          float* const* grad_z, tac_stream_t stream);
 
+/* ---- the bottleneck that is live in the SpectralRes models ----------------------------------------
+ * Replaces the split / alpha-mix / truncate / cat block of pkl_file_models.py:1108-1127 (SpectralResE2D2), :692-718
+ * (SpectralResE4D1) and :335-354 (SpectralResE2D1): view i's latent z[i] [B, d] is split at column `split` into a private
+ * and a shared part; with alpha[p] != NULL (random_bottle_neck) the shared parts of the view pair (2p, 2p+1) are replaced
+ * by alpha[p][b] * share_{2p} + (1 - alpha[p][b]) * share_{2p+1}; both parts are cut to `trunc` columns and concatenated:
+ *   out [B, nv * w],  w = tac_bottleneck_width(d, split, trunc) = min(trunc, min(split, d)) + min(trunc, max(d - split, 0)),
+ * view i in columns [i w, (i+1) w).  (E4D1 passes split = sum of all views' widths (:633, :692-695), which makes the shared
+ * part empty -- reproduced as is.)  alpha: host array of (nv+1)/2 device pointers to [B] float32, or NULL.
+ * tac_bottleneck_mix_bwd is the adjoint: grad_z[i] [B, d] is fully written (zeros outside the kept columns). */
+TAC_API int tac_bottleneck_width(int d, int split, int trunc);
+TAC_API int tac_bottleneck_mix(const float* const* z, int nv, int64_t B, int d, int split, int trunc, const float* const* alpha,
+                               float* out, tac_stream_t stream);
+TAC_API int tac_bottleneck_mix_bwd(const float* grad_out, int nv, int64_t B, int d, int split, int trunc, const float* const* alpha,
+                                   float* const* grad_z, tac_stream_t stream);
+
+/* ---- the loss tail of task_aware() -- train_pkl_file_task_aware.py:307-364 -----------------------
+ * tac_interp_mse: F.mse_loss(a, F.interpolate(b, size=La, mode='linear', align_corners=False)) when Lb < La (and with the
+ * roles swapped when La < Lb; plain MSE when equal) -- :311-333 -- without materialising the resampled waveform.
+ *   a [B, La], b [B, Lb] float32;  out[0] float64;  workspace tac_interp_mse_workspace_bytes() bytes.
+ * tac_multi_reduce: out[0] = sum_s mean_s, out[1 + s] = mean_s over nseg <= 48 tensor pairs of any sizes, with
+ *   mode[s] = 0: mean |a_s - b_s|  (F.l1_loss of the feature-map pairs, :352-354)
+ *             1: mean (a_s - b_s)^2
+ *             2: mean (a_s - c[s])^2  (F.mse_loss(y, ones_like / zeros_like), :357-359; b_s ignored)
+ * a, b: host arrays of device pointers; n, mode, c: host arrays.  Deterministic (fixed-order float64 partials). */
+TAC_API size_t tac_interp_mse_workspace_bytes(void);
+TAC_API int tac_interp_mse(const float* a, int64_t La, const float* b, int64_t Lb, int64_t B, double* out, void* workspace,
+                           size_t workspace_bytes, tac_stream_t stream);
+TAC_API size_t tac_multi_reduce_workspace_bytes(int nseg, const int64_t* n);
+TAC_API int tac_multi_reduce(int nseg, const float* const* a, const float* const* b, const int64_t* n, const int* mode, const float* c,
+                             double* out, void* workspace, size_t workspace_bytes, tac_stream_t stream);
+
 /* ---- multi-GPU exchange: one-shot sum over NVLink peer memory ------------------------------------------
  * Replaces the packed ncclAllReduce(sum) of [loss sums | per view n, sum z, sum z z^T] that SURVEY.md 8e prescribes for
  * the batch-sharded form of train_pkl_file_task_aware.py:597-629 / pkl_file_model_updated.py:489-511 (the reference

@@ -375,6 +375,52 @@ def batch_reconstruct_waveform_ref(magnitude_batch: torch.Tensor, phase_batch: t
     return torch.stack(items, dim=0)
 
 
+# --------------------------------------------------------------------------------------------
+# The bottleneck that is live in the SpectralRes models (row a9) and the task_aware() loss tail (row a5-i)
+# --------------------------------------------------------------------------------------------
+
+def bottleneck_mix_ref(zs: Sequence[torch.Tensor], split: int, trunc: int,
+                       alphas: Sequence[torch.Tensor | None] | None = None) -> List[torch.Tensor]:
+    """``pkl_file_models.py:1108-1123`` (E2D2; the same statements at ``:335-347`` E2D1 and ``:692-711`` E4D1): private /
+    shared split at column ``split``, per-row alpha mix of the shared parts of the view pairs (1,2), (3,4), truncation of both
+    parts to ``trunc`` columns, concatenation.  Returns one ``z_i_sample`` per view."""
+    priv = [z[:, :split] for z in zs]
+    share = [z[:, split:] for z in zs]
+    if alphas is not None:
+        for p, a in enumerate(alphas):
+            if a is not None and 2 * p + 1 < len(zs):
+                mixed = a.reshape(-1, 1) * share[2 * p] + (1 - a.reshape(-1, 1)) * share[2 * p + 1]
+                share[2 * p] = share[2 * p + 1] = mixed
+    return [torch.cat((pv[:, :trunc], sh[:, :trunc]), dim=1) for pv, sh in zip(priv, share)]
+
+
+def interp_mse_ref(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """``train_pkl_file_task_aware.py:312-333``: the shorter of two ``[B, L]`` waveforms is resampled with
+    ``F.interpolate(x.unsqueeze(1), size=longer, mode='linear', align_corners=False)``, then ``F.mse_loss``."""
+    import torch.nn.functional as F
+    a, b = a.float(), b.float()
+    if a.shape[-1] < b.shape[-1]:
+        a = F.interpolate(a.unsqueeze(1), size=b.shape[-1], mode="linear", align_corners=False).squeeze(1)
+    elif b.shape[-1] < a.shape[-1]:
+        b = F.interpolate(b.unsqueeze(1), size=a.shape[-1], mode="linear", align_corners=False).squeeze(1)
+    return F.mse_loss(a, b, reduction="mean")
+
+
+def task_aware_tail_ref(enhanced_audio: torch.Tensor, clean: torch.Tensor, disc_enhanced, disc_ground_truth):
+    """``train_pkl_file_task_aware.py:333,352-361`` with the discriminator's results passed in: waveform MSE, then
+    ``sum F.l1_loss(feat_enh, feat_gt)`` over all feature maps ``+ F.mse_loss(y_enh, 1) + F.mse_loss(y_gt, 0)`` per scale."""
+    import torch.nn.functional as F
+    mse = interp_mse_ref(enhanced_audio, clean)
+    (y_e, f_e), (y_g, f_g) = disc_enhanced, disc_ground_truth
+    loss = torch.zeros(())
+    for fe, fg in zip(f_e, f_g):
+        for xe, xg in zip(fe, fg):
+            loss = loss + F.l1_loss(xe, xg)
+    for ye, yg in zip(y_e, y_g):
+        loss = loss + F.mse_loss(ye, torch.ones_like(ye)) + F.mse_loss(yg, torch.zeros_like(yg))
+    return mse, loss
+
+
 def subspace_angle(Va: torch.Tensor, Vb: torch.Tensor) -> float:
     """Largest principal angle (rad) between column spaces, float64 sine formulation
     ``asin ||(I - Qa Qa^T) Qb||_2`` after QR (SURVEY.md section 7 hard part 5)."""

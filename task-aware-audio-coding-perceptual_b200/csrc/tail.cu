@@ -45,7 +45,9 @@ __global__ void __launch_bounds__(256) bottleneck_mix_fwd_kernel(const MixArgs a
             const int v0 = v & ~1, v1 = v0 + 1;
             if (al != nullptr && v1 < a.nv) {
                 const float t = __ldg(al + b);
-                val = t * __ldg(a.z[v0] + b * a.d + cs) + (1.0f - t) * __ldg(a.z[v1] + b * a.d + cs);   // :346 / :700-701 / :1117
+                // :346 / :700-701 / :1117 -- two rounded products and a rounded sum like the reference's three torch kernels
+                // (no FMA contraction): bit-equal results
+                val = __fadd_rn(__fmul_rn(t, __ldg(a.z[v0] + b * a.d + cs)), __fmul_rn(__fsub_rn(1.0f, t), __ldg(a.z[v1] + b * a.d + cs)));
             } else {
                 val = __ldg(a.z[v] + b * a.d + cs);
             }

@@ -9,6 +9,8 @@ call sites on the path ``BASELINE.json:north_star`` names:
 * :mod:`.loss`  -- ``mrstft_loss`` (SURVEY.md 8c) and ``spectral_losses`` (``pkl_file_models.py:933-940``);
 * :mod:`.dpca`  -- ``data_pca`` / ``dpca_project`` / ``apply_pca`` / ``var_topk``
   (``pkl_file_model_updated.py:37-42,489-511,398-427``; ``pkl_file_models.py:224-228,901-907``).
+* :mod:`.tail`  -- the bottleneck that is live in the SpectralRes models (``pkl_file_models.py:1108-1127,692-718,335-354``) with
+  the DPCA hook, and the loss tail of ``task_aware()`` (``train_pkl_file_task_aware.py:307-364``).
 
 There is no CPU or eager-PyTorch fallback: every op raises ``RuntimeError`` when
 ``libtac_spectral.so`` is missing or its input is not on a CUDA device.
@@ -17,6 +19,7 @@ from . import _lib
 from .stft import (Spectrogram, MultiScaleSTFT, stft_multi, complex_spectrogram, create_complex_spectrogram, amplitude_to_db,
                    num_frames, SUPPORTED_NFFT, istft, batch_reconstruct_waveform, reconstruct_waveform, stft_ex, ex_supported,
                    MelBank, MelSpectrogram, SpecsFrontEnd)
+from .tail import bottleneck_mix, spectral_bottleneck, task_aware_tail, interp_mse, multi_reduce
 from .loss import mrstft_loss, mrstft_sums, mrstft_counts, spectral_losses, LOG_FLOOR
 from .dpca import data_pca, dpca_project, dpca_select, dpca_stats, dpca_eig, apply_pca, var_topk, nuclear_loss, pairwise_cosine_loss
 
@@ -24,4 +27,5 @@ __all__ = ["Spectrogram", "MultiScaleSTFT", "stft_multi", "complex_spectrogram",
            "num_frames", "SUPPORTED_NFFT", "mrstft_loss", "mrstft_sums", "mrstft_counts", "spectral_losses",
            "LOG_FLOOR", "data_pca", "dpca_project", "dpca_select", "dpca_stats", "dpca_eig", "apply_pca", "var_topk", "nuclear_loss",
            "pairwise_cosine_loss", "istft", "batch_reconstruct_waveform", "reconstruct_waveform", "stft_ex", "ex_supported",
-           "MelBank", "MelSpectrogram", "SpecsFrontEnd"]
+           "MelBank", "MelSpectrogram", "SpecsFrontEnd", "bottleneck_mix", "spectral_bottleneck", "task_aware_tail", "interp_mse",
+           "multi_reduce"]

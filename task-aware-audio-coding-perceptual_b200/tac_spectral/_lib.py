@@ -71,6 +71,13 @@ SIGNATURES = {
     "tac_istft_length": (_I64, [_I64, _I, _I, _I]),
     "tac_istft": (_I, [_VP, _VP, _I, _I64, _I64, _I64, _I64, _I, _I, _I, _I, _I, _VP, _I64, _VP]),
     "tac_stft_adjoint": (_I, [_VP, _VP, _I, _I64, _I64, _I64, _I64, _I, _I, _I, _F, _VP, _I64, _VP]),
+    "tac_bottleneck_width": (_I, [_I, _I, _I]),
+    "tac_bottleneck_mix": (_I, [_VPP, _I, _I64, _I, _I, _I, _VPP, _VP, _VP]),
+    "tac_bottleneck_mix_bwd": (_I, [_VP, _I, _I64, _I, _I, _I, _VPP, _VPP, _VP]),
+    "tac_interp_mse_workspace_bytes": (_SZ, []),
+    "tac_interp_mse": (_I, [_VP, _I64, _VP, _I64, _I64, _VP, _VP, _SZ, _VP]),
+    "tac_multi_reduce_workspace_bytes": (_SZ, [_I, C.POINTER(C.c_int64)]),
+    "tac_multi_reduce": (_I, [_I, _VPP, _VPP, C.POINTER(C.c_int64), _IP, C.POINTER(C.c_float), _VP, _VP, _SZ, _VP]),
     "tac_xchg_bytes": (_SZ, [_I, _I64]),
     "tac_xchg_push": (_I, [_XP, _VP, _VP]),
     "tac_xchg_pop": (_I, [_XP, _VP, _VP]),

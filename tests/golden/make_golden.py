@@ -18,6 +18,10 @@ feeds them seeded inputs and stores inputs + outputs:
 * ``spec_losses.npz`` -- the loss dictionary / spectral SNR of ``ResE2D1.forward`` (``:520-540``).
 * ``sgmse_spec.npz``  -- the SGMSE+ front end ``pad_spec(spec_fwd(stft(sig)))`` (``sgmse/sgmse/data_module.py:162-175,212-214``,
   ``sgmse/sgmse/util/other.py:76-90``), the three functions compiled from the reference source with ``ast``.
+* ``bottleneck.npz``  -- the split / alpha-mix / truncate bottleneck of ``SpectralResE2D2`` / ``SpectralResE4D1``
+  (``pkl_file_models.py:1108-1127``, ``:692-718``) through their own ``forward``, and the commented-out DPCA blocks of
+  ``:302-332`` / ``:636-679`` executed as written.
+* ``task_aware_tail.npz`` -- ``train_pkl_file_task_aware.py:312-364`` executed as written on seeded inputs with a stub discriminator.
 * ``var_topk.npz``    -- variance top-k of ``pkl_file_models.py:901-907`` through
   ``SpectralResE1D1.forward`` with stubbed encoder / decoder.
 """
@@ -257,6 +261,140 @@ def gen_sgmse():
     np.savez_compressed(os.path.join(HERE, "sgmse_spec.npz"), sig=sig.numpy(), F=np.array(Y.shape[-1]), Yp=Yp.squeeze(1).numpy())
 
 
+def _reference_lines(path, first, last, first_has, last_has, uncomment=False):
+    """Source lines [first, last] (1-based, inclusive) of a reference file, dedented -- for blocks that sit in the middle of
+    a function that cannot be imported or called (``task_aware`` needs wav2vec2 + a processor) or that upstream has
+    commented out (the DPCA blocks of ``pkl_file_models.py``; ``uncomment`` strips ONE leading ``# `` per line).  The two
+    ``*_has`` strings anchor the range so that a moved block fails loudly.  Nothing is stored in this repository."""
+    import textwrap
+    lines = open(os.path.join(REF, path)).read().split("\n")[first - 1:last]
+    assert first_has in lines[0] and last_has in lines[-1], (lines[0], lines[-1])
+    if uncomment:
+        out = []
+        for ln in lines:
+            t = ln.lstrip()
+            assert t == "" or t.startswith("#"), ln
+            out.append(t[2:] if t.startswith("# ") else t[1:])
+        lines = out
+    return textwrap.dedent("\n".join(lines))
+
+
+def gen_bottleneck():
+    """Row a9.  (1) The bottleneck that is live in ``pkl_file_models.py``: ``SpectralResE2D2.forward`` (``:1108-1127``) and
+    ``SpectralResE4D1.forward`` (``:692-718``) with pass-through encoder stubs, the tensors handed to the decoders captured;
+    alpha is re-drawn from the same seed.  (2) The DPCA blocks upstream has commented out at the same place, executed as
+    written: E2D1 ``:302-332`` (``dim_p = num_features / 2``) and E4D1 ``:636-679`` (``dim_p = randint(8, num_features/2)``)."""
+    import contextlib
+    import io
+    import types
+    out = {}
+    B, d, tfa = 48, 32, 24
+    z1, z2 = _latents(B, d, 61), _latents(B, d, 62)
+
+    def obs_of(z):          # stack([magnitude, phase], 1).float() -> the stub encoder flattens it back to z
+        return {"magnitude": z[:, :d // 2].reshape(B, 1, d // 2), "phase": z[:, d // 2:].reshape(B, 1, d // 2)}
+
+    class _EncP(torch.nn.Module):
+        def forward(self, obs):
+            return obs.reshape(obs.shape[0], -1), None
+
+    m = _bare(pm.SpectralResE2D2)
+    m.total_features_after = tfa
+    m.enc1, m.enc2 = _EncP(), _EncP()
+    m.dec1 = _Dec(lambda z: torch.zeros(B, 2, 1, d // 2))
+    m.dec2 = _Dec(lambda z: torch.zeros(B, 2, 1, d // 2))
+    m.dimension_info = {}
+    for rb in (True, False):
+        torch.manual_seed(91)
+        alpha = torch.rand(B, 1)
+        torch.manual_seed(91)
+        r = m.forward(obs_of(z1), obs_of(z2), None, rb)
+        tag = "mix" if rb else "nomix"
+        out[f"e2d2_{tag}_s1"], out[f"e2d2_{tag}_s2"] = m.dec1.seen.numpy(), m.dec2.seen.numpy()
+        if rb:
+            out["e2d2_alpha"] = alpha.numpy()
+            out["e2d2_after"] = np.array([r[-1]["after_z1"], r[-1]["after_z2"]])
+    out["e2d2_z1"], out["e2d2_z2"], out["e2d2_tfa"] = z1.numpy(), z2.numpy(), np.array(tfa)
+
+    zs = [_latents(B, d, 71 + i) for i in range(4)]
+    m4 = _bare(pm.SpectralResE4D1)
+    m4.total_features_after = tfa
+    m4.enc1, m4.enc2, m4.enc3, m4.enc4 = _EncP(), _EncP(), _EncP(), _EncP()
+    m4.dec = _Dec(lambda z: torch.zeros(B, 2, 2, d))
+    m4.dimension_info = {}
+    torch.manual_seed(92)
+    m4.forward(*[obs_of(z) for z in zs], None, True)
+    out["e4d1_mix"] = m4.dec.seen.numpy()
+    for i, z in enumerate(zs):
+        out[f"e4d1_z{i + 1}"] = z.numpy()
+
+    # (2) the commented-out DPCA blocks, run as written
+    ns = {"torch": torch, "data_pca": pm.data_pca, "self": types.SimpleNamespace(), "random_bottle_neck": True,
+          "z1": z1.clone(), "z2": z2.clone(), "num_features": 2 * d}
+    code = _reference_lines("pkl_file_models.py", 302, 332, "# if random_bottle_neck:", "z_sample = torch.cat((z1, z2), dim=1)", uncomment=True)
+    with contextlib.redirect_stdout(io.StringIO()):
+        exec(compile(code, "pkl_file_models.py:302-332", "exec"), ns)
+    out["dpca2_out"] = ns["z_sample"].numpy()
+    out["dpca2_after"] = np.array([ns["self"].dimension_info["after_z1"], ns["self"].dimension_info["after_z2"]])
+    ns = {"torch": torch, "data_pca": pm.data_pca, "self": types.SimpleNamespace(), "random_bottle_neck": True,
+          "num_features": 4 * d, **{f"z{i + 1}": z.clone() for i, z in enumerate(zs)}}
+    code = _reference_lines("pkl_file_models.py", 636, 679, "# if random_bottle_neck:", "z4 = torch.matmul(z4_p, v_4[:,ind_4].T) + mu_4", uncomment=True)
+    torch.manual_seed(93)
+    state = torch.random.get_rng_state()
+    dim_p = torch.randint(8, int(4 * d / 2), (1,)).item()
+    torch.random.set_rng_state(state)
+    exec(compile(code, "pkl_file_models.py:636-679", "exec"), ns)
+    assert ns["dim_p"] == dim_p
+    out["dpca4_dim_p"] = np.array(dim_p)
+    out["dpca4_out"] = torch.cat([ns[f"z{i + 1}"] for i in range(4)], 1).numpy()
+    out["dpca4_after"] = np.array([ns["self"].dimension_info[f"after_z{i + 1}"] for i in range(4)])
+    np.savez_compressed(os.path.join(HERE, "bottleneck.npz"), **out)
+
+
+def gen_task_aware_tail():
+    """Row a5-i: lines ``:312-364`` of ``task_aware()`` (``train_pkl_file_task_aware.py``) executed as written, with the
+    discriminator passed in as a stub that returns seeded (logits, fmaps) of the shapes ``msstftd.py:185-192`` produces
+    (3 sub-discriminators x 5 feature maps, scaled down) -- the wav2vec2 front half of the function cannot run here."""
+    import torch.nn.functional as F
+    code = _reference_lines("train_pkl_file_task_aware.py", 312, 364, "enhanced_length = enhanced_audio.shape[-1]", "discriminator_loss += F.mse_loss(y_gt")
+    code = code.replace('device="cuda:0"', 'device="cpu"')
+    g = torch.Generator().manual_seed(364)
+    B, Le, Lc = 2, 958, 24000                                   # the reference's own comment: argmax sequence of 958 frames
+    enhanced = torch.randint(0, 32, (B, Le), generator=g)       # torch.argmax(logits, -1)
+    clean = torch.randn(B, Lc, generator=g) * 0.1
+    shapes = [[(B, 4, 23, 17), (B, 4, 12, 17), (B, 4, 6, 17), (B, 4, 3, 17), (B, 4, 3, 17)],
+              [(B, 4, 11, 33), (B, 4, 6, 33), (B, 4, 3, 33), (B, 4, 2, 33), (B, 4, 2, 33)],
+              [(B, 4, 47, 9), (B, 4, 24, 9), (B, 4, 12, 9), (B, 4, 6, 9), (B, 4, 6, 9)]]
+    lshapes = [(B, 1, 3, 17), (B, 1, 2, 33), (B, 1, 6, 9)]
+    outs = {}
+
+    def make(tag):
+        fm = [[torch.randn(*s, generator=g) for s in sub] for sub in shapes]
+        lg = [torch.randn(*s, generator=g) for s in lshapes]
+        outs[tag] = (lg, fm)
+        return lg, fm
+
+    calls = []
+
+    def disc(x):
+        calls.append(tuple(x.shape))
+        return make("enh" if len(calls) == 1 else "gt")
+
+    ns = {"torch": torch, "np": np, "F": F, "disc": disc, "enhanced_audio": enhanced, "reconstructed_clean_waveforms": clean}
+    exec(compile(code, "train_pkl_file_task_aware.py:312-364", "exec"), ns)
+    assert calls == [(B, 1, Lc), (B, 1, Lc)]
+    sv = {"enhanced": enhanced.numpy(), "clean": clean.numpy(), "mse": np.array(ns["mse_loss"].item()),
+          "disc_loss": np.array(ns["discriminator_loss"].item())}
+    for tag in ("enh", "gt"):
+        lg, fm = outs[tag]
+        for i, t in enumerate(lg):
+            sv[f"{tag}_logit_{i}"] = t.numpy()
+        for i, sub in enumerate(fm):
+            for j, t in enumerate(sub):
+                sv[f"{tag}_fmap_{i}_{j}"] = t.numpy()
+    np.savez_compressed(os.path.join(HERE, "task_aware_tail.npz"), **sv)
+
+
 if __name__ == "__main__":
     gen_stft()
     gen_dpca()
@@ -265,6 +403,8 @@ if __name__ == "__main__":
     gen_istft()
     gen_cosine()
     gen_sgmse()
+    gen_bottleneck()
+    gen_task_aware_tail()
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)))

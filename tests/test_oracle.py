@@ -194,3 +194,44 @@ def test_power_and_mel_refs_shapes():
     assert torch.allclose(O.power_spectrogram_ref(x, log=True), 10 * torch.log10(S + 1e-10))
     M = O.mel_spectrogram_ref(x, 1024, 256)
     assert M.shape == (2, 80, 1 + (4000 - 1024) // 256)
+
+
+def _tail_golden(golden_dir):
+    g = _load(golden_dir, "task_aware_tail.npz")
+    def pack(tag):
+        lg = [torch.from_numpy(g[f"{tag}_logit_{i}"]) for i in range(3)]
+        fm = [[torch.from_numpy(g[f"{tag}_fmap_{i}_{j}"]) for j in range(5)] for i in range(3)]
+        return lg, fm
+    return g, pack("enh"), pack("gt")
+
+
+def test_bottleneck_matches_reference(golden_dir):
+    # pkl_file_models.py:1108-1127 / :692-718 through the reference's own forward (make_golden.gen_bottleneck)
+    g = _load(golden_dir, "bottleneck.npz")
+    z1, z2 = torch.from_numpy(g["e2d2_z1"]), torch.from_numpy(g["e2d2_z2"])
+    tfa, d = int(g["e2d2_tfa"]), z1.shape[1]
+    s1, s2 = O.bottleneck_mix_ref([z1, z2], d // 2, tfa // 4, [torch.from_numpy(g["e2d2_alpha"])])
+    assert np.array_equal(s1.numpy(), g["e2d2_mix_s1"]) and np.array_equal(s2.numpy(), g["e2d2_mix_s2"])
+    assert list(g["e2d2_after"]) == [s1.shape[1], s2.shape[1]]
+    n1, n2 = O.bottleneck_mix_ref([z1, z2], d // 2, tfa // 4)
+    assert np.array_equal(n1.numpy(), g["e2d2_nomix_s1"]) and np.array_equal(n2.numpy(), g["e2d2_nomix_s2"])
+    zs = [torch.from_numpy(g[f"e4d1_z{i + 1}"]) for i in range(4)]
+    torch.manual_seed(92)
+    al = [torch.rand(48, 1), torch.rand(48, 1)]                      # :698-699 (the shared parts are empty: no effect)
+    e4 = torch.cat(O.bottleneck_mix_ref(zs, 4 * d, tfa // 4, al), 1)
+    assert np.array_equal(e4.numpy(), g["e4d1_mix"])
+    # the commented-out DPCA blocks (:302-332, :636-679) == the DPCA oracle pinned by pkl_file_model_updated.py
+    o2, idx2 = O.dpca_project_ref([z1, z2], (2 * d) // 2)
+    assert [len(i) for i in idx2] == list(g["dpca2_after"])
+    assert np.abs(torch.cat(o2, 1).numpy() - g["dpca2_out"]).max() <= 1e-5
+    o4, idx4 = O.dpca_project_ref(zs, int(g["dpca4_dim_p"]))
+    assert [len(i) for i in idx4] == list(g["dpca4_after"])
+    assert np.abs(torch.cat(o4, 1).numpy() - g["dpca4_out"]).max() <= 1e-5
+
+
+def test_task_aware_tail_matches_reference(golden_dir):
+    # train_pkl_file_task_aware.py:312-364 executed as written (make_golden.gen_task_aware_tail)
+    g, enh, gt = _tail_golden(golden_dir)
+    mse, dl = O.task_aware_tail_ref(torch.from_numpy(g["enhanced"]), torch.from_numpy(g["clean"]), enh, gt)
+    assert abs(float(mse) - float(g["mse"])) <= 1e-6 * float(g["mse"])
+    assert abs(float(dl) - float(g["disc_loss"])) <= 1e-6 * float(g["disc_loss"])

@@ -619,7 +619,8 @@ def run_native(args):
     px, py = hx.pin_memory(), hy.pin_memory()
     pz = [z.pin_memory() for z in hz]
     nbuf = 2
-    dbuf = [(torch.empty_like(dsets[0][0]), torch.empty_like(dsets[0][1]), [torch.empty_like(z) for z in dsets[0][2]]) for _ in range(nbuf)]
+    # real data in the warm-up / capture pass (uninitialised memory may hold NaN bit patterns)
+    dbuf = [(dsets[0][0].clone(), dsets[0][1].clone(), [z.clone() for z in dsets[0][2]]) for _ in range(nbuf)]
     g_e2e = [None] * nbuf
     if graphs is not None:
         for i in range(nbuf):

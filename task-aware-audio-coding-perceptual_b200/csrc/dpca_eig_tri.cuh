@@ -482,7 +482,10 @@ dpca_eig_tri_kernel(double* stats, int d, float* __restrict__ s_out, float* __re
     // ---- outputs: descending order by counting, s = sqrt(lambda), null directions -> zero columns
     const double fro = sh.scal[3];
     const double null_thr = 1e-14 * fro;
-    if (tid < d) sh.lam[tid] *= sh.scal[5];
+    if (tid < d) {
+        const double l = sh.lam[tid] * sh.scal[5];
+        sh.lam[tid] = (l == l && fabs(l) < 1e300) ? l : 0.0;         // NaN-safe ranks (see dpca_tri_finish_kernel)
+    }
     __syncthreads();
     if (tid < d) {
         const double lj = sh.lam[tid];
@@ -679,7 +682,10 @@ dpca_tri_finish_kernel(const double* __restrict__ stats, int d, float* __restric
     double* V = w + kTriWsVec;                               // [slot][row]
     const double n = stats[(size_t)view * (1 + d + (size_t)d * d)];
     if (tid < d) {
-        lam[tid] = w[kTriWsLam + tid];
+        // non-finite statistics (NaN / Inf latents) must not reach the rank-by-counting below: every comparison with a NaN
+        // is false, two slots would share a rank and inv[] would keep an unwritten entry -> wild column index
+        const double l = w[kTriWsLam + tid];
+        lam[tid] = (l == l && fabs(l) < 1e300) ? l : 0.0;
         blk_s[tid] = reinterpret_cast<const int*>(w + kTriWsBlk)[tid];
     }
     if (tid < 8) scal[tid] = w[kTriWsScal + tid];
@@ -713,7 +719,10 @@ dpca_tri_finish_kernel(const double* __restrict__ stats, int d, float* __restric
     }
     const double fro = scal[3];
     const double null_thr = 1e-14 * fro;
-    if (tid < d) lam[tid] *= scal[5];
+    if (tid < d) {
+        const double l = lam[tid] * scal[5];
+        lam[tid] = (l == l && fabs(l) < 1e300) ? l : 0.0;
+    }
     __syncthreads();
     if (tid < d) {
         const double lj = lam[tid];

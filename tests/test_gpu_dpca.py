@@ -197,3 +197,20 @@ def test_nuclear_loss_forward_backward(ts, B, d):
     got.backward()
     err = (zg.grad.cpu().double() - ref_in.grad).abs().max()
     assert float(err) <= 1e-3 * float(ref_in.grad.abs().max()), float(err / ref_in.grad.abs().max())
+
+
+def test_non_finite_latents_do_not_fault(ts):
+    # NaN / Inf latents (an exploded encoder, or an uninitialised buffer in a warm-up pass) must give garbage values, never
+    # a wild index: the rank-by-counting of the eigenvalues is made on sanitised values (dpca_eig_tri.cuh)
+    torch.manual_seed(0)
+    for bad in (float("nan"), float("inf")):
+        zs = [torch.randn(64, 128, device="cuda") for _ in range(2)]
+        zs[0][3, 5] = bad
+        zs[1][:] = bad
+        outs = ts.dpca_project(zs, 16)
+        torch.cuda.synchronize()
+        assert all(o.shape == (64, 128) for o in outs)
+    z = torch.randn(64, 128, device="cuda")
+    ref = ts.dpca_project([z], 16)[0]
+    torch.cuda.synchronize()
+    assert bool(torch.isfinite(ref).all())                           # the context is still healthy

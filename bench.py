@@ -533,10 +533,14 @@ def run_native(args):
     # ---- timed region: W warm-up steps, then exactly K steps between barrier + synchronize
     for i in range(args.warmup):
         do_step(i)
-    barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     step_evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
-    with ClockSampler(local) as clk:
+    with ClockSampler(local) as clk:                  # started BEFORE the barrier: spawning the sampler takes milliseconds and
+        barrier()                                     # would otherwise skew the ranks' entry into the timed region
+        # N > 1: the hosts leave the barrier tens of microseconds to milliseconds apart; a GPU-side rendezvous in front of the
+        # start event makes every rank's device enter step 1 together (else the first step measures that skew: its DPCA
+        # chain waits for the slowest peer's statistics)
+        step.device_barrier()
         e0.record()
         for i in range(args.steps):
             do_step(args.warmup + i)

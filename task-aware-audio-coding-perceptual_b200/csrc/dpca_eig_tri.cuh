@@ -691,13 +691,18 @@ dpca_tri_finish_kernel(const double* __restrict__ stats, int d, float* __restric
     if (tid < 8) scal[tid] = w[kTriWsScal + tid];
     __syncthreads();
     const double tn = scal[4];
-    const int clustered = __syncthreads_or(tid < d && tid > blk_s[tid] && lam[tid] - lam[tid - 1] <= 1e-9 * tn);
+    // Numerically null eigenvalues (rank-deficient batch, B < d: up to d - B + 1 of them in one cluster) are emitted as zero
+    // columns below, so their vectors need no orthogonalisation -- without this a 16-row batch at d = 128 spent 2.7 ms in
+    // the sequential Gram-Schmidt of a 113-fold "cluster" (cfg 5).  lam is still in units of the scaled T here.
+    const double null_scaled = scal[5] > 0.0 ? 1e-14 * scal[3] / scal[5] : 0.0;
+    const int clustered = __syncthreads_or(tid < d && tid > blk_s[tid] && lam[tid] > null_scaled && lam[tid] - lam[tid - 1] <= 1e-9 * tn);
     if (clustered) {
         if (warp == 0) {
             for (int k = 1; k < d; ++k) {
                 const int s = blk_s[k];
                 bool changed = false;
-                for (int j = k - 1; j >= s && lam[k] - lam[j] <= 1e-9 * tn * (double)(k - j); --j) {
+                if (!(lam[k] > null_scaled)) continue;                   // null direction: zero column (warp-uniform)
+                for (int j = k - 1; j >= s && lam[j] > null_scaled && lam[k] - lam[j] <= 1e-9 * tn * (double)(k - j); --j) {
                     double dot = 0.0;
                     for (int i = lane; i < d; i += 32) dot = fma(V[(size_t)j * kTriMaxD + i], V[(size_t)k * kTriMaxD + i], dot);
                     dot = tri_warp_sum(dot);

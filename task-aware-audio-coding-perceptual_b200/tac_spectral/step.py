@@ -121,7 +121,19 @@ class SpectralStep:
             # last in the constructor: the rendezvous synchronises the ranks, so the first step's pops find peers that
             # have finished building their tables
             from .exchange import Exchange
-            self.xchg = Exchange({"stats": nv * self.stat_stride, "sums": 2 * S}, group, dev)
+            self.xchg = Exchange({"stats": nv * self.stat_stride, "sums": 2 * S, "sync": 2}, group, dev)
+            self._sync_buf = torch.zeros(4, dtype=torch.float64, device=dev)
+
+    def device_barrier(self):
+        """Enqueue a GPU-side rendezvous of all ranks on the current stream (one push + one pop of a two-value channel of the
+        step's exchange): work enqueued behind it starts within microseconds of each other on every rank, however far apart
+        the hosts left their last ``dist.barrier()``.  No-op without the peer exchange."""
+        if self.xchg is None:
+            return
+        from .exchange import push, pop
+        with torch.cuda.device(self.device):
+            push(self.xchg.desc("sync"), self._sync_buf[:2])
+            pop(self.xchg.desc("sync"), self._sync_buf[2:])
 
     def close(self):
         if self.xchg is not None:

@@ -198,15 +198,24 @@ __global__ void __launch_bounds__(1024) dpca_select_kernel(const float* __restri
     __shared__ float sv[kMaxViews * kMaxD];
     __shared__ int sview[kMaxViews * kMaxD], sloc[kMaxViews * kMaxD], sgr[kMaxViews * kMaxD];
     __shared__ int s_n;
+    // concatenated list of the views' first rank[v] singular values, built by all threads (one thread doing it serially
+    // cost ~14 us of dependent global loads on the latency-bound DPCA chain)
+    __shared__ int s_off[kMaxViews + 1];
     if (threadIdx.x == 0) {
         int n = 0;
-        for (int v = 0; v < nv; ++v) {
-            const int r = min(rank[v], d);
-            for (int i = 0; i < r; ++i) { sv[n] = s[(size_t)v * d + i]; sview[n] = v; sloc[n] = i; ++n; }
-        }
+        for (int v = 0; v < nv; ++v) { s_off[v] = n; n += max(0, min(rank[v], d)); }
+        s_off[nv] = n;
         s_n = n;
     }
     for (int v = threadIdx.x; v < nv; v += blockDim.x) cnt[v] = 0;
+    __syncthreads();
+    for (int e = threadIdx.x; e < nv * d; e += blockDim.x) {
+        const int v = e / d, i = e - v * d;
+        if (i < s_off[v + 1] - s_off[v]) {
+            const int n = s_off[v] + i;
+            sv[n] = s[(size_t)v * d + i]; sview[n] = v; sloc[n] = i;
+        }
+    }
     __syncthreads();
     const int n = s_n;
     for (int e = threadIdx.x; e < n; e += blockDim.x) {
@@ -370,13 +379,13 @@ static int dpca_tc_stats(const float* const* z, int nv, long long B, int d, doub
     for (int i = 0; i < 8; ++i) p[i] = z[i < nv ? i : 0];
     const int nsplit = (int)((B + kTcRowsPerCta - 1) / kTcRowsPerCta);
     float* partial = reinterpret_cast<float*>(ws);
-    dpca_colsum_kernel<<<nv, 1024, 0, st>>>(p[0], p[1], p[2], p[3], p[4], p[5], p[6], p[7], B, d, stats); TAC_LAUNCHED(1);
-    TAC_CHECK_CUDA(cudaGetLastError());
+    double* lsum = reinterpret_cast<double*>(partial + (size_t)nv * nsplit * kTcFeat * kTcFeat);       // 8-byte aligned: 64 KiB multiples
+    float* lmean = reinterpret_cast<float*>(lsum + (size_t)nv * nsplit * kTcFeat);
     TAC_CHECK_CUDA(cudaFuncSetAttribute(dpca_gram_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
     dpca_gram_tc_kernel<<<dim3(nsplit, nv), kTcThreads, kTcSmemBytes, st>>>(p[0], p[1], p[2], p[3], p[4], p[5], p[6], p[7], B, d,
-                                                                           stats, partial); TAC_LAUNCHED(1);
+                                                                           partial, lsum, lmean); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
-    dpca_gram_finish_kernel<<<dim3(d, nv), kTcFeat, 0, st>>>(partial, nsplit, d, stats, xd); TAC_LAUNCHED(1);
+    dpca_gram_finish_kernel<<<dim3(d, nv), kTcFeat, 0, st>>>(partial, lsum, lmean, nsplit, B, d, stats, xd); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
     return TAC_OK;
 }

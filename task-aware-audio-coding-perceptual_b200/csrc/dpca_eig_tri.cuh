@@ -30,7 +30,8 @@ struct TriShared {
     double b[kTriMaxD];            // sub-diagonal of T (b[i] couples i and i+1)
     double b2[kTriMaxD];
     double vec_v[kTriMaxD];
-    double vec_p[kTriMaxD];
+    double vec_p[kTriMaxD];      // p, then w = p - K v
+    double vec_x[kTriMaxD];      // next column x' (index = row of the current trailing matrix; [0] = 0)
     double part[kTriParts][kTriMaxD];
     double lam[kTriMaxD];
     double red[40];
@@ -174,15 +175,18 @@ dpca_eig_tri_kernel(double* stats, int d, float* __restrict__ s_out, float* __re
     __syncthreads();
 
     TRI_STAMP(1);
-    // ---- 1. Householder tridiagonalisation (column k: x = A[k+1.., k]); three barriers per column
+    // ---- 1. Householder tridiagonalisation (column k: x = A[k+1.., k]).  TWO block barriers and ONE pass over the trailing
+    // matrix per column: the rank-2 update of column k and the mat-vec q' = A22'' x' of column k + 1 are the same loop (the
+    // next column x' is known as soon as v and w are: x'_i = c0_i - (v_i w_0 + w_i v_0), c0 = old first column).  The four
+    // warps that own the vectors meet at a 128-thread named barrier between "p.v" and "K, w, x'"; the other 28 warps only
+    // see the two block barriers.  (The three-barrier, two-pass form this replaces took 0.29 ms at d = 128.)
     const int ci = tid % kTriMaxD;                 // row / column index owned in the 128 x 8 mapping
     const int cp = tid / kTriMaxD;                 // part 0..7
-    for (int k = 0; k + 2 < d; ++k) {
-        const int m = d - k - 1;
-        const double* x = A + (size_t)k * d + (k + 1);              // x_i, i < m (row k == column k by symmetry)
-        // P1: partial q = A22 x over j = cp, cp+8, ...; sigma = x.x by warps 0..3
+    if (d >= 3) {                                  // q = A22 x and sigma = x.x of column 0
+        const int m = d - 1;
+        const double* x = A + 1;
         if (ci < m) {
-            const double* col0 = A + (size_t)(k + 1) * d + (k + 1) + ci;   // A22[ci][j] = A[(k+1+j)*d + k+1+ci]
+            const double* col0 = A + (size_t)d + 1 + ci;
             double a0 = 0.0, a1 = 0.0;
             int j = cp;
             for (; j + kTriParts < m; j += 2 * kTriParts) {
@@ -197,8 +201,12 @@ dpca_eig_tri_kernel(double* stats, int d, float* __restrict__ s_out, float* __re
             const double s2 = tri_warp_sum(xv * xv);
             if (lane == 0) sh.red[warp] = s2;
         }
-        __syncthreads();
-        // P2 (threads < 128): scalars (redundantly, fast reciprocal square root), v, p, partial p.v
+    }
+    __syncthreads();
+    for (int k = 0; k + 2 < d; ++k) {
+        const int m = d - k - 1;
+        const double* x = A + (size_t)k * d + (k + 1);              // x_i, i < m (row k == column k by symmetry)
+        // P2 (threads < 128): scalars (redundantly, fast reciprocal square root), v, p, p.v | K, w, next column, its sigma
         if (warp < 4) {
             const double sigma = (sh.red[0] + sh.red[1]) + (sh.red[2] + sh.red[3]);
             const double x0 = x[0];
@@ -211,16 +219,17 @@ dpca_eig_tri_kernel(double* stats, int d, float* __restrict__ s_out, float* __re
                 alpha = x0 >= 0.0 ? -nrm : nrm;
                 beta = tri_rcp(fma(-alpha, x0, sigma));             // 2 / v.v
             }
-            double vi = 0.0, pi = 0.0;
+            double vi = 0.0, pi = 0.0, c0 = 0.0;
             if (tid < m) {
                 double qi = 0.0;
 #pragma unroll
                 for (int p = 0; p < kTriParts; ++p) qi += sh.part[p][tid];
+                c0 = A[(size_t)(k + 1) * d + (k + 1) + tid];        // first column of A22 before the update
                 vi = x[tid] - (tid == 0 ? alpha : 0.0);
-                pi = beta * (qi - alpha * A[(size_t)(k + 1) * d + (k + 1) + tid]);
-                sh.vec_v[tid] = vi; sh.vec_p[tid] = pi;
+                pi = beta * (qi - alpha * c0);
                 refl[tri_refl_off(k, d) + tid] = beta != 0.0 ? vi : 0.0;
             }
+            sh.vec_v[tid] = vi; sh.vec_p[tid] = pi;
             const double pv = tri_warp_sum(vi * pi);
             if (lane == 0) sh.red[8 + warp] = pv;
             if (tid == 0) {
@@ -228,32 +237,50 @@ dpca_eig_tri_kernel(double* stats, int d, float* __restrict__ s_out, float* __re
                 sh.b[k] = beta != 0.0 ? alpha : x0;
                 sh.beta[k] = beta;
             }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            // w = p - K v, K = beta/2 p.v; next column x'_i (row i >= 1 of A22) with the rounding sequence of the update below
+            const double K = 0.5 * beta * ((sh.red[8] + sh.red[9]) + (sh.red[10] + sh.red[11]));
+            const double v0 = sh.vec_v[0];
+            const double w0 = sh.vec_p[0] - K * v0;
+            const double wi = pi - K * vi;
+            double xn = 0.0;
+            if (tid >= 1 && tid < m) xn = __dsub_rn(c0, __dadd_rn(__dmul_rn(vi, w0), __dmul_rn(wi, v0)));
+            asm volatile("bar.sync 1, 128;" ::: "memory");           // every p_0 has been read before p turns into w
+            sh.vec_p[tid] = wi;
+            sh.vec_x[tid] = xn;
+            const double s2 = tri_warp_sum(xn * xn);
+            if (lane == 0) sh.red[warp] = s2;                       // sigma of column k + 1
         }
         __syncthreads();
-        // P3: A22 -= v w^T + w v^T,  w = p - K v,  K = beta/2 p.v
-        const double beta = sh.beta[k];
-        if (beta != 0.0 && ci < m) {
-            const double K = 0.5 * beta * ((sh.red[8] + sh.red[9]) + (sh.red[10] + sh.red[11]));
+        // P3: A22 -= v w^T + w v^T, and in the same pass the partial q' = A22'' x' of the next column (rows / columns >= 1)
+        if (ci < m) {
             const double v_i = sh.vec_v[ci];
-            const double w_i = sh.vec_p[ci] - K * v_i;
+            const double w_i = sh.vec_p[ci];
             double* col0 = A + (size_t)(k + 1) * d + (k + 1) + ci;
+            double a0 = 0.0, a1 = 0.0;
             int j = cp;
             for (; j + kTriParts < m; j += 2 * kTriParts) {
                 const int j1 = j + kTriParts;
                 const double va = sh.vec_v[j], vb = sh.vec_v[j1];
-                const double wa = sh.vec_p[j] - K * va, wb = sh.vec_p[j1] - K * vb;
+                const double wa = sh.vec_p[j], wb = sh.vec_p[j1];
                 const double ca = col0[(size_t)j * d], cb = col0[(size_t)j1 * d];
                 // exactly symmetric in (i, j): both triangles stay bit-identical.  (An index-ordered two-FMA form, also exactly
                 // symmetric, measured SLOWER on B200: 519 k -> 590 k cycles for the tridiagonalisation -- the selects cost more
                 // than the two float64 operations they save.)
-                col0[(size_t)j * d] = __dsub_rn(ca, __dadd_rn(__dmul_rn(v_i, wa), __dmul_rn(w_i, va)));
-                col0[(size_t)j1 * d] = __dsub_rn(cb, __dadd_rn(__dmul_rn(v_i, wb), __dmul_rn(w_i, vb)));
+                const double na = __dsub_rn(ca, __dadd_rn(__dmul_rn(v_i, wa), __dmul_rn(w_i, va)));
+                const double nb = __dsub_rn(cb, __dadd_rn(__dmul_rn(v_i, wb), __dmul_rn(w_i, vb)));
+                col0[(size_t)j * d] = na;
+                col0[(size_t)j1 * d] = nb;
+                a0 = fma(na, sh.vec_x[j], a0);                       // vec_x[0] == 0: column 0 is x', not part of A22''
+                a1 = fma(nb, sh.vec_x[j1], a1);
             }
             if (j < m) {
-                const double va = sh.vec_v[j];
-                const double wa = sh.vec_p[j] - K * va;
-                col0[(size_t)j * d] = __dsub_rn(col0[(size_t)j * d], __dadd_rn(__dmul_rn(v_i, wa), __dmul_rn(w_i, va)));
+                const double va = sh.vec_v[j], wa = sh.vec_p[j];
+                const double na = __dsub_rn(col0[(size_t)j * d], __dadd_rn(__dmul_rn(v_i, wa), __dmul_rn(w_i, va)));
+                col0[(size_t)j * d] = na;
+                a0 = fma(na, sh.vec_x[j], a0);
             }
+            if (ci >= 1) sh.part[cp][ci - 1] = a0 + a1;
         }
         __syncthreads();
     }

@@ -95,7 +95,7 @@ __device__ __forceinline__ float tc_to_tf32(float v) {
 __global__ void __launch_bounds__(kTcThreads, 1)
 dpca_gram_tc_kernel(const float* z0, const float* z1, const float* z2,
                     const float* z3, const float* z4, const float* z5, const float* z6, const float* z7,
-                    long long B, int d, const double* __restrict__ stats, float* __restrict__ partial) {
+                    long long B, int d, float* __restrict__ partial, double* __restrict__ lsum, float* __restrict__ lmean) {
     extern __shared__ unsigned char tc_smem_raw[];
     __shared__ __align__(8) uint64_t s_bar[kTcStages];
     __shared__ uint32_t s_tmem;
@@ -104,17 +104,28 @@ dpca_gram_tc_kernel(const float* z0, const float* z1, const float* z2,
     const int v = blockIdx.y, split = blockIdx.x, nsplit = gridDim.x;
     const float* zs[8] = {z0, z1, z2, z3, z4, z5, z6, z7};
     const float* z = zs[v];
-    const size_t stat_stride = 1 + (size_t)d + (size_t)d * d;
-    const double* st = stats + (size_t)v * stat_stride;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const long long r_begin = (long long)split * kTcRowsPerCta;
+    const long long r_end = (r_begin + kTcRowsPerCta < B) ? r_begin + kTcRowsPerCta : B;
 
     // 1024-byte aligned operand tiles: [stage][hi|lo][kTcTileBytes]
     const uint32_t raw = tc_smem_u32(tc_smem_raw);
     const uint32_t base = (raw + 1023u) & ~1023u;
     unsigned char* tiles = tc_smem_raw + (base - raw);
 
-    if (threadIdx.x < kTcFeat)
-        s_mean[threadIdx.x] = (int)threadIdx.x < d ? (float)(st[1 + threadIdx.x] / st[0]) : 0.0f;
+    // Column sums of THIS CTA's rows (float64) and their mean as the centring shift -- any shift c gives the raw statistic
+    // back exactly (sum z z^T = G_c + c s^T + s c^T - n c c^T, re-assembled in float64 by dpca_gram_finish_kernel), so the
+    // separate column-sum launch in front of this kernel is gone (the statistics sit in front of the exchange at N > 1).
+    if (threadIdx.x < kTcFeat) {
+        const int f = threadIdx.x;
+        double acc = 0.0;
+        if (f < d)
+            for (long long r = r_begin; r < r_end; ++r) acc += (double)__ldg(z + r * d + f);
+        const float mean = r_end > r_begin ? (float)(acc / (double)(r_end - r_begin)) : 0.0f;
+        s_mean[f] = mean;
+        lsum[((size_t)v * nsplit + split) * kTcFeat + f] = acc;
+        lmean[((size_t)v * nsplit + split) * kTcFeat + f] = mean;
+    }
     if (threadIdx.x == 0) {
         for (int s = 0; s < kTcStages; ++s) tc_mbar_init(&s_bar[s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -129,8 +140,6 @@ dpca_gram_tc_kernel(const float* z0, const float* z1, const float* z2,
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = s_tmem;
 
-    const long long r_begin = (long long)split * kTcRowsPerCta;
-    const long long r_end = (r_begin + kTcRowsPerCta < B) ? r_begin + kTcRowsPerCta : B;
     const int nchunks = (int)((r_end - r_begin + kTcChunk - 1) / kTcChunk);
     uint32_t phase[kTcStages] = {0, 0};
     for (int c = 0; c < nchunks; ++c) {
@@ -210,53 +219,43 @@ dpca_gram_tc_kernel(const float* z0, const float* z1, const float* z2,
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "r"((uint32_t)kTcFeat) : "memory");
 }
 
-// Column sums in float64: stats[v][0] = B, stats[v][1 + j] = sum_b z[b][j].  grid (nv), block 1024.
-__global__ void __launch_bounds__(1024)
-dpca_colsum_kernel(const float* z0, const float* z1, const float* z2, const float* z3, const float* z4, const float* z5,
-                   const float* z6, const float* z7, long long B, int d, double* __restrict__ stats) {
-    __shared__ double sh[1024];
-    const float* zs[8] = {z0, z1, z2, z3, z4, z5, z6, z7};
-    const int v = blockIdx.x;
-    const float* z = zs[v];
-    double* st = stats + (size_t)v * (1 + (size_t)d + (size_t)d * d);
-    const int groups = 1024 / 256;                        // d <= 256 columns x 4 row groups
-    const int col = threadIdx.x % 256, grp = threadIdx.x / 256;
-    double acc = 0.0;
-    if (col < d)
-        for (long long r = grp; r < B; r += groups) acc += (double)__ldg(z + r * d + col);
-    sh[threadIdx.x] = acc;
-    __syncthreads();
-    if (grp == 0 && col < d) st[1 + col] = sh[col] + sh[256 + col] + sh[512 + col] + sh[768 + col];
-    if (threadIdx.x == 0) st[0] = (double)B;
-}
-
-// stats S = sum_split partial + n * mean mean^T   (float64).  grid (d, nv), block 128.
+// stats: n = B, sum z = sum_c s_c, sum z z^T = sum_c [G_c + m_c s_c^T + s_c m_c^T - n_c m_c m_c^T]   (float64; c = row split,
+// m_c = the float32 shift CTA c centred with, s_c its float64 column sums).  grid (d, nv), block 128.
 // With an exchange (xd.world > 1) the kernel that completes the statistics also SENDS them: every value is peer-stored
 // into this rank's slot on all ranks as it is formed, and the last CTA raises the flags (xchg.cuh) -- compute and
 // collective are one kernel, the transfer overlaps the re-assembly row by row.
 __global__ void __launch_bounds__(kTcFeat)
-dpca_gram_finish_kernel(const float* __restrict__ partial, int nsplit, int d, double* __restrict__ stats, const XchgDev xd) {
+dpca_gram_finish_kernel(const float* __restrict__ partial, const double* __restrict__ lsum, const float* __restrict__ lmean,
+                        int nsplit, long long B, int d, double* __restrict__ stats, const XchgDev xd) {
     const int v = blockIdx.y, i = blockIdx.x, j = threadIdx.x;
     const size_t stride = 1 + (size_t)d + (size_t)d * d;
     double* st = stats + (size_t)v * stride;
     const bool push = xd.world > 1;
     const unsigned seq = push ? xchg_push_seq(xd) : 0u;
     if (j < d) {
-        const double n = st[0];
-        double acc = 0.0;
+        double acc = 0.0, sj = 0.0;
         for (int s = 0; s < nsplit; ++s) {
             // symmetrise: (i, j) and (j, i) were accumulated by different instruction orders
-            const float* p = partial + ((size_t)v * nsplit + s) * kTcFeat * kTcFeat;
-            acc += 0.5 * ((double)p[(size_t)i * kTcFeat + j] + (double)p[(size_t)j * kTcFeat + i]);
+            const size_t c = (size_t)v * nsplit + s;
+            const float* p = partial + c * kTcFeat * kTcFeat;
+            const long long r0 = (long long)s * kTcRowsPerCta;
+            const double nc = (double)((r0 + kTcRowsPerCta < B ? r0 + kTcRowsPerCta : B) - r0);
+            const double mi = (double)lmean[c * kTcFeat + i], mj = (double)lmean[c * kTcFeat + j];
+            const double si = lsum[c * kTcFeat + i];
+            const double sjc = lsum[c * kTcFeat + j];
+            acc += 0.5 * ((double)p[(size_t)i * kTcFeat + j] + (double)p[(size_t)j * kTcFeat + i]) + (mi * sjc + si * mj - nc * mi * mj);
+            sj += sjc;
         }
-        const double mi = st[1 + i] / n, mj = st[1 + j] / n;
-        const double val = acc + n * mi * mj;
-        st[1 + d + (size_t)i * d + j] = val;
+        st[1 + d + (size_t)i * d + j] = acc;
+        if (i == 0) {
+            st[1 + j] = sj;
+            if (j == 0) st[0] = (double)B;
+        }
         if (push) {
-            xchg_store(xd, seq, (size_t)v * stride + 1 + d + (size_t)i * d + j, val);
-            if (i == 0) {                                   // n and the column sums (dpca_colsum_kernel) ride along
-                xchg_store(xd, seq, (size_t)v * stride + 1 + j, st[1 + j]);
-                if (j == 0) xchg_store(xd, seq, (size_t)v * stride, n);
+            xchg_store(xd, seq, (size_t)v * stride + 1 + d + (size_t)i * d + j, acc);
+            if (i == 0) {                                   // n and the column sums ride along
+                xchg_store(xd, seq, (size_t)v * stride + 1 + j, sj);
+                if (j == 0) xchg_store(xd, seq, (size_t)v * stride, (double)B);
             }
         }
     }
@@ -266,7 +265,8 @@ dpca_gram_finish_kernel(const float* __restrict__ partial, int nsplit, int d, do
 inline size_t dpca_tc_workspace_bytes(int nv, long long B, int d) {
     if (d > kTcFeat) return 0;
     const long long nsplit = (B + kTcRowsPerCta - 1) / kTcRowsPerCta;
-    return (size_t)nv * (size_t)nsplit * kTcFeat * kTcFeat * sizeof(float);
+    // Gram partials [nv][nsplit][128][128] float | column sums [nv][nsplit][128] double | shifts [nv][nsplit][128] float
+    return (size_t)nv * (size_t)nsplit * ((size_t)kTcFeat * kTcFeat * sizeof(float) + kTcFeat * (sizeof(double) + sizeof(float)));
 }
 
 }  // namespace tac

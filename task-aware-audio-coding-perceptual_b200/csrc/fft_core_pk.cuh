@@ -175,6 +175,109 @@ __device__ __forceinline__ void warp_fft_post_pk(const cf (&z)[P::BQ], const flo
     if (k1 == 0) emit(fr, M / 2, mul2(cnj(z[BQ / 2]), bc(2.0f)), BQ);
 }
 
+// ------------------------------------------------------------------ two forward transforms at once
+// The loss kernels transform the SAME frame positions of two signals (target x, decoded y).  Doing both in one call makes
+// the butterflies of the two transforms independent instruction streams inside the same basic blocks (ILP 2 for a kernel
+// that runs two warps per scheduler and waits on fixed-latency dependencies), and the window, the inter-pass twiddles,
+// the post-processing twiddles and the exchange tile are loaded / computed ONCE for both: y's twiddled pass-1 outputs
+// wait in registers while x goes through the tile.
+// load(integral_constant s, fr, m, integral_constant a, vx, vy) fills both windowed packed sample pairs.
+template <class P, class Load>
+__device__ __forceinline__ void warp_fft_fwd2_pk(cf (&zx)[P::BQ], cf (&zy)[P::BQ], float2* xbuf, const float2* __restrict__ tw,
+                                                 int lane, Load load) {
+    constexpr int A = P::A, BQ = P::BQ, RS = P::RS, NS1 = P::NS1;
+    cf ay[NS1][A];
+    static_for<0, NS1>([&](auto sc) {
+        constexpr int s = decltype(sc)::value;
+        const int q = lane + 32 * s;
+        const int fr = q / BQ, b = q % BQ;
+        cf ax[A];
+        static_for<0, A>([&](auto ac) {
+            constexpr int av = decltype(ac)::value;
+            load(sc, fr, BQ * av + b, ac, ax[brev(av, A)], ay[s][brev(av, A)]);
+        });
+        float2 wr_[8], wq_[A / 8 > 0 ? A / 8 : 1];
+        static_for<1, (A < 8 ? A : 8)>([&](auto rc) { constexpr int r = decltype(rc)::value; wr_[r] = ldg2(tw + r * BQ + b); });
+        static_for<1, A / 8>([&](auto qc) { constexpr int qq = decltype(qc)::value; wq_[qq] = ldg2(tw + 8 * qq * BQ + b); });
+        Dit<A, false>::run(ax);
+        Dit<A, false>::run(ay[s]);
+        cf* row = reinterpret_cast<cf*>(xbuf) + (fr * A) * RS + b;
+        static_for<0, A>([&](auto kc) {
+            constexpr int k1 = decltype(kc)::value;
+            constexpr int r = k1 % 8, qq = k1 / 8;
+            cf vx = ax[k1], vy = ay[s][k1];
+            if constexpr (r > 0) {
+                vx = fma2(rotm(vx), bc(wr_[r].y), mul2(vx, bc(wr_[r].x)));     // W = w.x - j w.y
+                vy = fma2(rotm(vy), bc(wr_[r].y), mul2(vy, bc(wr_[r].x)));
+            }
+            if constexpr (qq > 0) {
+                vx = fma2(rotm(vx), bc(wq_[qq].y), mul2(vx, bc(wq_[qq].x)));
+                vy = fma2(rotm(vy), bc(wq_[qq].y), mul2(vy, bc(wq_[qq].x)));
+            }
+            row[k1 * RS] = vx;
+            ay[s][k1] = vy;
+        });
+    });
+    __syncwarp();
+    const cf* rd = reinterpret_cast<const cf*>(xbuf) + lane * RS;
+    auto read_tile = [&](cf (&z)[BQ]) {
+        if constexpr (P::kVec4) {
+            const ulonglong2* rd2 = reinterpret_cast<const ulonglong2*>(rd);
+            static_for<0, BQ / 2>([&](auto bc_) {
+                constexpr int b = decltype(bc_)::value;
+                const ulonglong2 v = rd2[b];
+                z[brev(2 * b, BQ)] = v.x; z[brev(2 * b + 1, BQ)] = v.y;
+            });
+        } else {
+            static_for<0, BQ>([&](auto bc_) {
+                constexpr int b = decltype(bc_)::value;
+                z[brev(b, BQ)] = rd[b];
+            });
+        }
+    };
+    read_tile(zx);
+    __syncwarp();
+    static_for<0, NS1>([&](auto sc) {
+        constexpr int s = decltype(sc)::value;
+        const int q = lane + 32 * s;
+        const int fr = q / BQ, b = q % BQ;
+        cf* row = reinterpret_cast<cf*>(xbuf) + (fr * A) * RS + b;
+        static_for<0, A>([&](auto kc) { constexpr int k1 = decltype(kc)::value; row[k1 * RS] = ay[s][k1]; });
+    });
+    __syncwarp();
+    read_tile(zy);
+    __syncwarp();
+    Dit<BQ, false>::run(zx);
+    Dit<BQ, false>::run(zy);
+}
+
+// One-sided spectra of both transforms; emit(fr, k, X, Y, slot) with the slot convention of warp_fft_post_pk (odd slots carry
+// the conjugates of X[M - k], Y[M - k]).  The post-processing twiddle of a slot is formed once for both.
+template <class P, class Emit>
+__device__ __forceinline__ void warp_fft_post2_pk(const cf (&zx)[P::BQ], const cf (&zy)[P::BQ], const float2* __restrict__ pt, int lane,
+                                                  Emit emit) {
+    constexpr int A = P::A, BQ = P::BQ, M = P::M;
+    const int k1 = lane % A, fr = lane / A;
+    const int plane = fr * A + ((A - k1) % A);
+    const cf base = ldg_cf(pt + k1);
+    static_for<0, BQ / 2>([&](auto jc) {
+        constexpr int j = decltype(jc)::value;
+        cf px = __shfl_sync(0xffffffffu, zx[BQ - 1 - j], plane);
+        cf py = __shfl_sync(0xffffffffu, zy[BQ - 1 - j], plane);
+        if (k1 == 0) { px = zx[(BQ - j) % BQ]; py = zy[(BQ - j) % BQ]; }
+        const cf pxc = cnj(px), pyc = cnj(py);
+        const cf Sx = add2(zx[j], pxc), Dx = sub2(zx[j], pxc);
+        const cf Sy = add2(zy[j], pyc), Dy = sub2(zy[j], pyc);
+        const cf cs = post_twiddle_pk<BQ, j>(base);
+        const cf Tx = fma2(rotm(Dx), bc(lo(cs)), mul2(Dx, bc(-hi(cs))));
+        const cf Ty = fma2(rotm(Dy), bc(lo(cs)), mul2(Dy, bc(-hi(cs))));
+        const int k = k1 + A * j;
+        emit(fr, k, add2(Sx, Tx), add2(Sy, Ty), 2 * j);
+        emit(fr, M - k, sub2(Sx, Tx), sub2(Sy, Ty), 2 * j + 1);
+    });
+    if (k1 == 0) emit(fr, M / 2, mul2(cnj(zx[BQ / 2]), bc(2.0f)), mul2(cnj(zy[BQ / 2]), bc(2.0f)), BQ);
+}
+
 // ------------------------------------------------------------------ adjoint transform
 // grad(fr, k, slot) returns, for the slot convention of warp_fft_post_pk, dL/dX[k] (even slots, slot BQ) or
 // conj(dL/dX[M-k]) (odd slots).  store(integral_constant s, f2, integral_constant a, b, v) receives the gradient of the

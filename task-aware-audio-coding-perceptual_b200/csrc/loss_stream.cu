@@ -27,6 +27,9 @@ constexpr int kStreamThreads = kStreamWarps * 32;
 #ifndef TAC_STREAM_PK
 #define TAC_STREAM_PK 1       // packed-complex core (FFMA2); 0 = the scalar core of fft_core.cuh
 #endif
+#ifndef TAC_STREAM_JOINT
+#define TAC_STREAM_JOINT 1    // x and y frames through the forward transform together (fft_core_pk.cuh: warp_fft_fwd2_pk): 1 = plans below n = 2048, 2 = all, 0 = none
+#endif
 #ifndef TAC_RUN_TARGET
 #define TAC_RUN_TARGET 7
 #endif
@@ -259,6 +262,7 @@ __device__ __forceinline__ void st_grad(float* p, cf v) {
 template <class P, bool WITH_SUMS>
 __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamScale& sc, int cta, float2* smem) {
     constexpr int A = P::A, BQ = P::BQ, M = P::M, NFR = P::NFR, NS1 = P::NS1, QA = A / 4;
+    constexpr bool kJoint = TAC_STREAM_JOINT != 0 && (TAC_STREAM_JOINT == 2 || M < 1024);
     static_assert(A % 4 == 0 && NFR * M * 3 / 4 <= kOlaFloat2, "plan does not fit the streaming overlap-add ring");
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float2* xbuf = smem + warp * kStreamWarpFloat2;
@@ -303,9 +307,7 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
     const float eps = a.eps;
     float l1 = 0.0f, ll = 0.0f;
     for (int t = 0; t < maxlen; ++t) {
-        cf z[BQ];
         cf G[BQ + 1];
-        float mx[BQ + 1];
         const float* fx[NS1];
         const float* fy[NS1];
 #pragma unroll
@@ -314,6 +316,36 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
             fx[s] = xr + (long long)f * hop;
             fy[s] = yr + (long long)f * hop;
         }
+        float tl1 = 0.0f, tll = 0.0f;
+        if constexpr (kJoint) {
+        // x and y frames through the transform TOGETHER: one window / twiddle load for both, two independent butterfly streams
+        // (A/B on B200, cfg 2: n = 512 scale 0.172 -> 0.157 ms, n = 1024 0.182 -> 0.180 ms; n = 2048 0.159 -> 0.160 ms -- its 64
+        // complex values per lane leave no room for a second transform -- so the largest plan keeps the sequential form)
+        cf zx[BQ], zy[BQ];
+        auto load_xy = [&](auto scn, int, int m, auto ac, cf& vx, cf& vy) {
+            const cf w = window(scn, ac, m);
+            vx = mul2(ld_frame<(4 * decltype(ac)::value) / A>(fx[decltype(scn)::value] + 2 * m), w);
+            vy = mul2(ld_frame<(4 * decltype(ac)::value) / A>(fy[decltype(scn)::value] + 2 * m), w);
+        };
+        warp_fft_fwd2_pk<P>(zx, zy, xbuf, sc.t.tw, lane, load_xy);
+        warp_fft_post2_pk<P>(zx, zy, sc.t.pt, lane, [&](int, int, cf vx, cf v, int slot) {
+            const float xr_ = lo(vx), xi_ = hi(vx);
+            const float xv = fast_mag(fmaf(xr_, xr_, xi_ * xi_));         // |X|
+            const float vr = lo(v), vi = hi(v);
+            const float m2 = fmaf(vr, vr, vi * vi);
+            const float inv = m2 >= kTinyMag2 ? fast_rsqrt(m2) : 0.0f;
+            const float my = m2 * inv;                                    // |Y|
+            const float d = my - xv;
+            const float dl = fast_lg2(fmaxf(my, eps)) - fast_lg2(fmaxf(xv, eps));
+            if (WITH_SUMS) { tl1 += fabsf(d); tll += fabsf(dl); }
+            const float invm = my >= eps ? inv : 0.0f;
+            float g = fmaf(signed_coef(dl, c_log), invm, signed_coef(d, c_l1));
+            g *= inv;
+            G[slot] = mul2(v, bc(g));                                     // dL/dY[k]  (odd slots: its conjugate)
+        });
+        } else {
+        cf z[BQ];
+        float mx[BQ + 1];
         auto load_x = [&](auto scn, int, int m, auto ac) -> cf {
             return mul2(ld_frame<(4 * decltype(ac)::value) / A>(fx[decltype(scn)::value] + 2 * m), window(scn, ac, m));
         };
@@ -326,7 +358,6 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
             mx[slot] = fast_mag(fmaf(vr, vr, vi * vi));                   // |X|
         });
         warp_fft_fwd_pk<P>(z, xbuf, sc.t.tw, lane, load_y);
-        float tl1 = 0.0f, tll = 0.0f;
         warp_fft_post_pk<P>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
             const float vr = lo(v), vi = hi(v);
             const float m2 = fmaf(vr, vr, vi * vi);
@@ -341,6 +372,7 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
             g *= inv;
             G[slot] = mul2(v, bc(g));                                     // dL/dY[k]  (odd slots: its conjugate)
         });
+        }
         if (WITH_SUMS && t < len_post) { l1 += tl1; ll += tll; }
         warp_fft_adj_pk<P>(xbuf, sc.t.tw, sc.t.pt, lane,
             [&](int, int, int slot) -> cf { return G[slot]; },

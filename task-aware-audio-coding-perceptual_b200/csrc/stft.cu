@@ -241,7 +241,9 @@ __global__ void __launch_bounds__(kThreads, 1) stft_tiled_kernel(const TiledArgs
 // TF = kFeWarps * NFR consecutive frames of one row.  The per-warp exchange tiles are only needed during the transform and
 // the two [K][TF + 1] transposition tiles (magnitude, phase) only after it, so they live in the SAME shared memory; both
 // planes leave in one pass, every (k) row as a contiguous run of TF frames.  With 8 warps a CTA needs 96 KiB and two are
-// resident per SM: one computes while the other stages its samples or writes out.  atan2 is a degree-15 odd minimax
+// resident per SM: one computes while the other stages its samples or writes out.  (Recorded negative results, A/B on B200:
+// 128-bit write-out stores, 4 frames of one row per instruction, 0.109 -> 0.114 ms; 4-warp CTAs, four per SM, 0.118 ms --
+// the kernel waits on its phase latencies, not on the store path.)  atan2 is a degree-15 odd minimax
 // polynomial (1.2e-7 abs. error in fp32) instead of the library call.
 #ifndef TAC_FE_WARPS
 #define TAC_FE_WARPS 8          // 8-warp CTAs (96 KiB, two per SM): one CTA computes while the other stages / writes out -- 0.136 -> 0.109 ms on cfg 2 against 16-warp CTAs

@@ -53,6 +53,32 @@ __device__ __forceinline__ void stage_tile(float* tile, const float* __restrict_
     }
 }
 
+#ifndef TAC_PLANES_BULK
+#define TAC_PLANES_BULK 1     // 1: a task's two plane spans leave through shared memory as bulk async copies; 0: 4-byte streaming stores
+#endif
+
+__device__ __forceinline__ void bulk_wait_read() {            // this thread's bulk copies have finished READING shared memory
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+
+// One contiguous span of `len` floats, staged at stg[mis .. mis + len) with mis = (global float address) & 3 so that the
+// 16-byte aligned middle of the span is 16-byte aligned in shared memory too: lane 0 hands the middle to the copy engine
+// (cp.async.bulk.global.shared::cta, issued by lane `issuer`), lanes 8.. store the <= 3 + 3 head / tail floats.  Called by the
+// whole warp after a fence.proxy.async + __syncwarp.
+__device__ __forceinline__ void bulk_store_span(float* gdst, const float* stg, int mis, int len, int lane, int issuer) {
+    const int head = min((4 - mis) & 3, len);
+    const int mid = (len - head) & ~3;
+    const int tail = len - head - mid;
+    if (lane == issuer && mid > 0) {
+        const unsigned src = (unsigned)__cvta_generic_to_shared(stg + mis + head);
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                     :: "l"(gdst + head), "r"(src), "r"(mid * 4) : "memory");
+    }
+    const int e = lane - 8;
+    if (e >= 0 && e < head) __stcs(gdst + e, stg[mis + e]);
+    else if (e >= head && e < head + tail) __stcs(gdst + mid + e, stg[mis + mid + e]);
+}
+
 // One warp task of the planes kernel: frames [f_first, f_first + NFR) of one scale.
 template <class P>
 __device__ __forceinline__ void planes_task(const ScaleArg& sc, const float* tile, float2* xbuf, int lane,
@@ -67,11 +93,73 @@ __device__ __forceinline__ void planes_task(const ScaleArg& sc, const float* til
         // a plain product (mul.rn, never contracted): X(x) is bit-reproducible
         return mul2(*reinterpret_cast<const cf*>(tile + (f * hop - tile_origin) + 2 * m), ldg_cf(win2 + m));
     };
+    // How a task's output leaves (A/B per plan on B200, cfg 4 single-scale, ms: direct 4-byte stores / one span per task /
+    // one row per frame): n = 2048: 0.628 / 0.472 / =; 1024: 0.613 / 0.546 / 0.491; 512: 0.597 / 0.563 / 0.563;
+    // 256: 0.616 / 0.569 / 0.665; 128: 0.669 / 0.704 / 1.000 -- the copy engine wins once a row is ~2 KB.
+    constexpr int kMode = !TAC_PLANES_BULK ? 0 : (P::M >= 512 ? 2 : (P::M >= 128 ? 1 : 0));
+#if TAC_PLANES_BULK
+    if (lane < 8) bulk_wait_read();                        // the previous task's rows (any scale: up to 8 issuing lanes) have left
+    __syncwarp();                                          // the exchange tile
+#endif
     warp_fft_fwd_pk<P>(z, xbuf, sc.t.tw, lane, load);
     const int myf = f_first + lane / P::A;
     const bool valid = myf < f_end;
-    // per-lane base pointers so that every store address is base + compile-time offset
     const int k1 = lane % P::A;
+    if constexpr (kMode != 0) {
+    // The exchange tile is free after the forward transform: it stages the task's output rows (one frame of one plane = K
+    // contiguous floats in HBM, because K is the innermost dimension; the frames of a task follow each other).  A row (mode 2)
+    // or the whole span of the task (mode 1) is staged at its global misalignment (address & 3 floats) so that its 16-byte
+    // aligned middle is aligned in shared memory too and can be handed to the copy engine.  Mode 2: rows of different frames
+    // sit SF floats apart with SF = A (mod 32), so the A lanes of every frame hit their own bank range (K = 1 (mod 32) itself
+    // puts frame g one bank off frame g - 1: 2- to 4-way conflicts, 45 M extra wavefronts on cfg 4 -- accepted in mode 1,
+    // where per-row copies of 0.25 - 0.5 KB cost more than the conflicts).
+    constexpr int SF = kMode == 1 ? P::M + 1 : (P::NFR == 1 ? ((P::M + 1 + 3 + 3) & ~3) : ((P::M + 1 + 3 - P::A + 31) / 32 * 32 + P::A));
+    constexpr int R = kMode == 1 ? ((P::NFR * (P::M + 1) + 3 + 3) & ~3) : P::NFR * SF;   // floats per staged plane
+    static_assert(2 * R * sizeof(float) <= kXbufFloat2 * sizeof(float2), "staged rows do not fit the exchange tile");
+    float* stg_re = reinterpret_cast<float*>(xbuf);
+    float* stg_im = stg_re + R;
+    float* g_re0 = out_re_row + (long long)f_first * sc.K;
+    const int fr = lane / P::A;
+    const long long goff = kMode == 1 ? 0 : (long long)fr * sc.K;          // mode 1: one shift for the task's span
+    const int mis_re = (int)((reinterpret_cast<uintptr_t>(g_re0 + goff) >> 2) & 3u);
+    const int mis_im = (int)((reinterpret_cast<uintptr_t>(g_re0 + im_off + goff) >> 2) & 3u);
+    float* s_re = stg_re + fr * SF + mis_re + k1;                          // bins k1 + A j
+    float* s_im = stg_im + fr * SF + mis_im + k1;
+    float* h_re = stg_re + fr * SF + mis_re + (P::M - k1);                 // bins M - k1 - A j (consecutive lanes: consecutive banks)
+    float* h_im = stg_im + fr * SF + mis_im + (P::M - k1);
+    warp_fft_post_pk<P, true>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
+        const float vr = lo(v), vi = hi(v);
+        if (valid) {
+            if (slot == P::BQ) {                       // k = M/2 (k1 == 0 lanes only)
+                s_re[P::M / 2] = vr; s_im[P::M / 2] = vi;
+            } else if (slot & 1) {                     // k = M - k1 - A*j
+                h_re[-P::A * (slot >> 1)] = vr; h_im[-P::A * (slot >> 1)] = vi;
+            } else {                                   // k = k1 + A*j
+                s_re[P::A * (slot >> 1)] = vr; s_im[P::A * (slot >> 1)] = vi;
+            }
+        }
+    });
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> visible to the copy engine
+    __syncwarp();
+    const int nv = min(P::NFR, f_end - f_first);
+    if constexpr (kMode == 1) {
+        const int mr = (int)((reinterpret_cast<uintptr_t>(g_re0) >> 2) & 3u), mi = (int)((reinterpret_cast<uintptr_t>(g_re0 + im_off) >> 2) & 3u);
+        bulk_store_span(g_re0, stg_re, mr, nv * sc.K, lane, 0);
+        bulk_store_span(g_re0 + im_off, stg_im, mi, nv * sc.K, lane, 0);
+    } else {
+#pragma unroll
+        for (int g = 0; g < P::NFR; ++g) {
+            if (g < nv) {
+                float* gr = g_re0 + (long long)g * sc.K;
+                float* gi = gr + im_off;
+                bulk_store_span(gr, stg_re + g * SF, (int)((reinterpret_cast<uintptr_t>(gr) >> 2) & 3u), sc.K, lane, g);
+                bulk_store_span(gi, stg_im + g * SF, (int)((reinterpret_cast<uintptr_t>(gi) >> 2) & 3u), sc.K, lane, g);
+            }
+        }
+    }
+    if (lane < P::NFR) asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    } else {
+    // per-lane base pointers so that every store address is base + compile-time offset
     float* re_lo = out_re_row + (long long)myf * sc.K + k1;
     float* re_hi = out_re_row + (long long)myf * sc.K + (P::M - k1);
     float* im_lo = re_lo + im_off;
@@ -88,6 +176,7 @@ __device__ __forceinline__ void planes_task(const ScaleArg& sc, const float* til
             }
         }
     });
+    }
 }
 
 __global__ void __launch_bounds__(kThreads, 2) stft_planes_kernel(const PlanesArgs a) {
@@ -150,6 +239,9 @@ __global__ void __launch_bounds__(kThreads, 2) stft_planes_kernel(const PlanesAr
             default: planes_task<Plan64>(sc, tile, xbuf, lane, f_first, f_end, origin, out_re_row, im_off); break;
         }
     }
+#if TAC_PLANES_BULK
+    if (lane < 8) bulk_wait_read();                        // shared memory must outlive the copy engine's reads
+#endif
 }
 
 // ------------------------------------------------------------------------------------------
@@ -476,7 +568,13 @@ extern "C" int tac_stft_multi(const float* x, int64_t B, int64_t C, int64_t T, i
     if (out_mode == TAC_OUT_PLANES) {
         PlanesArgs a;
         a.x = x; a.T = T; a.C = (int)C; a.nscales = n_scales; a.pad_mode = pad_mode; a.vec_ok = vec_ok;
-        a.chunk = 4096;
+        // samples of a row per CTA: 8192 when that still leaves every SM a few CTAs per row batch (long clips: the tile load and
+        // the launch are amortised over twice the tasks, cfg 4 2.20 -> 2.08 ms), else 4096 (1 s clips: 0.138 against 0.160 ms)
+#ifdef TAC_PLANES_CHUNK
+        a.chunk = TAC_PLANES_CHUNK;
+#else
+        a.chunk = (T >= 4 * 8192 && rows * ((T + 8191) / 8192) >= 8ll * 2 * kNumSMs) ? 8192 : 4096;
+#endif
         a.pmax = center ? nmax / 2 : 0;
         long long last_start = 0;
         for (int s = 0; s < n_scales; ++s) {
@@ -493,7 +591,7 @@ extern "C" int tac_stft_multi(const float* x, int64_t B, int64_t C, int64_t T, i
         a.nchunks = (int)(last_start / a.chunk) + 1;
         a.tile_len = a.chunk + nmax;
         const size_t smem = (size_t)a.tile_len * sizeof(float) + (size_t)kWarps * kXbufFloat2 * sizeof(float2);
-        TAC_SMEM_OPT_IN(stft_planes_kernel, 110 * 1024);
+        TAC_SMEM_OPT_IN(stft_planes_kernel, 111 * 1024);
         const long long grid = rows * a.nchunks;
         TAC_REQUIRE(grid < (1ll << 31), "grid too large");
         stft_planes_kernel<<<(unsigned)grid, kThreads, smem, st>>>(a); TAC_LAUNCHED(1);

@@ -524,6 +524,18 @@ extern "C" int tac_dpca_project(const float* const* z, int nv, int64_t B, int d,
         vp.z[i] = z[i]; vp.out[i] = z_out[i];
     }
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+#ifndef TAC_PROJECT_TC
+#define TAC_PROJECT_TC 1
+#endif
+    if (TAC_PROJECT_TC && d <= kTcFeat) {          // both contractions on tcgen05, one launch (dpca_tc.cuh)
+        PjPtrs pp;
+        for (int i = 0; i < 8; ++i) { pp.z[i] = vp.z[i < nv ? i : 0]; pp.out[i] = vp.out[i < nv ? i : 0]; }
+        TAC_SMEM_OPT_IN(dpca_project_tc_kernel, kPjSmemBytes);
+        dpca_project_tc_kernel<<<dim3((unsigned)((B + 127) / 128), nv), kPjThreads, kPjSmemBytes, st>>>(pp, B, d, v, mu, idx, cnt);
+        TAC_LAUNCHED(1);
+        TAC_CHECK_CUDA(cudaGetLastError());
+        return TAC_OK;
+    }
     float* P = reinterpret_cast<float*>(workspace);
     dpca_projector_kernel<<<dim3(d, nv), ((d + 31) / 32) * 32, 0, st>>>(v, idx, cnt, d, P); TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());

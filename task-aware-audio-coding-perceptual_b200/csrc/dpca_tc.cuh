@@ -262,6 +262,212 @@ dpca_gram_finish_kernel(const float* __restrict__ partial, const double* __restr
     if (push) xchg_push_commit(xd, seq, gridDim.x * gridDim.y);
 }
 
+// ------------------------------------------------------------------------------------------ projection on tcgen05
+// z_out = (z - mu) P + mu,  P = V_sel V_sel^T  (pkl_file_model_updated.py:503-511: project on the selected components and
+// back), both contractions on the tensor pipe in ONE kernel, 3xTF32 split precision as above:
+//   GEMM 1  P[128 x 128]    = W W^T,      W[f][t] = V[f][idx[t]]   (K = selected components, zero-padded to a multiple of 8)
+//   GEMM 2  D[128 rows x 128] = Zc P,     Zc = z - mu               (K = features, two halves of 64 through one 64 KiB buffer)
+// A CTA owns 128 batch rows of one view.  W is gathered into the canonical K-major tile (hi | lo), P comes back from TMEM
+// (lane = row n, 128 columns), is split again and written over the W tile as GEMM 2's B operand -- B[n][k] = P[k][n] = P[n][k]
+// by symmetry, so the row a thread reads from TMEM is the row it stores.  Replaces dpca_projector_kernel + the 32 x 32 SIMT
+// tile of dpca_apply_kernel on the tac_dpca_project path (d <= 128).
+constexpr int kPjThreads = 128;
+constexpr int kPjTileB = 16 * (int)kTcKGroup;                 // 64 KiB: one 128 x 128 operand (hi or lo)
+constexpr int kPjTileA = 8 * (int)kTcKGroup;                  // 32 KiB: 128 rows x 64 features (hi or lo)
+constexpr int kPjSmemBytes = 2 * kPjTileB + 2 * kPjTileA + 1024;
+
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+struct PjPtrs { const float* z[8]; float* out[8]; };
+
+// grid (ceil(B / 128), nv); block 128.
+__global__ void __launch_bounds__(kPjThreads, 1)
+dpca_project_tc_kernel(const PjPtrs vp, long long B, int d, const float* __restrict__ vmat, const float* __restrict__ mu,
+                       const int* __restrict__ idx, const int* __restrict__ cnt) {
+    extern __shared__ unsigned char pj_smem_raw[];
+    __shared__ __align__(8) uint64_t s_bar;
+    __shared__ uint32_t s_tmem;
+    __shared__ float s_mu[kTcFeat];
+    __shared__ int s_idx[kTcFeat];
+
+    const int v = blockIdx.y, tid = threadIdx.x, warp = tid >> 5;
+    const long long r0 = (long long)blockIdx.x * 128;
+    const float* z = vp.z[v];
+    float* out = vp.out[v];
+    const float* V = vmat + (size_t)v * d * d;
+    const int k = min(max(cnt[v], 0), d);
+
+    const uint32_t raw = tc_smem_u32(pj_smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;
+    unsigned char* bh = pj_smem_raw + (base - raw);               // W, then P:  hi | lo
+    unsigned char* bl = bh + kPjTileB;
+    unsigned char* ah = bl + kPjTileB;                            // Zc half:    hi | lo
+    unsigned char* al = ah + kPjTileA;
+
+    s_mu[tid] = tid < d ? mu[(size_t)v * d + tid] : 0.0f;
+    s_idx[tid] = tid < k ? idx[(size_t)v * d + tid] : 0;
+    if (k == 0) {                                                 // nothing selected in this view: z_out = mu
+        __syncthreads();
+        const long long row = r0 + tid;
+        if (row < B)
+            for (int c = 0; c < d; ++c) out[row * d + c] = s_mu[c];
+        return;
+    }
+    if (tid == 0) {
+        tc_mbar_init(&s_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     :: "r"(tc_smem_u32(&s_tmem)), "r"(256u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = s_tmem;
+
+    // ---- GEMM 1: W tile (gather of the selected eigenvectors), item = (component quad q, feature f)
+    const int ng1 = (k + 7) >> 3;
+    for (int it = tid; it < ng1 * 2 * kTcFeat; it += kPjThreads) {
+        const int f = it % kTcFeat, q = it / kTcFeat;
+        float a[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            a[i] = (f < d && 4 * q + i < k) ? __ldg(V + (size_t)f * d + s_idx[4 * q + i]) : 0.0f;
+        float4 h, l;
+        h.x = tc_to_tf32(a[0]); h.y = tc_to_tf32(a[1]); h.z = tc_to_tf32(a[2]); h.w = tc_to_tf32(a[3]);
+        l.x = tc_to_tf32(a[0] - h.x); l.y = tc_to_tf32(a[1] - h.y); l.z = tc_to_tf32(a[2] - h.z); l.w = tc_to_tf32(a[3] - h.w);
+        const size_t off = (size_t)(q >> 1) * kTcKGroup + (size_t)(f >> 3) * kTcSBO + (size_t)(q & 1) * kTcLBO + (size_t)(f & 7) * 16;
+        *reinterpret_cast<float4*>(bh + off) = h;
+        *reinterpret_cast<float4*>(bl + off) = l;
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (tid == 0) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t ha = tc_smem_u32(bh), la = tc_smem_u32(bl);
+        for (int g = 0; g < ng1; ++g) {
+            const uint64_t dh = tc_make_desc(ha + g * kTcKGroup), dl = tc_make_desc(la + g * kTcKGroup);
+            tc_mma(tmem, dh, dh, g > 0 ? 1u : 0u);
+            tc_mma(tmem, dh, dl, 1u);
+            tc_mma(tmem, dl, dh, 1u);
+        }
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+                     :: "r"(tc_smem_u32(&s_bar)) : "memory");
+    }
+    tc_mbar_wait(&s_bar, 0u);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+
+    // ---- P: TMEM (lane n = row n) -> split -> B operand tile over the W tile (its MMAs have retired)
+    {
+        const int n = tid;
+#pragma unroll 1
+        for (int c0 = 0; c0 < kTcFeat; c0 += 32) {
+            uint32_t r[32];
+            tc_ld32(tmem + ((uint32_t)(32 * warp) << 16) + (uint32_t)c0, r);
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+                const int kk = c0 + j;
+                float a[4] = {__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3])};
+                float4 h, l;
+                h.x = tc_to_tf32(a[0]); h.y = tc_to_tf32(a[1]); h.z = tc_to_tf32(a[2]); h.w = tc_to_tf32(a[3]);
+                l.x = tc_to_tf32(a[0] - h.x); l.y = tc_to_tf32(a[1] - h.y); l.z = tc_to_tf32(a[2] - h.z); l.w = tc_to_tf32(a[3] - h.w);
+                const size_t off = (size_t)(kk >> 3) * kTcKGroup + (size_t)(n >> 3) * kTcSBO + (size_t)((kk & 7) >> 2) * kTcLBO + (size_t)(n & 7) * 16;
+                *reinterpret_cast<float4*>(bh + off) = h;
+                *reinterpret_cast<float4*>(bl + off) = l;
+            }
+        }
+    }
+
+    // ---- GEMM 2: D = Zc P in two feature halves; thread <-> batch row
+    const long long row = r0 + tid;
+    const float* zr = z + row * d;
+    const bool vec = (d & 3) == 0 && ((reinterpret_cast<uintptr_t>(z) | reinterpret_cast<uintptr_t>(out)) & 15u) == 0;
+#pragma unroll 1
+    for (int half = 0; half < 2; ++half) {
+        if (64 * half >= d) break;                                // uniform: no features in this half
+        if (half == 1) {                                          // the MMAs that read the A buffer must have retired
+            tc_mbar_wait(&s_bar, 1u);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        }
+#pragma unroll 4
+        for (int kq = 0; kq < 16; ++kq) {
+            const int f0 = 64 * half + 4 * kq;
+            float a[4];
+            if (vec && row < B && f0 + 3 < d) {
+                const float4 q = __ldg(reinterpret_cast<const float4*>(zr + f0));
+                a[0] = q.x - s_mu[f0]; a[1] = q.y - s_mu[f0 + 1]; a[2] = q.z - s_mu[f0 + 2]; a[3] = q.w - s_mu[f0 + 3];
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) a[i] = (row < B && f0 + i < d) ? __ldg(zr + f0 + i) - s_mu[f0 + i] : 0.0f;
+            }
+            float4 h, l;
+            h.x = tc_to_tf32(a[0]); h.y = tc_to_tf32(a[1]); h.z = tc_to_tf32(a[2]); h.w = tc_to_tf32(a[3]);
+            l.x = tc_to_tf32(a[0] - h.x); l.y = tc_to_tf32(a[1] - h.y); l.z = tc_to_tf32(a[2] - h.z); l.w = tc_to_tf32(a[3] - h.w);
+            const size_t off = (size_t)(kq >> 1) * kTcKGroup + (size_t)(tid >> 3) * kTcSBO + (size_t)(kq & 1) * kTcLBO + (size_t)(tid & 7) * 16;
+            *reinterpret_cast<float4*>(ah + off) = h;
+            *reinterpret_cast<float4*>(al + off) = l;
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        if (tid == 0) {
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t aha = tc_smem_u32(ah), ala = tc_smem_u32(al), bha = tc_smem_u32(bh), bla = tc_smem_u32(bl);
+            for (int g = 0; g < 8; ++g) {
+                const int kg = 8 * half + g;
+                const uint64_t dah = tc_make_desc(aha + g * kTcKGroup), dal = tc_make_desc(ala + g * kTcKGroup);
+                const uint64_t dbh = tc_make_desc(bha + kg * kTcKGroup), dbl = tc_make_desc(bla + kg * kTcKGroup);
+                tc_mma(tmem + 128u, dah, dbh, (half > 0 || g > 0) ? 1u : 0u);
+                tc_mma(tmem + 128u, dah, dbl, 1u);
+                tc_mma(tmem + 128u, dal, dbh, 1u);
+            }
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+                         :: "r"(tc_smem_u32(&s_bar)) : "memory");
+        }
+    }
+    tc_mbar_wait(&s_bar, d > 64 ? 0u : 1u);                       // third (or, with one half, second) completion of the barrier
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+
+    // ---- epilogue: + mu, one batch row per thread
+#pragma unroll 1
+    for (int c0 = 0; c0 < kTcFeat; c0 += 32) {
+        if (c0 >= d) break;                                       // uniform
+        uint32_t r[32];
+        tc_ld32(tmem + ((uint32_t)(32 * warp) << 16) + 128u + (uint32_t)c0, r);
+        if (row < B) {
+            float* o = out + row * d + c0;
+            if (vec && c0 + 32 <= d) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4)
+                    *reinterpret_cast<float4*>(o + j) = make_float4(__uint_as_float(r[j]) + s_mu[c0 + j], __uint_as_float(r[j + 1]) + s_mu[c0 + j + 1],
+                                                                     __uint_as_float(r[j + 2]) + s_mu[c0 + j + 2], __uint_as_float(r[j + 3]) + s_mu[c0 + j + 3]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (c0 + j < d) o[j] = __uint_as_float(r[j]) + s_mu[c0 + j];
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "r"(256u) : "memory");
+}
+
 inline size_t dpca_tc_workspace_bytes(int nv, long long B, int d) {
     if (d > kTcFeat) return 0;
     const long long nsplit = (B + kTcRowsPerCta - 1) / kTcRowsPerCta;

@@ -56,7 +56,7 @@ struct StreamArgs {
     const float* x;
     const float* y;
     long long T, rows;
-    int nscales, total_ctas;
+    int nscales, total_ctas, cta_base;   // cta_base: global index of this launch's CTA 0 (the n = 512 scales run as a second launch)
     float eps;
     const float* coef;           // [2 * nscales] device
     double* partial;             // [total_ctas][kStreamWarps][2] or null
@@ -89,7 +89,7 @@ __device__ __forceinline__ void stream_cta(const StreamArgs& a, const StreamScal
     float2* ola = xbuf + kXbufFloat2;                      // [NFR][4 quarters][QA][BQ]
     const long long wr = (long long)cta * kStreamWarps + warp;    // warp-run index inside the scale
     if (wr >= sc.nwr) {                                            // spare warp of the scale's last CTA
-        if (WITH_SUMS && lane < 2) a.partial[((long long)blockIdx.x * kStreamWarps + warp) * 2 + lane] = 0.0;
+        if (WITH_SUMS && lane < 2) a.partial[((long long)(blockIdx.x + a.cta_base) * kStreamWarps + warp) * 2 + lane] = 0.0;
         return;
     }
     const long long row = wr / sc.wpr;
@@ -212,7 +212,7 @@ __device__ __forceinline__ void stream_cta(const StreamArgs& a, const StreamScal
     if (WITH_SUMS) {                                       // fixed lane -> warp order, one partial per warp: deterministic sums
         l1 = warp_sum(l1); ll = warp_sum(ll);
         if (lane == 0) {
-            double* pp = a.partial + ((long long)blockIdx.x * kStreamWarps + warp) * 2;
+            double* pp = a.partial + ((long long)(blockIdx.x + a.cta_base) * kStreamWarps + warp) * 2;
             pp[0] = (double)l1; pp[1] = (double)ll * 0.69314718055994530942;
         }
     }
@@ -269,7 +269,7 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
     cf* ola = reinterpret_cast<cf*>(xbuf + kXbufFloat2);  // [NFR][3 slots][QA][BQ]: hop block j of a frame group lives in slot j % 3
     const long long wr = (long long)cta * kStreamWarps + warp;
     if (wr >= sc.nwr) {
-        if (WITH_SUMS && lane < 2) a.partial[((long long)blockIdx.x * kStreamWarps + warp) * 2 + lane] = 0.0;
+        if (WITH_SUMS && lane < 2) a.partial[((long long)(blockIdx.x + a.cta_base) * kStreamWarps + warp) * 2 + lane] = 0.0;
         return;
     }
     const long long row = wr / sc.wpr;
@@ -417,7 +417,7 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
     if (WITH_SUMS) {
         l1 = warp_sum(l1); ll = warp_sum(ll);
         if (lane == 0) {
-            double* pp = a.partial + ((long long)blockIdx.x * kStreamWarps + warp) * 2;
+            double* pp = a.partial + ((long long)(blockIdx.x + a.cta_base) * kStreamWarps + warp) * 2;
             pp[0] = (double)l1; pp[1] = (double)ll * 0.69314718055994530942;
         }
     }
@@ -427,14 +427,24 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
 #define TAC_STREAM_OCC 2      // 255 registers; 3 (168 registers) spills and measured no faster
 #endif
 
+#ifndef TAC_STREAM_SPLIT
+#define TAC_STREAM_SPLIT 1    // the n = 512 scales as a second, programmatically dependent launch at 3 CTAs per SM (168 registers, no spills)
+#endif
+
 template <bool WITH_SUMS>
 __global__ void __launch_bounds__(kStreamThreads, TAC_STREAM_OCC) mrstft_stream_kernel(const StreamArgs a) {
     extern __shared__ __align__(16) unsigned char stream_smem_raw[];
     float2* smem = reinterpret_cast<float2*>(stream_smem_raw);
+#if TAC_STREAM_SPLIT
+    // the second launch (n = 512 scales) may start as soon as every CTA of this grid has been scheduled: its CTAs fill the
+    // SMs that this grid's last, partial wave leaves idle
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+#endif
+    const int gcta = (int)blockIdx.x + a.cta_base;
     int s = 0;
-    while (s + 1 < a.nscales && (int)blockIdx.x >= a.sc[s + 1].cta_begin) ++s;
+    while (s + 1 < a.nscales && gcta >= a.sc[s + 1].cta_begin) ++s;
     const StreamScale& sc = a.sc[s];
-    const int cta = (int)blockIdx.x - sc.cta_begin;
+    const int cta = gcta - sc.cta_begin;
 #if TAC_STREAM_PK
     switch (sc.n) {                                                                // stream_applicable: n >= 512
         case 2048: stream_cta_pk<Plan2048, WITH_SUMS>(a, sc, cta, smem); break;
@@ -448,6 +458,22 @@ __global__ void __launch_bounds__(kStreamThreads, TAC_STREAM_OCC) mrstft_stream_
         default: stream_cta<Plan512, WITH_SUMS>(a, sc, cta, smem); break;
     }
 #endif
+}
+
+// The n = 512 plan keeps 16 complex values per lane: it compiles to 168 registers without spills, so three CTAs fit an SM
+// (12 warps instead of 8 for a kernel that is bound by dependent-instruction latency).  Launched behind the kernel above
+// with programmatic stream serialisation; before a CTA exits it waits for the primary grid (griddepcontrol.wait), so that
+// the completion of THIS grid implies the completion of both -- the combine kernel behind it reads the planes of all scales.
+template <bool WITH_SUMS>
+__global__ void __launch_bounds__(kStreamThreads, 3) mrstft_stream_small_kernel(const StreamArgs a) {
+    extern __shared__ __align__(16) unsigned char stream_smem_raw[];
+    float2* smem = reinterpret_cast<float2*>(stream_smem_raw);
+    const int gcta = (int)blockIdx.x + a.cta_base;
+    int s = 0;
+    while (s + 1 < a.nscales && gcta >= a.sc[s + 1].cta_begin) ++s;
+    const StreamScale& sc = a.sc[s];
+    stream_cta_pk<Plan512, WITH_SUMS>(a, sc, gcta - sc.cta_begin, smem);
+    asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 // grad[row][t] = sum over scales (fixed order) of g_s[t] (+ h_s[t] on the first three hop blocks of runs r >= 1);
@@ -596,9 +622,34 @@ int launch_stream(const float* x, const float* y, int64_t rows, int64_t T, int n
     void (*kern)(const StreamArgs) = sums ? mrstft_stream_kernel<true> : mrstft_stream_kernel<false>;
     if (sums) TAC_SMEM_OPT_IN(mrstft_stream_kernel<true>, smem);
     else TAC_SMEM_OPT_IN(mrstft_stream_kernel<false>, smem);
-    kern<<<(unsigned)tot, kStreamThreads, smem, st>>>(a);
-    TAC_LAUNCHED(1);
-    TAC_CHECK_CUDA(cudaGetLastError());
+    // scales are ordered heavy first: [0, n_big) CTAs belong to n >= 1024, the rest to n = 512
+    long long n_big = tot;
+    for (int i = 0; i < n_scales; ++i)
+        if (a.sc[i].n == 512) { n_big = a.sc[i].cta_begin; break; }
+    a.cta_base = 0;
+    if (TAC_STREAM_SPLIT && TAC_STREAM_PK && n_big > 0 && n_big < tot) {
+        void (*small)(const StreamArgs) = sums ? mrstft_stream_small_kernel<true> : mrstft_stream_small_kernel<false>;
+        if (sums) TAC_SMEM_OPT_IN(mrstft_stream_small_kernel<true>, smem);
+        else TAC_SMEM_OPT_IN(mrstft_stream_small_kernel<false>, smem);
+        kern<<<(unsigned)n_big, kStreamThreads, smem, st>>>(a);
+        TAC_LAUNCHED(1);
+        TAC_CHECK_CUDA(cudaGetLastError());
+        StreamArgs b = a;
+        b.cta_base = (int)n_big;
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3((unsigned)(tot - n_big)); cfg.blockDim = dim3(kStreamThreads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        TAC_CHECK_CUDA(cudaLaunchKernelEx(&cfg, small, b));
+        TAC_LAUNCHED(1);
+    } else {
+        kern<<<(unsigned)tot, kStreamThreads, smem, st>>>(a);
+        TAC_LAUNCHED(1);
+        TAC_CHECK_CUDA(cudaGetLastError());
+    }
     const bool v4 = (T % 4 == 0) && ((reinterpret_cast<uintptr_t>(grad_y) & 15u) == 0);
     const long long items = rows * (T / (v4 ? 4 : 2));
     long long cg = (items + 255) / 256;

@@ -87,9 +87,16 @@ def _check_grad(got, ref, what):
     scale = float(ref.abs().max())
     err = (got - ref).abs()
     bad = err > 1e-4 * scale + 1e-4 * ref.abs()
-    assert float(bad.float().mean()) < 0.05, f"{what}: {int(bad.sum())} of {bad.numel()} elements off, max {float(err.max()):.2e} vs scale {scale:.2e}"
-    assert float(err.median()) < 2e-6 * scale, f"{what}: median error {float(err.median()):.2e} vs scale {scale:.2e}"
-    assert float(err.norm() / ref.norm()) < 5e-3, what
+    bad_frac, med, l2 = float(bad.float().mean()), float(err.median()) / scale, float(err.norm() / ref.norm())
+    print(f"{what}: bad fraction {bad_frac:.3e}, median error / scale {med:.2e}, relative L2 {l2:.2e}")
+    # Measured on B200 over the four CASES and both floors (tools/diag_grad_tol.py, gpurun_out/grad_tol_r02.log): bad fraction
+    # 0 .. 1.3e-2 (ONE flipped bin of a 1024-sample frame marks ~400 of 32 000 elements), median 3e-8 .. 6e-7, relative L2
+    # 4e-7 .. 8.3e-4; torch's own fp32 path against float64 shows flips of the same size on these inputs (4.3e-3 / 1.8e-4 on
+    # the five-scale case).  Bounds = 2.5x the worst measured case; every element is checked strictly where no bin can flip
+    # (test_mrstft_backward_no_kinks, all CASES, both signs).
+    assert bad_frac < 0.03, f"{what}: {int(bad.sum())} of {bad.numel()} elements off, max {float(err.max()):.2e} vs scale {scale:.2e}"
+    assert med < 2e-6, f"{what}: median error {float(err.median()):.2e} vs scale {scale:.2e}"
+    assert l2 < 2e-3, what
 
 
 @pytest.mark.parametrize("B,T,n_ffts", CASES)
@@ -112,12 +119,15 @@ def test_mrstft_backward_default_floor(ts, B, T, n_ffts):
     print(f"relative L2 vs float64: kernel {e_ours:.2e}, torch-fp32 {e_t32:.2e}")
 
 
-def test_mrstft_backward_no_kinks(ts):
-    """Strict check where no bin sits near a kink: y = 0.5 * x makes Y = X / 2 in every bin, so
-    sign(X - Y) = +1 everywhere and the float64 oracle must be matched to rtol 1e-4 on EVERY element."""
-    (x,), _ = O.synth_audio(2, 16000, 1, seed=21)
-    y = 0.5 * x
-    got, _, ref = _grads(ts, x, y, (1024, 2048, 512), eps=1e-2)
+@pytest.mark.parametrize("gain", [0.5, 1.5])
+@pytest.mark.parametrize("B,T,n_ffts", CASES)
+def test_mrstft_backward_no_kinks(ts, B, T, n_ffts, gain):
+    """Strict check where no bin sits near a kink: y = gain * x makes Y = gain * X in every bin, so sign(X - Y) is the
+    same everywhere (+1 for gain 0.5, -1 for 1.5) and the float64 oracle must be matched to rtol 1e-4 on EVERY element --
+    all plans, ragged lengths, run boundaries and edge frames of CASES included."""
+    (x,), _ = O.synth_audio(B, T, 1, seed=21)
+    y = gain * x
+    got, _, ref = _grads(ts, x, y, n_ffts, eps=1e-2)
     scale = float(ref.abs().max())
     err = (got - ref).abs()
     assert bool((err <= 1e-4 * scale + 1e-4 * ref.abs()).all()), float(err.max() / scale)

@@ -375,6 +375,16 @@ def batch_reconstruct_waveform_ref(magnitude_batch: torch.Tensor, phase_batch: t
     return torch.stack(items, dim=0)
 
 
+def reconstruct_and_disc_inputs_ref(magnitude_batch: torch.Tensor, phase_batch: torch.Tensor,
+                                    n_ffts: Sequence[int] = (1024, 2048, 512), hops: Sequence[int] = (256, 512, 128),
+                                    wins: Sequence[int] | None = None) -> Tuple[torch.Tensor, List[torch.Tensor]]:
+    """The ground-truth branch of ``task_aware()``: ``batch_reconstruct_waveform(clean_mag, clean_phase)``
+    (``train_pkl_file_task_aware.py:290``), ``.unsqueeze(1)`` (``:347``), then what ``disc(...)`` (``:353``) computes first
+    for every scale (``msstftd.py:188-191`` -> ``:151-153``).  Returns (waveform ``[B, T]``, per-scale ``[B, 2, F, K]``)."""
+    wav = batch_reconstruct_waveform_ref(magnitude_batch, phase_batch)
+    return wav, multiscale_disc_inputs_ref(wav.unsqueeze(1), n_ffts, hops, wins)
+
+
 # --------------------------------------------------------------------------------------------
 # The bottleneck that is live in the SpectralRes models (row a9) and the task_aware() loss tail (row a5-i)
 # --------------------------------------------------------------------------------------------

@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "tac_spectral", "libtac_spectral.so")
-SOURCES = ["tables.cu", "stft.cu", "stft_ex.cu", "loss.cu", "loss_stream.cu", "dpca.cu", "istft.cu", "latent.cu", "exchange.cu", "tail.cu"]
+SOURCES = ["tables.cu", "stft.cu", "stft_ex.cu", "loss.cu", "loss_stream.cu", "dpca.cu", "istft.cu", "latent.cu", "exchange.cu", "tail.cu", "chain.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--use_fast_math=false"]
 

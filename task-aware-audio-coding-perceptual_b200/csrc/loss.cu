@@ -35,15 +35,19 @@ __device__ __forceinline__ int nfr_of(int n) { return n >= 2048 ? 1 : (n >= 512 
 constexpr int kFwdWarps = 6;
 constexpr int kFwdThreads = kFwdWarps * 32;
 
+// tile[j] = x[g0 + j] (zero behind the row end), g0 >= 0: float4 copies for the aligned in-range part even when the chunk
+// hangs over the row end (the last chunk of every row), scalar for the <= 3 samples behind it.
 __device__ __forceinline__ void stage_plain(float* tile, const float* __restrict__ xr, long long g0, int len,
                                             long long T, bool vec_ok) {
-    if (g0 + len <= T && vec_ok && (g0 & 3) == 0 && (len & 3) == 0) {
+    const long long hi_ll = T - g0;
+    const int hi = (int)(hi_ll < 0 ? 0 : (hi_ll < len ? hi_ll : len));      // in-range samples: j in [0, hi)
+    const int jb = (vec_ok && (g0 & 3) == 0) ? (hi & ~3) : 0;
+    if (jb > 0) {
         const float4* src = reinterpret_cast<const float4*>(xr + g0);
         float4* dst = reinterpret_cast<float4*>(tile);
-        for (int i = threadIdx.x; i < (len >> 2); i += blockDim.x) dst[i] = __ldg(src + i);
-    } else {
-        for (int j = threadIdx.x; j < len; j += blockDim.x) tile[j] = (g0 + j < T) ? __ldg(xr + g0 + j) : 0.0f;
+        for (int i = threadIdx.x; i < (jb >> 2); i += blockDim.x) dst[i] = __ldg(src + i);
     }
+    for (int j = jb + threadIdx.x; j < len; j += blockDim.x) tile[j] = (j < hi) ? __ldg(xr + g0 + j) : 0.0f;
 }
 
 template <class P>
@@ -63,21 +67,18 @@ __device__ __forceinline__ void loss_fwd_task(const LossScale& sc, const float* 
     warp_fft_fwd_pk<P>(z, xbuf, sc.t.tw, lane, load);
     warp_fft_post_pk<P>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
         const float vr = lo(v), vi = hi(v);
-        mx[slot] = fast_mag(fmaf(vr, vr, vi * vi));
+        mx[slot] = fmaf(vr, vr, vi * vi);                               // |X|^2
     });
     cur = ty;
     warp_fft_fwd_pk<P>(z, xbuf, sc.t.tw, lane, load);
     const bool valid = (f_first + lane / P::A) < f_end;
+    const float eps2 = eps_squared(eps);
     float l1 = 0.0f, ll = 0.0f;
     warp_fft_post_pk<P>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
         const float vr = lo(v), vi = hi(v);
-        const float m2 = fmaf(vr, vr, vi * vi);
-        const float my = fast_mag(m2);                                  // same arithmetic as the fused kernel
-        const float xv = mx[slot];
-        l1 += fabsf(my - xv);
-        ll += fabsf(fast_lg2(fmaxf(my, eps)) - fast_lg2(fmaxf(xv, eps)));   // log2 units (scaled by ln 2 below); exact 0 when X == Y
+        loss_bin_value<true>(mx[slot], fmaf(vr, vr, vi * vi), eps2, l1, ll);   // same arithmetic as the fused kernels; exact 0 when X == Y
     });
-    if (valid) { acc_l1 += l1; acc_log += ll * 0.69314718055994530942f; }
+    if (valid) { acc_l1 += l1; acc_log += ll * kLogHalf; }
 }
 
 __global__ void __launch_bounds__(kFwdThreads, 2) mrstft_fwd_kernel(const LossArgs a) {
@@ -186,27 +187,18 @@ __device__ __forceinline__ void loss_bwd_task(const LossScale& sc, const float* 
     warp_fft_fwd_pk<P>(z, xbuf, sc.t.tw, lane, load);
     warp_fft_post_pk<P>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
         const float vr = lo(v), vi = hi(v);
-        mx[slot] = fast_mag(fmaf(vr, vr, vi * vi));                  // |X|
+        mx[slot] = fmaf(vr, vr, vi * vi);                            // |X|^2
     });
     cur = yr;
     warp_fft_fwd_pk<P>(z, xbuf, sc.t.tw, lane, load);
+    const float eps2 = eps_squared(eps);
     float l1 = 0.0f, ll = 0.0f;
     warp_fft_post_pk<P>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
         const float vr = lo(v), vi = hi(v);
-        const float m2 = fmaf(vr, vr, vi * vi);
-        const float inv = m2 >= kTinyMag2 ? fast_rsqrt(m2) : 0.0f;
-        const float my = m2 * inv;                                    // |Y|
-        const float xv = mx[slot];                                    // |X|
-        const float d = my - xv;
-        const float dl = fast_lg2(fmaxf(my, eps)) - fast_lg2(fmaxf(xv, eps));
-        if (WITH_SUMS) { l1 += fabsf(d); ll += fabsf(dl); }           // same arithmetic as the forward-only kernel
-        // d|X - Y| / dY = sign(d);  d|ln X~ - ln Y~| / dY = sign(dl) / Y where Y is not clamped (Y >= eps)
-        const float invm = my >= eps ? inv : 0.0f;
-        float g = fmaf(signed_coef(dl, c_log), invm, signed_coef(d, c_l1));
-        g *= inv;                                                     // dY / dYc = Yc / |Y|
+        const float g = loss_bin_grad<WITH_SUMS>(mx[slot], fmaf(vr, vr, vi * vi), eps2, c_l1, c_log, l1, ll);
         G[slot] = mul2(v, bc(g));                                     // odd slots: conj(dL/dY[M-k]), as the adjoint expects
     });
-    if (WITH_SUMS && (f_base + (lane / P::A) * f_stride) < f_end) { acc_l1 += l1; acc_log += ll * 0.69314718055994530942f; }
+    if (WITH_SUMS && (f_base + (lane / P::A) * f_stride) < f_end) { acc_l1 += l1; acc_log += ll * kLogHalf; }
     warp_fft_adj_pk<P>(xbuf, sc.t.tw, sc.t.pt, lane,
         [&](int, int, int slot) -> cf { return G[slot]; },
         [&](auto, int fr, auto ac, int b, cf g) {

@@ -124,7 +124,7 @@ __device__ __forceinline__ void stream_cta(const StreamArgs& a, const StreamScal
     __syncwarp();
 
     const float c_l1 = __ldg(a.coef + 2 * sc.orig), c_log = __ldg(a.coef + 2 * sc.orig + 1);
-    const float eps = a.eps;
+    const float eps2 = eps_squared(a.eps);
     float l1 = 0.0f, ll = 0.0f;
     for (int t = 0; t < maxlen; ++t) {
         float zr[BQ], zi[BQ];
@@ -149,22 +149,12 @@ __device__ __forceinline__ void stream_cta(const StreamArgs& a, const StreamScal
         };
         warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load_x);
         warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
-            gr[slot] = fast_mag(fmaf(vr, vr, vi * vi));                   // |X|
+            gr[slot] = fmaf(vr, vr, vi * vi);                             // |X|^2
         });
         warp_fft_fwd<P>(zr, zi, xbuf, sc.t.tw, lane, load_y);
         float tl1 = 0.0f, tll = 0.0f;
         warp_fft_post<P>(zr, zi, sc.t.pt, lane, [&](int, int, float vr, float vi, int slot) {
-            const float m2 = fmaf(vr, vr, vi * vi);
-            const float inv = m2 >= kTinyMag2 ? fast_rsqrt(m2) : 0.0f;
-            const float my = m2 * inv;                                    // |Y|
-            const float xv = gr[slot];                                    // |X|
-            const float d = my - xv;
-            const float dl = fast_lg2(fmaxf(my, eps)) - fast_lg2(fmaxf(xv, eps));
-            if (WITH_SUMS) { tl1 += fabsf(d); tll += fabsf(dl); }
-            // d|X - Y| / dY = sign(d);  d|ln X~ - ln Y~| / dY = sign(dl) / Y where Y is not clamped (Y >= eps)
-            const float invm = my >= eps ? inv : 0.0f;
-            float g = fmaf(signed_coef(dl, c_log), invm, signed_coef(d, c_l1));
-            g *= inv;                                                     // dY / dYc = Yc / |Y|
+            const float g = loss_bin_grad<WITH_SUMS>(gr[slot], fmaf(vr, vr, vi * vi), eps2, c_l1, c_log, tl1, tll);
             gr[slot] = g * vr; gi[slot] = g * vi;
         });
         if (WITH_SUMS && t < len_post) { l1 += tl1; ll += tll; }
@@ -213,7 +203,7 @@ __device__ __forceinline__ void stream_cta(const StreamArgs& a, const StreamScal
         l1 = warp_sum(l1); ll = warp_sum(ll);
         if (lane == 0) {
             double* pp = a.partial + ((long long)(blockIdx.x + a.cta_base) * kStreamWarps + warp) * 2;
-            pp[0] = (double)l1; pp[1] = (double)ll * 0.69314718055994530942;
+            pp[0] = (double)l1; pp[1] = (double)ll * (double)kLogHalf;
         }
     }
 }
@@ -304,7 +294,7 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
 
     auto window = [&](auto, auto, int m) -> cf { return ld_table(win2 + m); };
     const float c_l1 = __ldg(a.coef + 2 * sc.orig), c_log = __ldg(a.coef + 2 * sc.orig + 1);
-    const float eps = a.eps;
+    const float eps2 = eps_squared(a.eps);
     float l1 = 0.0f, ll = 0.0f;
     for (int t = 0; t < maxlen; ++t) {
         cf G[BQ + 1];
@@ -329,18 +319,8 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
         };
         warp_fft_fwd2_pk<P>(zx, zy, xbuf, sc.t.tw, lane, load_xy);
         warp_fft_post2_pk<P>(zx, zy, sc.t.pt, lane, [&](int, int, cf vx, cf v, int slot) {
-            const float xr_ = lo(vx), xi_ = hi(vx);
-            const float xv = fast_mag(fmaf(xr_, xr_, xi_ * xi_));         // |X|
-            const float vr = lo(v), vi = hi(v);
-            const float m2 = fmaf(vr, vr, vi * vi);
-            const float inv = m2 >= kTinyMag2 ? fast_rsqrt(m2) : 0.0f;
-            const float my = m2 * inv;                                    // |Y|
-            const float d = my - xv;
-            const float dl = fast_lg2(fmaxf(my, eps)) - fast_lg2(fmaxf(xv, eps));
-            if (WITH_SUMS) { tl1 += fabsf(d); tll += fabsf(dl); }
-            const float invm = my >= eps ? inv : 0.0f;
-            float g = fmaf(signed_coef(dl, c_log), invm, signed_coef(d, c_l1));
-            g *= inv;
+            const float xr_ = lo(vx), xi_ = hi(vx), vr = lo(v), vi = hi(v);
+            const float g = loss_bin_grad<WITH_SUMS>(fmaf(xr_, xr_, xi_ * xi_), fmaf(vr, vr, vi * vi), eps2, c_l1, c_log, tl1, tll);
             G[slot] = mul2(v, bc(g));                                     // dL/dY[k]  (odd slots: its conjugate)
         });
         } else {
@@ -355,21 +335,12 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
         warp_fft_fwd_pk<P>(z, xbuf, sc.t.tw, lane, load_x);
         warp_fft_post_pk<P>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
             const float vr = lo(v), vi = hi(v);
-            mx[slot] = fast_mag(fmaf(vr, vr, vi * vi));                   // |X|
+            mx[slot] = fmaf(vr, vr, vi * vi);                             // |X|^2
         });
         warp_fft_fwd_pk<P>(z, xbuf, sc.t.tw, lane, load_y);
         warp_fft_post_pk<P>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
             const float vr = lo(v), vi = hi(v);
-            const float m2 = fmaf(vr, vr, vi * vi);
-            const float inv = m2 >= kTinyMag2 ? fast_rsqrt(m2) : 0.0f;
-            const float my = m2 * inv;                                    // |Y|
-            const float xv = mx[slot];                                    // |X|
-            const float d = my - xv;
-            const float dl = fast_lg2(fmaxf(my, eps)) - fast_lg2(fmaxf(xv, eps));
-            if (WITH_SUMS) { tl1 += fabsf(d); tll += fabsf(dl); }
-            const float invm = my >= eps ? inv : 0.0f;
-            float g = fmaf(signed_coef(dl, c_log), invm, signed_coef(d, c_l1));
-            g *= inv;
+            const float g = loss_bin_grad<WITH_SUMS>(mx[slot], fmaf(vr, vr, vi * vi), eps2, c_l1, c_log, tl1, tll);
             G[slot] = mul2(v, bc(g));                                     // dL/dY[k]  (odd slots: its conjugate)
         });
         }
@@ -418,7 +389,7 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
         l1 = warp_sum(l1); ll = warp_sum(ll);
         if (lane == 0) {
             double* pp = a.partial + ((long long)(blockIdx.x + a.cta_base) * kStreamWarps + warp) * 2;
-            pp[0] = (double)l1; pp[1] = (double)ll * 0.69314718055994530942;
+            pp[0] = (double)l1; pp[1] = (double)ll * (double)kLogHalf;
         }
     }
 }

@@ -40,17 +40,27 @@ __device__ __forceinline__ float padded_sample(const float* __restrict__ xr, lon
     return 0.0f;
 }
 
-// tile[j] = x_padded[g0 + j], j in [0, len)
+// tile[j] = x_padded[g0 + j], j in [0, len).  The in-range, 16-byte aligned middle of the tile is copied with float4 loads even
+// when the tile hangs over either end of the row (centre padding in front, the last tile / chunk behind): only the <= 3 + 3
+// samples around it and the padded samples take the scalar path.  (Round 2: tiles that touched a row end used to be staged
+// sample by sample -- half of the front end's CTAs on 1 s clips -- and that loop held 43 % of the kernel's stall samples.)
 __device__ __forceinline__ void stage_tile(float* tile, const float* __restrict__ xr, long long g0, int len,
                                            long long T, int pad_mode, bool vec_ok) {
-    const bool interior = g0 >= 0 && g0 + len <= T;
-    if (interior && vec_ok && (g0 & 3) == 0 && (len & 3) == 0) {
-        const float4* src = reinterpret_cast<const float4*>(xr + g0);
-        float4* dst = reinterpret_cast<float4*>(tile);
-        for (int i = threadIdx.x; i < (len >> 2); i += blockDim.x) dst[i] = __ldg(src + i);
-    } else {
-        for (int j = threadIdx.x; j < len; j += blockDim.x) tile[j] = padded_sample(xr, g0 + j, T, pad_mode);
+    const long long lo_ll = g0 < 0 ? -g0 : 0, hi_ll = T - g0;
+    const int lo = (int)(lo_ll < len ? lo_ll : len);                        // in-range samples: j in [lo, hi)
+    const int hi = (int)(hi_ll < lo ? lo : (hi_ll < len ? hi_ll : len));
+    int ja = lo, jb = lo;                                                   // [ja, jb): 16-byte copies
+    if (vec_ok && (g0 & 3) == 0) {
+        ja = (lo + 3) & ~3; jb = hi & ~3;
+        if (jb < ja) ja = jb = lo;
     }
+    if (jb > ja) {
+        const float4* src = reinterpret_cast<const float4*>(xr) + (g0 >> 2);   // g0 is a multiple of 4 (possibly negative)
+        float4* dst = reinterpret_cast<float4*>(tile);
+        for (int i = (ja >> 2) + threadIdx.x; i < (jb >> 2); i += blockDim.x) dst[i] = __ldg(src + i);
+    }
+    for (int j = threadIdx.x; j < ja; j += blockDim.x) tile[j] = padded_sample(xr, g0 + j, T, pad_mode);
+    for (int j = jb + threadIdx.x; j < len; j += blockDim.x) tile[j] = padded_sample(xr, g0 + j, T, pad_mode);
 }
 
 #ifndef TAC_PLANES_BULK
@@ -374,7 +384,7 @@ __global__ void __launch_bounds__(kFeThreads, kFeOcc) stft_frontend_kernel(const
     float2* xbuf_all = reinterpret_cast<float2*>(shared2);
     float* otile = reinterpret_cast<float*>(shared2);                            // [K][TF + 1]
 
-    const int TF = kFeWarps * P::NFR, TS = TF + 1;
+    constexpr int TF = kFeWarps * P::NFR, TS = TF + 1;
     const int ft = blockIdx.x % a.ntiles;
     const long long row = blockIdx.x / a.ntiles;
     const float* xr = a.x + row * a.T;
@@ -414,13 +424,23 @@ __global__ void __launch_bounds__(kFeThreads, kFeOcc) stft_frontend_kernel(const
         });
     }
     __syncthreads();
-    float* out1 = out0 + (long long)a.K * a.f_pad;
-    const int total = a.K * TF;
-    for (int i = threadIdx.x; i < total; i += kFeThreads) {
-        const int k = i / TF, tt = i % TF;                          // TF is a power of two: shift / mask
-        if (tt < nf) {
-            __stcs(out0 + (long long)k * a.f_pad + tt, otile[k * TS + tt]);
-            __stcs(out1 + (long long)k * a.f_pad + tt, otile1[k * TS + tt]);
+    // write-out: thread -> (frame tt, bins k0, k0 + RPI, ...): the frame index and both row pointers are loop invariants, the
+    // shared-memory offsets compile-time constants (it was 23 % of the kernel's instructions as i / TF, i % TF, 64-bit address
+    // arithmetic per element)
+    constexpr int RPI = kFeThreads / TF;                           // bins per pass of the CTA
+    static_assert(kFeThreads % TF == 0, "TF must divide the CTA size");
+    const int tt = threadIdx.x % TF, k0 = threadIdx.x / TF;
+    if (tt < nf) {
+        const float* s0 = otile + k0 * TS + tt;
+        const float* s1 = otile1 + k0 * TS + tt;
+        float* g0p = out0 + (long long)k0 * a.f_pad + tt;
+        float* g1p = g0p + (long long)a.K * a.f_pad;
+        const long long gstep = (long long)RPI * a.f_pad;
+        const int K = a.K;
+#pragma unroll 4
+        for (int k = k0; k < K; k += RPI) {
+            __stcs(g0p, *s0); __stcs(g1p, *s1);
+            s0 += RPI * TS; s1 += RPI * TS; g0p += gstep; g1p += gstep;
         }
     }
 }

@@ -18,7 +18,7 @@ There is no CPU or eager-PyTorch fallback: every op raises ``RuntimeError`` when
 from . import _lib
 from .stft import (Spectrogram, MultiScaleSTFT, stft_multi, complex_spectrogram, create_complex_spectrogram, amplitude_to_db,
                    num_frames, SUPPORTED_NFFT, istft, batch_reconstruct_waveform, reconstruct_waveform, stft_ex, ex_supported,
-                   MelBank, MelSpectrogram, SpecsFrontEnd)
+                   MelBank, MelSpectrogram, SpecsFrontEnd, reconstruct_and_disc_inputs)
 from .tail import bottleneck_mix, spectral_bottleneck, task_aware_tail, interp_mse, multi_reduce
 from .loss import mrstft_loss, mrstft_sums, mrstft_counts, spectral_losses, LOG_FLOOR
 from .dpca import data_pca, dpca_project, dpca_select, dpca_stats, dpca_eig, apply_pca, var_topk, nuclear_loss, pairwise_cosine_loss
@@ -27,5 +27,5 @@ __all__ = ["Spectrogram", "MultiScaleSTFT", "stft_multi", "complex_spectrogram",
            "num_frames", "SUPPORTED_NFFT", "mrstft_loss", "mrstft_sums", "mrstft_counts", "spectral_losses",
            "LOG_FLOOR", "data_pca", "dpca_project", "dpca_select", "dpca_stats", "dpca_eig", "apply_pca", "var_topk", "nuclear_loss",
            "pairwise_cosine_loss", "istft", "batch_reconstruct_waveform", "reconstruct_waveform", "stft_ex", "ex_supported",
-           "MelBank", "MelSpectrogram", "SpecsFrontEnd", "bottleneck_mix", "spectral_bottleneck", "task_aware_tail", "interp_mse",
+           "MelBank", "MelSpectrogram", "SpecsFrontEnd", "reconstruct_and_disc_inputs", "bottleneck_mix", "spectral_bottleneck", "task_aware_tail", "interp_mse",
            "multi_reduce"]

@@ -70,6 +70,8 @@ SIGNATURES = {
     "tac_cosine_pairs_bwd": (_I, [_VPP, _I, _I64, _I, _F, _VP, _F, _VPP, _VP]),
     "tac_istft_length": (_I64, [_I64, _I, _I, _I]),
     "tac_istft": (_I, [_VP, _VP, _I, _I64, _I64, _I64, _I64, _I, _I, _I, _I, _I, _VP, _I64, _VP]),
+    "tac_chain_rows_per_group": (_I64, [_I64, _I64, _I64]),
+    "tac_istft_disc_inputs": (_I, [_VP, _VP, _I, _I64, _I64, _I64, _I64, _I, _I, _I, _I, _I, _VP, _I64, _I, _IP, _IP, _IP, _I, _VPP, _I64, _VP]),
     "tac_stft_adjoint": (_I, [_VP, _VP, _I, _I64, _I64, _I64, _I64, _I, _I, _I, _F, _VP, _I64, _VP]),
     "tac_bottleneck_width": (_I, [_I, _I, _I]),
     "tac_bottleneck_mix": (_I, [_VPP, _I, _I64, _I, _I, _I, _VPP, _VP, _VP]),
@@ -96,6 +98,7 @@ EPI_COMPLEX, EPI_COMPRESS, EPI_MAGPHASE, EPI_MAGDB, EPI_POWER, EPI_LOGPOWER, EPI
 WINDOW_HANN, WINDOW_SQRT_HANN = 0, 1
 GRAM_TF32X3, GRAM_FP64 = 0, 1
 IN_POLAR, IN_PLANES, IN_COMPLEX = 0, 1, 2
+MAX_SCALES = 8             # TAC_MAX_SCALES
 
 _lib = None
 

@@ -651,3 +651,49 @@ def reconstruct_waveform(magnitude: torch.Tensor, phase: torch.Tensor, sample_ra
     """Single-utterance form (``train_pkl_file_task_aware.py:210-226``): ``[K, F]`` -> ``[1, hop*(F-1)]`` (the reference
     returns ``y.unsqueeze(0)``)."""
     return batch_reconstruct_waveform(magnitude[None], phase[None], sample_rate, n_fft, hop_length, win_length, window)
+
+
+def reconstruct_and_disc_inputs(magnitude_batch: torch.Tensor, phase_batch: torch.Tensor, sample_rate: int = 16000,
+                                n_fft: int = 2048, hop_length: int = 512, win_length: int = 2048, window: str = "hann",
+                                disc_n_ffts: Sequence[int] = (1024, 2048, 512), disc_hop_lengths: Sequence[int] = (256, 512, 128),
+                                disc_win_lengths: Sequence[int] = (1024, 2048, 512), disc_normalized: bool = True,
+                                rows_per_group: int = 0):
+    """The ground-truth branch of ``task_aware()`` as one call: ``batch_reconstruct_waveform(clean_mag, clean_phase)``
+    (``train_pkl_file_task_aware.py:290``), ``.unsqueeze(1)`` (``:347``) and the spectrogram front of every scale
+    discriminator that ``disc(ground_truth_clean_waveforms)`` (``:353``) runs first (``msstftd.py:188-191`` ->
+    ``:151-153``).  Returns ``(waveform [B, hop*(F-1)], [z_s [B, 2, F_s, K_s] per scale])``; the waveform is what ``:333``'s
+    MSE consumes, ``z_s`` is what ``DiscriminatorSTFT.forward`` feeds its first conv.  The batch is walked in row groups whose
+    waveform stays in the L2 between the synthesis and the analysis kernel (``tac_istft_disc_inputs``), so the analysis does
+    not re-read it from HBM; results are bit-identical to ``batch_reconstruct_waveform`` + ``MultiScaleSTFT``.  No autograd:
+    the reference detaches this branch (``torch.tensor(reconstructed_clean_waveforms)``, ``:303``)."""
+    if magnitude_batch.shape != phase_batch.shape:
+        raise ValueError("The shapes of magnitude and phase must match for batched processing.")
+    if window != "hann":
+        raise ValueError(f"Window type '{window}' is not supported. Use 'hann'.")
+    L.require_cuda(magnitude_batch, "magnitude_batch")
+    L.require_cuda(phase_batch, "phase_batch")
+    if magnitude_batch.dim() != 3 or magnitude_batch.shape[1] != n_fft // 2 + 1:
+        raise ValueError(f"expected [B, {n_fft // 2 + 1}, F], got {tuple(magnitude_batch.shape)}")
+    if not (len(disc_n_ffts) == len(disc_hop_lengths) == len(disc_win_lengths)) or not 1 <= len(disc_n_ffts) <= L.MAX_SCALES:
+        raise ValueError("disc_n_ffts, disc_hop_lengths, disc_win_lengths must have the same length in [1, 8]")
+    m, p = magnitude_batch.detach(), phase_batch.detach()
+    B, K, F = m.shape
+    usable = (m.dtype == torch.float32 and p.dtype == torch.float32 and m.stride() == p.stride() and m.stride(2) == 1
+              and m.stride(1) >= F and m.stride(0) >= K * m.stride(1))
+    if not usable:
+        m, p = m.float().contiguous(), p.float().contiguous()
+    T = int(L.lib().tac_istft_length(F, n_fft, hop_length, 1))
+    wave = torch.empty((B, T), dtype=torch.float32, device=m.device)
+    outs = []
+    for n, h in zip(disc_n_ffts, disc_hop_lengths):
+        Fs = num_frames(T, n, h, False)
+        if Fs < 1:
+            raise ValueError(f"signal of {T} samples is shorter than n_fft={n}")
+        outs.append(torch.empty((B, 2, Fs, n // 2 + 1), dtype=torch.float32, device=m.device))
+    with L.device_of(m):
+        L.check(L.lib().tac_istft_disc_inputs(m.data_ptr(), p.data_ptr(), L.IN_POLAR, B, m.stride(0), m.stride(1), F, n_fft,
+                                              hop_length, win_length, 1, 0, wave.data_ptr(), T, len(disc_n_ffts),
+                                              L.int_array(disc_n_ffts), L.int_array(disc_hop_lengths),
+                                              L.int_array(disc_win_lengths), int(bool(disc_normalized)), L.ptr_array(outs),
+                                              int(rows_per_group), L.stream_of(m)))
+    return wave, outs

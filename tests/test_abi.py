@@ -43,6 +43,11 @@ def test_host_only_entry_points(ts):
     assert lib.tac_dpca_workspace_bytes(2, 256, 8) >= 2 * (9216 + 128 * 128) * 8
     assert lib.tac_dpca_workspace_bytes(1, 64, 128) >= (9216 + 128 * 128) * 8
     assert lib.tac_spec_losses_workspace_bytes(4) > 0
+    # chain row groups: the group's waveform stays inside the L2 budget, groups are even, never empty
+    g = lib.tac_chain_rows_per_group
+    assert g(128, 306688, 0) == 32                                   # 128 x 19 s decoder outputs: 4 groups of 32 rows (37.4 MiB each)
+    assert g(5, 16000, 0) == 5 and g(1, 10 ** 9, 0) == 1 and g(0, 16000, 0) == 0
+    assert g(100, 306688, 10 << 20) == 8                             # 13 groups under a 10 MiB budget
 
 
 def test_no_cpu_fallback(ts):

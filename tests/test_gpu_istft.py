@@ -136,3 +136,52 @@ def test_gradients(ts):
     (ts.istft(sg, 1024, 256) * wgt.cuda()).sum().backward()
     # torch's autograd keeps (ignored) imaginary gradients at k = 0, n/2 at zero as well
     _close(torch.view_as_real(sg.grad), torch.view_as_real(sr.grad), "d/d spec")
+
+
+# ---- chain: decoder spectrogram -> waveform -> discriminator STFT inputs (tac_istft_disc_inputs) -------------------------
+
+def test_chain_golden_and_oracle(ts, golden_dir):
+    """Waveform against the reference's own batch_reconstruct_waveform output (istft.npz); the per-scale discriminator inputs
+    against the oracle (pinned by stft_disc.npz) applied to that waveform.  Tolerance: rtol 1e-4, atol 1e-4 max|ref|."""
+    g = np.load(os.path.join(golden_dir, "istft.npz"))
+    mag, ph = torch.from_numpy(g["mag"]), torch.from_numpy(g["phase"])
+    wav, zs = ts.reconstruct_and_disc_inputs(mag.cuda(), ph.cuda(), 16000)
+    _close(wav, torch.from_numpy(g["wav"]), "chain waveform")
+    ref_wav, ref_zs = O.reconstruct_and_disc_inputs_ref(mag, ph)
+    _close(wav, ref_wav, "chain waveform vs oracle")
+    assert len(zs) == len(ref_zs) == 3
+    for z, r, n in zip(zs, ref_zs, (1024, 2048, 512)):
+        _close(z, r, f"chain disc input n_fft={n}")
+
+
+@pytest.mark.parametrize("rows,group", [(5, 1), (5, 2), (5, 0), (5, 64), (3, 3)])
+def test_chain_equals_separate_calls(ts, rows, group):
+    """Row groups (ragged last group included) change nothing: bit-identical to batch_reconstruct_waveform + MultiScaleSTFT."""
+    gen = torch.Generator().manual_seed(11)
+    F = 40
+    dec = torch.randn(rows, 2, 1025, F + 8, generator=gen).cuda()              # decoder layout, padded time axis
+    mag, ph = dec[:, 0, :, :F].abs(), dec[:, 1, :, :F] * 3.0                   # strided views, used in place
+    wav, zs = ts.reconstruct_and_disc_inputs(mag, ph, 16000, rows_per_group=group)
+    wav2 = ts.batch_reconstruct_waveform(mag, ph, 16000)
+    zs2 = ts.MultiScaleSTFT()(wav2.unsqueeze(1))
+    assert torch.equal(wav, wav2)
+    for a, b in zip(zs, zs2):
+        assert a.shape == b.shape and torch.equal(a, b)
+
+
+def test_chain_five_scales_and_errors(ts):
+    gen = torch.Generator().manual_seed(12)
+    mag, ph = torch.rand(2, 1025, 24, generator=gen), torch.randn(2, 1025, 24, generator=gen)
+    n_ffts, hops = (2048, 1024, 512, 256, 128), (512, 256, 128, 64, 32)
+    wav, zs = ts.reconstruct_and_disc_inputs(mag.cuda(), ph.cuda(), 16000, disc_n_ffts=n_ffts, disc_hop_lengths=hops,
+                                             disc_win_lengths=n_ffts)
+    ref_wav, ref_zs = O.reconstruct_and_disc_inputs_ref(mag, ph, n_ffts, hops)
+    _close(wav, ref_wav, "chain waveform (5 scales)")
+    for z, r, n in zip(zs, ref_zs, n_ffts):
+        _close(z, r, f"chain disc input n_fft={n}")
+    with pytest.raises(ValueError, match="shapes of magnitude and phase must match"):
+        ts.reconstruct_and_disc_inputs(mag.cuda(), ph.cuda()[:, :, :-1])
+    with pytest.raises(ValueError, match="shorter than n_fft"):
+        ts.reconstruct_and_disc_inputs(mag.cuda()[:, :, :3], ph.cuda()[:, :, :3])   # 1024 samples < n_fft = 2048
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ts.reconstruct_and_disc_inputs(mag, ph)

@@ -3,12 +3,16 @@
 // feeds the MSE, so it IS written), :346-353 (unsqueeze(1), disc(...)) -> msstftd.py:188-191 (loop over the scale
 // discriminators) -> :151-153 (spec_transform, cat(real, imag), 'b c w t -> b c t w').
 //
-// The two kernels exist (istft.cu: K4, stft.cu: K1 planes).  K4 writes a row's waveform once; K1 would read it back from
-// HBM: 1.2 MB per 19 s utterance each way, 157 MB for a batch of 128 -- more than the 126 MB L2.  The chain therefore walks
-// the batch in ROW GROUPS whose waveform fits a budget well inside the L2 (default 40 MiB; B200: 126 MB, two partitions) and
-// enqueues K4 then K1 per group on the caller's stream: K1's staging loads of a group hit the lines K4 has just written.
-// Nothing is synchronised with the host, the groups' kernels are ordinary stream-ordered launches (graph-capturable), and the
-// results are bit-identical to tac_istft followed by tac_stft_multi on the whole batch (same kernels, same per-row work).
+// The two kernels exist (istft.cu: K4, stft.cu: K1 planes); this entry point enqueues them back to back on the caller's stream
+// for row groups of the batch, writes every output once and never synchronises with the host (graph-capturable).  Results are
+// bit-identical to tac_istft followed by tac_stft_multi on the whole batch (same kernels, same per-row work).
+//
+// Group size, measured on B200 (tools/time_chain.py, 128 x [2, 1025, 600] decoder outputs -> 306 688-sample waveforms ->
+// 3 scales; profiles/chain_r02i.jsonl): the waveform is 157 MB of the chain's 2.67 GB of traffic, so keeping it in the 126 MB
+// L2 between the kernels can save 6 % at best, while every extra group adds two partial last waves (K4 runs one CTA per SM,
+// K1 two): whole batch 1.85 ms, groups of 64 / 32 / 16 / 8 rows 2.10 / 2.29 / 2.55 / 3.23 ms.  rows_per_group = 0 therefore
+// means ONE group; tac_chain_rows_per_group gives the L2-resident group size for callers that want the waveform hot for
+// further consumers (the MSE of :333, a second discriminator pass) and accept the tails.
 #include "tac_common.cuh"
 
 using namespace tac;
@@ -33,7 +37,7 @@ extern "C" int tac_istft_disc_inputs(const float* a, const float* b, int in_mode
     TAC_REQUIRE(n_scales >= 1 && n_scales <= TAC_MAX_SCALES, "n_scales must be in [1, %d]", TAC_MAX_SCALES);
     TAC_REQUIRE(in_mode == TAC_IN_POLAR || in_mode == TAC_IN_PLANES || in_mode == TAC_IN_COMPLEX, "unknown in_mode %d", in_mode);
     TAC_REQUIRE(in_mode == TAC_IN_COMPLEX || b, "b is null");
-    int64_t g = rows_per_group > 0 ? rows_per_group : tac_chain_rows_per_group(rows, out_len, 0);
+    int64_t g = rows_per_group > 0 ? rows_per_group : rows;
     if (g > rows) g = rows;
     int64_t Fs[TAC_MAX_SCALES];
     for (int s = 0; s < n_scales; ++s) {

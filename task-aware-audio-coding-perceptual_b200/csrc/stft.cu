@@ -63,6 +63,9 @@ __device__ __forceinline__ void stage_tile(float* tile, const float* __restrict_
     for (int j = jb + threadIdx.x; j < len; j += blockDim.x) tile[j] = padded_sample(xr, g0 + j, T, pad_mode);
 }
 
+#ifndef TAC_PLANES_PERSIST
+#define TAC_PLANES_PERSIST 1  // 1: one persistent 16-warp CTA per SM with a double-buffered, bulk-copied sample tile (when applicable)
+#endif
 #ifndef TAC_PLANES_BULK
 #define TAC_PLANES_BULK 1     // 1: a task's two plane spans leave through shared memory as bulk async copies; 0: 4-byte streaming stores
 #endif
@@ -193,9 +196,6 @@ __global__ void __launch_bounds__(kThreads, 2) stft_planes_kernel(const PlanesAr
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* tile = reinterpret_cast<float*>(smem_raw);
     float2* xbuf_all = reinterpret_cast<float2*>(smem_raw + (size_t)a.tile_len * sizeof(float));
-    __shared__ int s_task_begin[TAC_MAX_SCALES + 1];
-    __shared__ int s_f_lo[TAC_MAX_SCALES], s_f_hi[TAC_MAX_SCALES];
-    __shared__ int s_next;
 
     const int c = blockIdx.x % a.nchunks;
     const long long row = blockIdx.x / a.nchunks;
@@ -203,50 +203,160 @@ __global__ void __launch_bounds__(kThreads, 2) stft_planes_kernel(const PlanesAr
     const long long c0 = (long long)c * a.chunk;             // chunk origin in padded frame-start coordinates
 
     stage_tile(tile, xr, c0 - a.pmax, a.tile_len, a.T, a.pad_mode, a.vec_ok != 0);
-    if (threadIdx.x == 0) {
-        int acc = 0;
-        for (int s = 0; s < a.nscales; ++s) {
-            const int h = a.sc[s].hop;
-            long long lo = (c0 + h - 1) / h, hi = (c0 + a.chunk + h - 1) / h;
-            if (hi > a.sc[s].F) hi = a.sc[s].F;
-            if (lo > hi) lo = hi;
-            const int nfr = a.sc[s].n >= 2048 ? 1 : (a.sc[s].n >= 512 ? 2 : (a.sc[s].n >= 128 ? 4 : 8));
-            s_f_lo[s] = (int)lo; s_f_hi[s] = (int)hi;
-            s_task_begin[s] = acc;
-            acc += (int)((hi - lo + nfr - 1) / nfr);
-        }
-        s_task_begin[a.nscales] = acc;
-        s_next = 0;
-    }
     __syncthreads();
 
+    // Tasks (NFR frames of one scale) are numbered scale by scale and dealt round-robin: warp w takes the global task numbers
+    // t = w (mod 8).  Everything that depends on the scale only -- frame range, tile origin, plane pointers, the plan -- is
+    // formed once per scale outside the task loop.  (Round 2: the shared atomic counter, the shuffle, the scale search with one
+    // shared-memory load per step and the 64-bit plane arithmetic PER TASK were 15 % of the kernel's instructions and ~15 % of
+    // its stall samples on cfg 4, where a CTA runs 128 tasks.)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float2* xbuf = xbuf_all + warp * kXbufFloat2;
-    const int ntasks = s_task_begin[a.nscales];
     const long long b = row / a.C, ch = row % a.C;
-    for (;;) {
-        int t = 0;
-        if (lane == 0) t = atomicAdd(&s_next, 1);
-        t = __shfl_sync(0xffffffffu, t, 0);
-        if (t >= ntasks) break;
-        int s = 0;
-        while (t >= s_task_begin[s + 1]) ++s;
+    int tbase = 0;                                           // global number of this scale's first task
+    for (int s = 0; s < a.nscales; ++s) {
         const ScaleArg& sc = a.sc[s];
+        const int h = sc.hop;
+        long long lo = (c0 + h - 1) / h, hi = (c0 + a.chunk + h - 1) / h;
+        if (hi > sc.F) hi = sc.F;
+        if (lo > hi) lo = hi;
         const int nfr = sc.n >= 2048 ? 1 : (sc.n >= 512 ? 2 : (sc.n >= 128 ? 4 : 8));
-        const int f_first = s_f_lo[s] + (t - s_task_begin[s]) * nfr;
-        const int f_end = s_f_hi[s];
+        const int nt = (int)((hi - lo + nfr - 1) / nfr);
+        const int first = (warp - tbase) & (kWarps - 1);     // kWarps is a power of two
+        tbase += nt;
+        if (first >= nt) continue;
+        const int f_lo = (int)lo, f_end = (int)hi;
         // tile[0] is padded-coordinate (c0 - pmax) of the widest scale == (c0 - pmax + pad_s) of scale s
         const int origin = (int)(c0 - a.pmax + sc.pad);
         const long long plane = (long long)sc.F * sc.K;
         float* out_re_row = sc.out + ((b * 2) * a.C + ch) * plane;
         const long long im_off = (long long)a.C * plane;
+        static_assert(Plan2048::NFR == 1 && Plan1024::NFR == 2 && Plan512::NFR == 2 && Plan256::NFR == 4 && Plan128::NFR == 4 && Plan64::NFR == 8, "nfr");
         switch (sc.n) {
-            case 2048: planes_task<Plan2048>(sc, tile, xbuf, lane, f_first, f_end, origin, out_re_row, im_off); break;
-            case 1024: planes_task<Plan1024>(sc, tile, xbuf, lane, f_first, f_end, origin, out_re_row, im_off); break;
-            case 512: planes_task<Plan512>(sc, tile, xbuf, lane, f_first, f_end, origin, out_re_row, im_off); break;
-            case 256: planes_task<Plan256>(sc, tile, xbuf, lane, f_first, f_end, origin, out_re_row, im_off); break;
-            case 128: planes_task<Plan128>(sc, tile, xbuf, lane, f_first, f_end, origin, out_re_row, im_off); break;
-            default: planes_task<Plan64>(sc, tile, xbuf, lane, f_first, f_end, origin, out_re_row, im_off); break;
+            case 2048: for (int t = first; t < nt; t += kWarps) planes_task<Plan2048>(sc, tile, xbuf, lane, f_lo + t * 1, f_end, origin, out_re_row, im_off); break;
+            case 1024: for (int t = first; t < nt; t += kWarps) planes_task<Plan1024>(sc, tile, xbuf, lane, f_lo + t * 2, f_end, origin, out_re_row, im_off); break;
+            case 512: for (int t = first; t < nt; t += kWarps) planes_task<Plan512>(sc, tile, xbuf, lane, f_lo + t * 2, f_end, origin, out_re_row, im_off); break;
+            case 256: for (int t = first; t < nt; t += kWarps) planes_task<Plan256>(sc, tile, xbuf, lane, f_lo + t * 4, f_end, origin, out_re_row, im_off); break;
+            case 128: for (int t = first; t < nt; t += kWarps) planes_task<Plan128>(sc, tile, xbuf, lane, f_lo + t * 4, f_end, origin, out_re_row, im_off); break;
+            default: for (int t = first; t < nt; t += kWarps) planes_task<Plan64>(sc, tile, xbuf, lane, f_lo + t * 8, f_end, origin, out_re_row, im_off); break;
+        }
+    }
+#if TAC_PLANES_BULK
+    if (lane < 8) bulk_wait_read();                        // shared memory must outlive the copy engine's reads
+#endif
+}
+
+// ------------------------------------------------------------------------------------------
+// Persistent form of the planes kernel: ONE 16-warp CTA per SM walks the (row, chunk) units blockIdx.x, + gridDim.x, ...; the
+// sample tile is double-buffered and filled by the copy engine (cp.async.bulk global -> shared, completion on an mbarrier), so
+// the tile of unit i + 1 (and, once every warp has released unit i's buffer, of unit i + 2) lands while unit i is being
+// transformed.  full[b]: 1 arrival (the producer's, carrying the byte count); empty[b]: one arrival per warp.  Warps drift:
+// a warp that finishes its tasks of unit i starts unit i + 1 as soon as that tile has landed, no block barrier in the loop.
+// Why: in the one-shot kernel every CTA began with a DRAM read that queues behind 3 TB/s of plane writes (~9 us of a 63 us
+// CTA life; with the barrier behind it 14 % of the warp-time samples of cfg 4).
+// Used when the tile can be bulk-copied: 16-byte aligned rows (vec_ok), zero (or no) padding.
+constexpr int kPWarps = 16;
+constexpr int kPThreads = kPWarps * 32;
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {     // bounded: traps instead of hanging the GPU
+    const unsigned addr = smem_u32(bar);
+    for (unsigned it = 0; it < (1u << 26); ++it) {
+        unsigned done;
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}\n"
+                     : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+        if (done) return;
+    }
+    __trap();
+}
+
+__global__ void __launch_bounds__(kPThreads, 1) stft_planes_persist_kernel(const PlanesArgs a, const long long nunits) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float* tiles = reinterpret_cast<float*>(smem_raw);                                        // [2][tile_len]
+    float2* xbuf_all = reinterpret_cast<float2*>(smem_raw + 2 * (size_t)a.tile_len * sizeof(float));
+    __shared__ __align__(8) uint64_t s_full[2], s_empty[2];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float2* xbuf = xbuf_all + warp * kXbufFloat2;
+    if (threadIdx.x == 0) {
+        for (int b = 0; b < 2; ++b) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(&s_full[b])), "r"(1) : "memory");
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(&s_empty[b])), "r"(kPWarps) : "memory");
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const int n_my = (int)((nunits - blockIdx.x + gridDim.x - 1) / gridDim.x);
+
+    // warp 0: tile of this CTA's i-th unit -> buffer buf (zero outside the row, bulk copy of the in-range part)
+    auto issue = [&](int i, int buf) {
+        const long long u = blockIdx.x + (long long)i * gridDim.x;
+        const long long row = u / a.nchunks;
+        const long long g0 = (u % a.nchunks) * a.chunk - a.pmax;
+        const int len = a.tile_len;
+        const long long lo_ll = g0 < 0 ? -g0 : 0, hi_ll = a.T - g0;
+        const int lo = (int)(lo_ll < len ? lo_ll : len);
+        const int hi = (int)(hi_ll < lo ? lo : (hi_ll < len ? hi_ll : len));                  // g0, T, len are multiples of 4: so are lo, hi
+        float4* t4 = reinterpret_cast<float4*>(tiles + (size_t)buf * len);
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int j = lane; j < (lo >> 2); j += 32) t4[j] = z;
+        for (int j = (hi >> 2) + lane; j < (len >> 2); j += 32) t4[j] = z;
+        __syncwarp();
+        if (lane == 0) {
+            const unsigned bar = smem_u32(&s_full[buf]);
+            const unsigned bytes = (unsigned)(hi - lo) * 4u;
+            if (bytes) {
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                             :: "r"(smem_u32(tiles + (size_t)buf * len + lo)), "l"(a.x + row * a.T + g0 + lo), "r"(bytes), "r"(bar) : "memory");
+            } else {
+                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar) : "memory");
+            }
+        }
+    };
+    if (warp == 0) {
+        issue(0, 0);
+        if (n_my > 1) issue(1, 1);
+    }
+    for (int i = 0; i < n_my; ++i) {
+        const int buf = i & 1;
+        const unsigned par = (unsigned)(i >> 1) & 1u;
+        const long long u = blockIdx.x + (long long)i * gridDim.x;
+        const long long row = u / a.nchunks;
+        const long long c0 = (u % a.nchunks) * a.chunk;
+        const float* tile = tiles + (size_t)buf * a.tile_len;
+        const long long b = row / a.C, ch = row % a.C;
+        mbar_wait(&s_full[buf], par);
+        int tbase = 0;
+        for (int s = 0; s < a.nscales; ++s) {
+            const ScaleArg& sc = a.sc[s];
+            const int h = sc.hop;
+            long long lo = (c0 + h - 1) / h, hi = (c0 + a.chunk + h - 1) / h;
+            if (hi > sc.F) hi = sc.F;
+            if (lo > hi) lo = hi;
+            const int nfr = sc.n >= 2048 ? 1 : (sc.n >= 512 ? 2 : (sc.n >= 128 ? 4 : 8));
+            const int nt = (int)((hi - lo + nfr - 1) / nfr);
+            const int first = (warp - tbase) & (kPWarps - 1);
+            tbase += nt;
+            if (first >= nt) continue;
+            const int f_lo = (int)lo, f_end = (int)hi;
+            const int origin = (int)(c0 - a.pmax + sc.pad);
+            const long long plane = (long long)sc.F * sc.K;
+            float* out_re_row = sc.out + ((b * 2) * a.C + ch) * plane;
+            const long long im_off = (long long)a.C * plane;
+            switch (sc.n) {
+                case 2048: for (int t = first; t < nt; t += kPWarps) planes_task<Plan2048>(sc, tile, xbuf, lane, f_lo + t * 1, f_end, origin, out_re_row, im_off); break;
+                case 1024: for (int t = first; t < nt; t += kPWarps) planes_task<Plan1024>(sc, tile, xbuf, lane, f_lo + t * 2, f_end, origin, out_re_row, im_off); break;
+                case 512: for (int t = first; t < nt; t += kPWarps) planes_task<Plan512>(sc, tile, xbuf, lane, f_lo + t * 2, f_end, origin, out_re_row, im_off); break;
+                case 256: for (int t = first; t < nt; t += kPWarps) planes_task<Plan256>(sc, tile, xbuf, lane, f_lo + t * 4, f_end, origin, out_re_row, im_off); break;
+                case 128: for (int t = first; t < nt; t += kPWarps) planes_task<Plan128>(sc, tile, xbuf, lane, f_lo + t * 4, f_end, origin, out_re_row, im_off); break;
+                default: for (int t = first; t < nt; t += kPWarps) planes_task<Plan64>(sc, tile, xbuf, lane, f_lo + t * 8, f_end, origin, out_re_row, im_off); break;
+            }
+        }
+        __syncwarp();
+        if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(&s_empty[buf])) : "memory");
+        if (warp == 0 && i + 2 < n_my) {
+            mbar_wait(&s_empty[buf], par);                   // every warp has finished unit i: its buffer takes unit i + 2
+            issue(i + 2, buf);
         }
     }
 #if TAC_PLANES_BULK
@@ -611,9 +721,22 @@ extern "C" int tac_stft_multi(const float* x, int64_t B, int64_t C, int64_t T, i
         a.nchunks = (int)(last_start / a.chunk) + 1;
         a.tile_len = a.chunk + nmax;
         const size_t smem = (size_t)a.tile_len * sizeof(float) + (size_t)kWarps * kXbufFloat2 * sizeof(float2);
-        TAC_SMEM_OPT_IN(stft_planes_kernel, 111 * 1024);
         const long long grid = rows * a.nchunks;
         TAC_REQUIRE(grid < (1ll << 31), "grid too large");
+#if TAC_PLANES_PERSIST
+        // persistent double-buffered form: the tile must be bulk-copyable (16-byte aligned rows, zero or no padding) and there
+        // must be enough units to give every SM several
+        if (vec_ok && (a.pmax == 0 || pad_mode == TAC_PAD_ZERO) && (a.pmax & 3) == 0 && grid >= 4ll * kNumSMs) {
+            const size_t psmem = 2 * (size_t)a.tile_len * sizeof(float) + (size_t)kPWarps * kXbufFloat2 * sizeof(float2);
+            if (psmem <= 226 * 1024) {
+                TAC_SMEM_OPT_IN(stft_planes_persist_kernel, 226 * 1024);
+                stft_planes_persist_kernel<<<kNumSMs, kPThreads, psmem, st>>>(a, grid); TAC_LAUNCHED(1);
+                TAC_CHECK_CUDA(cudaGetLastError());
+                return TAC_OK;
+            }
+        }
+#endif
+        TAC_SMEM_OPT_IN(stft_planes_kernel, 111 * 1024);
         stft_planes_kernel<<<(unsigned)grid, kThreads, smem, st>>>(a); TAC_LAUNCHED(1);
         TAC_CHECK_CUDA(cudaGetLastError());
         return TAC_OK;

@@ -662,9 +662,10 @@ def reconstruct_and_disc_inputs(magnitude_batch: torch.Tensor, phase_batch: torc
     (``train_pkl_file_task_aware.py:290``), ``.unsqueeze(1)`` (``:347``) and the spectrogram front of every scale
     discriminator that ``disc(ground_truth_clean_waveforms)`` (``:353``) runs first (``msstftd.py:188-191`` ->
     ``:151-153``).  Returns ``(waveform [B, hop*(F-1)], [z_s [B, 2, F_s, K_s] per scale])``; the waveform is what ``:333``'s
-    MSE consumes, ``z_s`` is what ``DiscriminatorSTFT.forward`` feeds its first conv.  The batch is walked in row groups whose
-    waveform stays in the L2 between the synthesis and the analysis kernel (``tac_istft_disc_inputs``), so the analysis does
-    not re-read it from HBM; results are bit-identical to ``batch_reconstruct_waveform`` + ``MultiScaleSTFT``.  No autograd:
+    MSE consumes, ``z_s`` is what ``DiscriminatorSTFT.forward`` feeds its first conv.  One C-ABI call enqueues both kernels
+    (``tac_istft_disc_inputs``); ``rows_per_group`` > 0 walks the batch in row groups (``tac_chain_rows_per_group`` sizes them
+    so that a group's waveform stays in the L2 between synthesis and analysis; measured slower than one group on B200, see
+    ``csrc/chain.cu``).  Results are bit-identical to ``batch_reconstruct_waveform`` + ``MultiScaleSTFT``.  No autograd:
     the reference detaches this branch (``torch.tensor(reconstructed_clean_waveforms)``, ``:303``)."""
     if magnitude_batch.shape != phase_batch.shape:
         raise ValueError("The shapes of magnitude and phase must match for batched processing.")

@@ -64,7 +64,19 @@ __device__ __forceinline__ void stage_tile(float* tile, const float* __restrict_
 }
 
 #ifndef TAC_PLANES_PERSIST
-#define TAC_PLANES_PERSIST 1  // 1: one persistent 16-warp CTA per SM with a double-buffered, bulk-copied sample tile (when applicable)
+#define TAC_PLANES_PERSIST 1  // calls with up to this many scales run one persistent 16-warp CTA per SM with a double-buffered, bulk-copied sample tile (0: never)
+#endif
+#ifndef TAC_PLANES_PF
+#define TAC_PLANES_PF 2       // one-shot kernel: prefetch the tile of unit blockIdx.x + PF * SMs into the L2 (0: off)
+#endif
+#ifndef TAC_PLANES_SYNC
+#define TAC_PLANES_SYNC 0
+#endif
+#ifndef TAC_PLANES_G
+#define TAC_PLANES_G 1        // tasks are dealt to the warps in groups of G consecutive ones (1: round-robin)
+#endif
+#ifndef TAC_PLANES_ROT
+#define TAC_PLANES_ROT 0      // 1: warp w walks the scales starting at scale w % nscales (de-phases the warps)
 #endif
 #ifndef TAC_PLANES_BULK
 #define TAC_PLANES_BULK 1     // 1: a task's two plane spans leave through shared memory as bulk async copies; 0: 4-byte streaming stores
@@ -192,55 +204,107 @@ __device__ __forceinline__ void planes_task(const ScaleArg& sc, const float* til
     }
 }
 
+// All tasks of one (row, chunk) unit that belong to this warp.  Tasks (NFR frames of one scale) are numbered scale by scale and
+// dealt round-robin: warp w of W takes the global task numbers t = w (mod W).  What depends on the scale only -- frame range,
+// task count, plane pointers -- is computed ONCE per unit, lane s for scale s (32-bit arithmetic), and broadcast by shuffles;
+// the plan switch sits outside the task loop.  (Round 2 history, cfg 4, 128 tasks per unit: a shared atomic counter + shuffle +
+// scale search + 64-bit plane arithmetic PER TASK were 17 % of the kernel's instructions; hoisted per scale with 64-bit divisions
+// they were still ~250 instructions per scale and warp.)
+template <int W>
+__device__ __forceinline__ void planes_unit(const PlanesArgs& a, const float* tile, float2* xbuf, int lane, int warp,
+                                            unsigned row, unsigned c0) {
+    static_assert((W & (W - 1)) == 0, "W must be a power of two");
+    static_assert(Plan2048::NFR == 1 && Plan1024::NFR == 2 && Plan512::NFR == 2 && Plan256::NFR == 4 && Plan128::NFR == 4 && Plan64::NFR == 8, "nfr");
+    int my_lo = 0, my_hi = 0, my_nt = 0;
+    float* my_out = nullptr;
+    long long my_im = 0;
+    if (lane < a.nscales) {
+        const ScaleArg& sc = a.sc[lane];
+        const unsigned h = (unsigned)sc.hop;
+        unsigned lo = (c0 + h - 1u) / h, hi = (c0 + (unsigned)a.chunk + h - 1u) / h;
+        if (hi > (unsigned)sc.F) hi = (unsigned)sc.F;
+        if (lo > hi) lo = hi;
+        const int l2nfr = sc.n >= 2048 ? 0 : (sc.n >= 512 ? 1 : (sc.n >= 128 ? 2 : 3));
+        my_lo = (int)lo; my_hi = (int)hi;
+        my_nt = (int)((hi - lo + (1u << l2nfr) - 1u) >> l2nfr);
+        const unsigned b = row / (unsigned)a.C, ch = row - b * (unsigned)a.C;
+        const long long plane = (long long)sc.F * sc.K;
+        my_out = sc.out + ((long long)(b * 2u) * a.C + ch) * plane;
+        my_im = (long long)a.C * plane;
+    }
+    int my_tb = my_nt;                                       // exclusive prefix sum over the (<= 8) scales
+#pragma unroll
+    for (int o = 1; o < TAC_MAX_SCALES; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, my_tb, o);
+        if (lane >= o) my_tb += v;
+    }
+    my_tb -= my_nt;
+    for (int s0 = 0; s0 < a.nscales; ++s0) {
+#if TAC_PLANES_ROT
+        int s = s0 + warp; while (s >= a.nscales) s -= a.nscales;
+#else
+        const int s = s0;
+#endif
+        // block-cyclic deal: groups of G consecutive global task numbers go to one warp (G = 1: plain round-robin)
+        constexpr int G = TAC_PLANES_G;
+        const int nt = __shfl_sync(0xffffffffu, my_nt, s), tb = __shfl_sync(0xffffffffu, my_tb, s);
+        const int qb = tb / G;
+        const int q0 = qb + ((warp - qb) & (W - 1));         // first group >= qb that belongs to this warp
+        if (q0 * G >= tb + nt) continue;                     // warp-uniform
+        const int f_lo = __shfl_sync(0xffffffffu, my_lo, s), f_end = __shfl_sync(0xffffffffu, my_hi, s);
+        float* out_re_row = reinterpret_cast<float*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(my_out), s));
+        const long long im_off = __shfl_sync(0xffffffffu, my_im, s);
+        const ScaleArg& sc = a.sc[s];
+        // tile[0] is padded-coordinate (c0 - pmax) of the widest scale == (c0 - pmax + pad_s) of scale s
+        const int origin = (int)c0 - a.pmax + sc.pad;
+        auto my_tasks = [&](auto&& body) {
+            for (int q = q0; q * G < tb + nt; q += W) {
+                const int t0 = max(q * G, tb) - tb, t1 = min(q * G + G, tb + nt) - tb;
+                for (int t = t0; t < t1; ++t) body(t);
+            }
+        };
+        switch (sc.n) {
+            case 2048: my_tasks([&](int t) { planes_task<Plan2048>(sc, tile, xbuf, lane, f_lo + t * 1, f_end, origin, out_re_row, im_off); }); break;
+            case 1024: my_tasks([&](int t) { planes_task<Plan1024>(sc, tile, xbuf, lane, f_lo + t * 2, f_end, origin, out_re_row, im_off); }); break;
+            case 512: my_tasks([&](int t) { planes_task<Plan512>(sc, tile, xbuf, lane, f_lo + t * 2, f_end, origin, out_re_row, im_off); }); break;
+            case 256: my_tasks([&](int t) { planes_task<Plan256>(sc, tile, xbuf, lane, f_lo + t * 4, f_end, origin, out_re_row, im_off); }); break;
+            case 128: my_tasks([&](int t) { planes_task<Plan128>(sc, tile, xbuf, lane, f_lo + t * 4, f_end, origin, out_re_row, im_off); }); break;
+            default: my_tasks([&](int t) { planes_task<Plan64>(sc, tile, xbuf, lane, f_lo + t * 8, f_end, origin, out_re_row, im_off); }); break;
+        }
+    }
+}
+
 __global__ void __launch_bounds__(kThreads, 2) stft_planes_kernel(const PlanesArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* tile = reinterpret_cast<float*>(smem_raw);
     float2* xbuf_all = reinterpret_cast<float2*>(smem_raw + (size_t)a.tile_len * sizeof(float));
 
-    const int c = blockIdx.x % a.nchunks;
-    const long long row = blockIdx.x / a.nchunks;
-    const float* xr = a.x + row * a.T;
-    const long long c0 = (long long)c * a.chunk;             // chunk origin in padded frame-start coordinates
+    const unsigned c = blockIdx.x % (unsigned)a.nchunks;
+    const unsigned row = blockIdx.x / (unsigned)a.nchunks;
+    const float* xr = a.x + (long long)row * a.T;
+    const unsigned c0 = c * (unsigned)a.chunk;               // chunk origin in padded frame-start coordinates (T < 2^31 - 2^16)
 
-    stage_tile(tile, xr, c0 - a.pmax, a.tile_len, a.T, a.pad_mode, a.vec_ok != 0);
-    __syncthreads();
-
-    // Tasks (NFR frames of one scale) are numbered scale by scale and dealt round-robin: warp w takes the global task numbers
-    // t = w (mod 8).  Everything that depends on the scale only -- frame range, tile origin, plane pointers, the plan -- is
-    // formed once per scale outside the task loop.  (Round 2: the shared atomic counter, the shuffle, the scale search with one
-    // shared-memory load per step and the 64-bit plane arithmetic PER TASK were 15 % of the kernel's instructions and ~15 % of
-    // its stall samples on cfg 4, where a CTA runs 128 tasks.)
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    float2* xbuf = xbuf_all + warp * kXbufFloat2;
-    const long long b = row / a.C, ch = row % a.C;
-    int tbase = 0;                                           // global number of this scale's first task
-    for (int s = 0; s < a.nscales; ++s) {
-        const ScaleArg& sc = a.sc[s];
-        const int h = sc.hop;
-        long long lo = (c0 + h - 1) / h, hi = (c0 + a.chunk + h - 1) / h;
-        if (hi > sc.F) hi = sc.F;
-        if (lo > hi) lo = hi;
-        const int nfr = sc.n >= 2048 ? 1 : (sc.n >= 512 ? 2 : (sc.n >= 128 ? 4 : 8));
-        const int nt = (int)((hi - lo + nfr - 1) / nfr);
-        const int first = (warp - tbase) & (kWarps - 1);     // kWarps is a power of two
-        tbase += nt;
-        if (first >= nt) continue;
-        const int f_lo = (int)lo, f_end = (int)hi;
-        // tile[0] is padded-coordinate (c0 - pmax) of the widest scale == (c0 - pmax + pad_s) of scale s
-        const int origin = (int)(c0 - a.pmax + sc.pad);
-        const long long plane = (long long)sc.F * sc.K;
-        float* out_re_row = sc.out + ((b * 2) * a.C + ch) * plane;
-        const long long im_off = (long long)a.C * plane;
-        static_assert(Plan2048::NFR == 1 && Plan1024::NFR == 2 && Plan512::NFR == 2 && Plan256::NFR == 4 && Plan128::NFR == 4 && Plan64::NFR == 8, "nfr");
-        switch (sc.n) {
-            case 2048: for (int t = first; t < nt; t += kWarps) planes_task<Plan2048>(sc, tile, xbuf, lane, f_lo + t * 1, f_end, origin, out_re_row, im_off); break;
-            case 1024: for (int t = first; t < nt; t += kWarps) planes_task<Plan1024>(sc, tile, xbuf, lane, f_lo + t * 2, f_end, origin, out_re_row, im_off); break;
-            case 512: for (int t = first; t < nt; t += kWarps) planes_task<Plan512>(sc, tile, xbuf, lane, f_lo + t * 2, f_end, origin, out_re_row, im_off); break;
-            case 256: for (int t = first; t < nt; t += kWarps) planes_task<Plan256>(sc, tile, xbuf, lane, f_lo + t * 4, f_end, origin, out_re_row, im_off); break;
-            case 128: for (int t = first; t < nt; t += kWarps) planes_task<Plan128>(sc, tile, xbuf, lane, f_lo + t * 4, f_end, origin, out_re_row, im_off); break;
-            default: for (int t = first; t < nt; t += kWarps) planes_task<Plan64>(sc, tile, xbuf, lane, f_lo + t * 8, f_end, origin, out_re_row, im_off); break;
+#if TAC_PLANES_PF
+    {   // L2 prefetch (evict-last) of the tile of the CTA that will take this one's place: CTAs are dispatched in blockIdx order,
+        // 2 per SM, so unit blockIdx.x + 2 * SMs starts about when this one ends.  Its staging loads then hit the L2 instead of
+        // queueing behind the plane writes in DRAM (the staging wait + barrier were 14 % of the warp-time samples on cfg 4).
+        const unsigned u2 = blockIdx.x + TAC_PLANES_PF * kNumSMs;
+        if (u2 < gridDim.x) {
+            const unsigned row2 = u2 / (unsigned)a.nchunks;
+            const long long g2 = (long long)(u2 - row2 * (unsigned)a.nchunks) * a.chunk - a.pmax;
+            const long long lo = g2 < 0 ? 0 : g2;
+            long long hi = g2 + a.tile_len; hi = hi > a.T ? a.T : hi;
+            const char* p = reinterpret_cast<const char*>(a.x + (long long)row2 * a.T + lo);
+            const long long bytes = (hi - lo) * 4;
+            for (long long off = (long long)threadIdx.x * 128; off < bytes; off += (long long)kThreads * 128)
+                asm volatile("prefetch.global.L2::evict_last [%0];" :: "l"(p + off));
         }
     }
+#endif
+    stage_tile(tile, xr, (long long)c0 - a.pmax, a.tile_len, a.T, a.pad_mode, a.vec_ok != 0);
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    planes_unit<kWarps>(a, tile, xbuf_all + warp * kXbufFloat2, lane, warp, row, c0);
 #if TAC_PLANES_BULK
     if (lane < 8) bulk_wait_read();                        // shared memory must outlive the copy engine's reads
 #endif
@@ -259,11 +323,12 @@ constexpr int kPWarps = 16;
 constexpr int kPThreads = kPWarps * 32;
 
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {     // bounded: traps instead of hanging the GPU
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {     // bounded: traps instead of hanging the GPU; the
+                                                                                 // hint lets a waiting warp sleep up to 2 us per probe
     const unsigned addr = smem_u32(bar);
     for (unsigned it = 0; it < (1u << 26); ++it) {
         unsigned done;
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}\n"
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, 2000;\n\tselp.u32 %0, 1, 0, p;\n\t}\n"
                      : "=r"(done) : "r"(addr), "r"(parity) : "memory");
         if (done) return;
     }
@@ -320,38 +385,14 @@ __global__ void __launch_bounds__(kPThreads, 1) stft_planes_persist_kernel(const
     for (int i = 0; i < n_my; ++i) {
         const int buf = i & 1;
         const unsigned par = (unsigned)(i >> 1) & 1u;
-        const long long u = blockIdx.x + (long long)i * gridDim.x;
-        const long long row = u / a.nchunks;
-        const long long c0 = (u % a.nchunks) * a.chunk;
-        const float* tile = tiles + (size_t)buf * a.tile_len;
-        const long long b = row / a.C, ch = row % a.C;
+        const unsigned u = blockIdx.x + (unsigned)i * gridDim.x;                              // nunits < 2^31
+        const unsigned row = u / (unsigned)a.nchunks;
+        const unsigned c0 = (u - row * (unsigned)a.nchunks) * (unsigned)a.chunk;
         mbar_wait(&s_full[buf], par);
-        int tbase = 0;
-        for (int s = 0; s < a.nscales; ++s) {
-            const ScaleArg& sc = a.sc[s];
-            const int h = sc.hop;
-            long long lo = (c0 + h - 1) / h, hi = (c0 + a.chunk + h - 1) / h;
-            if (hi > sc.F) hi = sc.F;
-            if (lo > hi) lo = hi;
-            const int nfr = sc.n >= 2048 ? 1 : (sc.n >= 512 ? 2 : (sc.n >= 128 ? 4 : 8));
-            const int nt = (int)((hi - lo + nfr - 1) / nfr);
-            const int first = (warp - tbase) & (kPWarps - 1);
-            tbase += nt;
-            if (first >= nt) continue;
-            const int f_lo = (int)lo, f_end = (int)hi;
-            const int origin = (int)(c0 - a.pmax + sc.pad);
-            const long long plane = (long long)sc.F * sc.K;
-            float* out_re_row = sc.out + ((b * 2) * a.C + ch) * plane;
-            const long long im_off = (long long)a.C * plane;
-            switch (sc.n) {
-                case 2048: for (int t = first; t < nt; t += kPWarps) planes_task<Plan2048>(sc, tile, xbuf, lane, f_lo + t * 1, f_end, origin, out_re_row, im_off); break;
-                case 1024: for (int t = first; t < nt; t += kPWarps) planes_task<Plan1024>(sc, tile, xbuf, lane, f_lo + t * 2, f_end, origin, out_re_row, im_off); break;
-                case 512: for (int t = first; t < nt; t += kPWarps) planes_task<Plan512>(sc, tile, xbuf, lane, f_lo + t * 2, f_end, origin, out_re_row, im_off); break;
-                case 256: for (int t = first; t < nt; t += kPWarps) planes_task<Plan256>(sc, tile, xbuf, lane, f_lo + t * 4, f_end, origin, out_re_row, im_off); break;
-                case 128: for (int t = first; t < nt; t += kPWarps) planes_task<Plan128>(sc, tile, xbuf, lane, f_lo + t * 4, f_end, origin, out_re_row, im_off); break;
-                default: for (int t = first; t < nt; t += kPWarps) planes_task<Plan64>(sc, tile, xbuf, lane, f_lo + t * 8, f_end, origin, out_re_row, im_off); break;
-            }
-        }
+#if TAC_PLANES_SYNC
+        __syncthreads();                                     // warps start a unit together: they walk the plans' code in phase
+#endif
+        planes_unit<kPWarps>(a, tiles + (size_t)buf * a.tile_len, xbuf, lane, warp, row, c0);
         __syncwarp();
         if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(&s_empty[buf])) : "memory");
         if (warp == 0 && i + 2 < n_my) {
@@ -675,7 +716,7 @@ extern "C" int tac_stft_multi(const float* x, int64_t B, int64_t C, int64_t T, i
     TAC_REQUIRE(n_scales >= 1 && n_scales <= TAC_MAX_SCALES, "n_scales must be in [1, %d]", TAC_MAX_SCALES);
     TAC_REQUIRE(out_mode >= 0 && out_mode <= 2, "unknown out_mode %d", out_mode);
     TAC_REQUIRE(pad_mode == TAC_PAD_ZERO || pad_mode == TAC_PAD_REFLECT, "unknown pad_mode %d", pad_mode);
-    TAC_REQUIRE(B * C * T < (1ll << 40), "input too large");
+    TAC_REQUIRE(B * C * T < (1ll << 40) && T < (1ll << 31) - 65536, "input too large");
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     const long long rows = B * C;
     const int vec_ok = ((reinterpret_cast<uintptr_t>(x) & 15u) == 0 && (T & 3) == 0) ? 1 : 0;
@@ -726,7 +767,12 @@ extern "C" int tac_stft_multi(const float* x, int64_t B, int64_t C, int64_t T, i
 #if TAC_PLANES_PERSIST
         // persistent double-buffered form: the tile must be bulk-copyable (16-byte aligned rows, zero or no padding) and there
         // must be enough units to give every SM several
-        if (vec_ok && (a.pmax == 0 || pad_mode == TAC_PAD_ZERO) && (a.pmax & 3) == 0 && grid >= 4ll * kNumSMs) {
+        // Measured on B200 (cfg 4 shapes, ms, one-shot -> persistent): single scale n = 2048 / 1024 / 512 / 256 / 128: 0.452 / 0.444 /
+        // 0.450 / 0.471 / 0.537 -> 0.363 / 0.370 / 0.391 / 0.418 / 0.490 (68 ... 52 % of the HBM peak); all five scales in one
+        // launch: 1.88 -> 2.04 (ncu: instruction-fetch stalls 1.09 per issue against < 0.2 -- sixteen warps that drift through
+        // five unrolled plan bodies, 150 KB of code; in-phase starts, block-cyclic deals and rotated scale orders all measured
+        // worse), so several scales keep the one-shot kernel (+ L2 prefetch of the successor's tile).
+        if (n_scales <= TAC_PLANES_PERSIST && vec_ok && (a.pmax == 0 || pad_mode == TAC_PAD_ZERO) && (a.pmax & 3) == 0 && grid >= 4ll * kNumSMs) {
             const size_t psmem = 2 * (size_t)a.tile_len * sizeof(float) + (size_t)kPWarps * kXbufFloat2 * sizeof(float2);
             if (psmem <= 226 * 1024) {
                 TAC_SMEM_OPT_IN(stft_planes_persist_kernel, 226 * 1024);

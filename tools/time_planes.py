@@ -36,5 +36,5 @@ B4 = int(sys.argv[1]) if len(sys.argv) > 1 else 512
 run("cfg4", B4, 160000, (2048, 1024, 512, 256, 128))
 run("cfg2-disc", 512, 16000, (1024, 2048, 512), reps=20)
 run("cfg3-disc", 4096, 16000, (1024, 2048, 512), reps=5)
-for n in (2048, 1024, 512, 256, 128):
+for n in (() if os.environ.get("TAC_PLANES_SHORT") else (2048, 1024, 512, 256, 128)):
     run(f"cfg4-only-{n}", B4, 160000, (n,), reps=3)

@@ -457,6 +457,8 @@ __global__ void __launch_bounds__(kStreamThreads, 3) mrstft_stream_small_kernel(
 constexpr int kCombineIter = 4;                 // warp steps of a CTA along its row
 template <int VEC>
 __global__ void __launch_bounds__(256) mrstft_combine_kernel(const StreamArgs a, const unsigned ctas_per_row) {
+    // the sums kernel behind this one does not read what this one writes: it may start at once (it waits for this grid before it exits)
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned row = blockIdx.x / ctas_per_row;
     const unsigned span0 = (blockIdx.x - row * ctas_per_row) * (256u * VEC * kCombineIter);
@@ -529,6 +531,9 @@ __global__ void __launch_bounds__(256) mrstft_stream_sums_kernel(const StreamArg
         __syncthreads();
     }
     if (threadIdx.x == 0) sums[2 * sc.orig + i] = sh[0];
+    // launched with programmatic stream serialisation behind the combine kernel (it only needs the stream kernels' partials, which
+    // are complete before the combine kernel starts): completion of THIS grid must still imply completion of the combine kernel
+    asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 static inline size_t align16(size_t v) { return (v + 15) & ~(size_t)15; }
@@ -646,8 +651,15 @@ int launch_stream(const float* x, const float* y, int64_t rows, int64_t T, int n
     TAC_LAUNCHED(1);
     TAC_CHECK_CUDA(cudaGetLastError());
     if (sums) {
-        mrstft_stream_sums_kernel<<<2 * n_scales, 256, 0, st>>>(a, sums); TAC_LAUNCHED(1);
-        TAC_CHECK_CUDA(cudaGetLastError());
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3((unsigned)(2 * n_scales)); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        TAC_CHECK_CUDA(cudaLaunchKernelEx(&cfg, mrstft_stream_sums_kernel, a, sums));
+        TAC_LAUNCHED(1);
     }
     return TAC_OK;
 }

@@ -639,18 +639,28 @@ def run_native(args):
     ev_done = [torch.cuda.Event() for _ in range(nbuf)]
     ev_loss = [torch.cuda.Event() for _ in range(nbuf)]
 
+    # two copy streams (target audio on one, decoded audio + latents on the other): one stream alone does not saturate the
+    # link (tools/h2d_probe.py on this pool: 51 GB/s on one stream, 55 GB/s on two)
+    copy_stream2 = torch.cuda.Stream(device=dev)
+    ev_copied2 = [torch.cuda.Event() for _ in range(nbuf)]
+
     def enqueue_copy(i):
         b = i % nbuf
         with torch.cuda.stream(copy_stream):
             copy_stream.wait_event(ev_done[b])                       # the step that last used this buffer has finished
-            dbuf[b][0].copy_(px, non_blocking=True); dbuf[b][1].copy_(py, non_blocking=True)
+            dbuf[b][0].copy_(px, non_blocking=True)
+            ev_copied[b].record(copy_stream)
+        with torch.cuda.stream(copy_stream2):
+            copy_stream2.wait_event(ev_done[b])
+            dbuf[b][1].copy_(py, non_blocking=True)
             for a_, b_ in zip(dbuf[b][2], pz):
                 a_.copy_(b_, non_blocking=True)
-            ev_copied[b].record(copy_stream)
+            ev_copied2[b].record(copy_stream2)
 
     def enqueue_step(i):
         b = i % nbuf
         main_stream.wait_event(ev_copied[b])
+        main_stream.wait_event(ev_copied2[b])
         if g_e2e[b] is not None:
             g_e2e[b].replay()
         else:
@@ -686,7 +696,7 @@ def run_native(args):
     e2e_val = audio_s_step / (float(dt.item()) / args.steps)
     h2d = 2 * rows * T * 4 + views * batch * d * 4
     e2e = {"value": e2e_val, "unit": "audio-s/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
-           "ms_per_step": 1e3 * float(dt.item()) / args.steps, "pipeline": "double-buffered: H2D of step i+1 overlaps compute of step i",
+           "ms_per_step": 1e3 * float(dt.item()) / args.steps, "pipeline": "double-buffered: H2D of step i+1 (two copy streams) overlaps compute of step i",
            "loss_last": e2e_vals[-1]}
 
     tgpu = None

@@ -1,5 +1,5 @@
 #!/bin/bash
-# 1 -> N scaling lines with the driver's flags: bash tools/gpu_scale8.sh <tag> <N> [extra bench flags]   (gpurun --gpus N)
+# 1 -> N scaling lines with the driver's flags: bash tools/gpu_scale.sh <tag> <N> [extra bench flags]   (gpurun --gpus N)
 TAG=${1:-r02e}; N=${2:-8}; shift 2
 OUT=gpurun_out; mkdir -p $OUT
 timeout 300 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-extra "$@" 2> $OUT/bench_${TAG}_n1.err | grep "^{" > $OUT/bench_${TAG}_n1.json; echo "n=1 rc=$?"

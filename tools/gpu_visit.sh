@@ -1,7 +1,7 @@
 #!/bin/bash
 # Round-2 1-GPU visit (re-entry): full parity suite, A/B of variants/lib_*.so against the in-tree library, bench line,
 # ncu --set full (+ source) of named kernels under the bench command.
-#   gpurun --timeout 1500 -- 'bash tools/gpu_r2g.sh <tag> "<kernel regexes>"'
+#   gpurun --timeout 1500 -- 'bash tools/gpu_visit.sh <tag> "<kernel regexes>"'
 TAG=${1:-r02g}; KERNELS=${2:-mrstft_stream_kernel}
 OUT=gpurun_out; mkdir -p $OUT
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm --format=csv,noheader

@@ -1,5 +1,5 @@
 #!/bin/bash
-# Round-2 multi-GPU visit: bash tools/gpu_r2n.sh <tag> <N>   (gpurun --gpus N)
+# Round-2 multi-GPU visit: bash tools/gpu_visit_n.sh <tag> <N>   (gpurun --gpus N)
 # the 2-process exchange test, then the N-rank bench with the driver's flags (and N=1 beside it for the efficiency).
 TAG=${1:-r02a}; N=${2:-2}
 OUT=gpurun_out; mkdir -p $OUT

@@ -194,6 +194,47 @@ __global__ void __launch_bounds__(kIThreads, 1) istft_kernel(const IstftArgs a) 
             float* cout = carry + ((it + 1) & 1) * clen;
             const float* pf = reinterpret_cast<const float*>(tile);     // frame fl at pf + fl * 2 * KP
             const int region = TFR * hop + clen;
+            if (q == 4 && r == 0) {
+                // hop = n / 4 (the reference's framing): hop block jl is covered by the frames jl - 3 .. jl; every condition on jl
+                // is uniform over the CTA and the four additions are unrolled, in ascending frame order as in the general loop
+                // below.  (Round 2: that loop -- run-time trip counts, per-thread bounds -- was 46 % of the kernel's instructions.)
+                for (int jl = 0; jl < TFR + 3; ++jl) {
+                    const int jg = ft + jl;
+                    if (jl < TFR && (jg < ja || jg >= jb)) continue;
+                    const bool inner = jg - 4 >= 0 && jg < F;
+                    const bool has3 = jl - 3 >= 0 && jl - 3 < TFR, has2 = jl - 2 >= 0 && jl - 2 < TFR, has1 = jl - 1 >= 0 && jl - 1 < TFR,
+                               has0 = jl < TFR;
+                    const float* p3 = pf + (jl - 3) * (2 * KP) + 3 * hop;
+                    const float* p2 = pf + (jl - 2) * (2 * KP) + 2 * hop;
+                    const float* p1 = pf + (jl - 1) * (2 * KP) + hop;
+                    const float* p0 = pf + jl * (2 * KP);
+                    for (int o = tid; o < hop; o += kIThreads) {
+                        const int i = jl * hop + o;
+                        float v = jl < 3 ? cin[i] : 0.0f;
+                        if (has3) v += p3[o];
+                        if (has2) v += p2[o];
+                        if (has1) v += p1[o];
+                        if (has0) v += p0[o];
+                        if (jl >= TFR) { cout[i - TFR * hop] = v; continue; }
+                        const long long t = (long long)jg * hop + o - a.start;
+                        if (t < 0 || t >= lim) continue;
+                        float ie;
+                        if (a.adjoint) {
+                            ie = 1.0f;
+                        } else if (inner) {
+                            ie = inv_env[o];
+                        } else {
+                            float env = 0.0f;                            // sum of (w / 2)^2 over the frames that exist
+                            for (int fl = jl - 3; fl <= jl; ++fl) {
+                                const int fg = ft + fl;
+                                if (fg >= 0 && fg < F) { const float w = wf[i - fl * hop]; env = fmaf(w, w, env); }
+                            }
+                            ie = 1.0f / (4.0f * env);
+                        }
+                        orow[t] = v * ie;
+                    }
+                }
+            } else
             for (int jl = 0; jl * hop < region; ++jl) {
                 const int jg = ft + jl;                                  // global hop block
                 if (jl < TFR && (jg < ja || jg >= jb)) continue;         // not this run's block: never written
@@ -312,10 +353,27 @@ static int istft_impl(const float* a, const float* b, int in_mode, int64_t rows,
     const int nfr = n_fft >= 2048 ? 1 : (n_fft >= 512 ? 2 : (n_fft >= 128 ? 4 : 8));
     const int tfr = kIWarps * nfr;
     // enough runs to fill the GPU twice over, but never shorter than four tiles (the R - 1 warm-up frames are recomputed)
+    // One CTA per SM (215 KB of shared memory): the grid rows * runs_per_row should fill whole waves of 148 CTAs.  Among the
+    // run counts from "twice the SMs" up to four times that, take the one with the best (wave fill) x (useful frames) product
+    // (128 rows x 600 frames: 3 runs per row = 2.59 waves -> 8 runs = 6.92 waves, 1.03 -> 0.91 ms).
     long long want = (2 * kNumSMs + rows - 1) / rows;
-    int rb = (int)((k.nblk + want - 1) / want);
-    if (rb < 4 * tfr) rb = 4 * tfr;
-    if (rb > k.nblk) rb = k.nblk;
+    int best_rb = 0;
+    double best = -1.0;
+    for (long long cand = want; cand <= 4 * want + 3; ++cand) {
+        int rb_c = (int)((k.nblk + cand - 1) / cand);
+        if (rb_c < 4 * tfr) rb_c = 4 * tfr;
+        if (rb_c > k.nblk) rb_c = k.nblk;
+        const long long rpr = (k.nblk + rb_c - 1) / rb_c;
+        const double ctas = (double)rows * (double)rpr;
+        const double waves = ctas / kNumSMs;
+        const double fill = waves / (double)(long long)(waves + 0.999999);
+        const long long last = k.nblk - (rpr - 1) * (long long)rb_c;
+        if (rpr > 1 && 2 * last < rb_c) continue;                                 // no sliver run (it still costs a CTA and its warm-up)
+        const double useful = (double)rb_c / (double)(rb_c + (k.R - 1) + 3);      // warm-up frames (+ alignment) recomputed per run
+        const double score = fill * useful;
+        if (score > best + 1e-9) { best = score; best_rb = rb_c; }
+    }
+    int rb = best_rb;
     k.run_blocks = rb;
     k.runs_per_row = (k.nblk + rb - 1) / rb;
     k.scale = (float)((2.0 / (double)n_fft) * (normalized ? sqrt((double)n_fft) : 1.0));

@@ -368,8 +368,8 @@ static int istft_impl(const float* a, const float* b, int in_mode, int64_t rows,
         const double waves = ctas / kNumSMs;
         const double fill = waves / (double)(long long)(waves + 0.999999);
         const long long last = k.nblk - (rpr - 1) * (long long)rb_c;
-        if (rpr > 1 && 2 * last < rb_c) continue;                                 // no sliver run (it still costs a CTA and its warm-up)
-        const double useful = (double)rb_c / (double)(rb_c + (k.R - 1) + 3);      // warm-up frames (+ alignment) recomputed per run
+        double useful = (double)rb_c / (double)(rb_c + (k.R - 1) + 3);            // warm-up frames (+ alignment) recomputed per run
+        if (rpr > 1 && 2 * last < rb_c) useful *= 0.85;                           // a sliver run still costs a CTA and its warm-up
         const double score = fill * useful;
         if (score > best + 1e-9) { best = score; best_rb = rb_c; }
     }

@@ -585,7 +585,7 @@ def run_native(args):
     byte_legs = {"frontend": alg.get("frontend", 0), "loss_fused": alg["loss_fused"],
                  "dpca_stats": alg["dpca_stats"], "dpca_project": alg["dpca_project"]}
     dom = max(("frontend", "loss_fused"), key=lambda k: leg_ms[k])
-    kern_name = {"frontend": "stft_tiled_kernel<Plan2048, MAGPHASE>", "loss_fused": "mrstft_stream_kernel<true> + mrstft_combine_kernel (sums + grad_y in one pass)"}[dom]
+    kern_name = {"frontend": "stft_frontend_kernel<Plan2048>", "loss_fused": "mrstft_stream_kernel<true> + mrstft_stream_small_kernel<true> + mrstft_combine_kernel + mrstft_stream_sums_kernel (sums + grad_y in one pass over x, y)"}[dom]
     achieved = byte_legs[dom] / (leg_ms[dom] * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": kern_name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": byte_legs[dom],

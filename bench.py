@@ -291,9 +291,40 @@ def bind_to_gpu_numa(index):
         if not cpus:
             return {"bound": False, "why": "NVML affinity mask empty inside this cpuset"}
         os.sched_setaffinity(0, cpus)
-        return {"bound": True, "cpus": len(cpus), "of": len(allowed)}
+        out = {"bound": True, "cpus": len(cpus), "of": len(allowed)}
+        out.update(prefer_gpu_memory_node(pynvml, h))
+        return out
     except Exception as e:
         return {"bound": False, "why": f"{type(e).__name__}: {e}"}
+
+
+def prefer_gpu_memory_node(pynvml, h):
+    """set_mempolicy(MPOL_PREFERRED, node of the GPU's PCIe slot) for this process, so that the pinned host buffers of the e2e
+    leg are allocated on the GPU's own socket even when the cpuset spans (or sits on) another one: with 8 ranks pulling
+    66 MB per step each from ONE node's DRAM the copies ran at 25 GB/s per GPU instead of 55.  Best effort."""
+    try:
+        import ctypes
+        bus = pynvml.nvmlDeviceGetPciInfo(h).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        cand = [bus.lower(), bus.lower()[4:] if len(bus) > 12 else bus.lower()]       # NVML pads the domain to 8 digits
+        node = None
+        for c in cand:
+            f = f"/sys/bus/pci/devices/{c}/numa_node"
+            if os.path.exists(f):
+                node = int(open(f).read().strip())
+                break
+        if node is None or node < 0:
+            return {"mem_node": None}
+        nodes = [d for d in os.listdir("/sys/devices/system/node") if d.startswith("node") and d[4:].isdigit()]
+        if len(nodes) < 2:
+            return {"mem_node": node, "mem_policy": "single node"}
+        libc = ctypes.CDLL(None, use_errno=True)
+        mask = ctypes.c_ulong(1 << node)
+        MPOL_PREFERRED, SYS_set_mempolicy = 1, 238                                    # x86_64
+        rc = libc.syscall(SYS_set_mempolicy, MPOL_PREFERRED, ctypes.byref(mask), ctypes.c_ulong(8 * ctypes.sizeof(mask)))
+        return {"mem_node": node, "mem_policy": "preferred" if rc == 0 else f"set_mempolicy errno {ctypes.get_errno()}"}
+    except Exception as e:
+        return {"mem_node": None, "mem_policy": f"{type(e).__name__}: {e}"}
 
 
 # ------------------------------------------------------------------------------------------ N-rank parity on hardware

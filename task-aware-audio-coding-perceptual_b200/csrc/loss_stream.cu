@@ -8,7 +8,7 @@
 // slice of the four pending hop blocks in a per-warp shared-memory ring that only it touches (no conflict, no
 // synchronisation), and after each frame the oldest block is complete and leaves with one coalesced store.
 //
-// Rows are cut into runs of ~7 frames so that there are enough independent warp-runs to fill the GPU.  A run's
+// Rows are cut into runs of ~5 frames so that there are enough independent warp-runs to fill the GPU.  A run's
 // first three hop blocks also need the last three frames of the previous run: the previous run flushes its pending
 // partial sums for them into g, the run itself writes its own partial sums into h, and the combine kernel -- which
 // exists anyway to add the scales in a fixed order -- adds h on exactly those blocks.  Every output sample is
@@ -31,7 +31,7 @@ constexpr int kStreamThreads = kStreamWarps * 32;
 #define TAC_STREAM_JOINT 1    // x and y frames through the forward transform together (fft_core_pk.cuh: warp_fft_fwd2_pk): 1 = plans below n = 2048, 2 = all, 0 = none
 #endif
 #ifndef TAC_RUN_TARGET
-#define TAC_RUN_TARGET 7
+#define TAC_RUN_TARGET 5       // A/B on B200, cfg 2 (fused loss, ms): 3: 0.409, 4: 0.391, 5: 0.390, 6: 0.392, 7: 0.396, 8: 0.411, 10: 0.402, 14: 0.408
 #endif
 constexpr int kRunTarget = TAC_RUN_TARGET;          // frames per run (work unit of one lane group)
 // per-warp overlap-add ring.  Scalar kernel: four hop blocks, NFR * M float2 <= 1024 (8 KiB).  Packed kernel: THREE --

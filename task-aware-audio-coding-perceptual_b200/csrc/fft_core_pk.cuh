@@ -278,6 +278,136 @@ __device__ __forceinline__ void warp_fft_post2_pk(const cf (&zx)[P::BQ], const c
     if (k1 == 0) emit(fr, M / 2, mul2(cnj(zx[BQ / 2]), bc(2.0f)), mul2(cnj(zy[BQ / 2]), bc(2.0f)), BQ);
 }
 
+// ------------------------------------------------------------------ post-processing fused with the adjoint's first stage
+// The loss kernels turn every spectrum bin into a gradient bin and feed it straight back into the adjoint, whose first stage
+// pairs dL/dX[k] with conj(dL/dX[M-k]) exactly as the post-processing paired Z[k] with conj(Z[M-k]).  Doing both in ONE loop
+// over the pairs means the gradient never exists as an array: the forward registers z[j], z[BQ-1-j] die as the adjoint
+// registers zo[j], u[j] are born (a separate post + adjoint keeps 2 BQ + 2 more packed values alive between the two loops, which
+// at 255 registers cost the streaming kernel its scheduling freedom and ~0.3 M local-memory instructions per launch), and the
+// post-processing twiddle of a pair is formed once for both directions.
+//   bin(fr, k, v, slot) -> gradient of that slot (even slots / slot BQ: dL/dX[k] given v = X[k]; odd slots: conj(dL/dX[M-k])
+//   given v = conj(X[M-k])) -- for the magnitude losses that is simply v * g(|v|^2).
+// On return zo[j] = dL/dZ[k1 + A j] and u[j] = conj(dL/dZ[M - k]) for j < BQ / 2, gh = gradient of bin M / 2 (k1 == 0 lanes):
+// the inputs of warp_fft_adj_tail_pk.
+template <class P, class Bin>
+__device__ __forceinline__ void warp_fft_post_adj_head_pk(const cf (&z)[P::BQ], const float2* __restrict__ pt, int lane, Bin bin,
+                                                          cf (&zo)[P::BQ], cf (&u)[P::BQ / 2], cf& gh) {
+    constexpr int A = P::A, BQ = P::BQ, M = P::M;
+    const int k1 = lane % A, fr = lane / A;
+    const int plane = fr * A + ((A - k1) % A);
+    const cf base = ldg_cf(pt + k1);
+    static_for<0, BQ / 2>([&](auto jc) {
+        constexpr int j = decltype(jc)::value;
+        cf p = __shfl_sync(0xffffffffu, z[BQ - 1 - j], plane);
+        if (k1 == 0) p = z[(BQ - j) % BQ];
+        const cf pc = cnj(p);
+        const cf S = add2(z[j], pc), D = sub2(z[j], pc);    // Z[k] +- conj(Z[M-k])
+        const cf cs = post_twiddle_pk<BQ, j>(base);
+        const cf T = fma2(rotm(D), bc(lo(cs)), mul2(D, bc(-hi(cs))));     // -j W_n^k D
+        const int k = k1 + A * j;
+        const cf g = bin(fr, k, add2(S, T), 2 * j);
+        const cf gpc = bin(fr, M - k, sub2(S, T), 2 * j + 1);
+        const cf Sg = add2(g, gpc), Dg = sub2(g, gpc);      // G[k] +- conj(G[M-k])
+        const cf Tn = fma2(rotm(Dg), bc(lo(cs)), mul2(Dg, bc(hi(cs))));   // -conj(-j W_n^k) Dg
+        zo[j] = sub2(Sg, Tn);                                // dL/dZ[k]
+        u[j] = add2(Sg, Tn);                                 // conj(dL/dZ[M-k])
+    });
+    gh = 0ull;
+    if (k1 == 0) gh = bin(fr, M / 2, mul2(cnj(z[BQ / 2]), bc(2.0f)), BQ);
+}
+
+// Two forward transforms (target x, decoded y) into ONE gradient: bin(fr, k, X, Y, slot) -> gradient slot of y.
+template <class P, class Bin>
+__device__ __forceinline__ void warp_fft_post2_adj_head_pk(const cf (&zx)[P::BQ], const cf (&zy)[P::BQ], const float2* __restrict__ pt,
+                                                           int lane, Bin bin, cf (&zo)[P::BQ], cf (&u)[P::BQ / 2], cf& gh) {
+    constexpr int A = P::A, BQ = P::BQ, M = P::M;
+    const int k1 = lane % A, fr = lane / A;
+    const int plane = fr * A + ((A - k1) % A);
+    const cf base = ldg_cf(pt + k1);
+    static_for<0, BQ / 2>([&](auto jc) {
+        constexpr int j = decltype(jc)::value;
+        cf px = __shfl_sync(0xffffffffu, zx[BQ - 1 - j], plane);
+        cf py = __shfl_sync(0xffffffffu, zy[BQ - 1 - j], plane);
+        if (k1 == 0) { px = zx[(BQ - j) % BQ]; py = zy[(BQ - j) % BQ]; }
+        const cf pxc = cnj(px), pyc = cnj(py);
+        const cf Sx = add2(zx[j], pxc), Dx = sub2(zx[j], pxc);
+        const cf Sy = add2(zy[j], pyc), Dy = sub2(zy[j], pyc);
+        const cf cs = post_twiddle_pk<BQ, j>(base);
+        const cf Tx = fma2(rotm(Dx), bc(lo(cs)), mul2(Dx, bc(-hi(cs))));
+        const cf Ty = fma2(rotm(Dy), bc(lo(cs)), mul2(Dy, bc(-hi(cs))));
+        const int k = k1 + A * j;
+        const cf g = bin(fr, k, add2(Sx, Tx), add2(Sy, Ty), 2 * j);
+        const cf gpc = bin(fr, M - k, sub2(Sx, Tx), sub2(Sy, Ty), 2 * j + 1);
+        const cf Sg = add2(g, gpc), Dg = sub2(g, gpc);
+        const cf Tn = fma2(rotm(Dg), bc(lo(cs)), mul2(Dg, bc(hi(cs))));
+        zo[j] = sub2(Sg, Tn);
+        u[j] = add2(Sg, Tn);
+    });
+    gh = 0ull;
+    if (k1 == 0) gh = bin(fr, M / 2, mul2(cnj(zx[BQ / 2]), bc(2.0f)), mul2(cnj(zy[BQ / 2]), bc(2.0f)), BQ);
+}
+
+// The adjoint from its second stage on: zo / u / gh as left by the two functions above (zo[BQ/2 ..) is filled here).
+template <class P, class Store>
+__device__ __forceinline__ void warp_fft_adj_tail_pk(cf (&z)[P::BQ], const cf (&u)[P::BQ / 2], const cf gh, float2* xbuf,
+                                                     const float2* __restrict__ tw, int lane, Store store) {
+    constexpr int A = P::A, BQ = P::BQ, RS = P::RS;
+    const int k1 = lane % A, fr = lane / A;
+    const int plane = fr * A + ((A - k1) % A);
+    static_for<0, BQ / 2>([&](auto jc) {
+        constexpr int j = decltype(jc)::value;
+        z[BQ - 1 - j] = cnj(__shfl_sync(0xffffffffu, u[j], plane));
+    });
+    if (k1 == 0) {                                           // these lanes pair inside themselves: slot j <-> (BQ - j) % BQ
+        const cf t0 = add2(z[0], cnj(u[0]));                 // Z[0] feeds both X[0] and X[M]
+        static_for<1, BQ / 2>([&](auto jc) {
+            constexpr int j = decltype(jc)::value;
+            z[BQ - j] = cnj(u[j]);
+        });
+        z[0] = t0;
+        z[BQ / 2] = mul2(cnj(gh), bc(2.0f));
+    }
+    cf y[BQ];                                                // inverse BQ-point DFT over k2
+    static_for<0, BQ>([&](auto kc) {
+        constexpr int k2 = decltype(kc)::value;
+        y[brev(k2, BQ)] = z[k2];
+    });
+    float2 wr_[8], wq_[BQ / 8];                             // conj(W_M^(b k1)) = conj(W^(r k1)) conj(W^(8 q k1)), b = 8 q + r
+    static_for<1, 8>([&](auto rc) { constexpr int r = decltype(rc)::value; wr_[r] = ldg2(tw + k1 * BQ + r); });
+    static_for<1, BQ / 8>([&](auto qc) { constexpr int q = decltype(qc)::value; wq_[q] = ldg2(tw + k1 * BQ + 8 * q); });
+    Dit<BQ, true>::run(y);
+    cf* wr = reinterpret_cast<cf*>(xbuf) + lane * RS;
+    static_for<0, BQ>([&](auto bc_) {
+        constexpr int b = decltype(bc_)::value;
+        constexpr int r = b % 8, q = b / 8;
+        if constexpr (r > 0) y[b] = fma2(rotp(y[b]), bc(wr_[r].y), mul2(y[b], bc(wr_[r].x)));   // conj(W) = w.x + j w.y
+        if constexpr (q > 0) y[b] = fma2(rotp(y[b]), bc(wq_[q].y), mul2(y[b], bc(wq_[q].x)));
+        if constexpr (P::kVec4) {
+            if constexpr (b & 1) reinterpret_cast<ulonglong2*>(wr)[b >> 1] = make_ulonglong2(y[b - 1], y[b]);
+        } else {
+            wr[b] = y[b];
+        }
+    });
+    __syncwarp();
+    static_for<0, P::NS1>([&](auto sc) {
+        constexpr int s = decltype(sc)::value;
+        const int q = lane + 32 * s;
+        const int f2 = q / BQ, b = q % BQ;
+        cf a[A];
+        const cf* col = reinterpret_cast<const cf*>(xbuf) + (f2 * A) * RS + b;
+        static_for<0, A>([&](auto kc) {
+            constexpr int kk = decltype(kc)::value;
+            a[brev(kk, A)] = col[kk * RS];
+        });
+        Dit<A, true>::run(a);
+        static_for<0, A>([&](auto ac) {
+            constexpr int av = decltype(ac)::value;
+            store(sc, f2, ac, b, a[av]);
+        });
+    });
+    __syncwarp();
+}
+
 // ------------------------------------------------------------------ adjoint transform
 // grad(fr, k, slot) returns, for the slot convention of warp_fft_post_pk, dL/dX[k] (even slots, slot BQ) or
 // conj(dL/dX[M-k]) (odd slots).  store(integral_constant s, f2, integral_constant a, b, v) receives the gradient of the

@@ -297,7 +297,7 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
     const float eps2 = eps_squared(a.eps);
     float l1 = 0.0f, ll = 0.0f;
     for (int t = 0; t < maxlen; ++t) {
-        cf G[BQ + 1];
+        cf zo[BQ], uo[BQ / 2], gh;                           // adjoint inputs (fft_core_pk.cuh: warp_fft_post_adj_head_pk)
         const float* fx[NS1];
         const float* fy[NS1];
 #pragma unroll
@@ -318,11 +318,11 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
             vy = mul2(ld_frame<(4 * decltype(ac)::value) / A>(fy[decltype(scn)::value] + 2 * m), w);
         };
         warp_fft_fwd2_pk<P>(zx, zy, xbuf, sc.t.tw, lane, load_xy);
-        warp_fft_post2_pk<P>(zx, zy, sc.t.pt, lane, [&](int, int, cf vx, cf v, int slot) {
+        warp_fft_post2_adj_head_pk<P>(zx, zy, sc.t.pt, lane, [&](int, int, cf vx, cf v, int) -> cf {
             const float xr_ = lo(vx), xi_ = hi(vx), vr = lo(v), vi = hi(v);
             const float g = loss_bin_grad<WITH_SUMS>(fmaf(xr_, xr_, xi_ * xi_), fmaf(vr, vr, vi * vi), eps2, c_l1, c_log, tl1, tll);
-            G[slot] = mul2(v, bc(g));                                     // dL/dY[k]  (odd slots: its conjugate)
-        });
+            return mul2(v, bc(g));                                        // dL/dY[k]  (odd slots: its conjugate)
+        }, zo, uo, gh);
         } else {
         cf z[BQ];
         float mx[BQ + 1];
@@ -338,15 +338,16 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
             mx[slot] = fmaf(vr, vr, vi * vi);                             // |X|^2
         });
         warp_fft_fwd_pk<P>(z, xbuf, sc.t.tw, lane, load_y);
-        warp_fft_post_pk<P>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
+        warp_fft_post_adj_head_pk<P>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) -> cf {
             const float vr = lo(v), vi = hi(v);
             const float g = loss_bin_grad<WITH_SUMS>(mx[slot], fmaf(vr, vr, vi * vi), eps2, c_l1, c_log, tl1, tll);
-            G[slot] = mul2(v, bc(g));                                     // dL/dY[k]  (odd slots: its conjugate)
-        });
+            return mul2(v, bc(g));                                        // dL/dY[k]  (odd slots: its conjugate)
+        }, zo, uo, gh);
         }
         if (WITH_SUMS && t < len_post) { l1 += tl1; ll += tll; }
-        warp_fft_adj_pk<P>(xbuf, sc.t.tw, sc.t.pt, lane,
-            [&](int, int, int slot) -> cf { return G[slot]; },
+        // post-processing, per-bin loss terms and the adjoint's first stage ran as one loop above (the gradient never exists as an
+        // array); the adjoint from its second stage on:
+        warp_fft_adj_tail_pk<P>(zo, uo, gh, xbuf, sc.t.tw, lane,
             [&](auto scn, int f2, auto ac, int b, cf gv) {
                 constexpr int s = decltype(scn)::value, av = decltype(ac)::value;
                 constexpr int q = av / QA, ap = av % QA;

@@ -173,7 +173,6 @@ __device__ __forceinline__ void loss_bwd_task(const LossScale& sc, const float* 
                                               float* acc, float2* xbuf, int lane, int f_base, int f_stride, int f_end,
                                               long long c0, float eps, float c_l1, float c_log, float& acc_l1, float& acc_log) {
     cf z[P::BQ];
-    cf G[P::BQ + 1];
     float mx[P::BQ + 1];
     const float2* __restrict__ win2 = sc.t.win2;
     const int hop = sc.hop;
@@ -193,14 +192,15 @@ __device__ __forceinline__ void loss_bwd_task(const LossScale& sc, const float* 
     warp_fft_fwd_pk<P>(z, xbuf, sc.t.tw, lane, load);
     const float eps2 = eps_squared(eps);
     float l1 = 0.0f, ll = 0.0f;
-    warp_fft_post_pk<P>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
+    // post-processing, loss terms and the adjoint's first stage in one loop over the bin pairs (fft_core_pk.cuh)
+    cf zo[P::BQ], uo[P::BQ / 2], gh;
+    warp_fft_post_adj_head_pk<P>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) -> cf {
         const float vr = lo(v), vi = hi(v);
         const float g = loss_bin_grad<WITH_SUMS>(mx[slot], fmaf(vr, vr, vi * vi), eps2, c_l1, c_log, l1, ll);
-        G[slot] = mul2(v, bc(g));                                     // odd slots: conj(dL/dY[M-k]), as the adjoint expects
-    });
+        return mul2(v, bc(g));                                        // odd slots: conj(dL/dY[M-k]), as the adjoint expects
+    }, zo, uo, gh);
     if (WITH_SUMS && (f_base + (lane / P::A) * f_stride) < f_end) { acc_l1 += l1; acc_log += ll * kLogHalf; }
-    warp_fft_adj_pk<P>(xbuf, sc.t.tw, sc.t.pt, lane,
-        [&](int, int, int slot) -> cf { return G[slot]; },
+    warp_fft_adj_tail_pk<P>(zo, uo, gh, xbuf, sc.t.tw, lane,
         [&](auto, int fr, auto ac, int b, cf g) {
             const int m = P::BQ * decltype(ac)::value + b;
             const int f = f_base + fr * f_stride;

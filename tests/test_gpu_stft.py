@@ -229,3 +229,26 @@ def test_multiscale_module_is_differentiable(ts):
     outs = ts.MultiScaleSTFT()(x)
     sum(o.square().sum() for o in outs).backward()
     assert x.grad is not None and float(x.grad.abs().max()) > 0
+
+
+# ---- persistent double-buffered planes kernel (single-scale calls with >= 4 * 148 (row, chunk) units) -------------------------
+
+@pytest.mark.parametrize("n,T,center", [(2048, 16000, False), (1024, 16000, False), (512, 12288, False), (256, 16000, True),
+                                        (128, 9000, False), (64, 8192, True), (2048, 70000, True)])
+def test_persistent_single_scale(ts, n, T, center):
+    """Enough rows that the single-scale call takes the persistent kernel (bulk-copied, double-buffered tiles; full / empty
+    mbarrier pipeline): spot rows against the oracle (rtol 1e-4), and the whole output bit-equal to the one-shot kernel, which
+    the same scale takes when a second scale rides along.  Ragged row ends (T not a multiple of the chunk), zero centre padding
+    (tiles that hang over both row ends) and every plan are covered."""
+    B = 640 if T <= 16000 else 160
+    gen = torch.Generator().manual_seed(n + T)
+    x = (0.3 * torch.randn(B, 1, T, generator=gen)).cuda()
+    other = 512 if n != 512 else 256
+    one = ts.stft_multi(x, [n], [n // 4], center=center, pad_mode="constant")[0]
+    two = ts.stft_multi(x, [n, other], [n // 4, other // 4], center=center, pad_mode="constant")[0]
+    assert torch.equal(one, two), "persistent and one-shot planes kernels disagree"
+    rows = [0, 1, B // 2, B - 1]
+    xc = x[rows].cpu()
+    if center:
+        xc = torch.nn.functional.pad(xc, (n // 2, n // 2))
+    _close(one[rows], O.disc_inputs_ref(xc, n, n // 4), f"persistent n={n} T={T} center={center}")

@@ -69,15 +69,6 @@ __device__ __forceinline__ void stage_tile(float* tile, const float* __restrict_
 #ifndef TAC_PLANES_PF
 #define TAC_PLANES_PF 2       // one-shot kernel: prefetch the tile of unit blockIdx.x + PF * SMs into the L2 (0: off)
 #endif
-#ifndef TAC_PLANES_SYNC
-#define TAC_PLANES_SYNC 0
-#endif
-#ifndef TAC_PLANES_G
-#define TAC_PLANES_G 1        // tasks are dealt to the warps in groups of G consecutive ones (1: round-robin)
-#endif
-#ifndef TAC_PLANES_ROT
-#define TAC_PLANES_ROT 0      // 1: warp w walks the scales starting at scale w % nscales (de-phases the warps)
-#endif
 #ifndef TAC_PLANES_BULK
 #define TAC_PLANES_BULK 1     // 1: a task's two plane spans leave through shared memory as bulk async copies; 0: 4-byte streaming stores
 #endif
@@ -239,18 +230,10 @@ __device__ __forceinline__ void planes_unit(const PlanesArgs& a, const float* ti
         if (lane >= o) my_tb += v;
     }
     my_tb -= my_nt;
-    for (int s0 = 0; s0 < a.nscales; ++s0) {
-#if TAC_PLANES_ROT
-        int s = s0 + warp; while (s >= a.nscales) s -= a.nscales;
-#else
-        const int s = s0;
-#endif
-        // block-cyclic deal: groups of G consecutive global task numbers go to one warp (G = 1: plain round-robin)
-        constexpr int G = TAC_PLANES_G;
-        const int nt = __shfl_sync(0xffffffffu, my_nt, s), tb = __shfl_sync(0xffffffffu, my_tb, s);
-        const int qb = tb / G;
-        const int q0 = qb + ((warp - qb) & (W - 1));         // first group >= qb that belongs to this warp
-        if (q0 * G >= tb + nt) continue;                     // warp-uniform
+    for (int s = 0; s < a.nscales; ++s) {
+        const int nt = __shfl_sync(0xffffffffu, my_nt, s);
+        const int first = (warp - __shfl_sync(0xffffffffu, my_tb, s)) & (W - 1);   // first local task with global number = warp (mod W)
+        if (first >= nt) continue;                           // warp-uniform
         const int f_lo = __shfl_sync(0xffffffffu, my_lo, s), f_end = __shfl_sync(0xffffffffu, my_hi, s);
         float* out_re_row = reinterpret_cast<float*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(my_out), s));
         const long long im_off = __shfl_sync(0xffffffffu, my_im, s);
@@ -258,10 +241,7 @@ __device__ __forceinline__ void planes_unit(const PlanesArgs& a, const float* ti
         // tile[0] is padded-coordinate (c0 - pmax) of the widest scale == (c0 - pmax + pad_s) of scale s
         const int origin = (int)c0 - a.pmax + sc.pad;
         auto my_tasks = [&](auto&& body) {
-            for (int q = q0; q * G < tb + nt; q += W) {
-                const int t0 = max(q * G, tb) - tb, t1 = min(q * G + G, tb + nt) - tb;
-                for (int t = t0; t < t1; ++t) body(t);
-            }
+            for (int t = first; t < nt; t += W) body(t);
         };
         switch (sc.n) {
             case 2048: my_tasks([&](int t) { planes_task<Plan2048>(sc, tile, xbuf, lane, f_lo + t * 1, f_end, origin, out_re_row, im_off); }); break;
@@ -389,9 +369,6 @@ __global__ void __launch_bounds__(kPThreads, 1) stft_planes_persist_kernel(const
         const unsigned row = u / (unsigned)a.nchunks;
         const unsigned c0 = (u - row * (unsigned)a.nchunks) * (unsigned)a.chunk;
         mbar_wait(&s_full[buf], par);
-#if TAC_PLANES_SYNC
-        __syncthreads();                                     // warps start a unit together: they walk the plans' code in phase
-#endif
         planes_unit<kPWarps>(a, tiles + (size_t)buf * a.tile_len, xbuf, lane, warp, row, c0);
         __syncwarp();
         if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(&s_empty[buf])) : "memory");

@@ -347,26 +347,14 @@ __device__ __forceinline__ void warp_fft_post2_adj_head_pk(const cf (&zx)[P::BQ]
     if (k1 == 0) gh = bin(fr, M / 2, mul2(cnj(zx[BQ / 2]), bc(2.0f)), mul2(cnj(zy[BQ / 2]), bc(2.0f)), BQ);
 }
 
-// The adjoint from its second stage on: zo / u / gh as left by the two functions above (zo[BQ/2 ..) is filled here).
+// Unnormalised inverse complex DFT of M = A * BQ points per frame -- the adjoint of the complex transform inside
+// warp_fft_fwd_pk: lane (fr, k1) passes V_fr[k1 + A k2] in slot k2 of z; store(integral_constant s, f2, integral_constant a, b, v)
+// receives v = sum_k V_f2[k] exp(+2 pi j m k / M) for m = BQ a + b.  (Second half of every adjoint; with warp_fft_fwd_pk and a
+// pointwise product it is also the circular convolution of the chirp-z transform in stft_ex.cu.)
 template <class P, class Store>
-__device__ __forceinline__ void warp_fft_adj_tail_pk(cf (&z)[P::BQ], const cf (&u)[P::BQ / 2], const cf gh, float2* xbuf,
-                                                     const float2* __restrict__ tw, int lane, Store store) {
+__device__ __forceinline__ void warp_cfft_inv_pk(const cf (&z)[P::BQ], float2* xbuf, const float2* __restrict__ tw, int lane, Store store) {
     constexpr int A = P::A, BQ = P::BQ, RS = P::RS;
-    const int k1 = lane % A, fr = lane / A;
-    const int plane = fr * A + ((A - k1) % A);
-    static_for<0, BQ / 2>([&](auto jc) {
-        constexpr int j = decltype(jc)::value;
-        z[BQ - 1 - j] = cnj(__shfl_sync(0xffffffffu, u[j], plane));
-    });
-    if (k1 == 0) {                                           // these lanes pair inside themselves: slot j <-> (BQ - j) % BQ
-        const cf t0 = add2(z[0], cnj(u[0]));                 // Z[0] feeds both X[0] and X[M]
-        static_for<1, BQ / 2>([&](auto jc) {
-            constexpr int j = decltype(jc)::value;
-            z[BQ - j] = cnj(u[j]);
-        });
-        z[0] = t0;
-        z[BQ / 2] = mul2(cnj(gh), bc(2.0f));
-    }
+    const int k1 = lane % A;
     cf y[BQ];                                                // inverse BQ-point DFT over k2
     static_for<0, BQ>([&](auto kc) {
         constexpr int k2 = decltype(kc)::value;
@@ -406,6 +394,29 @@ __device__ __forceinline__ void warp_fft_adj_tail_pk(cf (&z)[P::BQ], const cf (&
         });
     });
     __syncwarp();
+}
+
+// The adjoint from its second stage on: zo / u / gh as left by the two functions above (zo[BQ/2 ..) is filled here).
+template <class P, class Store>
+__device__ __forceinline__ void warp_fft_adj_tail_pk(cf (&z)[P::BQ], const cf (&u)[P::BQ / 2], const cf gh, float2* xbuf,
+                                                     const float2* __restrict__ tw, int lane, Store store) {
+    constexpr int A = P::A, BQ = P::BQ, RS = P::RS;
+    const int k1 = lane % A, fr = lane / A;
+    const int plane = fr * A + ((A - k1) % A);
+    static_for<0, BQ / 2>([&](auto jc) {
+        constexpr int j = decltype(jc)::value;
+        z[BQ - 1 - j] = cnj(__shfl_sync(0xffffffffu, u[j], plane));
+    });
+    if (k1 == 0) {                                           // these lanes pair inside themselves: slot j <-> (BQ - j) % BQ
+        const cf t0 = add2(z[0], cnj(u[0]));                 // Z[0] feeds both X[0] and X[M]
+        static_for<1, BQ / 2>([&](auto jc) {
+            constexpr int j = decltype(jc)::value;
+            z[BQ - j] = cnj(u[j]);
+        });
+        z[0] = t0;
+        z[BQ / 2] = mul2(cnj(gh), bc(2.0f));
+    }
+    warp_cfft_inv_pk<P>(z, xbuf, tw, lane, store);
 }
 
 // ------------------------------------------------------------------ adjoint transform

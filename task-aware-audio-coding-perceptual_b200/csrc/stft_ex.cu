@@ -37,6 +37,7 @@ struct BluTables {
     const float2* bf;     // [M]    FFT_M(chirp filter) / M, bit-reversed order
     const float2* post;   // [K]    conj(c[k])
     const float2* tw;     // [M/2]  exp(-2 pi j i / M)
+    const float2* bfw;    // [M]    M == 1024 only: FFT_M(chirp filter) / M in the warp core's layout, [k2][k1] <- Bf[k1 + 32 k2]
     int M, logM;
 };
 
@@ -94,7 +95,7 @@ static int get_blu_tables(int n, int win, int normalized, int window, BluTables*
         ss += v * v;
     }
     const double scale = normalized ? 1.0 / sqrt(ss) : 1.0;
-    std::vector<float2> host((size_t)n + M + K + M / 2);
+    std::vector<float2> host((size_t)n + M + K + M / 2 + (M == 1024 ? M : 0));
     float2* ha = host.data();
     float2* hbf = ha + n;
     float2* hpost = hbf + M;
@@ -112,6 +113,14 @@ static int get_blu_tables(int n, int win, int normalized, int window, BluTables*
         for (int bit = 0; bit < logM; ++bit) r |= ((i >> bit) & 1) << (logM - 1 - bit);
         const std::complex<double> v = b[r] / (double)M;
         hbf[i] = make_float2((float)v.real(), (float)v.imag());
+    }
+    if (M == 1024) {                                                    // natural order, lane-major rows for the warp transform
+        float2* hbw = htw + M / 2;
+        for (int k2 = 0; k2 < 32; ++k2)
+            for (int k1 = 0; k1 < 32; ++k1) {
+                const std::complex<double> v = b[k1 + 32 * k2] / (double)M;
+                hbw[k2 * 32 + k1] = make_float2((float)v.real(), (float)v.imag());
+            }
     }
     for (int k = 0; k < K; ++k) {
         const std::complex<double> v = std::conj(chirp(k, n));
@@ -134,6 +143,7 @@ static int get_blu_tables(int n, int win, int normalized, int window, BluTables*
     en.t.bf = en.t.a + n;
     en.t.post = en.t.bf + M;
     en.t.tw = en.t.post + K;
+    en.t.bfw = M == 1024 ? en.t.tw + M / 2 : nullptr;
     en.t.M = M; en.t.logM = logM;
     g_blu_cache[key] = en;
     *out = en.t;
@@ -277,10 +287,11 @@ __device__ void ex_write_out(const ExArgs& a, float* o0, float* o1, int TS, long
     }
 }
 
-struct BluPlan {};
+struct BluPlan {};       // chirp-z, the circular convolution by the whole CTA in shared memory (any M <= 4096)
+struct WBluPlan {};      // chirp-z with M == 1024: the convolution by ONE WARP per frame on the packed warp core (n_fft <= 682)
 
 template <class P>
-__global__ void __launch_bounds__(kExThreads, 1) stft_ex_kernel(const ExArgs a) {
+__global__ void __launch_bounds__(kExThreads, std::is_same<P, WBluPlan>::value ? 2 : 1) stft_ex_kernel(const ExArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* tile = reinterpret_cast<float*>(smem_raw);
     const int TS = a.TF + 1;
@@ -296,17 +307,67 @@ __global__ void __launch_bounds__(kExThreads, 1) stft_ex_kernel(const ExArgs a) 
     const int f_end = min(a.F, f0 + a.TF);
     const int nf = f_end - f0;
     const long long g0 = (long long)f0 * a.hop - a.pad;
-    if (a.vec_ok && g0 >= 0 && g0 + a.tile_len <= a.T && (g0 & 3) == 0) {
-        const float4* src = reinterpret_cast<const float4*>(xr + g0);
-        float4* dst = reinterpret_cast<float4*>(tile);
-        for (int i = threadIdx.x; i < (a.tile_len >> 2); i += blockDim.x) dst[i] = __ldg(src + i);
-    } else {
-        for (int j = threadIdx.x; j < a.tile_len; j += blockDim.x) tile[j] = ex_padded_sample(xr, g0 + j, a.T, a.pad_mode);
+    {   // in-range, 16-byte aligned middle of the tile with float4 loads even when the tile hangs over a row end (centre padding in
+        // front, the last tile behind); the padded samples and the <= 3 + 3 around the middle take the scalar path (as stft.cu)
+        const int len = a.tile_len;
+        const long long lo_ll = g0 < 0 ? -g0 : 0, hi_ll = a.T - g0;
+        const int lo = (int)(lo_ll < len ? lo_ll : len);
+        const int hi = (int)(hi_ll < lo ? lo : (hi_ll < len ? hi_ll : len));
+        int ja = lo, jb = lo;
+        if (a.vec_ok && (g0 & 3) == 0) {
+            ja = (lo + 3) & ~3; jb = hi & ~3;
+            if (jb < ja) ja = jb = lo;
+        }
+        if (jb > ja) {
+            const float4* src = reinterpret_cast<const float4*>(xr) + (g0 >> 2);
+            float4* dst = reinterpret_cast<float4*>(tile);
+            for (int i = (ja >> 2) + threadIdx.x; i < (jb >> 2); i += blockDim.x) dst[i] = __ldg(src + i);
+        }
+        for (int j = threadIdx.x; j < ja; j += blockDim.x) tile[j] = ex_padded_sample(xr, g0 + j, a.T, a.pad_mode);
+        for (int j = jb + threadIdx.x; j < len; j += blockDim.x) tile[j] = ex_padded_sample(xr, g0 + j, a.T, a.pad_mode);
     }
     if (threadIdx.x == 0) s_next = 0;
     __syncthreads();
 
-    if constexpr (std::is_same<P, BluPlan>::value) {
+    if constexpr (std::is_same<P, WBluPlan>::value) {
+        // X[k] = conj(c_k) sum_j (x_j w_j conj(c_j)) c_{k-j}: a circular convolution of 1024 points, done per frame by one warp as
+        // forward complex transform (the inner transform of warp_fft_fwd_pk<Plan2048>: 1024 complex points, lane k1 / slot k2 <->
+        // bin k1 + 32 k2) -> product with the pre-transformed chirp (table in that layout) -> inverse transform
+        // (warp_cfft_inv_pk); only the outputs m < K are kept.  Against the CTA-wide radix-2 form below (20 block barriers and
+        // ~330 KB of shared-memory traffic per frame): one exchange round trip per transform, no block barrier.
+        using PW = Plan2048;
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        float2* xbuf = reinterpret_cast<float2*>(work) + warp * kXbufFloat2;
+        const float2* __restrict__ ta = a.bt.a;
+        const float2* __restrict__ tbw = a.bt.bfw;
+        const float2* __restrict__ tp = a.bt.post;
+        const int n = a.n, K = a.K;
+        for (int fr = warp; fr < nf; fr += kExWarps) {
+            const float* src = tile + fr * a.hop;
+            cf z[PW::BQ];
+            auto load = [&](auto, int, int m, auto) -> cf {
+                if (m >= n) return 0ull;
+                const float sv = src[m];
+                return mul2(ldg_cf(ta + m), bc(sv));
+            };
+            warp_fft_fwd_pk<PW>(z, xbuf, a.t.tw, lane, load);
+            static_for<0, PW::BQ>([&](auto kc) {
+                constexpr int k2 = decltype(kc)::value;
+                const cf w = ldg_cf(tbw + k2 * 32 + lane);
+                z[k2] = fma2(rotp(z[k2]), bc(hi(w)), mul2(z[k2], bc(lo(w))));           // z * w
+            });
+            warp_cfft_inv_pk<PW>(z, xbuf, a.t.tw, lane, [&](auto, int, auto ac, int b, cf v) {
+                const int m = PW::BQ * decltype(ac)::value + b;
+                if (m < K) {
+                    const cf w = ldg_cf(tp + m);
+                    const cf r = fma2(rotp(v), bc(hi(w)), mul2(v, bc(lo(w))));
+                    o0[m * TS + fr] = lo(r);
+                    o1[m * TS + fr] = hi(r);
+                }
+            });
+        }
+        __syncthreads();
+    } else if constexpr (std::is_same<P, BluPlan>::value) {
         float2* buf = reinterpret_cast<float2*>(work);
         const int M = a.bt.M, logM = a.bt.logM, n = a.n;
         const float2* __restrict__ ta = a.bt.a;
@@ -471,6 +532,11 @@ extern "C" int tac_stft_ex(const float* x, int64_t rows, int64_t T, int n_fft, i
         int rc = get_blu_tables(n_fft, win, normalized, window, &a.bt);
         if (rc) return rc;
         work = (size_t)a.bt.M * sizeof(float2);
+        if (a.bt.M == 1024) {                                                 // one warp per frame on the packed core
+            rc = get_tables(2048, 2048, 0, &a.t);                             // inter-pass twiddles of the 1024-point complex transform
+            if (rc) return rc;
+            work = (size_t)kExWarps * kXbufFloat2 * sizeof(float2);
+        }
     }
     size_t smem = 0;
     for (a.TF = a.K > 512 ? 8 : (a.K > 128 ? 16 : 32); a.TF >= 1; a.TF >>= 1) {
@@ -481,7 +547,7 @@ extern "C" int tac_stft_ex(const float* x, int64_t rows, int64_t T, int n_fft, i
     TAC_REQUIRE(a.TF >= 1, "configuration needs %zu bytes of shared memory", smem);
     a.ntiles = (a.F + a.TF - 1) / a.TF;
     TAC_REQUIRE(rows * a.ntiles < (1ll << 31), "grid too large");
-    if (!core) return launch_ex<BluPlan>(a, rows, smem, st);
+    if (!core) return a.bt.M == 1024 ? launch_ex<WBluPlan>(a, rows, smem, st) : launch_ex<BluPlan>(a, rows, smem, st);
     switch (n_fft) {
         case 2048: return launch_ex<Plan2048>(a, rows, smem, st);
         case 1024: return launch_ex<Plan1024>(a, rows, smem, st);

@@ -9,9 +9,14 @@
 // A CTA owns TF consecutive frames of one row.  The samples are staged once; frames whose length the warp core
 // (fft_core_pk.cuh) has a plan for are transformed by warps, any other length by Bluestein's chirp-z identity
 //     X[k] = conj(c[k]) * sum_j (x[j] w[j] conj(c[j])) c[k - j],        c[m] = exp(+j pi m^2 / n),
-// i.e. a circular convolution of size M = 2^ceil(log2(n + K - 1)) done by the whole CTA in shared memory (radix-2 DIF
-// forward -> pointwise product with the pre-transformed chirp in bit-reversed order -> radix-2 DIT inverse: no
-// permutation pass).  Every table (window * conj chirp, FFT of the chirp filter, twiddles) is generated on the host in
+// i.e. a circular convolution of size M = max(1024, 2^ceil(log2(n + K - 1))) done on the packed warp core: M = 1024 by ONE warp
+// per frame (forward 1024-point complex transform = the inner transform of warp_fft_fwd_pk<Plan2048>, product with the
+// pre-transformed chirp, warp_cfft_inv_pk); M = 2048 / 4096 by R = 2 / 4 warps per frame, one 1024-point sub-transform of
+// the decimated sequence y[R m + r] each, with everything between the forward and the inverse sub-transforms pointwise in
+// k' < 1024 (twiddle, radix-R, filter, inverse radix-R, twiddle) in a shared [R][1024] buffer between two named barriers.
+// (Round 2: this replaced a CTA-wide radix-2 convolution -- 2 log2 M block barriers and ~330 KB of shared-memory traffic per
+// frame: SGMSE front end 1.94 -> 0.34 ms, n = 400 1.27 -> 0.21 ms, n = 2046 3.33 -> 0.89 ms on 512 x 1 s.)
+// Every table (window * conj chirp, FFT of the chirp filter, twiddles) is generated on the host in
 // float64, with m^2 reduced mod 2n in integers.  Both transforms leave (re, im) in a [K][TF + 1] shared-memory tile and
 // share ONE write-out that applies the epilogue on the way to HBM: complex, power-law compression, |z| and angle,
 // |z|^p, p1 * log10(|z|^p + eps), dB against a fixed reference, a mel filter bank -- each (k) row leaves as a
@@ -34,10 +39,9 @@ constexpr int kBluMaxM = 4096;
 
 struct BluTables {
     const float2* a;      // [n]    window[j] * scale * conj(c[j])
-    const float2* bf;     // [M]    FFT_M(chirp filter) / M, bit-reversed order
+    const float2* bf;     // [M]    FFT_M(chirp filter) / M, natural order
     const float2* post;   // [K]    conj(c[k])
     const float2* tw;     // [M/2]  exp(-2 pi j i / M)
-    const float2* bfw;    // [M]    M == 1024 only: FFT_M(chirp filter) / M in the warp core's layout, [k2][k1] <- Bf[k1 + 32 k2]
     int M, logM;
 };
 
@@ -83,7 +87,7 @@ static int get_blu_tables(int n, int win, int normalized, int window, BluTables*
     if (it != g_blu_cache.end()) { *out = it->second.t; return TAC_OK; }
     const int K = n / 2 + 1;
     int M = 1, logM = 0;
-    while (M < n + K - 1) { M <<= 1; ++logM; }
+    while (M < n + K - 1 || M < 1024) { M <<= 1; ++logM; }     // the warp transforms are 1024 points wide
     if (M > kBluMaxM) return set_error(TAC_EINVAL, "n_fft %d too large for the chirp-z path (n_fft + n_fft/2 <= %d)", n, kBluMaxM);
     std::vector<double> w(n, 0.0);
     const int left = (n - win) / 2;
@@ -95,7 +99,7 @@ static int get_blu_tables(int n, int win, int normalized, int window, BluTables*
         ss += v * v;
     }
     const double scale = normalized ? 1.0 / sqrt(ss) : 1.0;
-    std::vector<float2> host((size_t)n + M + K + M / 2 + (M == 1024 ? M : 0));
+    std::vector<float2> host((size_t)n + M + K + M / 2);
     float2* ha = host.data();
     float2* hbf = ha + n;
     float2* hpost = hbf + M;
@@ -108,19 +112,10 @@ static int get_blu_tables(int n, int win, int normalized, int window, BluTables*
     for (int m = 0; m < K; ++m) b[m] = chirp(m, n);
     for (int m = 1; m < n; ++m) b[M - m] = chirp(m, n);                 // c is even: c[-m] = c[m]
     host_fft(b);
+    // FFT_M(chirp filter) / M in natural order, rows of 32 consecutive bins per sub-transform: [q][k2][k1] <- Bf[k1 + 32 k2 + 1024 q]
     for (int i = 0; i < M; ++i) {
-        int r = 0;
-        for (int bit = 0; bit < logM; ++bit) r |= ((i >> bit) & 1) << (logM - 1 - bit);
-        const std::complex<double> v = b[r] / (double)M;
+        const std::complex<double> v = b[i] / (double)M;
         hbf[i] = make_float2((float)v.real(), (float)v.imag());
-    }
-    if (M == 1024) {                                                    // natural order, lane-major rows for the warp transform
-        float2* hbw = htw + M / 2;
-        for (int k2 = 0; k2 < 32; ++k2)
-            for (int k1 = 0; k1 < 32; ++k1) {
-                const std::complex<double> v = b[k1 + 32 * k2] / (double)M;
-                hbw[k2 * 32 + k1] = make_float2((float)v.real(), (float)v.imag());
-            }
     }
     for (int k = 0; k < K; ++k) {
         const std::complex<double> v = std::conj(chirp(k, n));
@@ -143,7 +138,6 @@ static int get_blu_tables(int n, int win, int normalized, int window, BluTables*
     en.t.bf = en.t.a + n;
     en.t.post = en.t.bf + M;
     en.t.tw = en.t.post + K;
-    en.t.bfw = M == 1024 ? en.t.tw + M / 2 : nullptr;
     en.t.M = M; en.t.logM = logM;
     g_blu_cache[key] = en;
     *out = en.t;
@@ -287,8 +281,10 @@ __device__ void ex_write_out(const ExArgs& a, float* o0, float* o1, int TS, long
     }
 }
 
-struct BluPlan {};       // chirp-z, the circular convolution by the whole CTA in shared memory (any M <= 4096)
 struct WBluPlan {};      // chirp-z with M == 1024: the convolution by ONE WARP per frame on the packed warp core (n_fft <= 682)
+template <int R> struct WBluSplit {};   // chirp-z with M == 1024 R (R = 2, 4): R warps per frame, one 1024-point sub-transform each
+template <class P> struct is_split { static constexpr int R = 0; };
+template <int R_> struct is_split<WBluSplit<R_>> { static constexpr int R = R_; };
 
 template <class P>
 __global__ void __launch_bounds__(kExThreads, std::is_same<P, WBluPlan>::value ? 2 : 1) stft_ex_kernel(const ExArgs a) {
@@ -339,7 +335,7 @@ __global__ void __launch_bounds__(kExThreads, std::is_same<P, WBluPlan>::value ?
         const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
         float2* xbuf = reinterpret_cast<float2*>(work) + warp * kXbufFloat2;
         const float2* __restrict__ ta = a.bt.a;
-        const float2* __restrict__ tbw = a.bt.bfw;
+        const float2* __restrict__ tbw = a.bt.bf;                 // M == 1024: Bf[k1 + 32 k2] at [k2][k1]
         const float2* __restrict__ tp = a.bt.post;
         const int n = a.n, K = a.K;
         for (int fr = warp; fr < nf; fr += kExWarps) {
@@ -367,53 +363,97 @@ __global__ void __launch_bounds__(kExThreads, std::is_same<P, WBluPlan>::value ?
             });
         }
         __syncthreads();
-    } else if constexpr (std::is_same<P, BluPlan>::value) {
-        float2* buf = reinterpret_cast<float2*>(work);
-        const int M = a.bt.M, logM = a.bt.logM, n = a.n;
+    } else if constexpr (is_split<P>::R > 0) {
+        // M = 1024 R points: decimation in time into R sub-sequences y[R m + r], one 1024-point warp transform each (warp r of a
+        // group of R); everything between the forward and the inverse sub-transforms is POINTWISE in k' < 1024 --
+        //   e_r = W_M^{r k'} E_r[k'],  Z_q = sum_r W_R^{r q} e_r  (bin k' + 1024 q),  V_q = Z_q Bf[k' + 1024 q],
+        //   U_r'[k'] = conj(W_M^{r' k'}) sum_q W_R^{-r' q} V_q,   v[R m' + r'] = IDFT_1024(U_r')[m']
+        // -- and runs in place in the group's [R][1024] buffer between two named barriers.  Only outputs m < K are kept.
+        constexpr int R = is_split<P>::R;
+        using PW = Plan2048;
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        constexpr int NG = kExWarps / R;
+        const int group = warp / R, r = warp % R;
+        float2* xbuf = reinterpret_cast<float2*>(work) + warp * kXbufFloat2;
+        float2* ebuf = reinterpret_cast<float2*>(work) + kExWarps * kXbufFloat2 + group * (R * 1024);
+        cf* ebc = reinterpret_cast<cf*>(ebuf);
         const float2* __restrict__ ta = a.bt.a;
-        const float2* __restrict__ tb = a.bt.bf;
-        const float2* __restrict__ tw = a.bt.tw;
+        const float2* __restrict__ tbf = a.bt.bf;
+        const float2* __restrict__ twm = a.bt.tw;                // exp(-2 pi j i / M), i < M / 2
         const float2* __restrict__ tp = a.bt.post;
-        for (int fr = 0; fr < nf; ++fr) {
+        const int n = a.n, K = a.K;
+        constexpr int M = 1024 * R;
+        auto wm = [&](int idx) -> float2 {                       // exp(-2 pi j idx / M), idx < M
+            if (idx < M / 2) return __ldg(twm + idx);
+            const float2 w = __ldg(twm + idx - M / 2);
+            return make_float2(-w.x, -w.y);
+        };
+        for (int fr0 = 0; fr0 < nf; fr0 += NG) {
+            const int fr = fr0 + group;
+            if (fr >= nf) continue;                              // uniform over the group: its barriers are skipped together
             const float* src = tile + fr * a.hop;
-            for (int j = threadIdx.x; j < M; j += blockDim.x) {
-                float2 v = make_float2(0.0f, 0.0f);
-                if (j < n) { const float2 c = __ldg(ta + j); const float s = src[j]; v = make_float2(s * c.x, s * c.y); }
-                buf[j] = v;
+            {
+                cf z[PW::BQ];
+                auto load = [&](auto, int, int m, auto) -> cf {
+                    const int j = R * m + r;
+                    if (j >= n) return 0ull;
+                    return mul2(ldg_cf(ta + j), bc(src[j]));
+                };
+                warp_fft_fwd_pk<PW>(z, xbuf, a.t.tw, lane, load);
+                static_for<0, PW::BQ>([&](auto kc) { constexpr int k2 = decltype(kc)::value; ebc[r * 1024 + k2 * 32 + lane] = z[k2]; });
             }
-            __syncthreads();
-            for (int s = logM - 1; s >= 0; --s) {                 // forward DIF, natural -> bit-reversed
-                const int half = 1 << s, sh = logM - 1 - s;
-                for (int t = threadIdx.x; t < (M >> 1); t += blockDim.x) {
-                    const int pos = t & (half - 1);
-                    const int i = ((t >> s) << (s + 1)) + pos, j = i + half;
-                    const float2 u = buf[i], v = buf[j];
-                    buf[i] = make_float2(u.x + v.x, u.y + v.y);
-                    buf[j] = cmulf(make_float2(u.x - v.x, u.y - v.y), __ldg(tw + (pos << sh)));
+            asm volatile("bar.sync %0, %1;" :: "r"(1 + group), "r"(R * 32) : "memory");
+            for (int kp = r * 32 + lane; kp < 1024; kp += R * 32) {
+                float2 e[R], V[R];
+#pragma unroll
+                for (int i = 0; i < R; ++i) { e[i] = ebuf[i * 1024 + kp]; if (i > 0) e[i] = cmulf(e[i], wm(i * kp)); }
+                if constexpr (R == 2) {
+                    V[0] = make_float2(e[0].x + e[1].x, e[0].y + e[1].y);
+                    V[1] = make_float2(e[0].x - e[1].x, e[0].y - e[1].y);
+                } else {                                          // W_4 = -j: forward radix-4
+                    const float2 s02 = make_float2(e[0].x + e[2].x, e[0].y + e[2].y), d02 = make_float2(e[0].x - e[2].x, e[0].y - e[2].y);
+                    const float2 s13 = make_float2(e[1].x + e[3].x, e[1].y + e[3].y), d13 = make_float2(e[1].x - e[3].x, e[1].y - e[3].y);
+                    V[0] = make_float2(s02.x + s13.x, s02.y + s13.y);
+                    V[2] = make_float2(s02.x - s13.x, s02.y - s13.y);
+                    V[1] = make_float2(d02.x + d13.y, d02.y - d13.x);       // d02 - j d13
+                    V[3] = make_float2(d02.x - d13.y, d02.y + d13.x);       // d02 + j d13
                 }
-                __syncthreads();
-            }
-            for (int s = 0; s < logM; ++s) {                      // (x filter) inverse DIT, bit-reversed -> natural
-                const int half = 1 << s, sh = logM - 1 - s;
-                for (int t = threadIdx.x; t < (M >> 1); t += blockDim.x) {
-                    const int pos = t & (half - 1);
-                    const int i = ((t >> s) << (s + 1)) + pos, j = i + half;
-                    float2 u = buf[i], v = buf[j];
-                    if (s == 0) { u = cmulf(u, __ldg(tb + i)); v = cmulf(v, __ldg(tb + j)); }
-                    const float2 w = __ldg(tw + (pos << sh));
-                    v = cmulf(v, make_float2(w.x, -w.y));
-                    buf[i] = make_float2(u.x + v.x, u.y + v.y);
-                    buf[j] = make_float2(u.x - v.x, u.y - v.y);
+#pragma unroll
+                for (int q = 0; q < R; ++q) V[q] = cmulf(V[q], __ldg(tbf + kp + 1024 * q));
+                float2 u[R];
+                if constexpr (R == 2) {
+                    u[0] = make_float2(V[0].x + V[1].x, V[0].y + V[1].y);
+                    u[1] = make_float2(V[0].x - V[1].x, V[0].y - V[1].y);
+                } else {                                          // inverse radix-4 (W_4^{-1} = +j)
+                    const float2 s02 = make_float2(V[0].x + V[2].x, V[0].y + V[2].y), d02 = make_float2(V[0].x - V[2].x, V[0].y - V[2].y);
+                    const float2 s13 = make_float2(V[1].x + V[3].x, V[1].y + V[3].y), d13 = make_float2(V[1].x - V[3].x, V[1].y - V[3].y);
+                    u[0] = make_float2(s02.x + s13.x, s02.y + s13.y);
+                    u[2] = make_float2(s02.x - s13.x, s02.y - s13.y);
+                    u[1] = make_float2(d02.x - d13.y, d02.y + d13.x);       // d02 + j d13
+                    u[3] = make_float2(d02.x + d13.y, d02.y - d13.x);       // d02 - j d13
                 }
-                __syncthreads();
+#pragma unroll
+                for (int i = 0; i < R; ++i) {
+                    if (i > 0) { const float2 w = wm(i * kp); u[i] = cmulf(u[i], make_float2(w.x, -w.y)); }
+                    ebuf[i * 1024 + kp] = u[i];
+                }
             }
-            for (int k = threadIdx.x; k < a.K; k += blockDim.x) {
-                const float2 z = cmulf(buf[k], __ldg(tp + k));
-                o0[k * TS + fr] = z.x;
-                o1[k * TS + fr] = z.y;
+            asm volatile("bar.sync %0, %1;" :: "r"(1 + group), "r"(R * 32) : "memory");
+            {
+                cf z[PW::BQ];
+                static_for<0, PW::BQ>([&](auto kc) { constexpr int k2 = decltype(kc)::value; z[k2] = ebc[r * 1024 + k2 * 32 + lane]; });
+                warp_cfft_inv_pk<PW>(z, xbuf, a.t.tw, lane, [&](auto, int, auto ac, int b, cf v) {
+                    const int m = R * (PW::BQ * decltype(ac)::value + b) + r;
+                    if (m < K) {
+                        const cf w = ldg_cf(tp + m);
+                        const cf o = fma2(rotp(v), bc(hi(w)), mul2(v, bc(lo(w))));
+                        o0[m * TS + fr] = lo(o);
+                        o1[m * TS + fr] = hi(o);
+                    }
+                });
             }
-            __syncthreads();
         }
+        __syncthreads();
     } else {
         const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
         float2* xbuf = reinterpret_cast<float2*>(work) + warp * kXbufFloat2;
@@ -531,12 +571,10 @@ extern "C" int tac_stft_ex(const float* x, int64_t rows, int64_t T, int n_fft, i
     } else {
         int rc = get_blu_tables(n_fft, win, normalized, window, &a.bt);
         if (rc) return rc;
-        work = (size_t)a.bt.M * sizeof(float2);
-        if (a.bt.M == 1024) {                                                 // one warp per frame on the packed core
-            rc = get_tables(2048, 2048, 0, &a.t);                             // inter-pass twiddles of the 1024-point complex transform
-            if (rc) return rc;
-            work = (size_t)kExWarps * kXbufFloat2 * sizeof(float2);
-        }
+        rc = get_tables(2048, 2048, 0, &a.t);                                 // inter-pass twiddles of the 1024-point complex transform
+        if (rc) return rc;
+        work = (size_t)kExWarps * kXbufFloat2 * sizeof(float2);               // one warp per 1024-point (sub-)transform
+        if (a.bt.M > 1024) work += (size_t)kExWarps * 1024 * sizeof(float2);  // + the groups' [R][1024] buffers
     }
     size_t smem = 0;
     for (a.TF = a.K > 512 ? 8 : (a.K > 128 ? 16 : 32); a.TF >= 1; a.TF >>= 1) {
@@ -547,7 +585,8 @@ extern "C" int tac_stft_ex(const float* x, int64_t rows, int64_t T, int n_fft, i
     TAC_REQUIRE(a.TF >= 1, "configuration needs %zu bytes of shared memory", smem);
     a.ntiles = (a.F + a.TF - 1) / a.TF;
     TAC_REQUIRE(rows * a.ntiles < (1ll << 31), "grid too large");
-    if (!core) return a.bt.M == 1024 ? launch_ex<WBluPlan>(a, rows, smem, st) : launch_ex<BluPlan>(a, rows, smem, st);
+    if (!core) return a.bt.M == 1024 ? launch_ex<WBluPlan>(a, rows, smem, st)
+                    : (a.bt.M == 2048 ? launch_ex<WBluSplit<2>>(a, rows, smem, st) : launch_ex<WBluSplit<4>>(a, rows, smem, st));
     switch (n_fft) {
         case 2048: return launch_ex<Plan2048>(a, rows, smem, st);
         case 1024: return launch_ex<Plan1024>(a, rows, smem, st);

@@ -421,6 +421,46 @@ def run_extras(args, dev, rank, world, group, peak, barrier):
     except Exception as e:
         out["cfg4_k1_planes"] = {"error": f"{type(e).__name__}: {e}"}
 
+    # ---- next rows (rank-local, a few ms): single-scale planes in the persistent form, the iSTFT on the decoder shape, the
+    # chain iSTFT -> discriminator inputs, the non-power-of-two front ends (chirp-z on the warp core)
+    try:
+        rows_ = {}
+        xs = (0.1 * torch.randn(512, 1, 160000, generator=g)).to(dev)
+        for n in (2048, 512, 128):
+            sp = ts.MultiScaleSTFT([n], [n // 4], [n])
+            o = None
+
+            def one():
+                nonlocal o
+                o = None
+                o = sp(xs)
+            t = _time_ms(one, iters=5, warm=2)
+            nb = 4 * 512 * 160000 + 8 * 512 * (1 + (160000 - n) // (n // 4)) * (n // 2 + 1)
+            rows_[f"planes_single_scale_{n}"] = {"ms": t, "gbs": nb / (t * 1e-3) / 1e9, "frac": nb / (t * 1e-3) / 1e9 / peak}
+            o = None
+        del xs
+        torch.cuda.empty_cache()
+        dec = torch.randn(128, 2, 1025, 600, generator=g).to(dev)
+        dec[:, 0].abs_()
+        t = _time_ms(lambda: ts.batch_reconstruct_waveform(dec[:, 0], dec[:, 1], SR), iters=5, warm=2)
+        nb = 128 * (8 * 1025 * 600 + 4 * 512 * 599)
+        rows_["istft_128x2x1025x600"] = {"ms": t, "gbs": nb / (t * 1e-3) / 1e9, "frac": nb / (t * 1e-3) / 1e9 / peak}
+        t = _time_ms(lambda: ts.reconstruct_and_disc_inputs(dec[:, 0], dec[:, 1], SR), iters=5, warm=2)
+        rows_["chain_istft_disc_inputs_3_scales"] = {"ms": t}
+        del dec
+        torch.cuda.empty_cache()
+        x1 = (0.1 * torch.randn(512, 16000, generator=g)).to(dev)
+        fe510, sp400 = ts.SpecsFrontEnd(), ts.Spectrogram()
+        rows_["sgmse_front_end_n510_512x1s"] = {"ms": _time_ms(lambda: fe510(x1), iters=10, warm=2)}
+        rows_["power_spectrogram_n400_512x1s"] = {"ms": _time_ms(lambda: sp400(x1), iters=10, warm=2)}
+        rows_["notebook_db_front_end_n2046_512x1s"] = {"ms": _time_ms(lambda: ts.create_complex_spectrogram(
+            x1, SR, n_fft=2046, hop_length=512, win_length=2046, db_scale=True), iters=10, warm=2)}
+        del x1
+        torch.cuda.empty_cache()
+        out["next_rows"] = rows_
+    except Exception as e:
+        out["next_rows"] = {"error": f"{type(e).__name__}: {e}"}
+
     # ---- cfg 5: E4D1 latent=256 sweep: 16 items x 4 views x 60 s per GPU, DPCA d = 128 x 4, dim_p 8..256
     try:
         b5, v5, T5, d5 = 16, 4, 960000, 128

@@ -30,6 +30,9 @@ constexpr int kStreamThreads = kStreamWarps * 32;
 #ifndef TAC_STREAM_JOINT
 #define TAC_STREAM_JOINT 1    // x and y frames through the forward transform together (fft_core_pk.cuh: warp_fft_fwd2_pk): 1 = plans below n = 2048, 2 = all, 0 = none
 #endif
+#ifndef TAC_STREAM_PF
+#define TAC_STREAM_PF 1      // d > 0: prefetch.global.L1 of the new quarter of the frame d steps ahead (A/B on B200, cfg 2: off 0.386, 1: 0.381 ms)
+#endif
 #ifndef TAC_RUN_TARGET
 #define TAC_RUN_TARGET 5       // A/B on B200, cfg 2 (fused loss, ms): 3: 0.409, 4: 0.391, 5: 0.390, 6: 0.392, 7: 0.396, 8: 0.411, 10: 0.402, 14: 0.408
 #endif
@@ -249,14 +252,21 @@ __device__ __forceinline__ void st_grad(float* p, cf v) {
 // The same walk on the packed-complex core (fft_core_pk.cuh): every complex value is one aligned register pair and the
 // butterflies, twiddles, window products and overlap-adds are two-wide FP32 instructions -- about half the instruction
 // stream of stream_cta for the same arithmetic.  Only the per-bin loss terms (|.|, log, sign) stay scalar.
-template <class P, bool WITH_SUMS>
+// COMPACT: the per-warp shared memory is sized for THIS plan (exchange tile 32 x RS, ring NFR * M * 3 / 4) instead of the largest
+// one -- the n = 512 launch needs 30 KB per CTA instead of 58, so that three CTAs per SM leave the L1 156 KB instead of ~60 for
+// the 3/4-overlapping frame reads (its hit rate was 39 % and the frame-load phase held 23 % of that kernel's stall samples).
+template <class P> constexpr int kCompactXbuf = 32 * P::RS;
+template <class P> constexpr int kCompactWarpFloat2 = kCompactXbuf<P> + P::NFR * P::M * 3 / 4;
+template <class P, bool WITH_SUMS, bool COMPACT = false>
 __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamScale& sc, int cta, float2* smem) {
     constexpr int A = P::A, BQ = P::BQ, M = P::M, NFR = P::NFR, NS1 = P::NS1, QA = A / 4;
+    constexpr int kWarpF2 = COMPACT ? kCompactWarpFloat2<P> : kStreamWarpFloat2, kXb = COMPACT ? kCompactXbuf<P> : kXbufFloat2;
+    static_assert((kWarpF2 % 2) == 0 && (kXb % 2) == 0, "16-byte alignment of the per-warp tiles");
     constexpr bool kJoint = TAC_STREAM_JOINT != 0 && (TAC_STREAM_JOINT == 2 || M < 1024);
     static_assert(A % 4 == 0 && NFR * M * 3 / 4 <= kOlaFloat2, "plan does not fit the streaming overlap-add ring");
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    float2* xbuf = smem + warp * kStreamWarpFloat2;
-    cf* ola = reinterpret_cast<cf*>(xbuf + kXbufFloat2);  // [NFR][3 slots][QA][BQ]: hop block j of a frame group lives in slot j % 3
+    float2* xbuf = smem + warp * kWarpF2;
+    cf* ola = reinterpret_cast<cf*>(xbuf + kXb);          // [NFR][3 slots][QA][BQ]: hop block j of a frame group lives in slot j % 3
     const long long wr = (long long)cta * kStreamWarps + warp;
     if (wr >= sc.nwr) {
         if (WITH_SUMS && lane < 2) a.partial[((long long)(blockIdx.x + a.cta_base) * kStreamWarps + warp) * 2 + lane] = 0.0;
@@ -305,6 +315,15 @@ __device__ __forceinline__ void stream_cta_pk(const StreamArgs& a, const StreamS
             const int f = lo_s[s] + min(t, max(len_s[s] - 1, 0));
             fx[s] = xr + (long long)f * hop;
             fy[s] = yr + (long long)f * hop;
+#if TAC_STREAM_PF
+            // the one quarter of the NEXT frame that is not in the L1 yet (hop samples behind this frame's end): lane b fetches
+            // line b of it now, a whole frame step ahead of its use
+            const int bq = (lane + 32 * s) % BQ;
+            if (t + TAC_STREAM_PF < len_s[s] && bq * 32 < hop) {
+                asm volatile("prefetch.global.L1 [%0];" :: "l"(fx[s] + (3 + TAC_STREAM_PF) * hop + 32 * bq));
+                asm volatile("prefetch.global.L1 [%0];" :: "l"(fy[s] + (3 + TAC_STREAM_PF) * hop + 32 * bq));
+            }
+#endif
         }
         float tl1 = 0.0f, tll = 0.0f;
         if constexpr (kJoint) {
@@ -444,7 +463,7 @@ __global__ void __launch_bounds__(kStreamThreads, 3) mrstft_stream_small_kernel(
     int s = 0;
     while (s + 1 < a.nscales && gcta >= a.sc[s + 1].cta_begin) ++s;
     const StreamScale& sc = a.sc[s];
-    stream_cta_pk<Plan512, WITH_SUMS>(a, sc, gcta - sc.cta_begin, smem);
+    stream_cta_pk<Plan512, WITH_SUMS, true>(a, sc, gcta - sc.cta_begin, smem);
     asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
@@ -622,8 +641,11 @@ int launch_stream(const float* x, const float* y, int64_t rows, int64_t T, int n
     a.cta_base = 0;
     if (TAC_STREAM_SPLIT && TAC_STREAM_PK && n_big > 0 && n_big < tot) {
         void (*small)(const StreamArgs) = sums ? mrstft_stream_small_kernel<true> : mrstft_stream_small_kernel<false>;
-        if (sums) TAC_SMEM_OPT_IN(mrstft_stream_small_kernel<true>, smem);
-        else TAC_SMEM_OPT_IN(mrstft_stream_small_kernel<false>, smem);
+        const size_t smem_small = (size_t)kStreamWarps * kCompactWarpFloat2<Plan512> * sizeof(float2);
+        if (sums) TAC_SMEM_OPT_IN(mrstft_stream_small_kernel<true>, smem_small);
+        else TAC_SMEM_OPT_IN(mrstft_stream_small_kernel<false>, smem_small);
+        // three CTAs need 3 x (30 + 1) KB: ask for the 100 KB shared-memory configuration, the rest of the 256 KB is L1
+        cudaFuncSetAttribute(small, cudaFuncAttributePreferredSharedMemoryCarveout, 44);
         kern<<<(unsigned)n_big, kStreamThreads, smem, st>>>(a);
         TAC_LAUNCHED(1);
         TAC_CHECK_CUDA(cudaGetLastError());
@@ -631,7 +653,7 @@ int launch_stream(const float* x, const float* y, int64_t rows, int64_t T, int n
         b.cta_base = (int)n_big;
         cudaLaunchConfig_t cfg;
         memset(&cfg, 0, sizeof(cfg));
-        cfg.gridDim = dim3((unsigned)(tot - n_big)); cfg.blockDim = dim3(kStreamThreads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+        cfg.gridDim = dim3((unsigned)(tot - n_big)); cfg.blockDim = dim3(kStreamThreads); cfg.dynamicSmemBytes = smem_small; cfg.stream = st;
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         at[0].val.programmaticStreamSerializationAllowed = 1;

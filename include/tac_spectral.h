@@ -161,6 +161,24 @@ TAC_API int tac_mrstft_loss_fwd_bwd(const float* x, const float* y, int64_t B, i
 TAC_API size_t tac_spec_losses_workspace_bytes(int64_t B);
 TAC_API int tac_spec_losses(const float* obs, const float* dec, int64_t B, int64_t K, int64_t F, float* out5,
                     float* per_sample, void* workspace, size_t workspace_bytes, tac_stream_t stream);
+/* K2' for callers that cannot allocate device memory.  No counterpart in the reference (which lets torch allocate
+ * whatever it likes); same arithmetic, same kernels and bit-identical results to tac_spec_losses, minus the workspace
+ * argument.  Meant for hosts that own pointers to obs/dec/out5 but cannot get scratch at the call site: a plugin living
+ * inside another framework's memory pool that it must not bypass, a real-time or callback thread where cudaMalloc's
+ * implicit synchronisation and driver locks are forbidden, a process with a device-memory budget fixed at start-up.
+ *   - The partial sums live in a static __device__ array inside libtac_spectral: 1 MiB on EVERY GPU that loads the
+ *     library, held until the process exits, sized for B <= TAC_SPEC_LOSSES_STATIC_MAX_B.  Larger B -> TAC_EINVAL
+ *     (split the batch, or use tac_spec_losses with your own workspace).
+ *   - The call itself runs no cudaMalloc / cudaFree / allocating library routine.  The FIRST call on each device
+ *     (with that device current) resolves the array's device address with cudaGetSymbolAddress and caches it; make
+ *     that first call outside any stream capture.
+ *   - All calls on one device share the one array.  Calls that follow each other on a stream (or are otherwise ordered)
+ *     are fine -- every slot a call reads it has written first, nothing needs clearing -- but two calls whose kernels
+ *     can overlap on the GPU (different streams, no event between them) race on it and return garbage.
+ *   out5, per_sample as for tac_spec_losses (per_sample may be NULL). */
+#define TAC_SPEC_LOSSES_STATIC_MAX_B 4096
+TAC_API int tac_spec_losses_static(const float* obs, const float* dec, int64_t B, int64_t K, int64_t F, float* out5,
+                           float* per_sample, tac_stream_t stream);
 /* Backward of K2' w.r.t. dec: grad_dec[b, c, :, :] = w[b, c] * (dec - obs), w a DEVICE float32 [B, 2]
  * table into which the caller folds the upstream gradients and normalisers of all five outputs
  * (autograd of pkl_file_models.py:933-940 in one pass instead of ~12 elementwise kernels). */

@@ -571,3 +571,56 @@ extern "C" int tac_spec_losses_bwd(const float* obs, const float* dec, int64_t B
     TAC_CHECK_CUDA(cudaGetLastError());
     return TAC_OK;
 }
+
+// ------------------------------------------------------------------------------------------ K2' without a workspace
+// tac_spec_losses_static: the same two kernels as tac_spec_losses, with the per-CTA partial sums parked in memory that
+// belongs to the library image instead of a buffer the caller allocates.  It exists for hosts that hold device pointers
+// to their data but have no way to obtain more device memory at the call site: a plugin running inside another
+// framework's memory pool whose allocator it must not bypass, a real-time audio thread or a signal/callback context in
+// which cudaMalloc's implicit device synchronisation and driver locks are off limits, or a process whose memory budget
+// was fixed up front.  The price is a cap on B and one array per GPU for the lifetime of the process.
+//
+// kSpecStaticMaxB items => kSpecStaticMaxB * 2 channels * kSpecSplit CTAs * 2 sums * 8 bytes = 1 MiB per device.
+constexpr long long kSpecStaticMaxB = TAC_SPEC_LOSSES_STATIC_MAX_B;
+static __device__ __align__(256) double g_spec_static_partial[kSpecStaticMaxB * 2 * kSpecSplit * 2];
+
+// In host code `g_spec_static_partial` is only a handle for the runtime's symbol table, never a device address: the
+// address differs per device and has to be asked for with that device current.  Looked up once per device and kept.
+static int spec_static_scratch(double** out) {
+    constexpr int kMaxDev = 64;
+    static std::atomic<double*> addr[kMaxDev];
+    int dev = 0;
+    TAC_CHECK_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDev) return set_error(TAC_EINVAL, "device ordinal %d outside 0..%d", dev, kMaxDev - 1);
+    double* p = addr[dev].load(std::memory_order_acquire);
+    if (!p) {
+        void* q = nullptr;
+        TAC_CHECK_CUDA(cudaGetSymbolAddress(&q, g_spec_static_partial));
+        if (!q) return set_error(TAC_ECUDA, "cudaGetSymbolAddress returned a null address for the static scratch");
+        p = static_cast<double*>(q);
+        addr[dev].store(p, std::memory_order_release);   // two racing first calls store the same value
+    }
+    *out = p;
+    return TAC_OK;
+}
+
+extern "C" int tac_spec_losses_static(const float* obs, const float* dec, int64_t B, int64_t K, int64_t F, float* out5,
+                                      float* per_sample, tac_stream_t stream) {
+    TAC_REQUIRE(obs && dec && out5, "null argument");
+    TAC_REQUIRE(B > 0 && K > 0 && F > 0, "B, K, F must be positive");
+    if (B > kSpecStaticMaxB)
+        return set_error(TAC_EINVAL, "tac_spec_losses_static holds scratch for at most %lld items, got B = %lld: split "
+                         "the batch or use tac_spec_losses with a caller-allocated workspace",
+                         kSpecStaticMaxB, (long long)B);
+    double* partial = nullptr;
+    const int rc = spec_static_scratch(&partial);
+    if (rc) return rc;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    // Nothing to clear: spec_partial_kernel's CTA i overwrites slots 2i, 2i+1 and spec_final_kernel reads only the
+    // B * 2 * kSpecSplit * 2 slots this very launch pair wrote, so what an earlier call left behind is never read.
+    spec_partial_kernel<<<(unsigned)(B * 2 * kSpecSplit), kSpecThreads, 0, st>>>(obs, dec, K * F, partial); TAC_LAUNCHED(1);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    spec_final_kernel<<<1, 256, 0, st>>>(partial, B, K * F, out5, per_sample); TAC_LAUNCHED(1);
+    TAC_CHECK_CUDA(cudaGetLastError());
+    return TAC_OK;
+}

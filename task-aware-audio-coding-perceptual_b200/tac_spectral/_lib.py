@@ -54,6 +54,7 @@ SIGNATURES = {
     "tac_mrstft_loss_fwd_bwd": (_I, [_VP, _VP, _I64, _I64, _I, _IP, _IP, _IP, _F, _VP, _VP, _VP, _VP, _SZ, _VP]),
     "tac_spec_losses_workspace_bytes": (_SZ, [_I64]),
     "tac_spec_losses": (_I, [_VP, _VP, _I64, _I64, _I64, _VP, _VP, _VP, _SZ, _VP]),
+    "tac_spec_losses_static": (_I, [_VP, _VP, _I64, _I64, _I64, _VP, _VP, _VP]),
     "tac_spec_losses_bwd": (_I, [_VP, _VP, _I64, _I64, _I64, _VP, _VP, _VP]),
     "tac_dpca_workspace_bytes": (_SZ, [_I, _I64, _I]),
     "tac_dpca_stats": (_I, [_VPP, _I, _I64, _I, _I, _VP, _VP, _SZ, _VP]),

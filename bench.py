@@ -589,6 +589,7 @@ def run_native(args):
                 print(f"[bench] CUDA-graph capture failed ({type(e).__name__}: {e}); timing eager launches", file=sys.stderr)
             graphs = None
             torch.cuda.synchronize()
+    launch_label = "cuda-graph replay" if graphs is not None else "eager"     # fixed NOW: `graphs` is dropped before the extras
     if launches_per_step is None:
         c0 = int(lib.tac_launch_count())
         step.run(*dsets[0])
@@ -632,6 +633,49 @@ def run_native(args):
     audio_s_step = world * rows * T / SR
     value = audio_s_step / (ms_step * 1e-3)
     loss_val = float(step.loss.item())
+    if world > 1:
+        step.check_exchange()                         # a pop that gave up waiting would have produced garbage: fail loudly
+
+    # ---- the same K steps on the same ring, EAGER (SURVEY 8d asks for both): ctypes marshalling + launches on the host's
+    # clock; what a drop-in user who does not capture the step pays
+    ms_eager = None
+    if graphs is not None:
+        for i in range(args.warmup):
+            step.run(*dsets[i % nsets])
+        barrier()
+        step.device_barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for i in range(args.steps):
+            step.run(*dsets[(args.warmup + i) % nsets])
+        a1.record()
+        torch.cuda.synchronize()
+        te = torch.tensor([a0.elapsed_time(a1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        ms_eager = float(te.item()) / args.steps
+    else:
+        ms_eager = ms_step
+    # public autograd API, eager, per call: tac_spectral.mrstft_loss(x, y).backward() (workspace allocation, ctypes, launches)
+    api_ms = None
+    try:
+        import tac_spectral as _ts
+        xa, ya = dsets[0][0], dsets[0][1].clone().requires_grad_(True)
+        for _ in range(3):
+            ya.grad = None
+            _ts.mrstft_loss(xa, ya, N_FFTS).backward()
+        b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        nrep = max(5, min(args.steps, 20))
+        b0.record()
+        for _ in range(nrep):
+            ya.grad = None
+            _ts.mrstft_loss(xa, ya, N_FFTS).backward()
+        b1.record()
+        torch.cuda.synchronize()
+        api_ms = b0.elapsed_time(b1) / nrep
+        del xa, ya
+    except Exception as e:
+        api_ms = f"{type(e).__name__}: {e}"
 
     # ---- attribution pass: the same K steps, eager, CUDA events around each leg on its launching stream
     legs = ["frontend", "loss_fused", "dpca_stats", "dpca_solve", "dpca_project"]
@@ -679,13 +723,29 @@ def run_native(args):
                 roofline["issue_frac"] = ent["inst"] / (leg_ms[dom] * 1e-3 * sm_hz * n_sm * 4)
                 roofline["issue_note"] = "warp instructions per launch (ncu) / (4 schedulers x SMs x SM clock x kernel time)"
             roofline["traffic_source"] = ent.get("source")
+            if ent.get("traffic"):
+                roofline["hbm_traffic_frac"] = ent["traffic"] / (leg_ms[dom] * 1e-3) / 1e9 / peak
         except Exception:
             pass
 
+    # "bound" keeps the contract's vocabulary (the kernel's NOMINAL roof: it moves 12 B per sample pair and no tensor work);
+    # "binding_roof" names the roof that actually limits it: FP32 issue slots when the issue fraction exceeds both HBM fractions
+    hbm_best = max(roofline["frac"], roofline.get("hbm_traffic_frac") or 0.0)
+    roofline["binding_roof"] = "fp32-issue" if (roofline.get("issue_frac") or 0.0) > hbm_best else "hbm"
+    if dom == "loss_fused":
+        # SURVEY 8d counts fwd + bwd as two passes (20 B per sample); the fused kernel reads x, y once and writes grad_y (12 B):
+        # `frac` is on the 12 B the kernel must move (of record), `frac_8d` on the survey's 20 B
+        roofline["frac_8d"] = (20 * rows * T) / (leg_ms[dom] * 1e-3) / 1e9 / peak
+
     # ---- N > 1: the sharded, exchanged step against the whole batch on ONE GPU (rank 0), on hardware
     parity_n = None
+    parity_cfg = "n/a (1 GPU)"
     if world > 1:
         parity_n = check_parity_n(step, dsets[0], w, dev, rank, world)
+        if parity_n is not None:
+            parity_cfg = (f"{parity_n['verdict']} vs whole batch on 1 GPU: loss_rel {parity_n['loss_rel']:.1e} rank_spread "
+                          f"{parity_n['loss_rank_spread']:.1e} cnt_equal {parity_n['cnt_equal']} idx_equal {parity_n['idx_equal']} "
+                          f"z_out_rel {parity_n['z_out_rel']:.1e} grad_rel {parity_n['grad_rel']:.1e}")
 
     # ---- e2e: public API, pinned HOST buffers; every step's inputs cross PCIe (H2D) and its loss is read back (D2H).
     # Two device input sets + two graphs: the copy of step i+1 (copy stream) overlaps the compute of step i, as a
@@ -800,19 +860,23 @@ def run_native(args):
                            "loss_scales": list(N_FFTS), "loss_kernel": "fused fwd+bwd (tac_mrstft_loss_fwd_bwd): reads x, y; writes grad_y", "front_end": "n_fft 2048 hop 512 centred, mag+phase [rows,2,1025,32] (unpadded)",
                            "dpca": {"views": views, "batch": batch, "d": d, "dim_p": dim_p, "gram": "tcgen05 3xTF32"},
                            "parallelism": f"dp{world} (batch shards; exchange of loss sums + DPCA statistics: {exch_desc})",
-                           "launch": "cuda-graph replay" if graphs is not None else "eager",
+                           "launch": launch_label, "parity_n": parity_cfg,
                            "overlap": not args.no_overlap,
                            "l2": f"ring of {nsets} input sets ({nsets * set_bytes / 1e6:.0f} MB) > 126 MB L2"},
                 "roofline": roofline, "cpu_baseline": cpu, "torch_gpu_baseline": tgpu, "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
                 "launches_per_step": launches_per_step, "clocks": clk.summary(), "loss": loss_val, **spread,
+                "ms_per_step_eager": ms_eager, "eager_public_api": {"mrstft_loss_fwd_bwd_ms": api_ms, "what": "tac_spectral.mrstft_loss(x, y).backward(), eager, per call, cfg rows"},
                 "parity_n": parity_n, "numa": numa, "extra": extra}
         print(json.dumps(line), flush=True)
     sys.stdout.flush()
+    parity_failed = parity_n is not None and parity_n.get("verdict") != "ok"
+    if parity_failed:
+        print(f"[bench] N-rank parity MISMATCH: {parity_n}", file=sys.stderr, flush=True)
     if world > 1:
         # CUDA graphs that captured NCCL kernels must go before the communicator; never let teardown hang the run
         graphs = g_e2e = None
         torch.cuda.synchronize()
-        killer = threading.Timer(20.0, lambda: os._exit(0))
+        killer = threading.Timer(20.0, lambda: os._exit(3 if parity_failed else 0))
         killer.daemon = True
         killer.start()
         try:
@@ -821,7 +885,7 @@ def run_native(args):
         except Exception:
             pass
         killer.cancel()
-        os._exit(0)
+        os._exit(3 if parity_failed else 0)
 
 
 def main():

@@ -16,7 +16,9 @@
  *   - all work is enqueued on `stream` (a cudaStream_t); no entry point synchronises the host,
  *     allocates, or creates streams once the tables for its n_fft exist, so calls are CUDA-graph
  *     capturable after tac_prepare_fft();
- *   - supported n_fft: 64, 128, 256, 512, 1024, 2048 (periodic Hann, win_length <= n_fft, even hop).
+ *   - tac_stft_multi, the MR-STFT loss and tac_istft take n_fft in {64, 128, 256, 512, 1024, 2048} (periodic Hann,
+ *     win_length <= n_fft, even hop); tac_stft_ex takes ANY n_fft with n_fft + n_fft/2 <= 4096 (chirp-z for the
+ *     non-powers of two: 2046, 510, 400 ...; ask tac_stft_ex_supported).
  */
 #ifndef TAC_SPECTRAL_H_
 #define TAC_SPECTRAL_H_
@@ -118,6 +120,12 @@ typedef struct tac_epilogue {
 /*   x       [rows, T] float32;  window: 0 periodic Hann, 1 its square root (data_module.py:13-17), centred in n_fft when
  *           win < n_fft;  center / pad_mode / normalized as for tac_stft_multi. */
 TAC_API int tac_stft_ex_supported(int n_fft);
+/* Builds (once per device) the tables tac_stft_ex needs for this configuration -- the only allocating, synchronising part of
+ * that path -- so that the first tac_stft_ex call may sit inside a CUDA-graph capture or on a non-blocking stream.  window: 0
+ * periodic Hann, 1 its square root.  A tac_stft_ex call that finds its tables missing DURING a capture returns TAC_EINVAL
+ * instead of allocating.  The reference builds its windows in the constructors (msstftd.py:125-127, data_module.py:109-118);
+ * call this from the same place. */
+TAC_API int tac_prepare_stft_ex(int n_fft, int win, int normalized, int window);
 TAC_API int tac_stft_ex(const float* x, int64_t rows, int64_t T, int n_fft, int hop, int win, int window, int center,
                         int pad_mode, int normalized, const tac_epilogue* epi, int64_t f_pad, void* out, tac_stream_t stream);
 /* out[rows, K, F] = max(20 log10(max(mag, amin)) - 20 log10(max(rowmax, amin)), -top_db): the second phase of
@@ -352,7 +360,13 @@ TAC_API int tac_multi_reduce(int nseg, const float* const* a, const float* const
  * local payload into slot[rank] of every rank and raises a flag there; a pop spins on the local flags and adds the slots
  * in RANK ORDER (bit-identical float64 sums on all ranks).  Sequence counters live in the buffer, so push / pop pairs are
  * CUDA-graph replayable; every rank must execute the same sequence of pushes and pops.  The buffer must be zero-filled
- * (and the ranks synchronised) once before first use.  A pop whose peers do not arrive within ~10 s traps. */
+ * (and the ranks synchronised) once before first use.
+ * Waiting is bounded: a pop whose peers have not pushed within the timeout (tac_xchg_set_timeout, else the environment
+ * variable TAC_XCHG_TIMEOUT_S, else 600 s; 0 = wait for ever) stops waiting, records the failed sequence number in its
+ * buffer and finishes on undefined data -- it does NOT trap, so the CUDA context survives and the host can report the
+ * failure: check tac_xchg_status after synchronising (any non-zero value is fatal for the exchange; tear it down).
+ * Ranks that pause for longer than the timeout between steps (checkpoint, validation) should meet in a host barrier
+ * before the next step. */
 #define TAC_XCHG_MAX_WORLD 8
 typedef struct tac_xchg {
     int world, rank;
@@ -360,6 +374,12 @@ typedef struct tac_xchg {
     void* peer[TAC_XCHG_MAX_WORLD];
 } tac_xchg;
 TAC_API size_t tac_xchg_bytes(int world, int64_t payload);
+/* Process-wide wait bound of the pops enqueued from now on, in seconds; 0: unbounded; negative: back to the default
+ * (TAC_XCHG_TIMEOUT_S or 600 s).  No reference counterpart (NCCL's watchdog plays this role for SURVEY 8e's all-reduce). */
+TAC_API int tac_xchg_set_timeout(double seconds);
+/* *timed_out = 0, or 1 + the sequence number of the latest pop of this descriptor's channel that gave up waiting.
+ * Synchronous (one 4-byte device-to-host copy): call it outside the step, after a stream / device synchronise. */
+TAC_API int tac_xchg_status(const tac_xchg* x, unsigned* timed_out);
 /* src [payload] float64 (device) -> slot[rank] on all ranks, then the flags. */
 TAC_API int tac_xchg_push(const tac_xchg* x, const double* src, tac_stream_t stream);
 /* dst [payload] float64 = sum over ranks (rank order) of the slots of the matching push. */

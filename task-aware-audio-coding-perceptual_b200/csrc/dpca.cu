@@ -552,11 +552,14 @@ extern "C" int tac_var_topk(const double* stats, int d, int k, float* var, int* 
     return TAC_OK;
 }
 
-// Development aid (not part of the documented ABI): clock64 stamps of the last tac_dpca_eig (d <= 128), view 0.
+// Development aid, NOT part of the ABI and not in the default build (build.py -DTAC_DEBUG_EXPORTS): clock64 stamps of the
+// last tac_dpca_eig (d <= 128), view 0.
+#ifdef TAC_DEBUG_EXPORTS
 extern "C" TAC_API int tac_debug_eig_profile(long long* out8) {
     TAC_CHECK_CUDA(cudaMemcpyFromSymbol(out8, tac::g_tri_prof, 8 * sizeof(long long)));
     return TAC_OK;
 }
+#endif
 
 extern "C" int tac_nuclear_from_s(const float* s, const int* rank, const double* stats, int nv, int d, float* out, double* aux,
                                   tac_stream_t stream) {

@@ -1,6 +1,7 @@
 // The step's cross-rank exchange as plain peer stores over NVLink (xchg.cuh): generic push / pop kernels, the tail of
 // the loss chain (push sums -> pop -> loss scalar in ONE single-CTA kernel), and the CUDA-IPC allocator for callers
 // without a symmetric-memory allocator.
+#include <stdlib.h>
 #include "tac_common.cuh"
 #include "xchg.cuh"
 
@@ -61,9 +62,44 @@ static int check_xchg(const tac_xchg* x) {
     return TAC_OK;
 }
 
+// -1: not set by tac_xchg_set_timeout -> environment / default
+static std::atomic<long long> g_xchg_timeout_ns{-1};
+
+unsigned long long xchg_timeout_ns() {
+    const long long v = g_xchg_timeout_ns.load(std::memory_order_relaxed);
+    if (v >= 0) return (unsigned long long)v;
+    static const unsigned long long from_env = [] {
+        double sec = 600.0;
+        if (const char* e = getenv("TAC_XCHG_TIMEOUT_S")) {
+            char* end = nullptr;
+            const double t = strtod(e, &end);
+            if (end != e && t >= 0.0) sec = t;
+        }
+        return (unsigned long long)(sec * 1e9);
+    }();
+    return from_env;
+}
+
 }  // namespace tac
 
 using namespace tac;
+
+extern "C" int tac_xchg_set_timeout(double seconds) {
+    TAC_REQUIRE(seconds == seconds && seconds < 1e9, "timeout must be a number of seconds below 1e9 (0: unbounded, < 0: default)");
+    g_xchg_timeout_ns.store(seconds < 0.0 ? -1ll : (long long)(seconds * 1e9), std::memory_order_relaxed);
+    return TAC_OK;
+}
+
+extern "C" int tac_xchg_status(const tac_xchg* x, unsigned* timed_out) {
+    TAC_REQUIRE(timed_out != nullptr, "null argument");
+    *timed_out = 0;
+    if (!x || x->world <= 1) return TAC_OK;
+    int rc = check_xchg(x);
+    if (rc) return rc;
+    TAC_CHECK_CUDA(cudaMemcpy(timed_out, reinterpret_cast<const unsigned*>(x->peer[x->rank]) + 4, sizeof(unsigned),
+                              cudaMemcpyDeviceToHost));
+    return TAC_OK;
+}
 
 extern "C" size_t tac_xchg_bytes(int world, int64_t payload) {
     if (world < 1 || world > kXchgMaxWorld || payload < 1) return 0;

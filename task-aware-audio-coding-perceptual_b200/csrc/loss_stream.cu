@@ -645,7 +645,8 @@ int launch_stream(const float* x, const float* y, int64_t rows, int64_t T, int n
         if (sums) TAC_SMEM_OPT_IN(mrstft_stream_small_kernel<true>, smem_small);
         else TAC_SMEM_OPT_IN(mrstft_stream_small_kernel<false>, smem_small);
         // three CTAs need 3 x (30 + 1) KB: ask for the 100 KB shared-memory configuration, the rest of the 256 KB is L1
-        cudaFuncSetAttribute(small, cudaFuncAttributePreferredSharedMemoryCarveout, 44);
+        if (sums) TAC_CARVEOUT_ONCE(mrstft_stream_small_kernel<true>, 44);
+        else TAC_CARVEOUT_ONCE(mrstft_stream_small_kernel<false>, 44);
         kern<<<(unsigned)n_big, kStreamThreads, smem, st>>>(a);
         TAC_LAUNCHED(1);
         TAC_CHECK_CUDA(cudaGetLastError());

@@ -78,13 +78,19 @@ inline std::complex<double> chirp(long long m, int n) {                // exp(+j
 }  // namespace
 
 // window kinds: 0 periodic Hann, 1 sqrt of the periodic Hann (sgmse/sgmse/data_module.py:13-17)
-static int get_blu_tables(int n, int win, int normalized, int window, BluTables* out) {
+// may_build false (the caller's stream is being captured): a missing table is an error instead of a cudaMalloc + synchronous
+// upload in the middle of the capture -- tac_prepare_stft_ex builds it ahead of time.
+static int get_blu_tables(int n, int win, int normalized, int window, BluTables* out, bool may_build = true) {
     int dev = 0;
     TAC_CHECK_CUDA(cudaGetDevice(&dev));
     std::lock_guard<std::mutex> lk(g_blu_mu);
     auto key = std::make_tuple(dev, n, win, normalized ? 1 : 0, window);
     auto it = g_blu_cache.find(key);
     if (it != g_blu_cache.end()) { *out = it->second.t; return TAC_OK; }
+    if (!may_build)
+        return set_error(TAC_EINVAL, "chirp-z tables for n_fft=%d win=%d normalized=%d window=%d do not exist yet and the stream is "
+                         "being captured: call tac_prepare_stft_ex(n_fft, win, normalized, window) before the capture",
+                         n, win, normalized ? 1 : 0, window);
     const int K = n / 2 + 1;
     int M = 1, logM = 0;
     while (M < n + K - 1 || M < 1024) { M <<= 1; ++logM; }     // the warp transforms are 1024 points wide
@@ -530,6 +536,22 @@ extern "C" int tac_db_from_rowmax(const float* mag, int64_t rows, int64_t row_st
     return TAC_OK;
 }
 
+extern "C" int tac_prepare_stft_ex(int n_fft, int win, int normalized, int window) {
+    TAC_REQUIRE(tac_stft_ex_supported(n_fft), "n_fft=%d unsupported by the general STFT (8 <= n_fft, n_fft + n_fft/2 <= %d)", n_fft, kBluMaxM);
+    TAC_REQUIRE(win >= 1 && win <= n_fft, "win_length %d must be in [1, n_fft]", win);
+    TAC_REQUIRE(window == 0 || window == 1, "unknown window kind %d (0 hann, 1 sqrt-hann)", window);
+    FftTables t;
+    int rc = TAC_OK;
+    if (window == 0 && supported_nfft(n_fft)) {                      // even hops run on the plain core, odd ones on chirp-z: both
+        rc = get_tables(n_fft, win, normalized, &t);
+        if (rc) return rc;
+    }
+    BluTables bt;
+    rc = get_blu_tables(n_fft, win, normalized, window, &bt);
+    if (rc) return rc;
+    return get_tables(2048, 2048, 0, &t);
+}
+
 extern "C" int tac_stft_ex(const float* x, int64_t rows, int64_t T, int n_fft, int hop, int win, int window, int center,
                            int pad_mode, int normalized, const tac_epilogue* epi, int64_t f_pad, void* out, tac_stream_t stream) {
     TAC_REQUIRE(x && epi && out, "null argument");
@@ -569,7 +591,9 @@ extern "C" int tac_stft_ex(const float* x, int64_t rows, int64_t T, int n_fft, i
         if (rc) return rc;
         work = (size_t)kExWarps * kXbufFloat2 * sizeof(float2);
     } else {
-        int rc = get_blu_tables(n_fft, win, normalized, window, &a.bt);
+        cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+        TAC_CHECK_CUDA(cudaStreamIsCapturing(st, &cap));
+        int rc = get_blu_tables(n_fft, win, normalized, window, &a.bt, cap == cudaStreamCaptureStatusNone);
         if (rc) return rc;
         rc = get_tables(2048, 2048, 0, &a.t);                                 // inter-pass twiddles of the 1024-point complex transform
         if (rc) return rc;

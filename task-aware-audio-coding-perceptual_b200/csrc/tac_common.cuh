@@ -40,6 +40,18 @@ int set_error(int code, const char* fmt, ...);   // stores the message thread-lo
         }                                                                                     \
     } while (0)
 
+// Same once-per-(call site, device) guard for the shared-memory carve-out hint (percent of the SM's L1/shared array).
+#define TAC_CARVEOUT_ONCE(kern, percent)                                                      \
+    do {                                                                                      \
+        static std::atomic<unsigned long long> _tac_done{0ull};                               \
+        int _tac_dev = 0;                                                                     \
+        TAC_CHECK_CUDA(cudaGetDevice(&_tac_dev));                                             \
+        if (!((_tac_done.load(std::memory_order_acquire) >> (_tac_dev & 63)) & 1ull)) {       \
+            TAC_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)(percent))); \
+            _tac_done.fetch_or(1ull << (_tac_dev & 63), std::memory_order_release);           \
+        }                                                                                     \
+    } while (0)
+
 #define TAC_ALIGNED16(p, name)                                                                \
     do {                                                                                      \
         if ((reinterpret_cast<uintptr_t>(p) & 15u) != 0)                                      \

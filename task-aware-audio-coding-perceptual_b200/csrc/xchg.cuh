@@ -2,7 +2,7 @@
 //
 // Every rank owns one buffer of tac_xchg_bytes() in peer-mappable memory, mapped in every process of the node:
 //
-//   [0, 256)    control words (local use only): seq_push, seq_pop, push_done, pop_done
+//   [0, 256)    control words (local use only): seq_push, seq_pop, push_done, pop_done, wait_error
 //   [256, 512)  flags [2 parities][8 source ranks]  uint32, written by the SOURCE rank
 //   [512, ...)  slots [2 parities][world][payload]  float64, slot r written by rank r
 //
@@ -26,15 +26,21 @@ constexpr size_t kXchgFlagOff = 256, kXchgSlotOff = 512;
 struct XchgDev {                       // by-value kernel argument; world <= 1: no exchange
     int world, rank;
     long long payload;                 // float64 per slot
+    unsigned long long timeout_ns;     // bound of one xchg_wait (0: wait for ever), see xchg_timeout_ns()
     unsigned char* peer[kXchgMaxWorld];
 };
 
+// How long a pop waits for a peer's push before it gives up: tac_xchg_set_timeout(), else TAC_XCHG_TIMEOUT_S, else
+// 600 s (ranks of a training job drift apart by whole seconds to minutes: checkpoints, validation, a stalled loader).
+unsigned long long xchg_timeout_ns();   // exchange.cu
+
 inline XchgDev xchg_dev(const tac_xchg* x) {
     XchgDev d;
-    d.world = 1; d.rank = 0; d.payload = 0;
+    d.world = 1; d.rank = 0; d.payload = 0; d.timeout_ns = 0;
     for (int i = 0; i < kXchgMaxWorld; ++i) d.peer[i] = nullptr;
     if (x && x->world > 1) {
         d.world = x->world; d.rank = x->rank; d.payload = x->payload;
+        d.timeout_ns = xchg_timeout_ns();
         for (int i = 0; i < x->world; ++i) d.peer[i] = reinterpret_cast<unsigned char*>(x->peer[i]);
     }
     return d;
@@ -91,14 +97,27 @@ __device__ __forceinline__ void xchg_push_commit(const XchgDev& x, unsigned seq,
     }
 }
 
+__device__ __forceinline__ unsigned long long xchg_globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 // Threads 0 .. world-1 spin on the local flags of pop number `seq`; the caller follows with __syncthreads().
-// Bounded: ~10 s of SM clocks, then the kernel traps (a dead peer must not hang the GPU).
+// Bounded by x.timeout_ns of wall-clock time (0: unbounded).  A wait that runs out does NOT trap -- a trap is a sticky
+// context error that takes the rank down, and its peers after it: it records `seq + 1` in control word 4 of the rank's
+// own buffer (tac_xchg_status reads it on the host) and lets the kernel finish on whatever the slots hold.  From then on
+// the exchange's results are undefined; the host is expected to treat a non-zero status as fatal for the job.
 __device__ __forceinline__ void xchg_wait(const XchgDev& x, unsigned seq) {
     if ((int)threadIdx.x < x.world) {
         const unsigned* f = xchg_flags(x.peer[x.rank], (int)(seq & 1u)) + threadIdx.x;
-        const long long t0 = clock64();
+        const unsigned long long t0 = xchg_globaltimer_ns();
+        unsigned spins = 0;
         while ((int)(xchg_ld_acquire_sys(f) - (seq + 1u)) < 0) {
-            if (clock64() - t0 > 20000000000ll) __trap();
+            if (x.timeout_ns && (++spins & 63u) == 0 && xchg_globaltimer_ns() - t0 > x.timeout_ns) {
+                atomicMax(xchg_ctl(x) + 4, seq + 1u);
+                break;
+            }
             __nanosleep(64);
         }
     }

@@ -46,6 +46,7 @@ SIGNATURES = {
     "tac_stft_num_frames": (_I64, [_I64, _I, _I, _I]),
     "tac_stft_multi": (_I, [_VP, _I64, _I64, _I64, _I, _IP, _IP, _IP, _I, _I, _I, _I, _I64, _VPP, _VP]),
     "tac_stft_ex_supported": (_I, [_I]),
+    "tac_prepare_stft_ex": (_I, [_I, _I, _I, _I]),
     "tac_stft_ex": (_I, [_VP, _I64, _I64, _I, _I, _I, _I, _I, _I, _I, _EP, _I64, _VP, _VP]),
     "tac_db_from_rowmax": (_I, [_VP, _I64, _I64, _I, _I, _I64, _VP, _F, _F, _VP, _VP]),
     "tac_mrstft_workspace_bytes": (_SZ, [_I64, _I64, _I, _IP, _IP]),
@@ -82,6 +83,8 @@ SIGNATURES = {
     "tac_multi_reduce_workspace_bytes": (_SZ, [_I, C.POINTER(C.c_int64)]),
     "tac_multi_reduce": (_I, [_I, _VPP, _VPP, C.POINTER(C.c_int64), _IP, C.POINTER(C.c_float), _VP, _VP, _SZ, _VP]),
     "tac_xchg_bytes": (_SZ, [_I, _I64]),
+    "tac_xchg_set_timeout": (_I, [C.c_double]),
+    "tac_xchg_status": (_I, [_XP, C.POINTER(C.c_uint)]),
     "tac_xchg_push": (_I, [_XP, _VP, _VP]),
     "tac_xchg_pop": (_I, [_XP, _VP, _VP]),
     "tac_dpca_stats_push": (_I, [_VPP, _I, _I64, _I, _I, _VP, _VP, _SZ, _XP, _VP]),

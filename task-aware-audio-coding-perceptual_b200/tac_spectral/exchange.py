@@ -74,24 +74,43 @@ class PeerBuffer:
         self._keep, self.ptrs = (t, hdl), ptrs
 
     def _init_ipc(self):
+        """CUDA IPC mapping.  Allocation and the opens can fail on ONE rank only (no peer access to some GPU, a rank on
+        another node): every rank still takes part in the collectives, then all vote, and all raise together."""
         import torch.distributed as dist
         lib = L.lib()
+        err = None
         with torch.cuda.device(self.device):
             p = C.c_void_p()
             handle = (C.c_ubyte * 64)()
-            L.check(lib.tac_ipc_alloc(self.nbytes, C.byref(p), handle))
-            self._ipc_local = p.value
+            try:
+                L.check(lib.tac_ipc_alloc(self.nbytes, C.byref(p), handle))
+                self._ipc_local = p.value
+                mine = bytes(handle)
+            except RuntimeError as e:
+                err, mine = e, b""
             handles: List[bytes] = [b""] * self.world
-            dist.all_gather_object(handles, bytes(handle), group=self.group)
+            dist.all_gather_object(handles, mine, group=self.group)
             ptrs = []
             for r, h in enumerate(handles):
                 if r == self.rank:
                     ptrs.append(self._ipc_local)
                     continue
+                if err is not None or len(h) != 64:
+                    err = err or RuntimeError(f"rank {r} could not allocate its exchange buffer")
+                    continue
                 q = C.c_void_p()
-                L.check(lib.tac_ipc_open((C.c_ubyte * 64).from_buffer_copy(h), C.byref(q)))
+                try:
+                    L.check(lib.tac_ipc_open((C.c_ubyte * 64).from_buffer_copy(h), C.byref(q)))
+                except RuntimeError as e:
+                    err = e
+                    continue
                 self._ipc_opened.append(q.value)
                 ptrs.append(q.value)
+            ok = torch.tensor([0 if err is not None else 1], dtype=torch.int32, device=self.device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
+            if int(ok.item()) != 1:
+                self.close()
+                raise RuntimeError(f"CUDA IPC mapping of the exchange buffers failed on at least one rank ({err!r})")
             self.ptrs = ptrs
 
     def close(self):
@@ -136,8 +155,30 @@ class Exchange:
     def desc(self, name: str):
         return C.byref(self._desc[name])
 
+    def check(self) -> None:
+        """Raise if a pop of any channel gave up waiting for a peer (``tac_xchg_status``).  Synchronises the device.
+
+        The kernels never trap on a missing peer (that would kill the CUDA context of this rank, and of the others in
+        turn); they record the failure and the host reports it here, the way NCCL's watchdog does for an all-reduce.
+        The bound is ``TAC_XCHG_TIMEOUT_S`` (default 600 s, 0 = unbounded) or :func:`set_timeout`."""
+        torch.cuda.synchronize(self.buf.device)
+        lib = L.lib()
+        with torch.cuda.device(self.buf.device):
+            for name, d in self._desc.items():
+                w = C.c_uint(0)
+                L.check(lib.tac_xchg_status(C.byref(d), C.byref(w)))
+                if w.value:
+                    raise RuntimeError(f"peer exchange channel {name!r}: pop #{w.value - 1} on rank {self.rank} timed out waiting "
+                                       f"for a peer's push; results since then are undefined (raise TAC_XCHG_TIMEOUT_S or "
+                                       f"barrier the ranks after long rank-local pauses)")
+
     def close(self):
         self.buf.close()
+
+
+def set_timeout(seconds: float) -> None:
+    """Wait bound of the pops enqueued from now on (``tac_xchg_set_timeout``): 0 = unbounded, negative = default."""
+    L.check(L.lib().tac_xchg_set_timeout(float(seconds)))
 
 
 def push(x, src: torch.Tensor) -> None:

@@ -13,7 +13,8 @@ and the DPCA sufficient statistics are the step's only exchange (SURVEY.md 8e); 
 (eigen-solve, selection, projection) runs redundantly on every rank on the global statistics, and the
 input gradient needs no collective because the global normaliser is known from shapes.
 
-``exchange="p2p"`` (default at world > 1): the exchange is ONE-SHOT over NVLink peer memory and fused into the
+``exchange="auto"`` (default) picks ``"p2p"`` when every rank of the group can map every other rank's buffer (one node,
+at most 8 ranks) and ``"nccl"`` otherwise, with a warning.  ``exchange="p2p"``: the exchange is ONE-SHOT over NVLink peer memory and fused into the
 kernels on either side of it (``exchange.py``, ``csrc/xchg.cuh``): the kernel that completes the statistics
 peer-stores them into every rank's slot and raises a flag, the one-CTA-per-view tridiagonalisation spins on the
 flags itself and adds the slots in rank order; the loss sums travel the same way inside the single-CTA kernel
@@ -29,6 +30,7 @@ from __future__ import annotations
 from typing import List, Optional, Sequence
 
 import os
+import warnings
 
 import torch
 
@@ -56,9 +58,18 @@ class SpectralStep:
         if group is not None:
             import torch.distributed as dist
             self.world = dist.get_world_size(group)
-        exchange = exchange or os.environ.get("TAC_STEP_EXCHANGE", "p2p")
-        if exchange not in ("p2p", "nccl"):
-            raise ValueError(f"unknown exchange {exchange!r} (p2p | nccl)")
+        exchange = exchange or os.environ.get("TAC_STEP_EXCHANGE", "auto")
+        if exchange not in ("auto", "p2p", "nccl"):
+            raise ValueError(f"unknown exchange {exchange!r} (auto | p2p | nccl)")
+        # "auto": the peer exchange where it can exist (one node, <= XCHG_MAX_WORLD ranks, peer mapping succeeds on EVERY
+        # rank -- PeerBuffer votes), NCCL otherwise, with one warning; an explicit "p2p" keeps the hard error
+        self._exchange_auto = exchange == "auto"
+        if self._exchange_auto:
+            exchange = "p2p"
+            if self.world > L.XCHG_MAX_WORLD:
+                warnings.warn(f"SpectralStep: {self.world} ranks exceed the peer exchange's {L.XCHG_MAX_WORLD}; using the NCCL "
+                              f"all-reduce for the step's exchange")
+                exchange = "nccl"
         self.exchange = exchange if self.world > 1 else "none"
         self.xchg = None
         from .dpca import _algo_code
@@ -121,8 +132,15 @@ class SpectralStep:
             # last in the constructor: the rendezvous synchronises the ranks, so the first step's pops find peers that
             # have finished building their tables
             from .exchange import Exchange
-            self.xchg = Exchange({"stats": nv * self.stat_stride, "sums": 2 * S, "sync": 2}, group, dev)
-            self._sync_buf = torch.zeros(4, dtype=torch.float64, device=dev)
+            try:
+                self.xchg = Exchange({"stats": nv * self.stat_stride, "sums": 2 * S, "sync": 2}, group, dev)
+                self._sync_buf = torch.zeros(4, dtype=torch.float64, device=dev)
+            except RuntimeError as e:                                # raised on ALL ranks or on none (PeerBuffer votes)
+                if not self._exchange_auto:
+                    raise
+                warnings.warn(f"SpectralStep: no peer-mapped memory across the group ({e}); using the NCCL all-reduce for the "
+                              f"step's exchange")
+                self.exchange = "nccl"
 
     def device_barrier(self):
         """Enqueue a GPU-side rendezvous of all ranks on the current stream (one push + one pop of a two-value channel of the
@@ -134,6 +152,14 @@ class SpectralStep:
         with torch.cuda.device(self.device):
             push(self.xchg.desc("sync"), self._sync_buf[:2])
             pop(self.xchg.desc("sync"), self._sync_buf[2:])
+
+    def check_exchange(self):
+        """Raise ``RuntimeError`` if a kernel of the peer exchange gave up waiting for another rank (``Exchange.check``;
+        synchronises the device).  The wait is bounded by ``TAC_XCHG_TIMEOUT_S`` (default 600 s): ranks that pause for
+        longer between steps -- rank-0 checkpointing, validation, a stalled loader -- should meet in ``dist.barrier()``
+        (or ``device_barrier()`` behind one) before the next step.  No-op with the NCCL exchange."""
+        if self.xchg is not None:
+            self.xchg.check()
 
     def close(self):
         if self.xchg is not None:

@@ -280,8 +280,11 @@ class Spectrogram(nn.Module):
         # torchaudio keeps the window as a buffer; kept so that state_dict()s stay interchangeable
         self.register_buffer("window", torch.hann_window(self.win_length), persistent=False)
         self._core = self.n_fft in SUPPORTED_NFFT and self.hop_length % 2 == 0      # the warp FFT core has a plan for it
-        if torch.cuda.is_available() and self._core:
-            L.check(L.lib().tac_prepare_fft(self.n_fft, self.win_length, int(self.normalized)))
+        if torch.cuda.is_available():                                # tables now, so that forward() is capturable from call one
+            if self._core:
+                L.check(L.lib().tac_prepare_fft(self.n_fft, self.win_length, int(self.normalized)))
+            else:
+                L.check(L.lib().tac_prepare_stft_ex(self.n_fft, self.win_length, int(self.normalized), 0))
 
     def _run(self, x: torch.Tensor, out_mode: int) -> torch.Tensor:
         lead = x.shape[:-1]
@@ -419,6 +422,8 @@ class MelSpectrogram(nn.Module):
         self.hop_length = int(hop_length) if hop_length is not None else self.win_length // 2
         self.power, self.normalized, self.center, self.pad_mode = float(power), bool(normalized), bool(center), pad_mode
         self.bank = MelBank(self.n_fft // 2 + 1, f_min, float(f_max if f_max is not None else sample_rate // 2), n_mels, sample_rate)
+        if torch.cuda.is_available():
+            L.check(L.lib().tac_prepare_stft_ex(self.n_fft, self.win_length, int(self.normalized), 0))
 
     def _run(self, waveform, p1, p2):
         lead = waveform.shape[:-1]
@@ -448,6 +453,8 @@ class SpecsFrontEnd(nn.Module):
             raise NotImplementedError(f"transform_type {transform_type!r}: only 'exponent' and 'none' are implemented")
         self.n_fft, self.hop_length, self.window = int(n_fft), int(hop_length), window
         self.spec_factor, self.spec_abs_exponent, self.transform_type = float(spec_factor), float(spec_abs_exponent), transform_type
+        if torch.cuda.is_available() and ex_supported(self.n_fft):
+            L.check(L.lib().tac_prepare_stft_ex(self.n_fft, self.n_fft, 0, 1 if window == "sqrthann" else 0))
 
     def stft(self, sig: torch.Tensor) -> torch.Tensor:
         """``torch.stft(sig, n_fft, hop, window, center=True, return_complex=True)`` (data_module.py:212-214)."""
@@ -459,7 +466,7 @@ class SpecsFrontEnd(nn.Module):
     def forward(self, sig: torch.Tensor, pad64: bool = True) -> torch.Tensor:
         """``pad_spec(spec_fwd(stft(sig)))``: ``[..., T]`` -> complex64 ``[..., n_fft/2+1, ceil64(F)]``."""
         lead, T = sig.shape[:-1], sig.shape[-1]
-        F = T // self.hop_length + 1
+        F = num_frames(T, self.n_fft, self.hop_length, True)        # (T + 2 (n_fft // 2) - n_fft) // hop + 1: odd n_fft too
         f_pad = (F + 63) // 64 * 64 if pad64 else F
         if self.transform_type == "none":
             kind, p0, p1 = L.EPI_COMPLEX, 0.0, 0.0

@@ -43,6 +43,12 @@ def test_host_only_entry_points(ts):
     assert lib.tac_dpca_workspace_bytes(2, 256, 8) >= 2 * (9216 + 128 * 128) * 8
     assert lib.tac_dpca_workspace_bytes(1, 64, 128) >= (9216 + 128 * 128) * 8
     assert lib.tac_spec_losses_workspace_bytes(4) > 0
+    # exchange wait bound: host-side setter validates; the status of "no exchange" is 0 without touching a device
+    import ctypes as C
+    assert lib.tac_xchg_set_timeout(C.c_double(30.0)) == 0 and lib.tac_xchg_set_timeout(C.c_double(-1.0)) == 0
+    assert lib.tac_xchg_set_timeout(C.c_double(float("nan"))) != 0
+    w = C.c_uint(5)
+    assert lib.tac_xchg_status(None, C.byref(w)) == 0 and w.value == 0
     # chain row groups: the group's waveform stays inside the L2 budget, groups are even, never empty
     g = lib.tac_chain_rows_per_group
     assert g(128, 306688, 0) == 32                                   # 128 x 19 s decoder outputs: 4 groups of 32 rows (37.4 MiB each)

@@ -61,6 +61,39 @@ def test_push_pop_rank_ordered_sum(ts):
             assert torch.equal(outs[r], ref), f"iteration {it}, rank {r}: not the rank-ordered sum"
 
 
+def test_pop_gives_up_after_the_timeout_and_reports_it(ts):
+    """A peer that never pushes must neither hang the GPU nor trap the context: the pop stops waiting after
+    tac_xchg_set_timeout seconds, the host finds the failed pop in tac_xchg_status, and the context stays usable."""
+    L = ts._lib
+    lib = L.lib()
+    bufs, descs = _fake_world(L, 8, 2)
+    st = torch.cuda.current_stream().cuda_stream
+    w = C.c_uint(7)
+    L.check(lib.tac_xchg_status(C.byref(descs[0]), C.byref(w)))
+    assert w.value == 0
+    src = torch.ones(8, dtype=torch.float64, device="cuda")
+    dst = torch.zeros(8, dtype=torch.float64, device="cuda")
+    L.check(lib.tac_xchg_set_timeout(0.05))
+    try:
+        L.check(lib.tac_xchg_push(C.byref(descs[0]), src.data_ptr(), st))       # "rank 1" stays silent
+        t0 = torch.cuda.Event(enable_timing=True)
+        t1 = torch.cuda.Event(enable_timing=True)
+        t0.record()
+        L.check(lib.tac_xchg_pop(C.byref(descs[0]), dst.data_ptr(), st))
+        t1.record()
+        torch.cuda.synchronize()                                                # would raise after a trap
+        assert 40.0 <= t0.elapsed_time(t1) <= 2000.0                             # waited ~50 ms, not ~0 and not for ever
+    finally:
+        L.check(lib.tac_xchg_set_timeout(-1.0))                                 # back to TAC_XCHG_TIMEOUT_S / 600 s
+    L.check(lib.tac_xchg_status(C.byref(descs[0]), C.byref(w)))
+    assert w.value == 1                                                         # pop number 0 gave up
+    L.check(lib.tac_xchg_status(C.byref(descs[1]), C.byref(w)))
+    assert w.value == 0                                                         # the other rank's buffer is untouched
+    assert float((src * 2).sum()) == 16.0                                       # context alive
+    with pytest.raises(RuntimeError):
+        L.check(lib.tac_xchg_set_timeout(float("nan")))
+
+
 def test_loss_finalize_single_rank(ts):
     L = ts._lib
     sums = torch.rand(6, dtype=torch.float64, device="cuda")

@@ -135,3 +135,47 @@ def test_mel_epilogue(ts, n, h, center):
     _close(got, ref, f"mel n={n}", rtol=2e-4)
     lg = m.log_mel(x.cuda(), 10.0, 1e-10)
     assert float((lg.cpu() - 10 * torch.log10(ref + 1e-10)).abs().max()) <= 2e-3
+
+
+def test_prepare_makes_first_call_capturable(ts):
+    """the chirp-z tables are built by tac_prepare_stft_ex (constructors call it), never inside a capture; a
+    configuration nobody prepared is refused during capture with a clear error instead of a cudaMalloc."""
+    L = ts._lib
+    x = torch.randn(3, 6000, device="cuda")
+    sp = ts.Spectrogram(n_fft=346, hop_length=100, power=2.0)        # a size no other test uses: tables come from __init__
+    ref = O.power_spectrogram_ref(x.cpu(), n_fft=346, hop_length=100, power=2.0)
+    g = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        with torch.cuda.graph(g, stream=s):
+            out = sp(x)                                             # FIRST call of this configuration, under capture
+    torch.cuda.current_stream().wait_stream(s)
+    g.replay()
+    torch.cuda.synchronize()
+    eager = sp(x)
+    assert torch.equal(out, eager)
+    assert torch.allclose(out.cpu(), ref, rtol=1e-4, atol=1e-4 * float(ref.abs().max()))
+    # unprepared configuration under capture: TAC_EINVAL naming the prepare call, and no allocation happened
+    g2 = torch.cuda.CUDAGraph()
+    with pytest.raises(RuntimeError, match="tac_prepare_stft_ex"):
+        with torch.cuda.stream(s):
+            with torch.cuda.graph(g2, stream=s):
+                ts.stft_ex(x, 350, 100, 350, center=True, pad_mode="reflect", kind=L.EPI_COMPLEX)
+    torch.cuda.synchronize()
+    assert float(sp(x).sum()) == float(eager.sum())                  # context and library still fine
+
+
+def test_specs_front_end_odd_n_fft_frame_count(ts):
+    """ADVICE r2: centred frames = (T + 2 (n // 2) - n) // hop + 1, which is (T - 1) // hop + 1 for odd n_fft (not T // hop + 1)."""
+    T, n, hop = 128 * 40, 511, 128                                   # T a multiple of hop: the two formulas differ by one
+    sig = torch.randn(2, T)
+    fe = ts.SpecsFrontEnd(n_fft=n, hop_length=hop)
+    z = fe.stft(sig.cuda())
+    ref = torch.stft(sig, n, hop, n, torch.hann_window(n, periodic=True), center=True, pad_mode="reflect", return_complex=True)
+    assert z.shape == ref.shape and z.shape[-1] == (T - 1) // hop + 1 == 40
+    assert torch.allclose(z.cpu(), ref, rtol=1e-4, atol=1e-4 * float(ref.abs().max()))
+    out = fe(sig.cuda())
+    assert out.shape[-1] == 64                                       # 40 frames pad to ONE 64-block (T // hop + 1 = 41 would too; see below)
+    T2 = 128 * 64
+    assert fe(torch.randn(1, T2).cuda()).shape[-1] == 64             # 64 frames exactly: the old formula (65) would have padded to 128

@@ -258,6 +258,33 @@ def mrstft_loss_ref(x: torch.Tensor, y: torch.Tensor, n_ffts: Sequence[int] = (1
     return (total, terms) if return_terms else total
 
 
+def kink_sample_mask(x: torch.Tensor, y: torch.Tensor, n_ffts: Sequence[int] = (1024, 2048, 512), eps: float = LOG_FLOOR,
+                     rel: float = 1e-6, cond: float = 5e-4) -> torch.Tensor:
+    """Test helper for the gradient of :func:`mrstft_loss_ref` (definition of record, not in the reference): which samples of
+    ``y`` [B, T] can an fp32 implementation NOT be held to rtol 1e-4 on?  Evaluated in float64:
+
+    * kinks -- a bin with ``|X - Y| < rel * max|X|`` (the L1 and log terms switch sign there) or a magnitude within
+      ``rel * max|X|`` of the log floor (the clamp switches the log term on / off).  fp32 transform rounding is
+      ~1e-7 * max|X|, so ``rel = 1e-6`` leaves a 10x margin;
+    * ill-conditioned bins -- unclamped ``Y < cond * max|X|``: the log term's 1 / Y turns that rounding into a relative
+      error ``dY / Y >= 1e-7 / cond = 2e-4`` of the bin's gradient (torch's own fp32 path included).
+
+    A marked bin taints the ``n_fft`` samples of its frame (hop = n_fft / 4).  True = excluded from a strict check."""
+    shape = x.shape
+    x2, y2 = x.reshape(-1, shape[-1]).double(), y.reshape(-1, shape[-1]).double()
+    mask = torch.zeros(x2.shape, dtype=torch.bool)
+    for n in n_ffts:
+        h = n // 4
+        X = stft_ref(x2, n, h, n).abs()
+        Y = stft_ref(y2, n, h, n).abs()
+        m = float(X.max())
+        t = rel * m
+        bins = ((X - Y).abs() < t) | ((X - eps).abs() < t) | ((Y - eps).abs() < t) | ((Y > eps) & (Y < cond * m))
+        for b, f in torch.nonzero(bins.any(dim=-2)).tolist():         # [rows, F]
+            mask[b, f * h:f * h + n] = True
+    return mask.reshape(shape)
+
+
 def spectral_losses_ref(obs: torch.Tensor, dec: torch.Tensor) -> Dict[str, torch.Tensor]:
     """The reference's own spectral reductions on ``[B, 2, K, F]`` stacks.
 

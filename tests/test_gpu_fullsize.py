@@ -77,7 +77,10 @@ def test_cfg5_long_clip_loss_and_grad(ts):
     r = y0.grad[0] / x.shape[0]
     err = (g1[0].double().cpu() - r).abs()
     scale = float(r.abs().max())
-    assert float((err > 1e-4 * scale + 1e-4 * r.abs()).float().mean()) < 0.05       # isolated sign(X - Y) flips, see test_gpu_loss
+    bad = err > 1e-4 * scale + 1e-4 * r.abs()
+    assert float(bad.float().mean()) < 0.03                          # isolated sign(X - Y) flips, see test_gpu_loss._check_grad
+    keep = ~O.kink_sample_mask(x[:1], y[:1], N3, 1e-5)[0]             # strict on every sample no kink / tiny bin can reach
+    assert float(keep.float().mean()) > 0.3 and not bool((bad & keep).any()), int((bad & keep).sum())
     assert float(err.median()) < 2e-6 * scale
 
 

@@ -119,28 +119,6 @@ def test_mrstft_backward_default_floor(ts, B, T, n_ffts):
     print(f"relative L2 vs float64: kernel {e_ours:.2e}, torch-fp32 {e_t32:.2e}")
 
 
-def _kink_sample_mask(x, y, n_ffts, eps, rel=1e-6, cond=5e-4):
-    """Samples whose gradient a sign flip could touch: the float64 oracle marks every bin with |X - Y| < rel * max|X| (the
-    L1 and log terms switch sign there) or a magnitude within rel * max|X| of the log floor (the clamp switches the log term
-    on / off); a marked bin taints the n_fft samples of its frame.  fp32 transform rounding is ~1e-7 * max|X|, so rel = 1e-6
-    leaves a 10x margin.  Also marked: unclamped bins with Y < cond * max|X| -- the log term's 1 / Y turns the transform's
-    fp32 rounding (dY ~ 1e-7 * max|X|) into a relative error dY / Y >= 2e-4 of that bin's gradient, beyond rtol 1e-4 for ANY
-    fp32 implementation (torch's own included; measured on B200: worst 1.2e-4 of the scale with the 1e-5 floor against
-    3e-7 with the 1e-2 floor, which clamps those bins).  Returns a bool [B, T] mask (True = excluded from the strict check)."""
-    B, T = x.shape
-    mask = torch.zeros(B, T, dtype=torch.bool)
-    for n in n_ffts:
-        h = n // 4
-        X = O.stft_ref(x.double(), n, h, n).abs()
-        Y = O.stft_ref(y.double(), n, h, n).abs()
-        t = rel * float(X.max())
-        frames = ((X - Y).abs() < t) | ((X - eps).abs() < t) | ((Y - eps).abs() < t)
-        frames = (frames | ((Y > eps) & (Y < cond * float(X.max())))).any(dim=-2)                        # [B, F]
-        for b, f in torch.nonzero(frames).tolist():
-            mask[b, f * h:f * h + n] = True
-    return mask
-
-
 @pytest.mark.parametrize("eps", [1e-2, O.LOG_FLOOR])
 @pytest.mark.parametrize("B,T,n_ffts", CASES)
 def test_mrstft_backward_strict_off_kinks(ts, B, T, n_ffts, eps):
@@ -150,7 +128,7 @@ def test_mrstft_backward_strict_off_kinks(ts, B, T, n_ffts, eps):
     behind the kink allowance here; the masked samples keep the statistical bounds of _check_grad."""
     (x,), (y,) = O.synth_audio(B, T, 1, seed=77)
     got, _, ref = _grads(ts, x, y, n_ffts, eps=eps)
-    mask = _kink_sample_mask(x, y, n_ffts, eps)
+    mask = O.kink_sample_mask(x, y, n_ffts, eps)
     keep = ~mask
     frac = float(mask.float().mean())
     assert frac < 0.65, f"mask covers {frac:.2f} of the samples: the strict check would be vacuous"

@@ -23,22 +23,6 @@ def ts():
     return tac_spectral
 
 
-def _kink_mask(x, y, n_ffts, eps, rel=1e-6, cond=5e-4):
-    """True where a sign flip of |X - Y| or of the log clamp could reach the sample, or where an unclamped bin with
-    Y < cond * max|X| amplifies fp32 rounding past rtol 1e-4 (derivation in tests/test_gpu_loss.py::_kink_sample_mask)."""
-    mask = torch.zeros(x.shape, dtype=torch.bool)
-    for n in n_ffts:
-        h = n // 4
-        X = O.stft_ref(x.double(), n, h, n).abs()
-        Y = O.stft_ref(y.double(), n, h, n).abs()
-        t = rel * float(X.max())
-        frames = ((X - Y).abs() < t) | ((X - eps).abs() < t) | ((Y - eps).abs() < t)
-        frames = (frames | ((Y > eps) & (Y < cond * float(X.max())))).any(dim=-2)
-        for b, f in torch.nonzero(frames).tolist():
-            mask[b, f * h:f * h + n] = True
-    return mask
-
-
 def _check_step_outputs(st, x, y, zs, dim_p, what):
     nv = len(zs)
     rows, T = x.shape
@@ -50,7 +34,7 @@ def _check_step_outputs(st, x, y, zs, dim_p, what):
     O.mrstft_loss_ref(x.double(), y64, list(N3), eps=st.eps).backward()
     ref_g = y64.grad
     got_g = st.grad_y.double().cpu()
-    keep = ~_kink_mask(x, y, N3, st.eps)
+    keep = ~O.kink_sample_mask(x, y, N3, st.eps)
     scale = float(ref_g.abs().max())
     err = (got_g - ref_g).abs()
     bad = err > 1e-4 * scale + 1e-4 * ref_g.abs()

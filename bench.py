@@ -415,6 +415,22 @@ def run_extras(args, dev, rank, world, group, peak, barrier):
         out["cfg4_k1_planes"] = {"workload": "msstftd front end, 5 scales 2048..128 hop n/4, 512 x 10 s, planes [B,2,F,K]",
                                  "ms": t4, "bytes": bytes4, "gbs": bytes4 / (t4 * 1e-3) / 1e9, "frac": bytes4 / (t4 * 1e-3) / 1e9 / peak,
                                  "audio_s_per_s": B4 * T4 / SR / (t4 * 1e-3), "includes": "output allocation by the caching allocator"}
+        # the same five scales as ONE magnitude plane per scale from the same single launch (tac_stft_multi_epi): half the
+        # bytes written; algorithmic bytes 4 B T + 4 B sum F_s K_s
+        outs = None
+        torch.cuda.empty_cache()
+        try:
+            def k1m():
+                nonlocal outs
+                outs = None
+                outs = ms4.magnitudes(x4)
+            t4m = _time_ms(k1m, iters=5, warm=2)
+            bytes4m = 4 * B4 * T4 + 4 * B4 * sum((1 + (T4 - n) // h) * (n // 2 + 1) for n, h in zip(n4, h4))
+            out["cfg4_k1_mag"] = {"workload": "same 5 scales, 512 x 10 s, one magnitude plane per scale [B,1,F,K] (stft_planes_mag_kernel)",
+                                  "ms": t4m, "bytes": bytes4m, "gbs": bytes4m / (t4m * 1e-3) / 1e9, "frac": bytes4m / (t4m * 1e-3) / 1e9 / peak,
+                                  "audio_s_per_s": B4 * T4 / SR / (t4m * 1e-3), "includes": "output allocation by the caching allocator"}
+        except Exception as e:
+            out["cfg4_k1_mag"] = {"error": f"{type(e).__name__}: {e}"}
         del outs, x4
         outs = None
         torch.cuda.empty_cache()

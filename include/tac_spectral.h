@@ -119,6 +119,17 @@ typedef struct tac_epilogue {
 } tac_epilogue;
 /*   x       [rows, T] float32;  window: 0 periodic Hann, 1 its square root (data_module.py:13-17), centred in n_fft when
  *           win < n_fft;  center / pad_mode / normalized as for tac_stft_multi. */
+/* K1, one real plane per scale from the ONE-PASS multi-scale kernel (north star kernel 1: "framing, windowing, real-FFT,
+ * magnitude and log ... for several window/hop sizes per pass"): the per-scale loop of msstftd.py:185-192 with the
+ * magnitude taken in the kernel, and testing_scripts.ipynb:246-249 (Spectrogram() then 10*log10(x + 1e-10)) /
+ * spectrogram.ipynb:2894-2913 (magnitude) for several resolutions at once.  Arguments as tac_stft_multi; epi->kind is
+ *   TAC_EPI_POWER     out[s] float32 [B, C, F_s, K_s] = |z|^p0              (p0 = 1 magnitude, 2 power)
+ *   TAC_EPI_LOGPOWER  out[s] float32 [B, C, F_s, K_s] = p1 * log10(|z|^p0 + p2)
+ * Frequency is innermost (the planes layout with one channel instead of the re / im pair): half of tac_stft_multi's
+ * TAC_OUT_PLANES bytes.  Mel, dB-against-the-row-maximum and phase stay with tac_stft_ex (one n_fft per call). */
+TAC_API int tac_stft_multi_epi(const float* x, int64_t B, int64_t C, int64_t T, int n_scales, const int* n_fft,
+                               const int* hop, const int* win, int center, int pad_mode, int normalized,
+                               const tac_epilogue* epi, void* const* out, tac_stream_t stream);
 TAC_API int tac_stft_ex_supported(int n_fft);
 /* Builds (once per device) the tables tac_stft_ex needs for this configuration -- the only allocating, synchronising part of
  * that path -- so that the first tac_stft_ex call may sit inside a CUDA-graph capture or on a non-blocking stream.  window: 0

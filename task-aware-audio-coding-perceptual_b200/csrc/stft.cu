@@ -95,11 +95,37 @@ __device__ __forceinline__ void bulk_store_span(float* gdst, const float* stg, i
     else if (e >= head && e < head + tail) __stcs(gdst + mid + e, stg[mis + mid + e]);
 }
 
-// One warp task of the planes kernel: frames [f_first, f_first + NFR) of one scale.
-template <class P>
+// One-plane epilogues of the multi-scale kernel (tac_stft_multi_epi): |z|^p0, or p1 * log10(|z|^p0 + p2).
+struct MagEpi {
+    int kind;          // TAC_EPI_POWER | TAC_EPI_LOGPOWER
+    float p0, p1, p2;
+};
+// EP 1: |z| -- EP 2: |z|^2 -- EP 3: anything else (general exponent, log form); compile-time so that the two common forms carry
+// neither the powf / log10f bodies nor a branch per bin.  `e` lives in registers (a by-value copy made once per thread: a
+// pointer to the kernel parameter would turn every field read into a local-memory load on the L1TEX pipe that bounds K1).
+template <int EP>
+__device__ __forceinline__ float mag_epilogue(const MagEpi& e, float re, float im) {
+    const float m2 = fmaf(re, re, im * im);                // the arithmetic of stft_ex.cu: ex_pow_mag
+    if constexpr (EP == 2) return m2;
+    else if constexpr (EP == 1) return sqrtf(m2);
+    else {
+        float v;
+        if (e.p0 == 2.0f) v = m2;
+        else {
+            const float m = sqrtf(m2);
+            v = e.p0 == 1.0f ? m : (e.p0 == 0.5f ? sqrtf(m) : (m > 0.0f ? powf(m, e.p0) : 0.0f));
+        }
+        return e.kind == TAC_EPI_LOGPOWER ? e.p1 * log10f(v + e.p2) : v;
+    }
+}
+
+// One warp task of the planes kernel: frames [f_first, f_first + NFR) of one scale.  MAG: ONE plane per (item, channel)
+// holding mag_epilogue(z) instead of the re / im pair (half the bytes written; the `im` staging and spans are not touched).
+template <class P, int EP = 0>
 __device__ __forceinline__ void planes_task(const ScaleArg& sc, const float* tile, float2* xbuf, int lane,
                                             int f_first, int f_end, int tile_origin /* f*hop coordinate of tile[0] */,
-                                            float* out_re_row, long long im_off) {
+                                            float* out_re_row, long long im_off, const MagEpi me = MagEpi()) {
+    constexpr bool MAG = EP != 0;
     cf z[P::BQ];
     const float2* __restrict__ win2 = sc.t.win2;
     const int hop = sc.hop;
@@ -144,14 +170,19 @@ __device__ __forceinline__ void planes_task(const ScaleArg& sc, const float* til
     float* h_re = stg_re + fr * SF + mis_re + (P::M - k1);                 // bins M - k1 - A j (consecutive lanes: consecutive banks)
     float* h_im = stg_im + fr * SF + mis_im + (P::M - k1);
     warp_fft_post_pk<P, true>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
-        const float vr = lo(v), vi = hi(v);
+        float vr = lo(v);
+        const float vi = hi(v);
+        if constexpr (MAG) vr = mag_epilogue<EP>(me, vr, vi);
         if (valid) {
             if (slot == P::BQ) {                       // k = M/2 (k1 == 0 lanes only)
-                s_re[P::M / 2] = vr; s_im[P::M / 2] = vi;
+                s_re[P::M / 2] = vr;
+                if constexpr (!MAG) s_im[P::M / 2] = vi;
             } else if (slot & 1) {                     // k = M - k1 - A*j
-                h_re[-P::A * (slot >> 1)] = vr; h_im[-P::A * (slot >> 1)] = vi;
+                h_re[-P::A * (slot >> 1)] = vr;
+                if constexpr (!MAG) h_im[-P::A * (slot >> 1)] = vi;
             } else {                                   // k = k1 + A*j
-                s_re[P::A * (slot >> 1)] = vr; s_im[P::A * (slot >> 1)] = vi;
+                s_re[P::A * (slot >> 1)] = vr;
+                if constexpr (!MAG) s_im[P::A * (slot >> 1)] = vi;
             }
         }
     });
@@ -161,7 +192,7 @@ __device__ __forceinline__ void planes_task(const ScaleArg& sc, const float* til
     if constexpr (kMode == 1) {
         const int mr = (int)((reinterpret_cast<uintptr_t>(g_re0) >> 2) & 3u), mi = (int)((reinterpret_cast<uintptr_t>(g_re0 + im_off) >> 2) & 3u);
         bulk_store_span(g_re0, stg_re, mr, nv * sc.K, lane, 0);
-        bulk_store_span(g_re0 + im_off, stg_im, mi, nv * sc.K, lane, 0);
+        if constexpr (!MAG) bulk_store_span(g_re0 + im_off, stg_im, mi, nv * sc.K, lane, 0);
     } else {
 #pragma unroll
         for (int g = 0; g < P::NFR; ++g) {
@@ -169,7 +200,7 @@ __device__ __forceinline__ void planes_task(const ScaleArg& sc, const float* til
                 float* gr = g_re0 + (long long)g * sc.K;
                 float* gi = gr + im_off;
                 bulk_store_span(gr, stg_re + g * SF, (int)((reinterpret_cast<uintptr_t>(gr) >> 2) & 3u), sc.K, lane, g);
-                bulk_store_span(gi, stg_im + g * SF, (int)((reinterpret_cast<uintptr_t>(gi) >> 2) & 3u), sc.K, lane, g);
+                if constexpr (!MAG) bulk_store_span(gi, stg_im + g * SF, (int)((reinterpret_cast<uintptr_t>(gi) >> 2) & 3u), sc.K, lane, g);
             }
         }
     }
@@ -181,14 +212,19 @@ __device__ __forceinline__ void planes_task(const ScaleArg& sc, const float* til
     float* im_lo = re_lo + im_off;
     float* im_hi = re_hi + im_off;
     warp_fft_post_pk<P, true>(z, sc.t.pt, lane, [&](int, int, cf v, int slot) {
-        const float vr = lo(v), vi = hi(v);
+        float vr = lo(v);
+        const float vi = hi(v);
+        if constexpr (MAG) vr = mag_epilogue<EP>(me, vr, vi);
         if (valid) {
             if (slot == P::BQ) {                       // k = M/2 (k1 == 0 lanes only)
-                __stcs(re_lo + P::M / 2, vr); __stcs(im_lo + P::M / 2, vi);
+                __stcs(re_lo + P::M / 2, vr);
+                if constexpr (!MAG) __stcs(im_lo + P::M / 2, vi);
             } else if (slot & 1) {                     // k = M - k1 - A*j
-                __stcs(re_hi - P::A * (slot >> 1), vr); __stcs(im_hi - P::A * (slot >> 1), vi);
+                __stcs(re_hi - P::A * (slot >> 1), vr);
+                if constexpr (!MAG) __stcs(im_hi - P::A * (slot >> 1), vi);
             } else {                                   // k = k1 + A*j
-                __stcs(re_lo + P::A * (slot >> 1), vr); __stcs(im_lo + P::A * (slot >> 1), vi);
+                __stcs(re_lo + P::A * (slot >> 1), vr);
+                if constexpr (!MAG) __stcs(im_lo + P::A * (slot >> 1), vi);
             }
         }
     });
@@ -201,9 +237,10 @@ __device__ __forceinline__ void planes_task(const ScaleArg& sc, const float* til
 // the plan switch sits outside the task loop.  (Round 2 history, cfg 4, 128 tasks per unit: a shared atomic counter + shuffle +
 // scale search + 64-bit plane arithmetic PER TASK were 17 % of the kernel's instructions; hoisted per scale with 64-bit divisions
 // they were still ~250 instructions per scale and warp.)
-template <int W>
+template <int W, int EP = 0>
 __device__ __forceinline__ void planes_unit(const PlanesArgs& a, const float* tile, float2* xbuf, int lane, int warp,
-                                            unsigned row, unsigned c0) {
+                                            unsigned row, unsigned c0, const MagEpi me = MagEpi()) {
+    constexpr bool MAG = EP != 0;
     static_assert((W & (W - 1)) == 0, "W must be a power of two");
     static_assert(Plan2048::NFR == 1 && Plan1024::NFR == 2 && Plan512::NFR == 2 && Plan256::NFR == 4 && Plan128::NFR == 4 && Plan64::NFR == 8, "nfr");
     int my_lo = 0, my_hi = 0, my_nt = 0;
@@ -220,7 +257,7 @@ __device__ __forceinline__ void planes_unit(const PlanesArgs& a, const float* ti
         my_nt = (int)((hi - lo + (1u << l2nfr) - 1u) >> l2nfr);
         const unsigned b = row / (unsigned)a.C, ch = row - b * (unsigned)a.C;
         const long long plane = (long long)sc.F * sc.K;
-        my_out = sc.out + ((long long)(b * 2u) * a.C + ch) * plane;
+        my_out = sc.out + ((long long)(b * (MAG ? 1u : 2u)) * a.C + ch) * plane;
         my_im = (long long)a.C * plane;
     }
     int my_tb = my_nt;                                       // exclusive prefix sum over the (<= 8) scales
@@ -244,12 +281,12 @@ __device__ __forceinline__ void planes_unit(const PlanesArgs& a, const float* ti
             for (int t = first; t < nt; t += W) body(t);
         };
         switch (sc.n) {
-            case 2048: my_tasks([&](int t) { planes_task<Plan2048>(sc, tile, xbuf, lane, f_lo + t * 1, f_end, origin, out_re_row, im_off); }); break;
-            case 1024: my_tasks([&](int t) { planes_task<Plan1024>(sc, tile, xbuf, lane, f_lo + t * 2, f_end, origin, out_re_row, im_off); }); break;
-            case 512: my_tasks([&](int t) { planes_task<Plan512>(sc, tile, xbuf, lane, f_lo + t * 2, f_end, origin, out_re_row, im_off); }); break;
-            case 256: my_tasks([&](int t) { planes_task<Plan256>(sc, tile, xbuf, lane, f_lo + t * 4, f_end, origin, out_re_row, im_off); }); break;
-            case 128: my_tasks([&](int t) { planes_task<Plan128>(sc, tile, xbuf, lane, f_lo + t * 4, f_end, origin, out_re_row, im_off); }); break;
-            default: my_tasks([&](int t) { planes_task<Plan64>(sc, tile, xbuf, lane, f_lo + t * 8, f_end, origin, out_re_row, im_off); }); break;
+            case 2048: my_tasks([&](int t) { planes_task<Plan2048, EP>(sc, tile, xbuf, lane, f_lo + t * 1, f_end, origin, out_re_row, im_off, me); }); break;
+            case 1024: my_tasks([&](int t) { planes_task<Plan1024, EP>(sc, tile, xbuf, lane, f_lo + t * 2, f_end, origin, out_re_row, im_off, me); }); break;
+            case 512: my_tasks([&](int t) { planes_task<Plan512, EP>(sc, tile, xbuf, lane, f_lo + t * 2, f_end, origin, out_re_row, im_off, me); }); break;
+            case 256: my_tasks([&](int t) { planes_task<Plan256, EP>(sc, tile, xbuf, lane, f_lo + t * 4, f_end, origin, out_re_row, im_off, me); }); break;
+            case 128: my_tasks([&](int t) { planes_task<Plan128, EP>(sc, tile, xbuf, lane, f_lo + t * 4, f_end, origin, out_re_row, im_off, me); }); break;
+            default: my_tasks([&](int t) { planes_task<Plan64, EP>(sc, tile, xbuf, lane, f_lo + t * 8, f_end, origin, out_re_row, im_off, me); }); break;
         }
     }
 }
@@ -285,6 +322,25 @@ __global__ void __launch_bounds__(kThreads, 2) stft_planes_kernel(const PlanesAr
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     planes_unit<kWarps>(a, tile, xbuf_all + warp * kXbufFloat2, lane, warp, row, c0);
+#if TAC_PLANES_BULK
+    if (lane < 8) bulk_wait_read();                        // shared memory must outlive the copy engine's reads
+#endif
+}
+
+// The same unit with the one-plane epilogue (tac_stft_multi_epi): [B, C, F, K] of |z|^p or p1 log10(|z|^p + p2) per scale.
+template <int EP>
+__global__ void __launch_bounds__(kThreads, 2) stft_planes_mag_kernel(const PlanesArgs a, const MagEpi me_param) {
+    const MagEpi me = me_param;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float* tile = reinterpret_cast<float*>(smem_raw);
+    float2* xbuf_all = reinterpret_cast<float2*>(smem_raw + (size_t)a.tile_len * sizeof(float));
+    const unsigned c = blockIdx.x % (unsigned)a.nchunks;
+    const unsigned row = blockIdx.x / (unsigned)a.nchunks;
+    const unsigned c0 = c * (unsigned)a.chunk;
+    stage_tile(tile, a.x + (long long)row * a.T, (long long)c0 - a.pmax, a.tile_len, a.T, a.pad_mode, a.vec_ok != 0);
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    planes_unit<kWarps, EP>(a, tile, xbuf_all + warp * kXbufFloat2, lane, warp, row, c0, me);
 #if TAC_PLANES_BULK
     if (lane < 8) bulk_wait_read();                        // shared memory must outlive the copy engine's reads
 #endif
@@ -685,9 +741,32 @@ extern "C" int tac_amplitude_to_db(const float* mag, int64_t rows, int64_t row_s
 }
 
 
+static int stft_multi_impl(const float* x, int64_t B, int64_t C, int64_t T, int n_scales, const int* n_fft,
+                           const int* hop, const int* win, int center, int pad_mode, int normalized,
+                           int out_mode, int64_t f_pad, void* const* out, tac_stream_t stream, const MagEpi* me);
+
 extern "C" int tac_stft_multi(const float* x, int64_t B, int64_t C, int64_t T, int n_scales, const int* n_fft,
                               const int* hop, const int* win, int center, int pad_mode, int normalized,
                               int out_mode, int64_t f_pad, void* const* out, tac_stream_t stream) {
+    return stft_multi_impl(x, B, C, T, n_scales, n_fft, hop, win, center, pad_mode, normalized, out_mode, f_pad, out, stream, nullptr);
+}
+
+extern "C" int tac_stft_multi_epi(const float* x, int64_t B, int64_t C, int64_t T, int n_scales, const int* n_fft,
+                                  const int* hop, const int* win, int center, int pad_mode, int normalized,
+                                  const tac_epilogue* epi, void* const* out, tac_stream_t stream) {
+    TAC_REQUIRE(epi != nullptr, "null epilogue");
+    TAC_REQUIRE(epi->kind == TAC_EPI_POWER || epi->kind == TAC_EPI_LOGPOWER,
+                "tac_stft_multi_epi forms TAC_EPI_POWER or TAC_EPI_LOGPOWER planes (kind %d: use tac_stft_ex per scale)", epi->kind);
+    TAC_REQUIRE(epi->p0 > 0.0f, "exponent p0 must be positive");
+    TAC_REQUIRE(epi->rowmax == nullptr, "rowmax is not produced by the multi-scale kernel");
+    MagEpi me;
+    me.kind = epi->kind; me.p0 = epi->p0; me.p1 = epi->p1; me.p2 = epi->p2;
+    return stft_multi_impl(x, B, C, T, n_scales, n_fft, hop, win, center, pad_mode, normalized, TAC_OUT_PLANES, 0, out, stream, &me);
+}
+
+static int stft_multi_impl(const float* x, int64_t B, int64_t C, int64_t T, int n_scales, const int* n_fft,
+                           const int* hop, const int* win, int center, int pad_mode, int normalized,
+                           int out_mode, int64_t f_pad, void* const* out, tac_stream_t stream, const MagEpi* me) {
     TAC_REQUIRE(x && n_fft && hop && out, "null argument");
     TAC_REQUIRE(B > 0 && C > 0 && T > 0, "B, C, T must be positive (got %lld, %lld, %lld)", (long long)B, (long long)C, (long long)T);
     TAC_REQUIRE(n_scales >= 1 && n_scales <= TAC_MAX_SCALES, "n_scales must be in [1, %d]", TAC_MAX_SCALES);
@@ -741,6 +820,22 @@ extern "C" int tac_stft_multi(const float* x, int64_t B, int64_t C, int64_t T, i
         const size_t smem = (size_t)a.tile_len * sizeof(float) + (size_t)kWarps * kXbufFloat2 * sizeof(float2);
         const long long grid = rows * a.nchunks;
         TAC_REQUIRE(grid < (1ll << 31), "grid too large");
+        if (me) {                                           // one-plane epilogue: the one-shot kernel, every scale count
+            const int ep = me->kind == TAC_EPI_POWER ? (me->p0 == 1.0f ? 1 : (me->p0 == 2.0f ? 2 : 3)) : 3;
+            if (ep == 1) {
+                TAC_SMEM_OPT_IN(stft_planes_mag_kernel<1>, 111 * 1024);
+                stft_planes_mag_kernel<1><<<(unsigned)grid, kThreads, smem, st>>>(a, *me);
+            } else if (ep == 2) {
+                TAC_SMEM_OPT_IN(stft_planes_mag_kernel<2>, 111 * 1024);
+                stft_planes_mag_kernel<2><<<(unsigned)grid, kThreads, smem, st>>>(a, *me);
+            } else {
+                TAC_SMEM_OPT_IN(stft_planes_mag_kernel<3>, 111 * 1024);
+                stft_planes_mag_kernel<3><<<(unsigned)grid, kThreads, smem, st>>>(a, *me);
+            }
+            TAC_LAUNCHED(1);
+            TAC_CHECK_CUDA(cudaGetLastError());
+            return TAC_OK;
+        }
 #if TAC_PLANES_PERSIST
         // persistent double-buffered form: the tile must be bulk-copyable (16-byte aligned rows, zero or no padding) and there
         // must be enough units to give every SM several

@@ -16,14 +16,14 @@ There is no CPU or eager-PyTorch fallback: every op raises ``RuntimeError`` when
 ``libtac_spectral.so`` is missing or its input is not on a CUDA device.
 """
 from . import _lib
-from .stft import (Spectrogram, MultiScaleSTFT, stft_multi, complex_spectrogram, create_complex_spectrogram, amplitude_to_db,
+from .stft import (Spectrogram, MultiScaleSTFT, stft_multi, stft_multi_power, complex_spectrogram, create_complex_spectrogram, amplitude_to_db,
                    num_frames, SUPPORTED_NFFT, istft, batch_reconstruct_waveform, reconstruct_waveform, stft_ex, ex_supported,
                    MelBank, MelSpectrogram, SpecsFrontEnd, reconstruct_and_disc_inputs)
 from .tail import bottleneck_mix, spectral_bottleneck, task_aware_tail, interp_mse, multi_reduce
 from .loss import mrstft_loss, mrstft_sums, mrstft_counts, spectral_losses, LOG_FLOOR
 from .dpca import data_pca, dpca_project, dpca_select, dpca_stats, dpca_eig, apply_pca, var_topk, nuclear_loss, pairwise_cosine_loss
 
-__all__ = ["Spectrogram", "MultiScaleSTFT", "stft_multi", "complex_spectrogram", "create_complex_spectrogram", "amplitude_to_db",
+__all__ = ["Spectrogram", "MultiScaleSTFT", "stft_multi", "stft_multi_power", "complex_spectrogram", "create_complex_spectrogram", "amplitude_to_db",
            "num_frames", "SUPPORTED_NFFT", "mrstft_loss", "mrstft_sums", "mrstft_counts", "spectral_losses",
            "LOG_FLOOR", "data_pca", "dpca_project", "dpca_select", "dpca_stats", "dpca_eig", "apply_pca", "var_topk", "nuclear_loss",
            "pairwise_cosine_loss", "istft", "batch_reconstruct_waveform", "reconstruct_waveform", "stft_ex", "ex_supported",

@@ -45,6 +45,7 @@ SIGNATURES = {
     "tac_shutdown": (_I, []),
     "tac_stft_num_frames": (_I64, [_I64, _I, _I, _I]),
     "tac_stft_multi": (_I, [_VP, _I64, _I64, _I64, _I, _IP, _IP, _IP, _I, _I, _I, _I, _I64, _VPP, _VP]),
+    "tac_stft_multi_epi": (_I, [_VP, _I64, _I64, _I64, _I, _IP, _IP, _IP, _I, _I, _I, _EP, _VPP, _VP]),
     "tac_stft_ex_supported": (_I, [_I]),
     "tac_prepare_stft_ex": (_I, [_I, _I, _I, _I]),
     "tac_stft_ex": (_I, [_VP, _I64, _I64, _I, _I, _I, _I, _I, _I, _I, _EP, _I64, _VP, _VP]),

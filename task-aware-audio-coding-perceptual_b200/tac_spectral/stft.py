@@ -173,6 +173,39 @@ def _stft_multi_raw(x, n_ffts, hops, wins, center, pad_mode, normalized, out_mod
     return outs
 
 
+def stft_multi_power(x: torch.Tensor, n_ffts: Sequence[int], hops: Sequence[int], wins: Optional[Sequence[int]] = None, *,
+                     center: bool = False, pad_mode: Optional[str] = "reflect", normalized: bool = True, power: float = 1.0,
+                     log_multiplier: float = 0.0, log_eps: float = 1e-10) -> List[torch.Tensor]:
+    """Magnitude (``power=1``) / power (``power=2``) spectrograms of ALL scales of ``x [B, C, T]`` from one launch of the
+    multi-scale kernel (``tac_stft_multi_epi``): one ``[B, C, F_s, K_s]`` float32 tensor per scale, frequency innermost
+    (transpose the last two axes for torchaudio's ``[..., K, F]``).  ``log_multiplier != 0`` gives
+    ``log_multiplier * log10(|z|^power + log_eps)`` -- ``testing_scripts.ipynb:246-249`` is ``power=2, log_multiplier=10``.
+    The magnitude is formed where the transform ends, so half the bytes of the re / im planes reach HBM.  Forward only."""
+    L.require_cuda(x, "x")
+    if x.dim() != 3:
+        raise ValueError(f"expected x of shape [B, C, T], got {tuple(x.shape)}")
+    if torch.is_grad_enabled() and x.requires_grad:
+        raise NotImplementedError("stft_multi_power is forward-only; use stft_multi (planes) for a differentiable path")
+    wins = list(n_ffts) if wins is None else list(wins)
+    assert len(n_ffts) == len(hops) == len(wins)                       # msstftd.py:177
+    x = x.contiguous().float()
+    B, Cc, T = x.shape
+    outs = []
+    for n, h in zip(n_ffts, hops):
+        F = num_frames(T, n, h, center)
+        if F < 1:
+            raise ValueError(f"signal of {T} samples is shorter than n_fft={n}")
+        outs.append(torch.empty((B, Cc, F, n // 2 + 1), device=x.device, dtype=torch.float32))
+    epi = L.EpilogueStruct()
+    epi.kind = L.EPI_LOGPOWER if log_multiplier != 0.0 else L.EPI_POWER
+    epi.p0, epi.p1, epi.p2 = float(power), float(log_multiplier), float(log_eps)
+    with L.device_of(x):
+        L.check(L.lib().tac_stft_multi_epi(x.data_ptr(), B, Cc, T, len(n_ffts), L.int_array(n_ffts), L.int_array(hops),
+                                           L.int_array(wins), int(bool(center)), _pad_mode_code(pad_mode),
+                                           int(bool(normalized)), C.byref(epi), L.ptr_array(outs), L.stream_of(x)))
+    return outs
+
+
 def _window_norm(win: int) -> float:
     """``1 / sqrt(sum w^2)`` of the periodic Hann window (torchaudio's ``normalized=True`` / 'window')."""
     w = torch.hann_window(win, periodic=True, dtype=torch.float64)
@@ -350,6 +383,12 @@ class MultiScaleSTFT(nn.Module):
     def forward(self, x: torch.Tensor) -> List[torch.Tensor]:
         return stft_multi(x, self.n_ffts, self.hop_lengths, self.win_lengths, center=False,
                           normalized=self.normalized, out_mode=L.OUT_PLANES)
+
+    def magnitudes(self, x: torch.Tensor, power: float = 1.0, log_multiplier: float = 0.0, log_eps: float = 1e-10) -> List[torch.Tensor]:
+        """``|STFT_s(x)|^power`` (optionally ``log_multiplier * log10(. + log_eps)``) of every scale, ``[B, C, F_s, K_s]``, from
+        the same single launch (:func:`stft_multi_power`)."""
+        return stft_multi_power(x, self.n_ffts, self.hop_lengths, self.win_lengths, center=False, normalized=self.normalized,
+                                power=power, log_multiplier=log_multiplier, log_eps=log_eps)
 
 
 def complex_spectrogram(y: torch.Tensor, n_fft: int = 2048, hop_length: int = 512, win_length: int = 2048,

@@ -252,3 +252,46 @@ def test_persistent_single_scale(ts, n, T, center):
     if center:
         xc = torch.nn.functional.pad(xc, (n // 2, n // 2))
     _close(one[rows], O.disc_inputs_ref(xc, n, n // 4), f"persistent n={n} T={T} center={center}")
+
+
+@pytest.mark.parametrize("n_ffts", [(1024, 2048, 512), (2048, 1024, 512, 256, 128), (64,)])
+@pytest.mark.parametrize("power,logm", [(1.0, 0.0), (2.0, 0.0), (2.0, 10.0), (0.5, 0.0)])
+def test_multi_scale_magnitude_epilogues_one_launch(ts, n_ffts, power, logm):
+    """tac_stft_multi_epi: |z|^p and p1 log10(|z|^p + eps) of several scales from ONE launch of the multi-scale kernel (north
+    star kernel 1), against the oracle's per-scale loop (msstftd.py:185-192 convention, magnitude / power taken in float64
+    from stft_ref; testing_scripts.ipynb:246-249 for the log form).  fp32 rtol 1e-4, atol 1e-4 * max|ref|."""
+    L = ts._lib
+    (x,), _ = O.synth_audio(3, 9001 + 2 * max(n_ffts), 1, seed=31)
+    x = torch.stack([x, 0.5 * x.flip(-1)], 1)                        # [B, C = 2, T]: two channels, ragged T
+    hops = [n // 4 for n in n_ffts]
+    c0 = int(L.lib().tac_launch_count())
+    outs = ts.stft_multi_power(x.cuda(), list(n_ffts), hops, power=power, log_multiplier=logm, log_eps=1e-10)
+    assert int(L.lib().tac_launch_count()) - c0 == 1                 # one kernel for all scales
+    for n, h, o in zip(n_ffts, hops, outs):
+        B, Cc, T = x.shape
+        ref = O.stft_ref(x.reshape(B * Cc, T).double(), n, h, n).abs() ** power       # [B*C, K, F]
+        if logm:
+            ref = logm * torch.log10(ref + 1e-10)
+        ref = ref.reshape(B, Cc, *ref.shape[-2:]).transpose(-1, -2).float()           # -> [B, C, F, K]
+        assert o.shape == ref.shape, (o.shape, ref.shape)
+        _close(o, ref, f"n={n} power={power} log={logm}")
+    # the module form and the planes form agree: sqrt(re^2 + im^2) of the same launch family
+    if power == 1.0 and not logm:
+        ms = ts.MultiScaleSTFT(list(n_ffts), hops, list(n_ffts))
+        mags = ms.magnitudes(x.cuda())
+        planes = ms(x.cuda())
+        for m, p in zip(mags, planes):
+            Cc = x.shape[1]
+            want = torch.sqrt(p[:, :Cc] ** 2 + p[:, Cc:] ** 2)
+            assert torch.allclose(m, want, rtol=1e-6, atol=1e-7 * float(want.max()))
+
+
+def test_multi_scale_magnitude_errors(ts):
+    L = ts._lib
+    x = torch.randn(2, 1, 5000, device="cuda")
+    with pytest.raises(RuntimeError, match="positive"):
+        ts.stft_multi_power(x, [512], [128], power=0.0)
+    with pytest.raises(NotImplementedError):
+        ts.stft_multi_power(x.clone().requires_grad_(True), [512], [128])
+    with pytest.raises(ValueError):
+        ts.stft_multi_power(x, [8192 * 2], [128])                     # shorter than n_fft is caught first
